@@ -1,0 +1,172 @@
+/* loam_b200.h -- C ABI of the B200-native LOAM per-sweep pipeline.
+ *
+ * Drop-in boundary: the reference (Maofei/loam_velodyne-1) has no linkable
+ * API; its contract is the ROS topic graph between four nodes.  Each entry point below replaces
+ * one ROS callback / loop body of the reference and keeps its argument meaning, ordering rules
+ * and "silently wait for more data" behaviour.  All functions return 0 (LOAM_OK), 1
+ * (LOAM_NOT_READY: the reference would `return`/`continue` without publishing) or a negative
+ * error; no C++ exception crosses this boundary; no torch / CUDA types appear in signatures.
+ * A handle is bound to one CUDA device and one stream and is NOT thread-safe; distinct handles
+ * are independent.  Point clouds are device-resident; use the *_download calls to read them.
+ * There is no CPU fallback: every call fails with LOAM_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef LOAM_B200_H_
+#define LOAM_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LOAM_OK 0
+#define LOAM_NOT_READY 1
+#define LOAM_ERR_ARG (-1)
+#define LOAM_ERR_CUDA (-2)
+#define LOAM_ERR_CAPACITY (-3)
+
+/* Every tunable that is a compile-time literal in the reference and that BASELINE.json's
+ * configs need to vary.  All other constants are fixed to the reference's. */
+typedef struct loam_params {
+  int n_scans;          /* scanRegistration.cpp:61  N_SCANS (16)                                  */
+  int ring_model;       /* 0: VLP-16 1-degree rounding, scanRegistration.cpp:248-256               */
+                        /* 1: linear lower..upper, the HDL-64E block of the bk variant (:268-274)  */
+  float ring_lower_deg; /* ring_model 1: elevation of ring 0                                      */
+  float ring_upper_deg; /* ring_model 1: elevation of ring n_scans-1                              */
+  int max_points;       /* scanRegistration.cpp:63-66, laserOdometry.cpp:84-91 array size (40000)  */
+  int system_delay;     /* scanRegistration.cpp:57 (20); benchmarks use 0 on both sides           */
+  int lo_max_iter;      /* laserOdometry.cpp:470 (25)                                             */
+  int lm_max_iter;      /* laserMapping.cpp:710 (10)                                              */
+  int map_arena_points; /* product only: capacity of each cube-map arena, in points               */
+  int reserved[7];
+} loam_params;
+
+/* preset: 1 = VLP-16 (reference defaults), 2 = HDL-64E, 4 = 128-ring (BASELINE.json configs) */
+int loam_params_preset(loam_params* p, int preset);
+
+/* cloud selectors for the download calls */
+enum loam_cloud {
+  LOAM_CLOUD_FULL = 0,        /* /velodyne_cloud_2        scanRegistration.cpp:584-588 */
+  LOAM_CLOUD_SHARP = 1,       /* /laser_cloud_sharp       :590-594 */
+  LOAM_CLOUD_LESS_SHARP = 2,  /* /laser_cloud_less_sharp  :596-600 */
+  LOAM_CLOUD_FLAT = 3,        /* /laser_cloud_flat        :602-606 */
+  LOAM_CLOUD_LESS_FLAT = 4,   /* /laser_cloud_less_flat   :608-612 */
+  LOAM_CLOUD_CORNER_LAST = 5, /* /laser_cloud_corner_last laserOdometry.cpp:913-917 */
+  LOAM_CLOUD_SURF_LAST = 6,   /* /laser_cloud_surf_last   :919-923 */
+  LOAM_CLOUD_FULL_END = 7,    /* /velodyne_cloud_3        :925-929 */
+  LOAM_CLOUD_REGISTERED = 8,  /* /velodyne_cloud_registered laserMapping.cpp:1060-1069 */
+  LOAM_CLOUD_SURROUND = 9,    /* /laser_cloud_surround    :1042-1057 */
+  LOAM_CLOUD_MAP_CORNER = 10, /* laserCloudCornerFromMap  :674-679 (local map used by the last LM) */
+  LOAM_CLOUD_MAP_SURF = 11,   /* laserCloudSurfFromMap */
+  LOAM_CLOUD_STACK_CORNER = 12, /* laserCloudCornerStack  :693-696 */
+  LOAM_CLOUD_STACK_SURF = 13    /* laserCloudSurfStack    :698-701 */
+};
+
+/* int-array selectors (debug / parity) */
+enum loam_ints {
+  LOAM_INTS_LABEL = 0,       /* cloudLabel[]           scanRegistration.cpp:66  */
+  LOAM_INTS_PICKED = 1,      /* cloudNeighborPicked[]  :65 (state after selection) */
+  LOAM_INTS_SORT_IND = 2,    /* cloudSortInd[]         :64 */
+  LOAM_INTS_SHARP_IDX = 3,   /* indices (into FULL) of the sharp cloud, emission order */
+  LOAM_INTS_LESS_SHARP_IDX = 4,
+  LOAM_INTS_FLAT_IDX = 5,
+  LOAM_INTS_CORNER_IND1 = 6, /* pointSearchCornerInd1[] laserOdometry.cpp:85 (last refresh) */
+  LOAM_INTS_CORNER_IND2 = 7,
+  LOAM_INTS_SURF_IND1 = 8,
+  LOAM_INTS_SURF_IND2 = 9,
+  LOAM_INTS_SURF_IND3 = 10,
+  LOAM_INTS_SCAN_START = 11, /* scanStartInd[] scanRegistration.cpp:221 */
+  LOAM_INTS_SCAN_END = 12
+};
+enum loam_floats {
+  LOAM_FLOATS_CURVATURE = 0  /* cloudCurvature[] scanRegistration.cpp:63 */
+};
+
+/* per-sweep result of the whole pipeline */
+typedef struct loam_sweep_result {
+  int sr_status, lo_status, lm_status; /* LOAM_OK / LOAM_NOT_READY per node */
+  int n_full, n_sharp, n_less_sharp, n_flat, n_less_flat;
+  int lo_iters;         /* LM iterations executed by laserOdometry (0..25) */
+  int lo_rows;          /* rows in the last odometry normal equations */
+  int lo_degenerate;    /* isDegenerate, laserOdometry.cpp:404 */
+  int lm_iters, lm_rows, lm_degenerate;
+  int n_map_corner, n_map_surf, n_stack_corner, n_stack_surf;
+  float transform[6];           /* laserOdometry.cpp:93  sweep-to-sweep motion */
+  float transform_sum[6];       /* laserOdometry.cpp:94  /laser_odom_to_init */
+  float transform_aft_mapped[6];/* laserMapping.cpp:100  /aft_mapped_to_init pose */
+  float transform_bef_mapped[6];/* laserMapping.cpp:99   (twist fields of that message) */
+  float transform_mapped[6];    /* transformMaintenance.cpp:51 /integrated_to_init */
+  float imu_trans[12];          /* scanRegistration.cpp:614-629 */
+} loam_sweep_result;
+
+/* ---- scanRegistration node (scanRegistration.cpp) ---- */
+typedef struct loam_sr loam_sr;
+int loam_sr_create(const loam_params* p, int device, loam_sr** out);
+void loam_sr_destroy(loam_sr* h);
+/* imuHandler, scanRegistration.cpp:638-660.  quat = (x,y,z,w) orientation, acc = linear_acceleration */
+int loam_sr_imu(loam_sr* h, double stamp, const double quat[4], const float acc[3]);
+/* laserCloudHandler, :211-636.  xyz: n points, `stride_bytes` apart, 3 floats each, HOST memory,
+ * sensor frame (x fwd, y left, z up), firing order.  NOT_READY while systemDelay swallows sweeps. */
+int loam_sr_process(loam_sr* h, const float* xyz, int n, int stride_bytes, double stamp);
+int loam_sr_download(loam_sr* h, int which_cloud, float* xyzi, int cap_points, int* n);
+int loam_sr_download_ints(loam_sr* h, int which, int* out, int cap, int* n);
+int loam_sr_download_floats(loam_sr* h, int which, float* out, int cap, int* n);
+int loam_sr_imu_trans(loam_sr* h, float out12[12]);
+
+/* ---- laserOdometry node (laserOdometry.cpp main loop :410-931) ---- */
+typedef struct loam_lo loam_lo;
+int loam_lo_create(const loam_params* p, int device, loam_lo** out);
+void loam_lo_destroy(loam_lo* h);
+/* consumes the six topics scanRegistration just produced (same device).  NOT_READY on the first
+ * sweep (:427-456).  *has_mapping_input = 1 on the sweeps whose clouds the reference publishes
+ * to laserMapping (every (skipFrameNum+1)-th, :910-930). */
+int loam_lo_process(loam_lo* h, loam_sr* features, int* has_mapping_input);
+int loam_lo_download(loam_lo* h, int which_cloud, float* xyzi, int cap_points, int* n);
+int loam_lo_download_ints(loam_lo* h, int which, int* out, int cap, int* n);
+int loam_lo_state(loam_lo* h, float transform[6], float transform_sum[6], int stats[4]);
+/* teacher forcing for parity tests: overwrite transform / transformSum (laserOdometry.cpp:93-94) */
+int loam_lo_set_state(loam_lo* h, const float transform[6], const float transform_sum[6]);
+
+/* ---- laserMapping node (laserMapping.cpp main loop :408-1096) ---- */
+typedef struct loam_lm loam_lm;
+int loam_lm_create(const loam_params* p, int device, loam_lm** out);
+void loam_lm_destroy(loam_lm* h);
+/* imuHandler, laserMapping.cpp:323-335 */
+int loam_lm_imu(loam_lm* h, double stamp, const double quat[4]);
+/* consumes corner_last / surf_last / velodyne_cloud_3 / laser_odom_to_init of `odom` */
+int loam_lm_process(loam_lm* h, loam_lo* odom, double stamp);
+int loam_lm_download(loam_lm* h, int which_cloud, float* xyzi, int cap_points, int* n);
+int loam_lm_state(loam_lm* h, float aft_mapped[6], float bef_mapped[6], float tobe_mapped[6], int stats[8]);
+
+/* ---- transformMaintenance node (transformMaintenance.cpp), host only ---- */
+typedef struct loam_tm loam_tm;
+int loam_tm_create(loam_tm** out);
+void loam_tm_destroy(loam_tm* h);
+/* odomAftMappedHandler :182-203 */
+int loam_tm_on_mapping(loam_tm* h, const float aft_mapped[6], const float bef_mapped[6]);
+/* laserOdometryHandler :147-180; writes /integrated_to_init */
+int loam_tm_on_odometry(loam_tm* h, const float transform_sum[6], float integrated[6]);
+
+/* ---- whole pipeline: sr -> lo -> (lm when lo publishes) -> tm, one stream, one device ---- */
+typedef struct loam_pipeline loam_pipeline;
+int loam_pipeline_create(const loam_params* p, int device, loam_pipeline** out);
+void loam_pipeline_destroy(loam_pipeline* h);
+int loam_pipeline_imu(loam_pipeline* h, double stamp, const double quat[4], const float acc[3]);
+/* synchronous: uploads the sweep, runs the nodes, downloads the poses into *res */
+int loam_pipeline_push(loam_pipeline* h, const float* xyz, int n, int stride_bytes, double stamp,
+                       loam_sweep_result* res);
+loam_sr* loam_pipeline_sr(loam_pipeline* h);
+loam_lo* loam_pipeline_lo(loam_pipeline* h);
+loam_lm* loam_pipeline_lm(loam_pipeline* h);
+
+/* number of kernel launches issued by this library on the calling process so far */
+long long loam_kernel_launch_count(void);
+/* per-kernel device time accumulated since the last reset (CUDA events; 0 when profiling is off) */
+int loam_profile_enable(int on);
+int loam_profile_report(char* buf, int cap);
+const char* loam_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LOAM_B200_H_ */

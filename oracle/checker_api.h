@@ -1,0 +1,25 @@
+/* ORACLE (test infrastructure).  The "checker API" exported identically by
+ *   oracle/liboracle_port.so        -- CPU restatement (loam_port.hpp)
+ *   oracle/liboracle_port_libm.so   -- same, glibc trig instead of detmath
+ *   oracle/_ref/libloam_ref.so      -- the reference's own .cpp files compiled from /root/reference
+ * One handle = the four nodes wired sr -> lo -> tm.onOdometry -> (lm -> tm.onMapping). */
+#ifndef LOAM_CHECKER_API_H_
+#define LOAM_CHECKER_API_H_
+#include "loam_b200.h"
+#ifdef __cplusplus
+extern "C" {
+#endif
+const char* chk_kind(void);
+void* chk_create(const loam_params* p);
+void chk_destroy(void* h);
+int chk_imu(void* h, double stamp, const double quat[4], const float acc[3]);
+int chk_push_sweep(void* h, const float* xyz, int n, double stamp, loam_sweep_result* out);
+int chk_get_cloud(void* h, int which, float* xyzi, int cap);
+int chk_get_ints(void* h, int which, int* out, int cap);
+int chk_get_floats(void* h, int which, float* out, int cap);
+void chk_busy_seconds(void* h, double out[4]);
+void chk_lo_set_state(void* h, const float transform[6], const float transformSum[6]);
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,171 @@
+// ORACLE (test infrastructure).  C interface ("checker API") over the CPU restatement in
+// loam_port.hpp so that tests/ and bench.py's cpu_baseline leg can drive it through ctypes.
+// oracle/_ref (the reference's own sources compiled from /root/reference) exports the SAME
+// symbols, so either can serve as the checker.
+#include <chrono>
+#include "loam_port.hpp"
+#include "checker_api.h"
+
+using namespace oracle;
+
+struct chk_handle {
+  loam_params P;
+  ScanRegistration sr;
+  LaserOdometry lo;
+  LaserMapping lm;
+  TransformMaintenance tm;
+  SRFeatures feat;
+  LOOutput odom;
+  loam_sweep_result res;
+  double busy[4];
+  chk_handle(const loam_params& p) : P(p), sr(p), lo(p), lm(p) { memset(&res, 0, sizeof(res)); busy[0] = busy[1] = busy[2] = busy[3] = 0; }
+};
+
+static int copy_cloud(const Cloud& c, float* out, int cap) {
+  int n = (int)c.points.size();
+  for (int i = 0; i < n && i < cap; i++) {
+    out[4 * i] = c.points[i].x; out[4 * i + 1] = c.points[i].y; out[4 * i + 2] = c.points[i].z; out[4 * i + 3] = c.points[i].intensity;
+  }
+  return n;
+}
+static int copy_ints(const std::vector<int>& v, int* out, int cap) {
+  for (int i = 0; i < (int)v.size() && i < cap; i++) out[i] = v[i];
+  return (int)v.size();
+}
+static double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+extern "C" {
+
+const char* chk_kind(void) {
+#ifdef ORACLE_LIBM
+  return "port-libm";
+#else
+  return "port";
+#endif
+}
+
+void* chk_create(const loam_params* p) { return new chk_handle(*p); }
+void chk_destroy(void* hv) { delete (chk_handle*)hv; }
+
+int chk_imu(void* hv, double stamp, const double quat[4], const float acc[3]) {
+  chk_handle* h = (chk_handle*)hv;
+  h->sr.imu(stamp, quat, acc);
+  h->lm.imu(stamp, quat);
+  return 0;
+}
+
+int chk_push_sweep(void* hv, const float* xyz, int n, double stamp, loam_sweep_result* out) {
+  chk_handle* h = (chk_handle*)hv;
+  loam_sweep_result& r = h->res;
+  r.sr_status = r.lo_status = r.lm_status = LOAM_NOT_READY;
+  double t0 = now_s();
+  bool ok = h->sr.process(xyz, n, 3, stamp, h->feat);
+  double t1 = now_s();
+  h->busy[0] += t1 - t0;
+  if (ok) {
+    r.sr_status = LOAM_OK;
+    r.n_full = (int)h->feat.full.size(); r.n_sharp = (int)h->feat.sharp.size(); r.n_less_sharp = (int)h->feat.lessSharp.size();
+    r.n_flat = (int)h->feat.flat.size(); r.n_less_flat = (int)h->feat.lessFlat.size();
+    memcpy(r.imu_trans, h->feat.imuTrans, sizeof(r.imu_trans));
+    bool lok = h->lo.process(h->feat, h->odom);
+    double t2 = now_s();
+    h->busy[1] += t2 - t1;
+    r.lo_iters = h->lo.lastIters; r.lo_rows = h->lo.lastRows; r.lo_degenerate = h->lo.isDegenerate;
+    memcpy(r.transform, h->lo.transform, sizeof(r.transform));
+    memcpy(r.transform_sum, h->lo.transformSum, sizeof(r.transform_sum));
+    if (lok) {
+      r.lo_status = LOAM_OK;
+      float sumMsg[6];
+      odometry_msg_roundtrip(h->odom.transformSum, sumMsg);
+      h->tm.onOdometry(sumMsg, r.transform_mapped);
+      double t3 = now_s();
+      h->busy[3] += t3 - t2;
+      if (h->odom.hasMappingInput) {
+        bool mok = h->lm.process(h->odom, sumMsg);
+        double t4 = now_s();
+        h->busy[2] += t4 - t3;
+        if (mok) {
+          r.lm_status = LOAM_OK;
+          r.lm_iters = h->lm.lastIters; r.lm_rows = h->lm.lastRows; r.lm_degenerate = h->lm.isDegenerate;
+          r.n_map_corner = h->lm.lastCornerFromMapNum; r.n_map_surf = h->lm.lastSurfFromMapNum;
+          r.n_stack_corner = h->lm.lastCornerStackNum; r.n_stack_surf = h->lm.lastSurfStackNum;
+          memcpy(r.transform_aft_mapped, h->lm.transformAftMapped, sizeof(float) * 6);
+          memcpy(r.transform_bef_mapped, h->lm.transformBefMapped, sizeof(float) * 6);
+          float aftMsg[6];
+          aft_mapped_msg_roundtrip(h->lm.transformAftMapped, aftMsg);
+          h->tm.onMapping(aftMsg, h->lm.transformBefMapped);
+        }
+      }
+    }
+  }
+  if (out) *out = r;
+  return r.sr_status;
+}
+
+int chk_get_cloud(void* hv, int which, float* out, int cap) {
+  chk_handle* h = (chk_handle*)hv;
+  switch (which) {
+    case LOAM_CLOUD_FULL: return copy_cloud(h->feat.full, out, cap);
+    case LOAM_CLOUD_SHARP: return copy_cloud(h->feat.sharp, out, cap);
+    case LOAM_CLOUD_LESS_SHARP: return copy_cloud(h->feat.lessSharp, out, cap);
+    case LOAM_CLOUD_FLAT: return copy_cloud(h->feat.flat, out, cap);
+    case LOAM_CLOUD_LESS_FLAT: return copy_cloud(h->feat.lessFlat, out, cap);
+    case LOAM_CLOUD_CORNER_LAST: return copy_cloud(*h->lo.laserCloudCornerLast, out, cap);
+    case LOAM_CLOUD_SURF_LAST: return copy_cloud(*h->lo.laserCloudSurfLast, out, cap);
+    case LOAM_CLOUD_FULL_END: return copy_cloud(h->odom.fullRes, out, cap);
+    case LOAM_CLOUD_REGISTERED: return copy_cloud(*h->lm.laserCloudFullRes, out, cap);
+    case LOAM_CLOUD_SURROUND: return copy_cloud(*h->lm.laserCloudSurround, out, cap);
+    case LOAM_CLOUD_MAP_CORNER: return copy_cloud(*h->lm.laserCloudCornerFromMap, out, cap);
+    case LOAM_CLOUD_MAP_SURF: return copy_cloud(*h->lm.laserCloudSurfFromMap, out, cap);
+    case LOAM_CLOUD_STACK_CORNER: return copy_cloud(*h->lm.laserCloudCornerStack, out, cap);
+    case LOAM_CLOUD_STACK_SURF: return copy_cloud(*h->lm.laserCloudSurfStack, out, cap);
+  }
+  return -1;
+}
+
+int chk_get_ints(void* hv, int which, int* out, int cap) {
+  chk_handle* h = (chk_handle*)hv;
+  int nfull = (int)h->feat.full.size();
+  auto arr = [&](const std::vector<int>& v, int n) { for (int i = 0; i < n && i < cap; i++) out[i] = v[i]; return n; };
+  auto farr = [&](const std::vector<float>& v, int n) { for (int i = 0; i < n && i < cap; i++) out[i] = (int)v[i]; return n; };
+  switch (which) {
+    case LOAM_INTS_LABEL: return arr(h->sr.cloudLabel, nfull);
+    case LOAM_INTS_PICKED: return arr(h->sr.cloudNeighborPicked, nfull);
+    case LOAM_INTS_SORT_IND: return arr(h->sr.cloudSortInd, nfull);
+    case LOAM_INTS_SHARP_IDX: return copy_ints(h->feat.sharpIdx, out, cap);
+    case LOAM_INTS_LESS_SHARP_IDX: return copy_ints(h->feat.lessSharpIdx, out, cap);
+    case LOAM_INTS_FLAT_IDX: return copy_ints(h->feat.flatIdx, out, cap);
+    case LOAM_INTS_CORNER_IND1: return farr(h->lo.pointSearchCornerInd1, (int)h->feat.sharp.size());
+    case LOAM_INTS_CORNER_IND2: return farr(h->lo.pointSearchCornerInd2, (int)h->feat.sharp.size());
+    case LOAM_INTS_SURF_IND1: return farr(h->lo.pointSearchSurfInd1, (int)h->feat.flat.size());
+    case LOAM_INTS_SURF_IND2: return farr(h->lo.pointSearchSurfInd2, (int)h->feat.flat.size());
+    case LOAM_INTS_SURF_IND3: return farr(h->lo.pointSearchSurfInd3, (int)h->feat.flat.size());
+    case LOAM_INTS_SCAN_START: return arr(h->sr.scanStartInd, (int)h->sr.scanStartInd.size());
+    case LOAM_INTS_SCAN_END: return arr(h->sr.scanEndInd, (int)h->sr.scanEndInd.size());
+    case 100: return copy_ints(h->lm.cornerNN, out, cap);  // LM 5-NN indices of the last iteration
+    case 101: return copy_ints(h->lm.surfNN, out, cap);
+  }
+  return -1;
+}
+
+int chk_get_floats(void* hv, int which, float* out, int cap) {
+  chk_handle* h = (chk_handle*)hv;
+  if (which == LOAM_FLOATS_CURVATURE) {
+    int n = (int)h->feat.full.size();
+    for (int i = 0; i < n && i < cap; i++) out[i] = h->sr.cloudCurvature[i];
+    return n;
+  }
+  return -1;
+}
+
+// per-node busy seconds accumulated so far: sr, lo, lm, tm
+void chk_busy_seconds(void* hv, double out[4]) { memcpy(out, ((chk_handle*)hv)->busy, sizeof(double) * 4); }
+
+// teacher forcing (parity tests): overwrite laserOdometry's transform / transformSum
+void chk_lo_set_state(void* hv, const float transform[6], const float transformSum[6]) {
+  chk_handle* h = (chk_handle*)hv;
+  memcpy(h->lo.transform, transform, sizeof(float) * 6);
+  memcpy(h->lo.transformSum, transformSum, sizeof(float) * 6);
+}
+
+}  // extern "C"
