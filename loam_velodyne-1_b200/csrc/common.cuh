@@ -1,0 +1,100 @@
+// common.cuh -- shared host/device utilities for the sm_100a LOAM kernels.
+// Device TUs are compiled with -fmad=false: every float expression that feeds an index-selecting
+// comparison must round exactly like the reference's x86-64 SSE2 code.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <map>
+#include <vector>
+#include "loam_b200.h"
+#include "loam/detmath.h"
+
+#ifndef M_PI
+#define M_PI 3.14159265358979323846
+#endif
+
+namespace loamgpu {
+namespace dm = loam::dm;
+
+void set_error(const char* fmt, ...);
+extern long long g_launches;
+extern bool g_profile;
+
+struct ProfEntry { double ms = 0; long long calls = 0; };
+std::map<std::string, ProfEntry>& prof_table();
+void prof_begin(cudaStream_t s);
+void prof_end(const char* name, cudaStream_t s);
+
+#define CUDA_OK(expr)                                                                     \
+  do {                                                                                    \
+    cudaError_t _e = (expr);                                                              \
+    if (_e != cudaSuccess) {                                                              \
+      loamgpu::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return LOAM_ERR_CUDA;                                                               \
+    }                                                                                     \
+  } while (0)
+
+// every kernel launch of the library goes through this macro: counts launches (bench.py's
+// gpu_launches) and, in profile mode, brackets the launch with CUDA events on its own stream
+#define LAUNCH(name, kern, grid, block, smem, stream, ...)                 \
+  do {                                                                     \
+    if (loamgpu::g_profile) loamgpu::prof_begin(stream);                   \
+    kern<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);              \
+    loamgpu::g_launches++;                                                 \
+    if (loamgpu::g_profile) loamgpu::prof_end(name, stream);               \
+  } while (0)
+
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  int alloc(size_t count) {
+    free();
+    n = count;
+    if (count == 0) return LOAM_OK;
+    cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
+    if (e != cudaSuccess) { set_error("cudaMalloc(%zu bytes) failed: %s", count * sizeof(T), cudaGetErrorString(e)); p = nullptr; return LOAM_ERR_CUDA; }
+    return LOAM_OK;
+  }
+  int alloc_zero(size_t count, cudaStream_t s = 0) {
+    int r = alloc(count);
+    if (r != LOAM_OK) return r;
+    if (count && cudaMemsetAsync(p, 0, count * sizeof(T), s) != cudaSuccess) return LOAM_ERR_CUDA;
+    return LOAM_OK;
+  }
+  void free() { if (p) cudaFree(p); p = nullptr; n = 0; }
+  ~DevBuf() { free(); }
+  DevBuf() {}
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+};
+
+template <typename T>
+struct PinnedBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  int alloc(size_t count) {
+    free();
+    n = count;
+    if (cudaMallocHost((void**)&p, count * sizeof(T)) != cudaSuccess) { set_error("cudaMallocHost failed"); p = nullptr; return LOAM_ERR_CUDA; }
+    return LOAM_OK;
+  }
+  void free() { if (p) cudaFreeHost(p); p = nullptr; n = 0; }
+  ~PinnedBuf() { free(); }
+};
+
+// order-preserving float <-> uint mapping for atomicMin/Max on floats
+__device__ __forceinline__ unsigned int float_flip(float f) {
+  unsigned int u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float float_unflip(unsigned int u) {
+  return __uint_as_float((u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u);
+}
+
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+
+}  // namespace loamgpu

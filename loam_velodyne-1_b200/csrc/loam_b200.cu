@@ -1,0 +1,179 @@
+// loam_b200.cu -- the one translation unit of libloam_b200.so: globals, profiling hooks and the
+// extern "C" boundary declared in include/loam_b200.h.  Compiled for sm_100a only, -fmad=false.
+#include <stdarg.h>
+#include <mutex>
+#include "common.cuh"
+#include "loam_sr.cuh"
+#include "loam_lo.cuh"
+#include "loam_lm.cuh"
+#include "loam_pipeline.cuh"
+
+namespace loamgpu {
+
+long long g_launches = 0;
+bool g_profile = false;
+static thread_local char g_err[512] = "";
+static cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+std::map<std::string, ProfEntry>& prof_table() {
+  static std::map<std::string, ProfEntry> t;
+  return t;
+}
+void prof_begin(cudaStream_t s) {
+  if (!g_ev0) { cudaEventCreate(&g_ev0); cudaEventCreate(&g_ev1); }
+  cudaEventRecord(g_ev0, s);
+}
+void prof_end(const char* name, cudaStream_t s) {
+  cudaEventRecord(g_ev1, s);
+  cudaEventSynchronize(g_ev1);
+  float ms = 0;
+  cudaEventElapsedTime(&ms, g_ev0, g_ev1);
+  ProfEntry& e = prof_table()[name];
+  e.ms += ms;
+  e.calls++;
+}
+
+template <typename T>
+static int download_array(const T* dev, int count, T* out, int cap, int* n, cudaStream_t s) {
+  if (n) *n = count;
+  int c = count < cap ? count : cap;
+  if (c > 0 && out) {
+    CUDA_OK(cudaMemcpyAsync(out, dev, sizeof(T) * (size_t)c, cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+  }
+  return LOAM_OK;
+}
+
+}  // namespace loamgpu
+
+using namespace loamgpu;
+
+struct loam_sr { SRHandle h; };
+struct loam_lo { LOHandle h; };
+struct loam_lm { LMHandle h; };
+struct loam_tm { TMHost h; };
+struct loam_pipeline { PipelineHandle h; };
+
+extern "C" {
+
+int loam_params_preset(loam_params* p, int preset) {
+  if (!p) return LOAM_ERR_ARG;
+  memset(p, 0, sizeof(*p));
+  p->system_delay = 20;
+  p->lo_max_iter = 25;
+  p->lm_max_iter = 10;
+  p->map_arena_points = 8 << 20;
+  switch (preset) {
+    case 1: p->n_scans = 16; p->ring_model = 0; p->ring_lower_deg = -15.f; p->ring_upper_deg = 15.f; p->max_points = 40000; break;
+    case 2: p->n_scans = 64; p->ring_model = 1; p->ring_lower_deg = -24.8f; p->ring_upper_deg = 2.0f; p->max_points = 160000; break;
+    case 4: p->n_scans = 128; p->ring_model = 1; p->ring_lower_deg = -25.f; p->ring_upper_deg = 15.f; p->max_points = 300000; break;
+    default: return LOAM_ERR_ARG;
+  }
+  return LOAM_OK;
+}
+
+const char* loam_last_error(void) { return g_err; }
+long long loam_kernel_launch_count(void) { return g_launches; }
+int loam_profile_enable(int on) {
+  g_profile = on != 0;
+  prof_table().clear();
+  return LOAM_OK;
+}
+int loam_profile_report(char* buf, int cap) {
+  std::string s;
+  char line[256];
+  for (auto& kv : prof_table()) {
+    snprintf(line, sizeof(line), "%s %lld %.6f\n", kv.first.c_str(), kv.second.calls, kv.second.ms);
+    s += line;
+  }
+  if (buf && cap > 0) {
+    strncpy(buf, s.c_str(), cap - 1);
+    buf[cap - 1] = 0;
+  }
+  return (int)s.size();
+}
+
+// ---------------- scanRegistration ----------------
+int loam_sr_create(const loam_params* p, int device, loam_sr** out) {
+  if (!p || !out) return LOAM_ERR_ARG;
+  loam_sr* h = new loam_sr();
+  int r = h->h.init(p, device, nullptr);
+  if (r != LOAM_OK) { delete h; return r; }
+  *out = h;
+  return LOAM_OK;
+}
+void loam_sr_destroy(loam_sr* h) { delete h; }
+int loam_sr_imu(loam_sr* h, double stamp, const double quat[4], const float acc[3]) {
+  if (!h) return LOAM_ERR_ARG;
+  return h->h.on_imu(stamp, quat, acc);
+}
+int loam_sr_process(loam_sr* h, const float* xyz, int n, int stride_bytes, double stamp) {
+  if (!h) return LOAM_ERR_ARG;
+  int r = h->h.process(xyz, n, stride_bytes, stamp);
+  if (r != LOAM_OK) return r;
+  return h->h.sync_counts();
+}
+int loam_sr_download(loam_sr* hh, int which, float* xyzi, int cap, int* n) {
+  if (!hh) return LOAM_ERR_ARG;
+  SRHandle& h = hh->h;
+  const SRCounts& c = h.last_counts;
+  const float4* src; int count;
+  switch (which) {
+    case LOAM_CLOUD_FULL: src = h.d_full.p; count = c.n_full; break;
+    case LOAM_CLOUD_SHARP: src = h.d_sharp.p; count = c.n_sharp; break;
+    case LOAM_CLOUD_LESS_SHARP: src = h.d_less_sharp.p; count = c.n_less_sharp; break;
+    case LOAM_CLOUD_FLAT: src = h.d_flat.p; count = c.n_flat; break;
+    case LOAM_CLOUD_LESS_FLAT: src = h.d_less_flat.p; count = c.n_less_flat; break;
+    default: return LOAM_ERR_ARG;
+  }
+  return download_array((const float4*)src, count, (float4*)xyzi, cap, n, h.stream);
+}
+int loam_sr_download_ints(loam_sr* hh, int which, int* out, int cap, int* n) {
+  if (!hh) return LOAM_ERR_ARG;
+  SRHandle& h = hh->h;
+  const SRCounts& c = h.last_counts;
+  switch (which) {
+    case LOAM_INTS_SORT_IND: return download_array(h.d_sort_ind.p, c.n_full, out, cap, n, h.stream);
+    case LOAM_INTS_SHARP_IDX: return download_array(h.d_sharp_idx.p, c.n_sharp, out, cap, n, h.stream);
+    case LOAM_INTS_LESS_SHARP_IDX: return download_array(h.d_less_sharp_idx.p, c.n_less_sharp, out, cap, n, h.stream);
+    case LOAM_INTS_FLAT_IDX: return download_array(h.d_flat_idx.p, c.n_flat, out, cap, n, h.stream);
+    case LOAM_INTS_SCAN_START: return download_array(h.d_scan_start.p, h.P.n_scans, out, cap, n, h.stream);
+    case LOAM_INTS_SCAN_END: return download_array(h.d_scan_end.p, h.P.n_scans, out, cap, n, h.stream);
+    case LOAM_INTS_LABEL:
+    case LOAM_INTS_PICKED: {
+      int cnt = c.n_full;
+      if (n) *n = cnt;
+      int m = cnt < cap ? cnt : cap;
+      std::vector<signed char> tmp(m > 0 ? m : 1);
+      const void* src = which == LOAM_INTS_LABEL ? (const void*)h.d_label.p : (const void*)h.d_picked.p;
+      if (m > 0) {
+        CUDA_OK(cudaMemcpyAsync(tmp.data(), src, m, cudaMemcpyDeviceToHost, h.stream));
+        CUDA_OK(cudaStreamSynchronize(h.stream));
+        for (int i = 0; i < m; i++) out[i] = tmp[i];
+      }
+      return LOAM_OK;
+    }
+  }
+  return LOAM_ERR_ARG;
+}
+int loam_sr_download_floats(loam_sr* hh, int which, float* out, int cap, int* n) {
+  if (!hh) return LOAM_ERR_ARG;
+  if (which != LOAM_FLOATS_CURVATURE) return LOAM_ERR_ARG;
+  return download_array(hh->h.d_curv.p, hh->h.last_counts.n_full, out, cap, n, hh->h.stream);
+}
+int loam_sr_imu_trans(loam_sr* h, float out12[12]) {
+  if (!h) return LOAM_ERR_ARG;
+  h->h.imu_trans(out12);
+  return LOAM_OK;
+}
+
+#include "loam_capi_rest.inc"
+
+}  // extern "C"

@@ -1,0 +1,230 @@
+// loam_sr.cuh -- host side of the scanRegistration node: owns the device buffers, keeps the IMU
+// ring buffer (sequential, host; scanRegistration.cpp:638-660,173-209) and enqueues the kernels.
+#pragma once
+#include <limits.h>
+#include "sr_kernels2.cuh"
+#include "pose_math.cuh"
+
+namespace loamgpu {
+
+struct SRHandle {
+  loam_params P;
+  SRParamsDev Pd;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  int cap = 0;       // max_points
+  int nblk_cap = 0;
+  // system delay (:213-219)
+  int systemInitCount = 0;
+  bool systemInited = false;
+  // device buffers
+  DevBuf<float> d_raw;
+  DevBuf<short> d_ring;
+  DevBuf<float> d_ori, d_reltime, d_curv;
+  DevBuf<int> d_hist, d_ring_start, d_scan_start, d_scan_end, d_pos, d_sort_ind;
+  DevBuf<unsigned char> d_picked, d_gap, d_steps;
+  DevBuf<signed char> d_label;
+  DevBuf<int> d_sharp_ring, d_less_sharp_ring, d_flat_ring, d_ring_counts, d_blockmax;
+  DevBuf<int> d_sharp_idx, d_less_sharp_idx, d_flat_idx;
+  DevBuf<float4> d_full, d_sharp, d_less_sharp, d_flat, d_less_flat, d_lessflat_tmp;
+  DevBuf<SRCounts> d_cnt;
+  DevBuf<ImuSnapshot> d_imu;
+  DevBuf<ImuState> d_imu_state;  // [2]
+  PinnedBuf<float> h_raw;
+  PinnedBuf<SRCounts> h_cnt;
+  PinnedBuf<ImuSnapshot> h_imu;
+  PinnedBuf<ImuState> h_imu_state;
+  int imu_parity = 0;
+  // host IMU ring buffer
+  ImuSnapshot imu;
+  float imuAcc[3][IMU_Q];
+  bool has_imu = false;
+  int last_n = 0;
+  double last_stamp = 0;
+  SRCounts last_counts;
+  bool processed = false;
+
+  int init(const loam_params* p, int dev, cudaStream_t s) {
+    P = *p;
+    device = dev;
+    if (P.n_scans < 1 || P.n_scans > SR_MAX_RINGS || P.max_points < 64) { set_error("bad params"); return LOAM_ERR_ARG; }
+    CUDA_OK(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    CUDA_OK(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major < 10) { set_error("device %d is sm_%d%d; this library is built for sm_100a only", dev, prop.major, prop.minor); return LOAM_ERR_CUDA; }
+    if (s) stream = s; else { CUDA_OK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking)); own_stream = true; }
+    Pd.n_scans = P.n_scans; Pd.ring_model = P.ring_model; Pd.ring_lower = P.ring_lower_deg; Pd.ring_upper = P.ring_upper_deg;
+    Pd.max_points = P.max_points;
+    cap = P.max_points;
+    nblk_cap = (cap + SR_BLK - 1) / SR_BLK;
+    int R = P.n_scans;
+    int r = LOAM_OK;
+    r |= d_raw.alloc((size_t)cap * 3); r |= d_ring.alloc(cap); r |= d_ori.alloc(cap); r |= d_reltime.alloc(cap);
+    r |= d_curv.alloc_zero(cap, stream); r |= d_hist.alloc((size_t)R * nblk_cap); r |= d_ring_start.alloc(R + 1);
+    r |= d_scan_start.alloc(R); r |= d_scan_end.alloc(R); r |= d_pos.alloc(cap); r |= d_sort_ind.alloc_zero(cap, stream);
+    r |= d_picked.alloc_zero(cap + 16, stream); r |= d_gap.alloc_zero(cap + 16, stream); r |= d_steps.alloc(cap);
+    r |= d_label.alloc_zero(cap, stream);
+    r |= d_sharp_ring.alloc((size_t)R * SR_SHARP_PER_RING); r |= d_less_sharp_ring.alloc((size_t)R * SR_LESS_SHARP_PER_RING);
+    r |= d_flat_ring.alloc((size_t)R * SR_FLAT_PER_RING); r |= d_ring_counts.alloc_zero((size_t)R * 4, stream);
+    r |= d_blockmax.alloc(nblk_cap);
+    r |= d_sharp_idx.alloc((size_t)R * SR_SHARP_PER_RING); r |= d_less_sharp_idx.alloc((size_t)R * SR_LESS_SHARP_PER_RING);
+    r |= d_flat_idx.alloc((size_t)R * SR_FLAT_PER_RING);
+    r |= d_full.alloc(cap); r |= d_sharp.alloc((size_t)R * SR_SHARP_PER_RING); r |= d_less_sharp.alloc((size_t)R * SR_LESS_SHARP_PER_RING);
+    r |= d_flat.alloc((size_t)R * SR_FLAT_PER_RING); r |= d_less_flat.alloc(cap); r |= d_lessflat_tmp.alloc((size_t)R * SR_RING_CAP);
+    r |= d_cnt.alloc_zero(1, stream); r |= d_imu.alloc(1); r |= d_imu_state.alloc_zero(2, stream);
+    r |= h_raw.alloc((size_t)cap * 3); r |= h_cnt.alloc(1); r |= h_imu.alloc(1); r |= h_imu_state.alloc(1);
+    if (r != LOAM_OK) return LOAM_ERR_CUDA;
+    memset(&imu, 0, sizeof(imu));
+    memset(imuAcc, 0, sizeof(imuAcc));
+    imu.pointer_last = -1;
+    memset(&last_counts, 0, sizeof(last_counts));
+    memset(h_imu_state.p, 0, sizeof(ImuState));
+    CUDA_OK(cudaFuncSetAttribute(sr_lessflat, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)((sizeof(unsigned long long) + sizeof(float4)) * SR_RING_CAP)));
+    CUDA_OK(cudaStreamSynchronize(stream));
+    return LOAM_OK;
+  }
+  ~SRHandle() { if (own_stream && stream) cudaStreamDestroy(stream); }
+
+  // imuHandler :638-660 + AccumulateIMUShift :173-209 (host, sequential)
+  int on_imu(double stamp, const double quat[4], const float acc[3]) {
+    double roll, pitch, yaw;
+    pm::rpy_from_quat(quat[0], quat[1], quat[2], quat[3], roll, pitch, yaw);
+    double lax = acc[0], lay = acc[1], laz = acc[2];
+    float accX = lay - dm::sin(roll) * dm::cos(pitch) * 9.81;
+    float accY = laz - dm::cos(roll) * dm::cos(pitch) * 9.81;
+    float accZ = lax + dm::sin(pitch) * 9.81;
+    int last = (imu.pointer_last + 1) % IMU_Q;
+    imu.pointer_last = last;
+    imu.time[last] = stamp;
+    imu.roll[last] = roll; imu.pitch[last] = pitch; imu.yaw[last] = yaw;
+    imuAcc[0][last] = accX; imuAcc[1][last] = accY; imuAcc[2][last] = accZ;
+    {
+      float r_ = imu.roll[last], p_ = imu.pitch[last], y_ = imu.yaw[last];
+      float aX = imuAcc[0][last], aY = imuAcc[1][last], aZ = imuAcc[2][last];
+      float x1 = dm::cos(r_) * aX - dm::sin(r_) * aY;
+      float y1 = dm::sin(r_) * aX + dm::cos(r_) * aY;
+      float z1 = aZ;
+      float x2 = x1;
+      float y2 = dm::cos(p_) * y1 - dm::sin(p_) * z1;
+      float z2 = dm::sin(p_) * y1 + dm::cos(p_) * z1;
+      aX = dm::cos(y_) * x2 + dm::sin(y_) * z2;
+      aY = y2;
+      aZ = -dm::sin(y_) * x2 + dm::cos(y_) * z2;
+      int back = (last + IMU_Q - 1) % IMU_Q;
+      double timeDiff = imu.time[last] - imu.time[back];
+      const double scanPeriod = 0.1;
+      if (timeDiff < scanPeriod) {
+        imu.shift[0][last] = imu.shift[0][back] + imu.velo[0][back] * timeDiff + aX * timeDiff * timeDiff / 2;
+        imu.shift[1][last] = imu.shift[1][back] + imu.velo[1][back] * timeDiff + aY * timeDiff * timeDiff / 2;
+        imu.shift[2][last] = imu.shift[2][back] + imu.velo[2][back] * timeDiff + aZ * timeDiff * timeDiff / 2;
+        imu.velo[0][last] = imu.velo[0][back] + aX * timeDiff;
+        imu.velo[1][last] = imu.velo[1][back] + aY * timeDiff;
+        imu.velo[2][last] = imu.velo[2][back] + aZ * timeDiff;
+      }
+    }
+    has_imu = true;
+    return LOAM_OK;
+  }
+
+  // laserCloudHandler :211-636.  Enqueues everything on `stream`; no host synchronisation.
+  int process(const float* xyz, int n, int stride_bytes, double stamp) {
+    processed = false;
+    if (!systemInited) {  // :213-219
+      systemInitCount++;
+      if (systemInitCount >= P.system_delay) systemInited = true;
+      return LOAM_NOT_READY;
+    }
+    if (n <= 0 || !xyz || stride_bytes < 12 || (stride_bytes & 3)) { set_error("bad sweep"); return LOAM_ERR_ARG; }
+    if (n > cap) { set_error("sweep of %d points exceeds max_points=%d", n, cap); return LOAM_ERR_CAPACITY; }
+    CUDA_OK(cudaSetDevice(device));
+    // stage through pinned memory (packed xyz); first/last finite points give startOri/endOri
+    CUDA_OK(cudaStreamSynchronize(stream));  // previous sweep may still read h_raw / d_raw
+    int sf = stride_bytes / 4;
+    int first = -1, lastf = -1;
+    for (int i = 0; i < n; i++) {
+      const float* p = xyz + (size_t)i * sf;
+      h_raw.p[3 * i] = p[0]; h_raw.p[3 * i + 1] = p[1]; h_raw.p[3 * i + 2] = p[2];
+    }
+    for (int i = 0; i < n; i++) {
+      const float* p = h_raw.p + 3 * i;
+      if (isfinite(p[0]) && isfinite(p[1]) && isfinite(p[2])) { first = i; break; }
+    }
+    for (int i = n - 1; i >= 0; i--) {
+      const float* p = h_raw.p + 3 * i;
+      if (isfinite(p[0]) && isfinite(p[1]) && isfinite(p[2])) { lastf = i; break; }
+    }
+    if (first < 0) return LOAM_NOT_READY;
+    // :230-238
+    float startOri = -dm::atan2(h_raw.p[3 * first + 1], h_raw.p[3 * first]);
+    float endOri = -dm::atan2(h_raw.p[3 * lastf + 1], h_raw.p[3 * lastf]) + 2 * M_PI;
+    if (endOri - startOri > 3 * M_PI) {
+      endOri -= 2 * M_PI;
+    } else if (endOri - startOri < M_PI) {
+      endOri += 2 * M_PI;
+    }
+    CUDA_OK(cudaMemcpyAsync(d_raw.p, h_raw.p, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, stream));
+    return process_device(n, first, startOri, endOri, stamp);
+  }
+
+  int process_device(int n, int first, float startOri, float endOri, double stamp) {
+    const int R = P.n_scans;
+    const int nblk = (n + SR_BLK - 1) / SR_BLK;
+    SRCounts init;
+    memset(&init, 0, sizeof(init));
+    init.h_min = INT_MAX;
+    init.last_valid = -1;
+    *h_cnt.p = init;
+    CUDA_OK(cudaMemcpyAsync(d_cnt.p, h_cnt.p, sizeof(SRCounts), cudaMemcpyHostToDevice, stream));
+    LAUNCH("sr_ring_ori", sr_ring_ori, nblk, SR_BLK, 0, stream, d_raw.p, n, 3, Pd, startOri, d_ring.p, d_ori.p, d_hist.p, nblk, d_cnt.p);
+    LAUNCH("sr_ring_scan", sr_ring_scan, 1, 1024, 0, stream, d_hist.p, nblk, R, d_ring_start.p, d_scan_start.p, d_scan_end.p, d_cnt.p, cap);
+    LAUNCH("sr_scatter", sr_scatter, nblk, SR_BLK, 0, stream, d_raw.p, n, 3, Pd, startOri, endOri, d_ring.p, d_ori.p, d_hist.p, nblk,
+           d_cnt.p, d_full.p, d_pos.p, d_reltime.p);
+    if (has_imu && imu.pointer_last >= 0) {  // :286
+      *h_imu.p = imu;
+      CUDA_OK(cudaMemcpyAsync(d_imu.p, h_imu.p, sizeof(ImuSnapshot), cudaMemcpyHostToDevice, stream));
+      ImuState* st_in = d_imu_state.p + imu_parity;
+      ImuState* st_out = d_imu_state.p + (imu_parity ^ 1);
+      CUDA_OK(cudaMemcpyAsync(st_out, st_in, sizeof(ImuState), cudaMemcpyDeviceToDevice, stream));
+      LAUNCH("sr_imu_steps", sr_imu_steps_kernel, nblk, SR_BLK, 0, stream, n, d_ring.p, d_reltime.p, stamp, d_imu.p, st_in, d_steps.p, d_blockmax.p);
+      LAUNCH("sr_imu_deskew", sr_imu_deskew, nblk, SR_BLK, 0, stream, n, first, d_ring.p, d_reltime.p, d_pos.p, stamp, d_imu.p, st_in, st_out,
+             d_steps.p, d_blockmax.p, nblk, d_full.p, cap, d_cnt.p);
+      imu_parity ^= 1;
+    }
+    int crblocks = (n + CR_TILE - 1) / CR_TILE;
+    LAUNCH("sr_curv_reject", sr_curv_reject, crblocks, CR_TILE, 0, stream, d_full.p, d_cnt.p, d_curv.p, d_sort_ind.p, d_picked.p, d_label.p, d_gap.p);
+    LAUNCH("sr_sort_sectors", sr_sort_sectors, dim3(6, R), 512, 0, stream, d_curv.p, d_sort_ind.p, d_scan_start.p, d_scan_end.p, d_cnt.p);
+    LAUNCH("sr_select", sr_select, R, 32, 0, stream, d_curv.p, d_sort_ind.p, d_scan_start.p, d_scan_end.p, d_ring_start.p, d_gap.p,
+           d_picked.p, d_label.p, d_sharp_ring.p, d_less_sharp_ring.p, d_flat_ring.p, d_ring_counts.p, d_cnt.p);
+    size_t smem = (sizeof(unsigned long long) + sizeof(float4)) * SR_RING_CAP;
+    LAUNCH("sr_lessflat", sr_lessflat, R, 1024, smem, stream, d_full.p, d_label.p, d_scan_start.p, d_scan_end.p, d_lessflat_tmp.p, d_ring_counts.p, d_cnt.p);
+    LAUNCH("sr_compact", sr_compact, R, 128, 0, stream, d_full.p, d_ring_counts.p, R, d_sharp_ring.p, d_less_sharp_ring.p, d_flat_ring.p,
+           d_lessflat_tmp.p, d_sharp.p, d_less_sharp.p, d_flat.p, d_less_flat.p, d_sharp_idx.p, d_less_sharp_idx.p, d_flat_idx.p, d_cnt.p, cap);
+    CUDA_OK(cudaGetLastError());
+    last_n = n;
+    last_stamp = stamp;
+    processed = true;
+    return LOAM_OK;
+  }
+
+  const ImuState* imu_state_dev() const { return d_imu_state.p + imu_parity; }
+
+  // blocking: fetch the counters of the last sweep
+  int sync_counts() {
+    CUDA_OK(cudaMemcpyAsync(h_cnt.p, d_cnt.p, sizeof(SRCounts), cudaMemcpyDeviceToHost, stream));
+    CUDA_OK(cudaMemcpyAsync(h_imu_state.p, imu_state_dev(), sizeof(ImuState), cudaMemcpyDeviceToHost, stream));
+    CUDA_OK(cudaStreamSynchronize(stream));
+    last_counts = *h_cnt.p;
+    if (last_counts.error) { set_error("scanRegistration capacity exceeded (flags %d)", last_counts.error); return LOAM_ERR_CAPACITY; }
+    return LOAM_OK;
+  }
+  void imu_trans(float out[12]) const {  // :614-629
+    const ImuState& s = *h_imu_state.p;
+    out[0] = s.rpy_start[1]; out[1] = s.rpy_start[2]; out[2] = s.rpy_start[0];
+    out[3] = s.rpy_cur[1]; out[4] = s.rpy_cur[2]; out[5] = s.rpy_cur[0];
+    for (int a = 0; a < 3; a++) { out[6 + a] = s.shift_from_start[a]; out[9 + a] = s.velo_from_start[a]; }
+  }
+};
+
+}  // namespace loamgpu
