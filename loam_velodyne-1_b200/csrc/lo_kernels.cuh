@@ -1,0 +1,364 @@
+// lo_kernels.cuh -- laserOdometry on sm_100a (SURVEY.md §8a rows LO-1 .. LO-12).
+//
+// The reference's LM loop (laserOdometry.cpp:470-827) is <= 25 strictly sequential iterations of
+// {transform every feature, (every 5th) kd-tree 1-NN + ring-window scans, residuals, Jacobian of
+// ALL rows accumulated so far, 6x6 normal equations, QR solve}.  Launch latency would dominate,
+// so the whole loop is ONE cooperative kernel: one warp per feature, one grid-wide barrier per
+// iteration, and every block redundantly finishes the (deterministic) 27-term reduction and the
+// 6x6 solve so no second barrier or broadcast is needed.
+#pragma once
+#include <cooperative_groups.h>
+#include "grid_index.cuh"
+#include "linalg.cuh"
+#include "pose_math.cuh"
+#include "sr_kernels.cuh"
+
+namespace loamgpu {
+namespace cg = cooperative_groups;
+
+constexpr int LO_THREADS = 512;
+constexpr int LO_WARPS = LO_THREADS / 32;
+constexpr int LO_NRED = 28;  // 21 (AtA upper) + 6 (AtB) + 1 (row count)
+
+struct LOState {
+  float transform[6];      // laserOdometry.cpp:93
+  float transformSum[6];   // :94
+  int isDegenerate;        // :404
+  float matP[36];          // :405
+  int cornerLastNum;       // :81 (zero until first set at :901)
+  int surfLastNum;         // :82
+  int iters, rows;         // stats of the last sweep
+  int index_enable;        // cornerLastNum > 10 && surfLastNum > 100 (:903)
+  int n_corner_last, n_surf_last, n_full_end;  // sizes of the device clouds
+};
+
+struct LOArgs {
+  LOState* st;
+  const SRCounts* cnt;          // n_sharp, n_flat of this sweep
+  const float4* sharp;
+  const float4* flat;
+  const float4* corner_last;    // original order (indices of the reference)
+  const float4* surf_last;
+  GridView corner_grid, surf_grid;
+  int* corner_ind1; int* corner_ind2;           // pointSearchCornerInd1/2 (:85-86)
+  int* surf_ind1; int* surf_ind2; int* surf_ind3;  // :89-91
+  float4* coeff;                // [max_iter][fcap] rows of every iteration (coeffSel accumulates, :458-459)
+  unsigned char* row_valid;     // [max_iter][fcap]
+  double* partials;             // [2][gridDim][LO_NRED]
+  const ImuState* imu;          // imuTrans of this sweep
+  int fcap;
+  int max_iter;
+};
+
+// TransformToStart :101-124
+__device__ __forceinline__ float4 lo_transform_to_start(const float4 pi, const float* transform) {
+  float s = 10 * (pi.w - int(pi.w));
+  float rx = s * transform[0];
+  float ry = s * transform[1];
+  float rz = s * transform[2];
+  float tx = s * transform[3];
+  float ty = s * transform[4];
+  float tz = s * transform[5];
+  float x1 = dm::cos(rz) * (pi.x - tx) + dm::sin(rz) * (pi.y - ty);
+  float y1 = -dm::sin(rz) * (pi.x - tx) + dm::cos(rz) * (pi.y - ty);
+  float z1 = (pi.z - tz);
+  float x2 = x1;
+  float y2 = dm::cos(rx) * y1 + dm::sin(rx) * z1;
+  float z2 = -dm::sin(rx) * y1 + dm::cos(rx) * z1;
+  float4 po;
+  po.x = dm::cos(ry) * x2 - dm::sin(ry) * z2;
+  po.y = y2;
+  po.z = dm::sin(ry) * x2 + dm::cos(ry) * z2;
+  po.w = pi.w;
+  return po;
+}
+
+// TransformToEnd :126-194
+__device__ __forceinline__ float4 lo_transform_to_end(const float4 pi, const float* transform, const float* imu /*12*/) {
+  float s = 10 * (pi.w - int(pi.w));
+  float rx = s * transform[0];
+  float ry = s * transform[1];
+  float rz = s * transform[2];
+  float tx = s * transform[3];
+  float ty = s * transform[4];
+  float tz = s * transform[5];
+  float x1 = dm::cos(rz) * (pi.x - tx) + dm::sin(rz) * (pi.y - ty);
+  float y1 = -dm::sin(rz) * (pi.x - tx) + dm::cos(rz) * (pi.y - ty);
+  float z1 = (pi.z - tz);
+  float x2 = x1;
+  float y2 = dm::cos(rx) * y1 + dm::sin(rx) * z1;
+  float z2 = -dm::sin(rx) * y1 + dm::cos(rx) * z1;
+  float x3 = dm::cos(ry) * x2 - dm::sin(ry) * z2;
+  float y3 = y2;
+  float z3 = dm::sin(ry) * x2 + dm::cos(ry) * z2;
+  rx = transform[0];
+  ry = transform[1];
+  rz = transform[2];
+  tx = transform[3];
+  ty = transform[4];
+  tz = transform[5];
+  float x4 = dm::cos(ry) * x3 + dm::sin(ry) * z3;
+  float y4 = y3;
+  float z4 = -dm::sin(ry) * x3 + dm::cos(ry) * z3;
+  float x5 = x4;
+  float y5 = dm::cos(rx) * y4 - dm::sin(rx) * z4;
+  float z5 = dm::sin(rx) * y4 + dm::cos(rx) * z4;
+  float x6 = dm::cos(rz) * x5 - dm::sin(rz) * y5 + tx;
+  float y6 = dm::sin(rz) * x5 + dm::cos(rz) * y5 + ty;
+  float z6 = z5 + tz;
+  const float imuPitchStart = imu[0], imuYawStart = imu[1], imuRollStart = imu[2];
+  const float imuPitchLast = imu[3], imuYawLast = imu[4], imuRollLast = imu[5];
+  const float imuShiftFromStartX = imu[6], imuShiftFromStartY = imu[7], imuShiftFromStartZ = imu[8];
+  float x7 = dm::cos(imuRollStart) * (x6 - imuShiftFromStartX) - dm::sin(imuRollStart) * (y6 - imuShiftFromStartY);
+  float y7 = dm::sin(imuRollStart) * (x6 - imuShiftFromStartX) + dm::cos(imuRollStart) * (y6 - imuShiftFromStartY);
+  float z7 = z6 - imuShiftFromStartZ;
+  float x8 = x7;
+  float y8 = dm::cos(imuPitchStart) * y7 - dm::sin(imuPitchStart) * z7;
+  float z8 = dm::sin(imuPitchStart) * y7 + dm::cos(imuPitchStart) * z7;
+  float x9 = dm::cos(imuYawStart) * x8 + dm::sin(imuYawStart) * z8;
+  float y9 = y8;
+  float z9 = -dm::sin(imuYawStart) * x8 + dm::cos(imuYawStart) * z8;
+  float x10 = dm::cos(imuYawLast) * x9 - dm::sin(imuYawLast) * z9;
+  float y10 = y9;
+  float z10 = dm::sin(imuYawLast) * x9 + dm::cos(imuYawLast) * z9;
+  float x11 = x10;
+  float y11 = dm::cos(imuPitchLast) * y10 + dm::sin(imuPitchLast) * z10;
+  float z11 = -dm::sin(imuPitchLast) * y10 + dm::cos(imuPitchLast) * z10;
+  float4 po;
+  po.x = dm::cos(imuRollLast) * x11 + dm::sin(imuRollLast) * y11;
+  po.y = -dm::sin(imuRollLast) * x11 + dm::cos(imuRollLast) * y11;
+  po.z = z11;
+  po.w = int(pi.w);
+  return po;
+}
+
+// imuTrans as laserOdometry receives it (:337-351) from scanRegistration's state (:614-629)
+__device__ __forceinline__ void lo_load_imu(const ImuState* s, float* imu /*12*/) {
+  imu[0] = s->rpy_start[1]; imu[1] = s->rpy_start[2]; imu[2] = s->rpy_start[0];
+  imu[3] = s->rpy_cur[1]; imu[4] = s->rpy_cur[2]; imu[5] = s->rpy_cur[0];
+  for (int a = 0; a < 3; a++) { imu[6 + a] = s->shift_from_start[a]; imu[9 + a] = s->velo_from_start[a]; }
+}
+
+__device__ __forceinline__ float lo_sqdist(const float4 pj, const float4 sel) {
+  return (pj.x - sel.x) * (pj.x - sel.x) + (pj.y - sel.y) * (pj.y - sel.y) + (pj.z - sel.z) * (pj.z - sel.z);
+}
+
+// warp-wide arg-min over (d, ord): the sequential loops update on strict '<', i.e. the earliest
+// evaluated candidate wins ties; `ord` is the evaluation order.
+__device__ __forceinline__ void warp_argmin(float& d, int& ord, int& idx) {
+  for (int o = 16; o > 0; o >>= 1) {
+    float od = __shfl_xor_sync(0xffffffffu, d, o);
+    int oo = __shfl_xor_sync(0xffffffffu, ord, o);
+    int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+    if (od < d || (od == d && oo < ord)) { d = od; ord = oo; idx = oi; }
+  }
+}
+
+// corner correspondence :478-527 for one feature (warp cooperative)
+__device__ void lo_corner_search(const LOArgs& A, const float4 sel, int n_sharp, int n_last, int& ind1, int& ind2) {
+  const int lane = lane_id();
+  int bi; float bd;
+  grid_nn1_warp(A.corner_grid, sel.x, sel.y, sel.z, 25.f, bi, bd);
+  int closestPointInd = -1, minPointInd2 = -1;
+  if (bi >= 0 && bd < 25) {
+    closestPointInd = bi;
+    int closestPointScan = int(A.corner_last[closestPointInd].w);
+    float best = 25.f; int bord = 0x7fffffff, bidx = -1;
+    int jend = min(n_sharp, n_last);  // forward bound is cornerPointsSharpNum (:486), kept
+    bool stop = false;
+    for (int base = closestPointInd + 1; base < jend && !stop; base += 32) {
+      int j = base + lane;
+      bool in = j < jend;
+      float4 pj = in ? A.corner_last[j] : make_float4(0, 0, 0, 0);
+      bool brk = in && (int(pj.w) > closestPointScan + 2.5);
+      unsigned int bm = __ballot_sync(0xffffffffu, brk);
+      int firstbrk = bm ? __ffs(bm) - 1 : 32;
+      if (in && lane < firstbrk && int(pj.w) > closestPointScan) {
+        float dd = lo_sqdist(pj, sel);
+        int ord = j - (closestPointInd + 1);
+        if (dd < best || (dd == best && ord < bord)) { best = dd; bord = ord; bidx = j; }
+      }
+      if (bm) stop = true;
+    }
+    stop = false;
+    for (int base = closestPointInd - 1; base >= 0 && !stop; base -= 32) {
+      int j = base - lane;
+      bool in = j >= 0;
+      float4 pj = in ? A.corner_last[j] : make_float4(0, 0, 0, 0);
+      bool brk = in && (int(pj.w) < closestPointScan - 2.5);
+      unsigned int bm = __ballot_sync(0xffffffffu, brk);
+      int firstbrk = bm ? __ffs(bm) - 1 : 32;
+      if (in && lane < firstbrk && int(pj.w) < closestPointScan) {
+        float dd = lo_sqdist(pj, sel);
+        int ord = 0x40000000 + (closestPointInd - 1 - j);
+        if (dd < best || (dd == best && ord < bord)) { best = dd; bord = ord; bidx = j; }
+      }
+      if (bm) stop = true;
+    }
+    warp_argmin(best, bord, bidx);
+    if (best < 25.f) minPointInd2 = bidx;
+  }
+  ind1 = closestPointInd;
+  ind2 = minPointInd2;
+}
+
+// surf correspondence :590-650
+__device__ void lo_surf_search(const LOArgs& A, const float4 sel, int n_flat, int n_last, int& ind1, int& ind2, int& ind3) {
+  const int lane = lane_id();
+  int bi; float bd;
+  grid_nn1_warp(A.surf_grid, sel.x, sel.y, sel.z, 25.f, bi, bd);
+  int closestPointInd = -1, minPointInd2 = -1, minPointInd3 = -1;
+  if (bi >= 0 && bd < 25) {
+    closestPointInd = bi;
+    int closestPointScan = int(A.surf_last[closestPointInd].w);
+    float best2 = 25.f, best3 = 25.f;
+    int ord2 = 0x7fffffff, ord3 = 0x7fffffff, idx2 = -1, idx3 = -1;
+    int jend = min(n_flat, n_last);  // forward bound is surfPointsFlatNum (:598), kept
+    bool stop = false;
+    for (int base = closestPointInd + 1; base < jend && !stop; base += 32) {
+      int j = base + lane;
+      bool in = j < jend;
+      float4 pj = in ? A.surf_last[j] : make_float4(0, 0, 0, 0);
+      bool brk = in && (int(pj.w) > closestPointScan + 2.5);
+      unsigned int bm = __ballot_sync(0xffffffffu, brk);
+      int firstbrk = bm ? __ffs(bm) - 1 : 32;
+      if (in && lane < firstbrk) {
+        float dd = lo_sqdist(pj, sel);
+        int ord = j - (closestPointInd + 1);
+        if (int(pj.w) <= closestPointScan) {
+          if (dd < best2 || (dd == best2 && ord < ord2)) { best2 = dd; ord2 = ord; idx2 = j; }
+        } else {
+          if (dd < best3 || (dd == best3 && ord < ord3)) { best3 = dd; ord3 = ord; idx3 = j; }
+        }
+      }
+      if (bm) stop = true;
+    }
+    stop = false;
+    for (int base = closestPointInd - 1; base >= 0 && !stop; base -= 32) {
+      int j = base - lane;
+      bool in = j >= 0;
+      float4 pj = in ? A.surf_last[j] : make_float4(0, 0, 0, 0);
+      bool brk = in && (int(pj.w) < closestPointScan - 2.5);
+      unsigned int bm = __ballot_sync(0xffffffffu, brk);
+      int firstbrk = bm ? __ffs(bm) - 1 : 32;
+      if (in && lane < firstbrk) {
+        float dd = lo_sqdist(pj, sel);
+        int ord = 0x40000000 + (closestPointInd - 1 - j);
+        if (int(pj.w) >= closestPointScan) {
+          if (dd < best2 || (dd == best2 && ord < ord2)) { best2 = dd; ord2 = ord; idx2 = j; }
+        } else {
+          if (dd < best3 || (dd == best3 && ord < ord3)) { best3 = dd; ord3 = ord; idx3 = j; }
+        }
+      }
+      if (bm) stop = true;
+    }
+    warp_argmin(best2, ord2, idx2);
+    warp_argmin(best3, ord3, idx3);
+    if (best2 < 25.f) minPointInd2 = idx2;
+    if (best3 < 25.f) minPointInd3 = idx3;
+  }
+  ind1 = closestPointInd; ind2 = minPointInd2; ind3 = minPointInd3;
+}
+
+// point-to-line residual :530-582.  returns validity
+__device__ __forceinline__ bool lo_corner_residual(const float4 pointSel, const float4 tripod1, const float4 tripod2, int iterCount, float4& coeff) {
+  float x0 = pointSel.x; float y0 = pointSel.y; float z0 = pointSel.z;
+  float x1 = tripod1.x; float y1 = tripod1.y; float z1 = tripod1.z;
+  float x2 = tripod2.x; float y2 = tripod2.y; float z2 = tripod2.z;
+  float a012 = dm::sqrt(((x0 - x1)*(y0 - y2) - (x0 - x2)*(y0 - y1))
+             * ((x0 - x1)*(y0 - y2) - (x0 - x2)*(y0 - y1))
+             + ((x0 - x1)*(z0 - z2) - (x0 - x2)*(z0 - z1))
+             * ((x0 - x1)*(z0 - z2) - (x0 - x2)*(z0 - z1))
+             + ((y0 - y1)*(z0 - z2) - (y0 - y2)*(z0 - z1))
+             * ((y0 - y1)*(z0 - z2) - (y0 - y2)*(z0 - z1)));
+  float l12 = dm::sqrt((x1 - x2)*(x1 - x2) + (y1 - y2)*(y1 - y2) + (z1 - z2)*(z1 - z2));
+  float la = ((y1 - y2)*((x0 - x1)*(y0 - y2) - (x0 - x2)*(y0 - y1))
+           + (z1 - z2)*((x0 - x1)*(z0 - z2) - (x0 - x2)*(z0 - z1))) / a012 / l12;
+  float lb = -((x1 - x2)*((x0 - x1)*(y0 - y2) - (x0 - x2)*(y0 - y1))
+           - (z1 - z2)*((y0 - y1)*(z0 - z2) - (y0 - y2)*(z0 - z1))) / a012 / l12;
+  float lc = -((x1 - x2)*((x0 - x1)*(z0 - z2) - (x0 - x2)*(z0 - z1))
+           + (y1 - y2)*((y0 - y1)*(z0 - z2) - (y0 - y2)*(z0 - z1))) / a012 / l12;
+  float ld2 = a012 / l12;
+  float s = 1;
+  if (iterCount >= 5) {
+    s = 1 - 1.8 * dm::fabs(ld2);
+  }
+  coeff.x = s * la;
+  coeff.y = s * lb;
+  coeff.z = s * lc;
+  coeff.w = s * ld2;
+  return (s > 0.1 && ld2 != 0);
+}
+
+// point-to-plane residual :653-693
+__device__ __forceinline__ bool lo_surf_residual(const float4 pointSel, const float4 tripod1, const float4 tripod2, const float4 tripod3,
+                                                 int iterCount, float4& coeff) {
+  float pa = (tripod2.y - tripod1.y) * (tripod3.z - tripod1.z) - (tripod3.y - tripod1.y) * (tripod2.z - tripod1.z);
+  float pb = (tripod2.z - tripod1.z) * (tripod3.x - tripod1.x) - (tripod3.z - tripod1.z) * (tripod2.x - tripod1.x);
+  float pc = (tripod2.x - tripod1.x) * (tripod3.y - tripod1.y) - (tripod3.x - tripod1.x) * (tripod2.y - tripod1.y);
+  float pd = -(pa * tripod1.x + pb * tripod1.y + pc * tripod1.z);
+  float ps = dm::sqrt(pa * pa + pb * pb + pc * pc);
+  pa /= ps;
+  pb /= ps;
+  pc /= ps;
+  pd /= ps;
+  float pd2 = pa * pointSel.x + pb * pointSel.y + pc * pointSel.z + pd;
+  float s = 1;
+  if (iterCount >= 5) {
+    s = 1 - 1.8 * dm::fabs(pd2) / dm::sqrt(dm::sqrt(pointSel.x * pointSel.x + pointSel.y * pointSel.y + pointSel.z * pointSel.z));
+  }
+  coeff.x = s * pa;
+  coeff.y = s * pb;
+  coeff.z = s * pc;
+  coeff.w = s * pd2;
+  return (s > 0.1 && pd2 != 0);
+}
+
+// one Jacobian row :709-763 -> accumulate into acc[28] (upper triangle of AtA, AtB, count)
+__device__ __forceinline__ void lo_row_accumulate(const float4 pointOri, const float4 coeffv, const float* tr6 /*srx,crx,sry,cry,srz,crz*/,
+                                                  const float* transform, double* acc) {
+  float s = 1;
+  float srx = tr6[0], crx = tr6[1], sry = tr6[2], cry = tr6[3], srz = tr6[4], crz = tr6[5];
+  float tx = s * transform[3];
+  float ty = s * transform[4];
+  float tz = s * transform[5];
+  struct { float x, y, z; } coeff = {coeffv.x, coeffv.y, coeffv.z};
+  float arx = (-s*crx*sry*srz*pointOri.x + s*crx*crz*sry*pointOri.y + s*srx*sry*pointOri.z
+            + s*tx*crx*sry*srz - s*ty*crx*crz*sry - s*tz*srx*sry) * coeff.x
+            + (s*srx*srz*pointOri.x - s*crz*srx*pointOri.y + s*crx*pointOri.z
+            + s*ty*crz*srx - s*tz*crx - s*tx*srx*srz) * coeff.y
+            + (s*crx*cry*srz*pointOri.x - s*crx*cry*crz*pointOri.y - s*cry*srx*pointOri.z
+            + s*tz*cry*srx + s*ty*crx*cry*crz - s*tx*crx*cry*srz) * coeff.z;
+  float ary = ((-s*crz*sry - s*cry*srx*srz)*pointOri.x
+            + (s*cry*crz*srx - s*sry*srz)*pointOri.y - s*crx*cry*pointOri.z
+            + tx*(s*crz*sry + s*cry*srx*srz) + ty*(s*sry*srz - s*cry*crz*srx)
+            + s*tz*crx*cry) * coeff.x
+            + ((s*cry*crz - s*srx*sry*srz)*pointOri.x
+            + (s*cry*srz + s*crz*srx*sry)*pointOri.y - s*crx*sry*pointOri.z
+            + s*tz*crx*sry - ty*(s*cry*srz + s*crz*srx*sry)
+            - tx*(s*cry*crz - s*srx*sry*srz)) * coeff.z;
+  float arz = ((-s*cry*srz - s*crz*srx*sry)*pointOri.x + (s*cry*crz - s*srx*sry*srz)*pointOri.y
+            + tx*(s*cry*srz + s*crz*srx*sry) - ty*(s*cry*crz - s*srx*sry*srz)) * coeff.x
+            + (-s*crx*crz*pointOri.x - s*crx*srz*pointOri.y
+            + s*ty*crx*srz + s*tx*crx*crz) * coeff.y
+            + ((s*cry*crz*srx - s*sry*srz)*pointOri.x + (s*crz*sry + s*cry*srx*srz)*pointOri.y
+            + tx*(s*sry*srz - s*cry*crz*srx) - ty*(s*crz*sry + s*cry*srx*srz)) * coeff.z;
+  float atx = -s*(cry*crz - srx*sry*srz) * coeff.x + s*crx*srz * coeff.y
+            - s*(crz*sry + cry*srx*srz) * coeff.z;
+  float aty = -s*(cry*srz + crz*srx*sry) * coeff.x - s*crx*crz * coeff.y
+            - s*(sry*srz - cry*crz*srx) * coeff.z;
+  float atz = s*crx*sry * coeff.x - s*srx * coeff.y - s*crx*cry * coeff.z;
+  float d2 = coeffv.w;
+  float b = -0.05 * d2;
+  float a[6] = {arx, ary, arz, atx, aty, atz};
+  int k = 0;
+#pragma unroll
+  for (int i = 0; i < 6; i++)
+#pragma unroll
+    for (int j = i; j < 6; j++) acc[k++] += (double)a[i] * (double)a[j];
+#pragma unroll
+  for (int i = 0; i < 6; i++) acc[21 + i] += (double)a[i] * (double)b;
+  acc[27] += 1.0;
+}
+
+}  // namespace loamgpu

@@ -1,3 +1,123 @@
+// loam_lo.cuh -- host side of the laserOdometry node (laserOdometry.cpp main loop :410-931).
 #pragma once
+#include "lo_kernels2.cuh"
 #include "loam_sr.cuh"
-namespace loamgpu { struct LOHandle { }; }
+
+namespace loamgpu {
+
+struct LOHandle {
+  loam_params P;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  cudaEvent_t ev_dep = nullptr;
+  int cap = 0, fcap = 0, coop_blocks = 0;
+  bool systemInited = false;      // :52
+  int frameCount = 1;             // :407 (= skipFrameNum)
+  static const int skipFrameNum = 1;
+  DevBuf<LOState> d_state;
+  DevBuf<float4> d_corner_last, d_surf_last, d_full_end, d_coeff;
+  DevBuf<unsigned char> d_row_valid;
+  DevBuf<int> d_c1, d_c2, d_s1, d_s2, d_s3;
+  DevBuf<double> d_partials;
+  GridStorage g_corner, g_surf;
+  PinnedBuf<LOState> h_state;
+  LOState last_state;
+  bool last_published = false;
+  int last_n_sharp = 0, last_n_flat = 0;
+
+  int init(const loam_params* p, int dev, cudaStream_t s) {
+    P = *p;
+    device = dev;
+    CUDA_OK(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    CUDA_OK(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major < 10) { set_error("device %d is not sm_100", dev); return LOAM_ERR_CUDA; }
+    if (s) stream = s; else { CUDA_OK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking)); own_stream = true; }
+    CUDA_OK(cudaEventCreateWithFlags(&ev_dep, cudaEventDisableTiming));
+    cap = P.max_points;
+    fcap = 36 * P.n_scans;
+    int per_sm = 0;
+    CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lo_optimize, LO_THREADS, 0));
+    if (per_sm < 1) { set_error("lo_optimize cannot be made resident"); return LOAM_ERR_CUDA; }
+    coop_blocks = prop.multiProcessorCount;  // one block per SM
+    int r = LOAM_OK;
+    r |= d_state.alloc_zero(1, stream);
+    r |= d_corner_last.alloc(cap); r |= d_surf_last.alloc(cap); r |= d_full_end.alloc(cap);
+    r |= d_coeff.alloc((size_t)P.lo_max_iter * fcap); r |= d_row_valid.alloc_zero((size_t)P.lo_max_iter * fcap, stream);
+    r |= d_c1.alloc_zero(fcap, stream); r |= d_c2.alloc_zero(fcap, stream);
+    r |= d_s1.alloc_zero(fcap, stream); r |= d_s2.alloc_zero(fcap, stream); r |= d_s3.alloc_zero(fcap, stream);
+    r |= d_partials.alloc_zero((size_t)2 * coop_blocks * LO_NRED, stream);
+    r |= g_corner.alloc(cap, 1 << 21, stream); r |= g_surf.alloc(cap, 1 << 21, stream);
+    r |= h_state.alloc(1);
+    if (r != LOAM_OK) return LOAM_ERR_CUDA;
+    memset(&last_state, 0, sizeof(last_state));
+    CUDA_OK(cudaStreamSynchronize(stream));
+    return LOAM_OK;
+  }
+  ~LOHandle() {
+    if (ev_dep) cudaEventDestroy(ev_dep);
+    if (own_stream && stream) cudaStreamDestroy(stream);
+  }
+
+  // one loop-body pass for the six topics scanRegistration just produced; enqueue only
+  int process(SRHandle& sr, bool* published) {
+    *published = false;
+    if (!sr.processed) return LOAM_NOT_READY;
+    CUDA_OK(cudaSetDevice(device));
+    if (sr.stream != stream) {
+      CUDA_OK(cudaEventRecord(ev_dep, sr.stream));
+      CUDA_OK(cudaStreamWaitEvent(stream, ev_dep, 0));
+    }
+    const ImuState* imu = sr.imu_state_dev();
+    GridPair gp;
+    gp.g[0] = g_corner.buf(d_corner_last.p, &d_state.p->n_corner_last, &d_state.p->index_enable, 1.0f);
+    gp.g[1] = g_surf.buf(d_surf_last.p, &d_state.p->n_surf_last, &d_state.p->index_enable, 1.0f);
+    const int nb = 148;
+    if (!systemInited) {  // :427-456
+      LAUNCH("lo_adopt_first", lo_adopt_first, nb, 256, 0, stream, sr.d_cnt.p, sr.d_less_sharp.p, sr.d_less_flat.p, d_corner_last.p, d_surf_last.p);
+      LAUNCH("lo_finish", lo_finish, 1, 32, 0, stream, d_state.p, sr.d_cnt.p, imu, 1, 0);
+      int r = grid_build_pair(gp, nb, stream);
+      if (r != LOAM_OK) return r;
+      systemInited = true;
+      last_published = false;
+      return LOAM_NOT_READY;
+    }
+    LOArgs A;
+    A.st = d_state.p; A.cnt = sr.d_cnt.p; A.sharp = sr.d_sharp.p; A.flat = sr.d_flat.p;
+    A.corner_last = d_corner_last.p; A.surf_last = d_surf_last.p;
+    A.corner_grid = g_corner.view(); A.surf_grid = g_surf.view();
+    A.corner_ind1 = d_c1.p; A.corner_ind2 = d_c2.p; A.surf_ind1 = d_s1.p; A.surf_ind2 = d_s2.p; A.surf_ind3 = d_s3.p;
+    A.coeff = d_coeff.p; A.row_valid = d_row_valid.p; A.partials = d_partials.p; A.imu = imu;
+    A.fcap = fcap; A.max_iter = P.lo_max_iter;
+    {
+      void* args[] = {&A};
+      if (g_profile) prof_begin(stream);
+      CUDA_OK(cudaLaunchCooperativeKernel((void*)lo_optimize, dim3(coop_blocks), dim3(LO_THREADS), args, 0, stream));
+      g_launches++;
+      if (g_profile) prof_end("lo_optimize", stream);
+    }
+    frameCount++;  // :885
+    int do_full = frameCount >= skipFrameNum + 1 ? 1 : 0;
+    ToEndArgs T;
+    T.st = d_state.p; T.cnt = sr.d_cnt.p; T.imu = imu;
+    T.less_sharp = sr.d_less_sharp.p; T.less_flat = sr.d_less_flat.p; T.full = sr.d_full.p;
+    T.corner_last = d_corner_last.p; T.surf_last = d_surf_last.p; T.full_end = d_full_end.p; T.do_full = do_full;
+    LAUNCH("lo_transform_to_end", lo_transform_to_end_kernel, 2 * nb, 256, 0, stream, T);
+    LAUNCH("lo_finish", lo_finish, 1, 32, 0, stream, d_state.p, sr.d_cnt.p, imu, 0, do_full);
+    int r = grid_build_pair(gp, nb, stream);
+    if (r != LOAM_OK) return r;
+    if (do_full) { frameCount = 0; *published = true; }  // :910-911
+    last_published = *published;
+    return LOAM_OK;
+  }
+
+  int sync_state() {
+    CUDA_OK(cudaMemcpyAsync(h_state.p, d_state.p, sizeof(LOState), cudaMemcpyDeviceToHost, stream));
+    CUDA_OK(cudaStreamSynchronize(stream));
+    last_state = *h_state.p;
+    return LOAM_OK;
+  }
+};
+
+}  // namespace loamgpu
