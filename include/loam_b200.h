@@ -136,6 +136,8 @@ int loam_lm_imu(loam_lm* h, double stamp, const double quat[4]);
 /* consumes corner_last / surf_last / velodyne_cloud_3 / laser_odom_to_init of `odom` */
 int loam_lm_process(loam_lm* h, loam_lo* odom, double stamp);
 int loam_lm_download(loam_lm* h, int which_cloud, float* xyzi, int cap_points, int* n);
+/* which = 100 / 101: the five neighbour indices per corner / surf query of the last LM iteration (-1 = rejected) */
+int loam_lm_download_ints(loam_lm* h, int which, int* out, int cap, int* n);
 int loam_lm_state(loam_lm* h, float aft_mapped[6], float bef_mapped[6], float tobe_mapped[6], int stats[8]);
 
 /* ---- transformMaintenance node (transformMaintenance.cpp), host only ---- */

@@ -97,6 +97,7 @@ def lib():
     L.loam_lm_imu.argtypes = [vp, cd, vp]
     L.loam_lm_process.argtypes = [vp, vp, cd]
     L.loam_lm_download.argtypes = [vp, ci, vp, ci, ctypes.POINTER(ci)]
+    L.loam_lm_download_ints.argtypes = [vp, ci, vp, ci, ctypes.POINTER(ci)]
     L.loam_lm_state.argtypes = [vp, vp, vp, vp, vp]
     L.loam_tm_on_mapping.argtypes = [vp, vp, vp]
     L.loam_tm_on_odometry.argtypes = [vp, vp, vp]
@@ -241,6 +242,9 @@ class LaserMapping(_Node):
 
     def cloud(self, which):
         return self._dl(self.L.loam_lm_download, which, np.float32, 4)
+
+    def ints(self, which):
+        return self._dl(self.L.loam_lm_download_ints, which, np.int32, 1, cap=5 * self.cap)
 
     def state(self):
         a = np.zeros(6, np.float32)

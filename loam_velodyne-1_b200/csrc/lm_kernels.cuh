@@ -1,0 +1,341 @@
+// lm_kernels.cuh -- laserMapping on sm_100a, part 1 (SURVEY.md §8a rows LM-1 .. LM-11):
+// pose prediction, cube-map bookkeeping, local-map assembly and the sweep-to-map LM loop.
+//
+// Map layout in HBM: the 21x11x21 cube array of the reference (laserMapping.cpp:64-70,88-91)
+// becomes a table of (offset, count) descriptors into a log-structured arena of float4 points
+// per feature type.  Cubes are immutable segments; every mapped sweep appends one new block with
+// the refiltered contents of the touched cubes (part 2), so shifting the window (:454-614) moves
+// 8-byte descriptors instead of point clouds and the local map is one gather of <= 125 segments.
+#pragma once
+#include <cooperative_groups.h>
+#include "grid_index.cuh"
+#include "linalg.cuh"
+#include "pose_math.cuh"
+#include "lo_kernels2.cuh"
+
+namespace loamgpu {
+
+constexpr int CUBE_W = 21, CUBE_H = 11, CUBE_D = 21;     // laserMapping.cpp:67-69
+constexpr int CUBE_NUM = CUBE_W * CUBE_H * CUBE_D;       // :70
+constexpr int PROC_MAX = 250;                            // cubes rewritten per mapped sweep
+constexpr int LM_THREADS = 512;
+constexpr int LM_WARPS = LM_THREADS / 32;
+
+struct CubeDesc { int off; int cnt; };
+
+struct LMImu {   // host-maintained ring buffer, laserMapping.cpp:102-108,323-335
+  double time[IMU_Q];
+  float roll[IMU_Q], pitch[IMU_Q];
+  int pointer_last;
+  int pad;
+};
+
+struct LMState {
+  float transformSum[6], transformIncre[6], transformTobeMapped[6], transformBefMapped[6], transformAftMapped[6];  // :96-100
+  int cenW, cenH, cenD;                 // laserCloudCenWidth/Height/Depth :64-66
+  int isDegenerate;                     // :385
+  float matP[36];                       // :386
+  int imuPointerFront;                  // :102
+  int validNum, surroundNum;            // :616-617
+  int validInd[125], surroundInd[125];  // :72-73
+  int gatherOff[2][126];                // start of each valid cube inside the local map
+  int mapN[2];                          // laserCloudCornerFromMapNum / SurfFromMapNum :680-681
+  int stackN2[2];                       // laserCloudCornerStackNum2 / Surf :683,688
+  int stackN[2];                        // laserCloudCornerStackNum / Surf after the filters :696,701
+  int optimize_enable;                  // :706
+  int iters, rows;
+  float predTrig[6];                    // sin/cos of the predicted transformTobeMapped (rx,ry,rz)
+  float predT[6];                       // the predicted transformTobeMapped
+  float pointOnYAxis[3];                // :440-444
+  int bump[2];                          // arena append pointers
+  int arenaCap;
+  int error;                            // bit0 arena full, bit1 too many cubes, bit2 voxel key range, bit3 local map cap
+  // refilter plan (part 2)
+  int nproc[2];
+  int procCube[2][PROC_MAX];
+  int procInOff[2][PROC_MAX + 1];       // start of each processed cube's old points inside E
+  int procOldOff[2][PROC_MAX];
+  int procOldCnt[2][PROC_MAX];
+  int En[2];                            // number of elements in E (old points + all stack points)
+  int outOff[2];                        // where this sweep's block starts in the arena
+  int outCount[2];                      // points written by the refilter
+  int segCount[2][256];                 // output points per processed cube
+  int surroundN;                        // surround cloud size (LM-14)
+  int surroundIn;
+  int registeredN;                      // size of the registered full-resolution cloud
+  int vxOverflow[4];
+};
+
+struct LMTrig { float srx, crx, sry, cry, srz, crz; };
+
+__device__ __forceinline__ LMTrig lm_trig(const float* t) {
+  LMTrig g;
+  g.srx = dm::sin(t[0]); g.crx = dm::cos(t[0]);
+  g.sry = dm::sin(t[1]); g.cry = dm::cos(t[1]);
+  g.srz = dm::sin(t[2]); g.crz = dm::cos(t[2]);
+  return g;
+}
+
+// pointAssociateToMap :234-252 with cos/sin(transformTobeMapped[k]) supplied (same values)
+__device__ __forceinline__ float4 lm_to_map(const float4 pi, const LMTrig& g, const float* t) {
+  float x1 = g.crz * pi.x - g.srz * pi.y;
+  float y1 = g.srz * pi.x + g.crz * pi.y;
+  float z1 = pi.z;
+  float x2 = x1;
+  float y2 = g.crx * y1 - g.srx * z1;
+  float z2 = g.srx * y1 + g.crx * z1;
+  float4 po;
+  po.x = g.cry * x2 + g.sry * z2 + t[3];
+  po.y = y2 + t[4];
+  po.z = -g.sry * x2 + g.cry * z2 + t[5];
+  po.w = pi.w;
+  return po;
+}
+
+// pointAssociateTobeMapped :254-272
+__device__ __forceinline__ float4 lm_to_sensor(const float4 pi, const LMTrig& g, const float* t) {
+  float x1 = g.cry * (pi.x - t[3]) - g.sry * (pi.z - t[5]);
+  float y1 = pi.y - t[4];
+  float z1 = g.sry * (pi.x - t[3]) + g.cry * (pi.z - t[5]);
+  float x2 = x1;
+  float y2 = g.crx * y1 + g.srx * z1;
+  float z2 = -g.srx * y1 + g.crx * z1;
+  float4 po;
+  po.x = g.crz * x2 + g.srz * y2;
+  po.y = -g.srz * x2 + g.crz * y2;
+  po.z = z2;
+  po.w = pi.w;
+  return po;
+}
+
+// cube index of a map coordinate :446-452 / :983-989 (double arithmetic, truncation + fix-up)
+__device__ __forceinline__ int lm_cube_coord(float v, int cen) {
+  int c = int((v + 25.0) / 50.0) + cen;
+  if (v + 25.0 < 0) c--;
+  return c;
+}
+
+struct LMSetupArgs {
+  LMState* st;
+  const LOState* lo;        // transformSum of this sweep, cloud sizes
+  CubeDesc* cubes[2];
+};
+
+// K1: one block.  /laser_odom_to_init hand-off (:304-318), transformAssociateToMap (:422),
+// FOV probe point, centre cube + window shifts (:446-614), cube selection (:616-672) and the
+// offsets of the local-map gather (:674-681).
+__global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
+  LMState* st = A.st;
+  __shared__ int s_shift[3], s_center[3];
+  __shared__ unsigned char s_fov[125], s_in[125];
+  __shared__ int s_ind[125];
+  if (threadIdx.x == 0) {
+    float sum[6];
+    pm::odometry_msg_roundtrip(A.lo->transformSum, sum);
+    for (int i = 0; i < 6; i++) st->transformSum[i] = sum[i];
+    pm::transformAssociateToMap(st->transformSum, st->transformBefMapped, st->transformAftMapped, st->transformIncre, st->transformTobeMapped);
+    const float* T = st->transformTobeMapped;
+    LMTrig g = lm_trig(T);
+    st->predTrig[0] = g.srx; st->predTrig[1] = g.crx; st->predTrig[2] = g.sry; st->predTrig[3] = g.cry; st->predTrig[4] = g.srz; st->predTrig[5] = g.crz;
+    for (int i = 0; i < 6; i++) st->predT[i] = T[i];
+    float4 py = lm_to_map(make_float4(0.0f, 10.0f, 0.0f, 0.f), g, T);
+    st->pointOnYAxis[0] = py.x; st->pointOnYAxis[1] = py.y; st->pointOnYAxis[2] = py.z;
+    int cI = lm_cube_coord(T[3], st->cenW), cJ = lm_cube_coord(T[4], st->cenH), cK = lm_cube_coord(T[5], st->cenD);
+    // net shifts per axis: +1 per `while (center < 3)`, -1 per `while (center >= dim - 3)`
+    int dims[3] = {CUBE_W, CUBE_H, CUBE_D};
+    int c[3] = {cI, cJ, cK};
+    for (int a = 0; a < 3; a++) {
+      int sh = 0;
+      while (c[a] < 3) { c[a]++; sh++; }
+      while (c[a] >= dims[a] - 3) { c[a]--; sh--; }
+      s_shift[a] = sh;
+      s_center[a] = c[a];
+    }
+    st->cenW += s_shift[0]; st->cenH += s_shift[1]; st->cenD += s_shift[2];
+    st->stackN2[0] = A.lo->n_corner_last; st->stackN2[1] = A.lo->n_surf_last;
+  }
+  __syncthreads();
+  // apply the shifts to the descriptor tables, one (line, type) per thread
+  for (int a = 0; a < 3; a++) {
+    int sh = s_shift[a];
+    if (sh == 0) continue;
+    int dims[3] = {CUBE_W, CUBE_H, CUBE_D};
+    int n = dims[a], n1 = dims[(a + 1) % 3], n2 = dims[(a + 2) % 3];
+    for (int line = threadIdx.x; line < n1 * n2 * 2; line += blockDim.x) {
+      int T = line / (n1 * n2), l = line % (n1 * n2);
+      int u = l / n2, v = l % n2;
+      CubeDesc* cubes = A.cubes[T];
+      int steps = sh > 0 ? sh : -sh;
+      for (int sidx = 0; sidx < steps; sidx++) {
+        if (sh > 0) {
+          for (int t = n - 1; t >= 1; t--) {
+            int cc[3], cp[3];
+            cc[a] = t; cc[(a + 1) % 3] = u; cc[(a + 2) % 3] = v;
+            cp[a] = t - 1; cp[(a + 1) % 3] = u; cp[(a + 2) % 3] = v;
+            cubes[cc[0] + CUBE_W * cc[1] + CUBE_W * CUBE_H * cc[2]] = cubes[cp[0] + CUBE_W * cp[1] + CUBE_W * CUBE_H * cp[2]];
+          }
+          int c0[3];
+          c0[a] = 0; c0[(a + 1) % 3] = u; c0[(a + 2) % 3] = v;
+          cubes[c0[0] + CUBE_W * c0[1] + CUBE_W * CUBE_H * c0[2]].cnt = 0;
+        } else {
+          for (int t = 0; t < n - 1; t++) {
+            int cc[3], cp[3];
+            cc[a] = t; cc[(a + 1) % 3] = u; cc[(a + 2) % 3] = v;
+            cp[a] = t + 1; cp[(a + 1) % 3] = u; cp[(a + 2) % 3] = v;
+            cubes[cc[0] + CUBE_W * cc[1] + CUBE_W * CUBE_H * cc[2]] = cubes[cp[0] + CUBE_W * cp[1] + CUBE_W * CUBE_H * cp[2]];
+          }
+          int c0[3];
+          c0[a] = n - 1; c0[(a + 1) % 3] = u; c0[(a + 2) % 3] = v;
+          cubes[c0[0] + CUBE_W * c0[1] + CUBE_W * CUBE_H * c0[2]].cnt = 0;
+        }
+      }
+    }
+    __syncthreads();
+  }
+  // 5x5x5 neighbourhood, FOV test on the 8 corners (:618-672)
+  if (threadIdx.x < 125) {
+    int di = threadIdx.x / 25, dj = (threadIdx.x / 5) % 5, dk = threadIdx.x % 5;
+    int i = s_center[0] - 2 + di, j = s_center[1] - 2 + dj, k = s_center[2] - 2 + dk;
+    bool in = i >= 0 && i < CUBE_W && j >= 0 && j < CUBE_H && k >= 0 && k < CUBE_D;
+    bool isInLaserFOV = false;
+    if (in) {
+      const float* T = st->transformTobeMapped;
+      const float* P = st->pointOnYAxis;
+      float centerX = 50.0 * (i - st->cenW);
+      float centerY = 50.0 * (j - st->cenH);
+      float centerZ = 50.0 * (k - st->cenD);
+      for (int ii = -1; ii <= 1; ii += 2) {
+        for (int jj = -1; jj <= 1; jj += 2) {
+          for (int kk = -1; kk <= 1; kk += 2) {
+            float cornerX = centerX + 25.0 * ii;
+            float cornerY = centerY + 25.0 * jj;
+            float cornerZ = centerZ + 25.0 * kk;
+            float squaredSide1 = (T[3] - cornerX) * (T[3] - cornerX) + (T[4] - cornerY) * (T[4] - cornerY) + (T[5] - cornerZ) * (T[5] - cornerZ);
+            float squaredSide2 = (P[0] - cornerX) * (P[0] - cornerX) + (P[1] - cornerY) * (P[1] - cornerY) + (P[2] - cornerZ) * (P[2] - cornerZ);
+            float check1 = 100.0 + squaredSide1 - squaredSide2 - 10.0 * dm::dsqrt(3.0) * dm::sqrt(squaredSide1);
+            float check2 = 100.0 + squaredSide1 - squaredSide2 + 10.0 * dm::dsqrt(3.0) * dm::sqrt(squaredSide1);
+            if (check1 < 0 && check2 > 0) isInLaserFOV = true;
+          }
+        }
+      }
+    }
+    s_in[threadIdx.x] = in ? 1 : 0;
+    s_fov[threadIdx.x] = isInLaserFOV ? 1 : 0;
+    s_ind[threadIdx.x] = in ? i + CUBE_W * j + CUBE_W * CUBE_H * k : -1;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int nv = 0, ns = 0;
+    for (int q = 0; q < 125; q++) {  // (i, j, k) loop order == q order
+      if (!s_in[q]) continue;
+      if (s_fov[q]) st->validInd[nv++] = s_ind[q];
+      st->surroundInd[ns++] = s_ind[q];
+    }
+    st->validNum = nv; st->surroundNum = ns;
+    for (int T = 0; T < 2; T++) {
+      int off = 0;
+      for (int v = 0; v < nv; v++) { st->gatherOff[T][v] = off; off += A.cubes[T][st->validInd[v]].cnt; }
+      st->gatherOff[T][nv] = off;
+      st->mapN[T] = off;
+    }
+    st->optimize_enable = (st->mapN[0] > 10 && st->mapN[1] > 100) ? 1 : 0;  // :706
+    st->iters = 0; st->rows = 0;
+  }
+}
+
+// K2: incoming clouds to the map with the predicted pose and back (:424-434, :683-691)
+struct LMStackArgs {
+  const LMState* st;
+  const float4* in[2];
+  float4* out[2];
+};
+__global__ void __launch_bounds__(256) lm_stack_transform(LMStackArgs A) {
+  const LMState* st = A.st;
+  LMTrig g;
+  g.srx = st->predTrig[0]; g.crx = st->predTrig[1]; g.sry = st->predTrig[2]; g.cry = st->predTrig[3]; g.srz = st->predTrig[4]; g.crz = st->predTrig[5];
+  float T[6];
+  for (int i = 0; i < 6; i++) T[i] = st->predT[i];
+  const int n0 = st->stackN2[0], n1 = st->stackN2[1];
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < n0 + n1; i += gridDim.x * 256) {
+    int t = i < n0 ? 0 : 1;
+    int k = t ? i - n0 : i;
+    A.out[t][k] = lm_to_sensor(lm_to_map(A.in[t][k], g, T), g, T);
+  }
+}
+
+// K4: local map = concat of the valid cubes in (i,j,k) loop order (:674-679)
+struct LMGatherArgs {
+  LMState* st;
+  const CubeDesc* cubes[2];
+  const float4* arena[2];
+  float4* E[2];
+  int ecap;
+};
+__global__ void __launch_bounds__(256) lm_gather_map(LMGatherArgs A) {
+  const LMState* st = A.st;
+  const int v = blockIdx.x, T = blockIdx.y;
+  if (v >= st->validNum) return;
+  CubeDesc d = A.cubes[T][st->validInd[v]];
+  int dst = st->gatherOff[T][v];
+  if (dst + d.cnt > A.ecap) { if (threadIdx.x == 0) atomicOr(&A.st->error, 8); return; }
+  const float4* src = A.arena[T] + d.off;
+  for (int k = threadIdx.x; k < d.cnt; k += 256) A.E[T][dst + k] = src[k];
+}
+
+// ---- exact 5-NN inside radius 1 (the only case the reference accepts, :719,:826) ------------
+// Returns true when the 5th neighbour has d2 < 1.0; idx/d2 ascending by (d2, index).
+__device__ __forceinline__ bool lm_knn5_warp(const GridView& g, float qx, float qy, float qz, int* idx5, float* d5) {
+  const GridDesc d = *g.desc;
+  const int lane = lane_id();
+  float ld[5]; int li[5];
+#pragma unroll
+  for (int k = 0; k < 5; k++) { ld[k] = 3.0e38f; li[k] = 0x7fffffff; }
+  if (d.valid) {
+    int cx = (int)floorf((qx - d.ox) * d.inv_h), cy = (int)floorf((qy - d.oy) * d.inv_h), cz = (int)floorf((qz - d.oz) * d.inv_h);
+    // cell size >= 1.02 m: every point with d2 < 1 lies in the 3x3x3 block around the query cell
+    for (int z = max(cz - 1, 0); z <= min(cz + 1, d.nz - 1); z++)
+      for (int y = max(cy - 1, 0); y <= min(cy + 1, d.ny - 1); y++)
+        for (int x = max(cx - 1, 0); x <= min(cx + 1, d.nx - 1); x++) {
+          int c = (z * d.ny + y) * d.nx + x;
+          int cnt = g.cell_count[c];
+          if (cnt == 0) continue;
+          int st = g.cell_start[c];
+          for (int t = lane; t < cnt; t += 32) {
+            float4 p = g.sorted_pts[st + t];
+            float dx = qx - p.x, dy = qy - p.y, dz = qz - p.z;
+            float dd = 0.f;
+            dd += dx * dx; dd += dy * dy; dd += dz * dz;
+            int id = g.sorted_idx[st + t];
+            if (nn_less(dd, id, ld[4], li[4])) {
+              ld[4] = dd; li[4] = id;
+#pragma unroll
+              for (int k = 4; k > 0; k--) {
+                if (nn_less(ld[k], li[k], ld[k - 1], li[k - 1])) {
+                  float td = ld[k]; ld[k] = ld[k - 1]; ld[k - 1] = td;
+                  int ti = li[k]; li[k] = li[k - 1]; li[k - 1] = ti;
+                }
+              }
+            }
+          }
+        }
+  }
+  // merge the 32 sorted lists: five rounds of warp arg-min, the winner pops its head
+#pragma unroll
+  for (int r = 0; r < 5; r++) {
+    float bd = ld[0]; int bi = li[0];
+    for (int o = 16; o > 0; o >>= 1) {
+      float od = __shfl_xor_sync(0xffffffffu, bd, o);
+      int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (nn_less(od, oi, bd, bi)) { bd = od; bi = oi; }
+    }
+    idx5[r] = bi; d5[r] = bd;
+    if (li[0] == bi && ld[0] == bd && bi != 0x7fffffff) {
+#pragma unroll
+      for (int k = 0; k < 4; k++) { ld[k] = ld[k + 1]; li[k] = li[k + 1]; }
+      ld[4] = 3.0e38f; li[4] = 0x7fffffff;
+    }
+  }
+  return idx5[4] != 0x7fffffff && d5[4] < 1.0;
+}
+
+}  // namespace loamgpu

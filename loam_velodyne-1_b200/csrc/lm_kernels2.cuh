@@ -1,0 +1,521 @@
+// lm_kernels2.cuh -- laserMapping on sm_100a, part 2: the cooperative sweep-to-map LM kernel
+// (LM-8 .. LM-11) and the map update (LM-12 .. LM-14).
+#pragma once
+#include "lm_kernels.cuh"
+#include "sort_voxel.cuh"
+
+namespace loamgpu {
+
+struct LMOptArgs {
+  LMState* st;
+  const float4* stack[2];     // laserCloudCornerStack / SurfStack (sensor frame)
+  const float4* map[2];       // laserCloudCornerFromMap / SurfFromMap
+  GridView grid[2];
+  double* partials;           // [2][gridDim][LO_NRED]
+  int* nn_dbg[2];             // 5 neighbour indices per query of the last iteration (-1 if rejected)
+  const LMImu* imu;
+  int has_imu;
+  double timeLaserOdometry;
+  int max_iter;
+};
+
+// corner: 5-NN mean, 3x3 covariance, eigen line test, point-to-line residual (:719-818)
+__device__ __forceinline__ bool lm_corner_fit(const float4* map, const int* idx, const float4 pointSel, float4& coeff) {
+  float cx = 0; float cy = 0; float cz = 0;
+  for (int j = 0; j < 5; j++) {
+    cx += map[idx[j]].x;
+    cy += map[idx[j]].y;
+    cz += map[idx[j]].z;
+  }
+  cx /= 5; cy /= 5; cz /= 5;
+  float a11 = 0; float a12 = 0; float a13 = 0; float a22 = 0; float a23 = 0; float a33 = 0;
+  for (int j = 0; j < 5; j++) {
+    float ax = map[idx[j]].x - cx;
+    float ay = map[idx[j]].y - cy;
+    float az = map[idx[j]].z - cz;
+    a11 += ax * ax; a12 += ax * ay; a13 += ax * az;
+    a22 += ay * ay; a23 += ay * az; a33 += az * az;
+  }
+  a11 /= 5; a12 /= 5; a13 /= 5; a22 /= 5; a23 /= 5; a33 /= 5;
+  float A1[9] = {a11, a12, a13, a12, a22, a23, a13, a23, a33};
+  float D1[3], V1[9];
+  la::jacobi_eigen(A1, D1, V1, 3);
+  if (!(D1[0] > 3 * D1[1])) return false;
+  float x0 = pointSel.x; float y0 = pointSel.y; float z0 = pointSel.z;
+  float x1 = cx + 0.1 * V1[0];
+  float y1 = cy + 0.1 * V1[1];
+  float z1 = cz + 0.1 * V1[2];
+  float x2 = cx - 0.1 * V1[0];
+  float y2 = cy - 0.1 * V1[1];
+  float z2 = cz - 0.1 * V1[2];
+  float a012 = dm::sqrt(((x0 - x1)*(y0 - y2) - (x0 - x2)*(y0 - y1))
+             * ((x0 - x1)*(y0 - y2) - (x0 - x2)*(y0 - y1))
+             + ((x0 - x1)*(z0 - z2) - (x0 - x2)*(z0 - z1))
+             * ((x0 - x1)*(z0 - z2) - (x0 - x2)*(z0 - z1))
+             + ((y0 - y1)*(z0 - z2) - (y0 - y2)*(z0 - z1))
+             * ((y0 - y1)*(z0 - z2) - (y0 - y2)*(z0 - z1)));
+  float l12 = dm::sqrt((x1 - x2)*(x1 - x2) + (y1 - y2)*(y1 - y2) + (z1 - z2)*(z1 - z2));
+  float la_ = ((y1 - y2)*((x0 - x1)*(y0 - y2) - (x0 - x2)*(y0 - y1))
+            + (z1 - z2)*((x0 - x1)*(z0 - z2) - (x0 - x2)*(z0 - z1))) / a012 / l12;
+  float lb = -((x1 - x2)*((x0 - x1)*(y0 - y2) - (x0 - x2)*(y0 - y1))
+           - (z1 - z2)*((y0 - y1)*(z0 - z2) - (y0 - y2)*(z0 - z1))) / a012 / l12;
+  float lc = -((x1 - x2)*((x0 - x1)*(z0 - z2) - (x0 - x2)*(z0 - z1))
+           + (y1 - y2)*((y0 - y1)*(z0 - z2) - (y0 - y2)*(z0 - z1))) / a012 / l12;
+  float ld2 = a012 / l12;
+  float s = 1 - 0.9 * dm::fabs(ld2);
+  coeff.x = s * la_;
+  coeff.y = s * lb;
+  coeff.z = s * lc;
+  coeff.w = s * ld2;
+  return s > 0.1;
+}
+
+// surf: 5x3 QR plane fit, 0.2 m validity, point-to-plane residual (:826-875)
+__device__ __forceinline__ bool lm_surf_fit(const float4* map, const int* idx, const float4 pointSel, float4& coeff) {
+  float A0[15], B0[5];
+  for (int j = 0; j < 5; j++) {
+    A0[j * 3 + 0] = map[idx[j]].x;
+    A0[j * 3 + 1] = map[idx[j]].y;
+    A0[j * 3 + 2] = map[idx[j]].z;
+    B0[j] = -1.f;
+  }
+  int ok = la::qr_solve(A0, 5, 3, B0, 1);
+  float pa = ok ? B0[0] : 0.f;
+  float pb = ok ? B0[1] : 0.f;
+  float pc = ok ? B0[2] : 0.f;
+  float pd = 1;
+  float ps = dm::sqrt(pa * pa + pb * pb + pc * pc);
+  pa /= ps; pb /= ps; pc /= ps; pd /= ps;
+  bool planeValid = true;
+  for (int j = 0; j < 5; j++) {
+    if (dm::fabs(pa * map[idx[j]].x + pb * map[idx[j]].y + pc * map[idx[j]].z + pd) > 0.2) {
+      planeValid = false;
+      break;
+    }
+  }
+  if (!planeValid) return false;
+  float pd2 = pa * pointSel.x + pb * pointSel.y + pc * pointSel.z + pd;
+  float s = 1 - 0.9 * dm::fabs(pd2) / dm::sqrt(dm::sqrt(pointSel.x * pointSel.x + pointSel.y * pointSel.y + pointSel.z * pointSel.z));
+  coeff.x = s * pa;
+  coeff.y = s * pb;
+  coeff.z = s * pc;
+  coeff.w = s * pd2;
+  return s > 0.1;
+}
+
+// Jacobian row :898-920
+__device__ __forceinline__ void lm_row_accumulate(const float4 pointOri, const float4 coeffv, const LMTrig& g, double* acc) {
+  float srx = g.srx, crx = g.crx, sry = g.sry, cry = g.cry, srz = g.srz, crz = g.crz;
+  struct { float x, y, z; } coeff = {coeffv.x, coeffv.y, coeffv.z};
+  float arx = (crx*sry*srz*pointOri.x + crx*crz*sry*pointOri.y - srx*sry*pointOri.z) * coeff.x
+            + (-srx*srz*pointOri.x - crz*srx*pointOri.y - crx*pointOri.z) * coeff.y
+            + (crx*cry*srz*pointOri.x + crx*cry*crz*pointOri.y - cry*srx*pointOri.z) * coeff.z;
+  float ary = ((cry*srx*srz - crz*sry)*pointOri.x
+            + (sry*srz + cry*crz*srx)*pointOri.y + crx*cry*pointOri.z) * coeff.x
+            + ((-cry*crz - srx*sry*srz)*pointOri.x
+            + (cry*srz - crz*srx*sry)*pointOri.y - crx*sry*pointOri.z) * coeff.z;
+  float arz = ((crz*srx*sry - cry*srz)*pointOri.x + (-cry*crz-srx*sry*srz)*pointOri.y)*coeff.x
+            + (crx*crz*pointOri.x - crx*srz*pointOri.y) * coeff.y
+            + ((sry*srz + cry*crz*srx)*pointOri.x + (crz*sry-cry*srx*srz)*pointOri.y)*coeff.z;
+  float a[6] = {arx, ary, arz, coeff.x, coeff.y, coeff.z};
+  float b = -coeffv.w;
+  int k = 0;
+#pragma unroll
+  for (int i = 0; i < 6; i++)
+#pragma unroll
+    for (int j = i; j < 6; j++) acc[k++] += (double)a[i] * (double)a[j];
+#pragma unroll
+  for (int i = 0; i < 6; i++) acc[21 + i] += (double)a[i] * (double)b;
+  acc[27] += 1.0;
+}
+
+// transformUpdate :199-232
+__device__ __forceinline__ void lm_transform_update(LMState* st, float* T, const LMImu* imu, int has_imu, double timeLaserOdometry) {
+  const float scanPeriod = 0.1;
+  if (has_imu && imu->pointer_last >= 0) {
+    float imuRollLast = 0, imuPitchLast = 0;
+    int front = st->imuPointerFront;
+    const int last = imu->pointer_last;
+    while (front != last) {
+      if (timeLaserOdometry + scanPeriod < imu->time[front]) break;
+      front = (front + 1) % IMU_Q;
+    }
+    st->imuPointerFront = front;
+    if (timeLaserOdometry + scanPeriod > imu->time[front]) {
+      imuRollLast = imu->roll[front];
+      imuPitchLast = imu->pitch[front];
+    } else {
+      int back = (front + IMU_Q - 1) % IMU_Q;
+      float ratioFront = (timeLaserOdometry + scanPeriod - imu->time[back]) / (imu->time[front] - imu->time[back]);
+      float ratioBack = (imu->time[front] - timeLaserOdometry - scanPeriod) / (imu->time[front] - imu->time[back]);
+      imuRollLast = imu->roll[front] * ratioFront + imu->roll[back] * ratioBack;
+      imuPitchLast = imu->pitch[front] * ratioFront + imu->pitch[back] * ratioBack;
+    }
+    T[0] = 0.998 * T[0] + 0.002 * imuPitchLast;
+    T[2] = 0.998 * T[2] + 0.002 * imuRollLast;
+  }
+  for (int i = 0; i < 6; i++) {
+    st->transformBefMapped[i] = st->transformSum[i];
+    st->transformAftMapped[i] = T[i];
+  }
+}
+
+// K6: the whole LM loop :706-978 as one cooperative kernel (one warp per query)
+__global__ void __launch_bounds__(LM_THREADS) lm_optimize(LMOptArgs A) {
+  cg::grid_group grid = cg::this_grid();
+  __shared__ float s_T[6];
+  __shared__ LMTrig s_trig;
+  __shared__ float s_matP[36];
+  __shared__ int s_deg, s_stop, s_rows;
+  __shared__ double s_red[LM_WARPS][LO_NRED];
+  __shared__ double s_tot[LO_NRED];
+  const int lane = lane_id(), warp = threadIdx.x >> 5;
+  const int gwarp = blockIdx.x * LM_WARPS + warp, nwarps = gridDim.x * LM_WARPS;
+  LMState* st = A.st;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 6; i++) s_T[i] = st->transformTobeMapped[i];
+    for (int i = 0; i < 36; i++) s_matP[i] = st->matP[i];
+    s_deg = st->isDegenerate;
+    s_rows = 0;
+  }
+  __syncthreads();
+  const int Qc = st->stackN[0], Qs = st->stackN[1];
+  int iters_done = 0;
+  const bool enabled = st->optimize_enable != 0;
+  if (enabled) {
+    for (int iterCount = 0; iterCount < A.max_iter; iterCount++) {
+      iters_done = iterCount + 1;
+      if (threadIdx.x == 0) s_trig = lm_trig(s_T);
+      __syncthreads();
+      const LMTrig g = s_trig;
+      double acc[LO_NRED];
+#pragma unroll
+      for (int k = 0; k < LO_NRED; k++) acc[k] = 0.0;
+      for (int q = gwarp; q < Qc + Qs; q += nwarps) {
+        const int T = q < Qc ? 0 : 1;
+        const int k = T ? q - Qc : q;
+        const float4 pointOri = A.stack[T][k];
+        const float4 pointSel = lm_to_map(pointOri, g, s_T);
+        int idx5[5]; float d5[5];
+        bool found = lm_knn5_warp(A.grid[T], pointSel.x, pointSel.y, pointSel.z, idx5, d5);
+        if (lane < 5) A.nn_dbg[T][(size_t)k * 5 + lane] = found ? idx5[lane] : -1;
+        if (lane == 0 && found) {
+          float4 coeff;
+          bool valid = T == 0 ? lm_corner_fit(A.map[0], idx5, pointSel, coeff) : lm_surf_fit(A.map[1], idx5, pointSel, coeff);
+          if (valid) lm_row_accumulate(pointOri, coeff, g, acc);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < LO_NRED; k++) {
+        double v = acc[k];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) s_red[warp][k] = v;
+      }
+      __syncthreads();
+      double* part = A.partials + (size_t)(iterCount & 1) * gridDim.x * LO_NRED;
+      if (threadIdx.x < LO_NRED) {
+        double v = 0.0;
+        for (int w = 0; w < LM_WARPS; w++) v += s_red[w][threadIdx.x];
+        part[(size_t)blockIdx.x * LO_NRED + threadIdx.x] = v;
+      }
+      __threadfence();
+      grid.sync();
+      if (threadIdx.x < LO_NRED) {
+        double v = 0.0;
+        for (int b = 0; b < (int)gridDim.x; b++) v += __ldcg(&part[(size_t)b * LO_NRED + threadIdx.x]);
+        s_tot[threadIdx.x] = v;
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        s_stop = 0;
+        int laserCloudSelNum = (int)s_tot[27];
+        s_rows = laserCloudSelNum;
+        if (laserCloudSelNum >= 50) {  // :887
+          float X[6];
+          lm_solve_step(s_tot, iterCount == 0, 100.f, &s_deg, s_matP, X);
+          for (int i = 0; i < 6; i++) s_T[i] += X[i];  // :956-961 (no NaN guard in this node)
+          if (lm_converged(X, 0.05)) s_stop = 1;
+        }
+      }
+      __syncthreads();
+      if (s_stop) break;
+    }
+  }
+  if (!enabled) {  // no search happened: report "rejected" for every query
+    for (int q = blockIdx.x * LM_THREADS + threadIdx.x; q < (Qc + Qs) * 5; q += gridDim.x * LM_THREADS) {
+      if (q < Qc * 5) A.nn_dbg[0][q] = -1; else A.nn_dbg[1][q - Qc * 5] = -1;
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    if (enabled) lm_transform_update(st, s_T, A.imu, A.has_imu, A.timeLaserOdometry);  // :977
+    for (int i = 0; i < 6; i++) st->transformTobeMapped[i] = s_T[i];
+    for (int i = 0; i < 36; i++) st->matP[i] = s_matP[i];
+    st->isDegenerate = s_deg;
+    st->iters = iters_done;
+    st->rows = s_rows;
+  }
+}
+
+// ---- map update ------------------------------------------------------------------------------
+struct LMInsertArgs {
+  LMState* st;
+  const float4* stack[2];
+  float4* ins_pts[2];
+  int* ins_cube[2];
+  int* touch_cnt[2];
+};
+// K7a: stack points to the map with the refined pose and their cube (:980-1016)
+__global__ void __launch_bounds__(256) lm_insert_ids(LMInsertArgs A) {
+  const LMState* st = A.st;
+  __shared__ LMTrig s_g;
+  __shared__ float s_T[6];
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 6; i++) s_T[i] = st->transformTobeMapped[i];
+    s_g = lm_trig(s_T);
+  }
+  __syncthreads();
+  const LMTrig g = s_g;
+  const int n0 = st->stackN[0], n1 = st->stackN[1];
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < n0 + n1; i += gridDim.x * 256) {
+    int T = i < n0 ? 0 : 1;
+    int k = T ? i - n0 : i;
+    float4 pointSel = lm_to_map(A.stack[T][k], g, s_T);
+    int cubeI = lm_cube_coord(pointSel.x, st->cenW), cubeJ = lm_cube_coord(pointSel.y, st->cenH), cubeK = lm_cube_coord(pointSel.z, st->cenD);
+    int cube = -1;
+    if (cubeI >= 0 && cubeI < CUBE_W && cubeJ >= 0 && cubeJ < CUBE_H && cubeK >= 0 && cubeK < CUBE_D) {
+      cube = cubeI + CUBE_W * cubeJ + CUBE_W * CUBE_H * cubeK;
+      atomicAdd(&A.touch_cnt[T][cube], 1);
+    }
+    A.ins_pts[T][k] = pointSel;
+    A.ins_cube[T][k] = cube;
+  }
+}
+
+struct LMPlanArgs {
+  LMState* st;
+  CubeDesc* cubes[2];
+  int* touch_cnt[2];
+  int* cube_rank[2];
+  int ecap;
+};
+// K7b: one block.  Which cubes get rewritten this sweep and where their points sit inside E:
+// ranks 0..validNum-1 = the valid cubes (their old points ARE the local map, already in E),
+// then every other cube that received points (ascending cube index).
+__global__ void __launch_bounds__(1024) lm_refilter_plan(LMPlanArgs A) {
+  LMState* st = A.st;
+  __shared__ int s_scan[32];
+  __shared__ int s_carry;
+  for (int T = 0; T < 2; T++) {
+    const int nv = st->validNum;
+    for (int r = threadIdx.x; r < nv; r += 1024) {
+      int c = st->validInd[r];
+      A.cube_rank[T][c] = r;
+      st->procCube[T][r] = c;
+    }
+    for (int r = threadIdx.x; r < 256; r += 1024) st->segCount[T][r] = 0;
+    if (threadIdx.x == 0) s_carry = nv;
+    __syncthreads();
+    for (int base = 0; base < CUBE_NUM; base += 1024) {
+      int c = base + threadIdx.x;
+      int flag = (c < CUBE_NUM && A.touch_cnt[T][c] > 0 && A.cube_rank[T][c] < 0) ? 1 : 0;
+      int x = flag;
+      for (int o = 1; o < 32; o <<= 1) {
+        int y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane_id() >= o) x += y;
+      }
+      if (lane_id() == 31) s_scan[threadIdx.x >> 5] = x;
+      __syncthreads();
+      if (threadIdx.x < 32) {
+        int w = s_scan[threadIdx.x], s = w;
+        for (int o = 1; o < 32; o <<= 1) {
+          int y = __shfl_up_sync(0xffffffffu, s, o);
+          if (lane_id() >= o) s += y;
+        }
+        s_scan[threadIdx.x] = s - w;
+      }
+      __syncthreads();
+      int r = s_carry + s_scan[threadIdx.x >> 5] + x - flag;
+      if (flag) {
+        if (r < PROC_MAX) { A.cube_rank[T][c] = r; st->procCube[T][r] = c; }
+        else atomicOr(&st->error, 2);
+      }
+      __syncthreads();
+      if (threadIdx.x == 1023) s_carry = r + flag;
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      int np = min(s_carry, PROC_MAX);
+      st->nproc[T] = np;
+      int off = 0;
+      for (int r = 0; r < np; r++) {
+        CubeDesc d = A.cubes[T][st->procCube[T][r]];
+        st->procInOff[T][r] = off;
+        st->procOldOff[T][r] = d.off;
+        st->procOldCnt[T][r] = d.cnt;
+        off += d.cnt;
+      }
+      st->procInOff[T][np] = off;
+      int En = off + st->stackN[T];
+      st->outOff[T] = st->bump[T];
+      if (En > A.ecap) { atomicOr(&st->error, 8); En = 0; }
+      if (st->bump[T] + En > st->arenaCap) { atomicOr(&st->error, 1); En = 0; }
+      st->En[T] = En;
+    }
+    __syncthreads();
+  }
+}
+
+struct LMFillArgs {
+  LMState* st;
+  const float4* arena[2];
+  float4* E[2];
+  const float4* ins_pts[2];
+  const int* ins_cube[2];
+  const int* cube_rank[2];
+  unsigned int* keys[2];
+  unsigned int* vals[2];
+};
+// voxel coordinate of a map point relative to its cube, 8 bits per axis
+__device__ __forceinline__ unsigned int lm_voxel_key(const float4 p, int cube, const LMState* st, int T, int* error) {
+  const float inv = T == 0 ? (1.0f / 0.2f) : (1.0f / 0.4f);   // 5.0f / 2.5f exactly, as PCL computes 1/leaf
+  const int cells = T == 0 ? 250 : 125;
+  int ci = cube % CUBE_W, cj = (cube / CUBE_W) % CUBE_H, ck = cube / (CUBE_W * CUBE_H);
+  int bi = (ci - st->cenW) * cells - (cells + 1) / 2 - 1;
+  int bj = (cj - st->cenH) * cells - (cells + 1) / 2 - 1;
+  int bk = (ck - st->cenD) * cells - (cells + 1) / 2 - 1;
+  int gx = (int)floorf(p.x * inv) - bi, gy = (int)floorf(p.y * inv) - bj, gz = (int)floorf(p.z * inv) - bk;
+  if ((gx | gy | gz) & ~255) {
+    atomicOr(error, 4);
+    gx = min(max(gx, 0), 255); gy = min(max(gy, 0), 255); gz = min(max(gz, 0), 255);
+  }
+  return ((unsigned int)gz << 16) | ((unsigned int)gy << 8) | (unsigned int)gx;  // PCL order: idx = i + j*dx + k*dx*dy
+}
+// K7c: build E = [old points of the processed cubes][stack points in stack order] with sort keys
+__global__ void __launch_bounds__(256) lm_refilter_fill(LMFillArgs A) {
+  LMState* st = A.st;
+  const int T = blockIdx.y;
+  const int En = st->En[T];
+  const int np = st->nproc[T], nv = st->validNum;
+  const int total_old = st->procInOff[T][np];
+  for (int e = blockIdx.x * 256 + threadIdx.x; e < En; e += gridDim.x * 256) {
+    unsigned int key;
+    if (e < total_old) {
+      int lo = 0, hi = np - 1;  // last r with procInOff[r] <= e
+      while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (st->procInOff[T][mid] <= e) lo = mid; else hi = mid - 1;
+      }
+      int r = lo;
+      int k = e - st->procInOff[T][r];
+      float4 p;
+      if (r < nv) p = A.E[T][e];  // already gathered as the local map
+      else { p = A.arena[T][st->procOldOff[T][r] + k]; A.E[T][e] = p; }
+      if (r < nv) key = ((unsigned int)r << 24) | lm_voxel_key(p, st->procCube[T][r], st, T, &st->error);
+      else key = ((unsigned int)r << 24) | (unsigned int)k;            // not refiltered: keep all, keep order
+    } else {
+      int i = e - total_old;
+      float4 p = A.ins_pts[T][i];
+      A.E[T][e] = p;
+      int cube = A.ins_cube[T][i];
+      int r = cube >= 0 ? A.cube_rank[T][cube] : -1;
+      if (r < 0) key = 0xffffffffu;                                      // outside the 21x11x21 window: dropped (:991-996)
+      else if (r < nv) key = ((unsigned int)r << 24) | lm_voxel_key(p, cube, st, T, &st->error);
+      else key = ((unsigned int)r << 24) | (unsigned int)(st->procOldCnt[T][r] + i);
+    }
+    A.keys[T][e] = key;
+    A.vals[T][e] = (unsigned int)e;
+  }
+}
+
+struct LMCommitArgs {
+  LMState* st;
+  CubeDesc* cubes[2];
+  int* touch_cnt[2];
+  int* cube_rank[2];
+};
+// K7e: new descriptors for the rewritten cubes; release the scratch tables
+__global__ void __launch_bounds__(1024) lm_refilter_commit(LMCommitArgs A) {
+  LMState* st = A.st;
+  for (int T = 0; T < 2; T++) {
+    if (threadIdx.x == 0 && st->En[T] > 0) {
+      int off = st->outOff[T];
+      for (int r = 0; r < st->nproc[T]; r++) {
+        CubeDesc d;
+        d.off = off; d.cnt = st->segCount[T][r];
+        A.cubes[T][st->procCube[T][r]] = d;
+        off += d.cnt;
+      }
+      st->bump[T] = off;
+    }
+    for (int c = threadIdx.x; c < CUBE_NUM; c += 1024) { A.touch_cnt[T][c] = 0; A.cube_rank[T][c] = -1; }
+  }
+}
+
+// K8: registered full-resolution cloud (:1060-1063)
+__global__ void __launch_bounds__(256) lm_registered(LMState* st, const float4* in, const int* n_ptr, float4* out) {
+  __shared__ LMTrig s_g;
+  __shared__ float s_T[6];
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 6; i++) s_T[i] = st->transformTobeMapped[i];
+    s_g = lm_trig(s_T);
+  }
+  __syncthreads();
+  const LMTrig g = s_g;
+  const int n = *n_ptr;
+  if (blockIdx.x == 0 && threadIdx.x == 0) st->registeredN = n;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) out[i] = lm_to_map(in[i], g, s_T);
+}
+
+// arena compaction: copy every live cube segment into the other arena (host-triggered)
+struct LMCompactArgs {
+  LMState* st;
+  CubeDesc* cubes[2];
+  const float4* src[2];
+  float4* dst[2];
+  int* new_off[2];   // [CUBE_NUM]
+};
+__global__ void __launch_bounds__(1024) lm_compact_plan(LMCompactArgs A) {
+  const int T = blockIdx.x;
+  __shared__ int s_scan[32];
+  __shared__ int s_carry;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  for (int base = 0; base < CUBE_NUM; base += 1024) {
+    int c = base + threadIdx.x;
+    int v = c < CUBE_NUM ? A.cubes[T][c].cnt : 0;
+    int x = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      int y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane_id() >= o) x += y;
+    }
+    if (lane_id() == 31) s_scan[threadIdx.x >> 5] = x;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      int w = s_scan[threadIdx.x], s = w;
+      for (int o = 1; o < 32; o <<= 1) {
+        int y = __shfl_up_sync(0xffffffffu, s, o);
+        if (lane_id() >= o) s += y;
+      }
+      s_scan[threadIdx.x] = s - w;
+    }
+    __syncthreads();
+    int excl = s_carry + s_scan[threadIdx.x >> 5] + x - v;
+    if (c < CUBE_NUM) A.new_off[T][c] = excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) s_carry = excl + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) A.st->bump[T] = s_carry;
+}
+__global__ void __launch_bounds__(256) lm_compact_copy(LMCompactArgs A) {
+  const int T = blockIdx.y;
+  for (int c = blockIdx.x; c < CUBE_NUM; c += gridDim.x) {
+    CubeDesc d = A.cubes[T][c];
+    int no = A.new_off[T][c];
+    for (int k = threadIdx.x; k < d.cnt; k += 256) A.dst[T][no + k] = A.src[T][d.off + k];
+    __syncthreads();
+    if (threadIdx.x == 0) A.cubes[T][c].off = no;
+  }
+}
+
+}  // namespace loamgpu

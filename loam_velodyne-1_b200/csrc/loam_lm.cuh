@@ -1,3 +1,292 @@
+// loam_lm.cuh -- host side of the laserMapping node (laserMapping.cpp main loop :408-1096) and
+// the host-only transformMaintenance node (transformMaintenance.cpp).
 #pragma once
+#include "lm_kernels2.cuh"
 #include "loam_lo.cuh"
-namespace loamgpu { struct LMHandle { }; struct TMHost { }; }
+
+namespace loamgpu {
+
+struct LMHandle {
+  loam_params P;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  cudaEvent_t ev_dep = nullptr;
+  int cap = 0, ecap = 0, arena_cap = 0, coop_blocks = 0;
+  int cur_arena = 0;
+  static const int stackFrameNum = 1, mapFrameNum = 5;  // :51-52
+  int frameCount = stackFrameNum - 1, mapFrameCount = mapFrameNum - 1;  // :404-405
+  DevBuf<LMState> d_state;
+  DevBuf<LMImu> d_imu;
+  DevBuf<CubeDesc> d_cubes[2];
+  DevBuf<int> d_touch[2], d_rank[2], d_newoff[2];
+  DevBuf<float4> d_arena[2][2];        // [type][A/B]
+  DevBuf<float4> d_stack2[2], d_stack[2], d_E[2], d_ins_pts[2], d_registered, d_surround;
+  DevBuf<int> d_ins_cube[2], d_nn[2];
+  DevBuf<unsigned int> d_skeys[2][2], d_svals[2][2], d_ekeys[2][2], d_evals[2][2], d_bbox[2];
+  DevBuf<int> d_shist[2], d_ehist[2], d_sdig[2], d_edig[2], d_sheads[2], d_eheads[2];
+  DevBuf<double> d_partials;
+  GridStorage g_map[2];
+  PinnedBuf<LMState> h_state;
+  PinnedBuf<LMImu> h_imu;
+  LMImu imu;
+  bool has_imu = false;
+  LMState last_state;
+  bool last_surround = false;
+  int last_n_registered = 0;
+
+  int init(const loam_params* p, int dev, cudaStream_t s) {
+    P = *p;
+    device = dev;
+    CUDA_OK(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    CUDA_OK(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major < 10) { set_error("device %d is not sm_100", dev); return LOAM_ERR_CUDA; }
+    if (s) stream = s; else { CUDA_OK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking)); own_stream = true; }
+    CUDA_OK(cudaEventCreateWithFlags(&ev_dep, cudaEventDisableTiming));
+    cap = P.max_points;
+    arena_cap = P.map_arena_points > 0 ? P.map_arena_points : (8 << 20);
+    ecap = arena_cap / 4;
+    if (ecap < 4 * cap) ecap = 4 * cap;
+    coop_blocks = prop.multiProcessorCount;
+    int per_sm = 0;
+    CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lm_optimize, LM_THREADS, 0));
+    if (per_sm < 1) { set_error("lm_optimize cannot be made resident"); return LOAM_ERR_CUDA; }
+    int r = LOAM_OK;
+    r |= d_state.alloc_zero(1, stream); r |= d_imu.alloc_zero(1, stream);
+    int snblk = (cap + RS_TILE - 1) / RS_TILE + 1, enblk = (ecap + RS_TILE - 1) / RS_TILE + 1;
+    int svblk = (cap + VX_TILE - 1) / VX_TILE + 1, evblk = (ecap + VX_TILE - 1) / VX_TILE + 1;
+    for (int T = 0; T < 2; T++) {
+      r |= d_cubes[T].alloc_zero(CUBE_NUM, stream); r |= d_touch[T].alloc_zero(CUBE_NUM, stream);
+      r |= d_rank[T].alloc(CUBE_NUM); r |= d_newoff[T].alloc(CUBE_NUM);
+      r |= d_arena[T][0].alloc(arena_cap); r |= d_arena[T][1].alloc(arena_cap);
+      r |= d_stack2[T].alloc(cap); r |= d_stack[T].alloc(cap); r |= d_E[T].alloc(ecap); r |= d_ins_pts[T].alloc(cap);
+      r |= d_ins_cube[T].alloc(cap); r |= d_nn[T].alloc((size_t)cap * 5);
+      for (int k = 0; k < 2; k++) {
+        r |= d_skeys[T][k].alloc(cap); r |= d_svals[T][k].alloc(cap); r |= d_ekeys[T][k].alloc(ecap); r |= d_evals[T][k].alloc(ecap);
+      }
+      r |= d_bbox[T].alloc(6);
+      r |= d_shist[T].alloc((size_t)256 * snblk); r |= d_ehist[T].alloc((size_t)256 * enblk);
+      r |= d_sdig[T].alloc(256); r |= d_edig[T].alloc(256); r |= d_sheads[T].alloc(svblk); r |= d_eheads[T].alloc(evblk);
+      r |= g_map[T].alloc(ecap, 1 << 22, stream);
+      if (r == LOAM_OK) {
+        if (cudaMemsetAsync(d_rank[T].p, 0xff, sizeof(int) * CUBE_NUM, stream) != cudaSuccess) r = LOAM_ERR_CUDA;
+        unsigned int init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+        if (cudaMemcpyAsync(d_bbox[T].p, init, sizeof(init), cudaMemcpyHostToDevice, stream) != cudaSuccess) r = LOAM_ERR_CUDA;
+        cudaStreamSynchronize(stream);
+      }
+    }
+    r |= d_registered.alloc(cap); r |= d_partials.alloc_zero((size_t)2 * coop_blocks * LO_NRED, stream);
+    r |= h_state.alloc(1); r |= h_imu.alloc(1);
+    if (r != LOAM_OK) return LOAM_ERR_CUDA;
+    LMState init;
+    memset(&init, 0, sizeof(init));
+    init.cenW = 10; init.cenH = 5; init.cenD = 10;  // :64-66
+    init.arenaCap = arena_cap;
+    *h_state.p = init;
+    CUDA_OK(cudaMemcpyAsync(d_state.p, h_state.p, sizeof(LMState), cudaMemcpyHostToDevice, stream));
+    memset(&imu, 0, sizeof(imu));
+    imu.pointer_last = -1;
+    last_state = init;
+    CUDA_OK(cudaStreamSynchronize(stream));
+    return LOAM_OK;
+  }
+  ~LMHandle() {
+    if (ev_dep) cudaEventDestroy(ev_dep);
+    if (own_stream && stream) cudaStreamDestroy(stream);
+  }
+
+  // imuHandler :323-335
+  int on_imu(double stamp, const double quat[4]) {
+    double roll, pitch, yaw;
+    pm::rpy_from_quat(quat[0], quat[1], quat[2], quat[3], roll, pitch, yaw);
+    int last = (imu.pointer_last + 1) % IMU_Q;
+    imu.pointer_last = last;
+    imu.time[last] = stamp;
+    imu.roll[last] = roll;
+    imu.pitch[last] = pitch;
+    has_imu = true;
+    return LOAM_OK;
+  }
+
+  SortPair sort_pair(bool forE) {
+    SortPair sp;
+    sp.njobs = 2;
+    for (int T = 0; T < 2; T++) {
+      SortJob& j = sp.j[T];
+      if (forE) {
+        j.keys[0] = d_ekeys[T][0].p; j.keys[1] = d_ekeys[T][1].p; j.vals[0] = d_evals[T][0].p; j.vals[1] = d_evals[T][1].p;
+        j.hist = d_ehist[T].p; j.digit_total = d_edig[T].p; j.n_ptr = &d_state.p->En[T]; j.nblk_cap = (ecap + RS_TILE - 1) / RS_TILE + 1;
+      } else {
+        j.keys[0] = d_skeys[T][0].p; j.keys[1] = d_skeys[T][1].p; j.vals[0] = d_svals[T][0].p; j.vals[1] = d_svals[T][1].p;
+        j.hist = d_shist[T].p; j.digit_total = d_sdig[T].p; j.n_ptr = &d_state.p->stackN2[T]; j.nblk_cap = (cap + RS_TILE - 1) / RS_TILE + 1;
+      }
+    }
+    return sp;
+  }
+
+  // one loop-body pass; consumes corner_last / surf_last / full_end / transformSum of `lo`
+  int process(LOHandle& lo, double stamp) {
+    if (!lo.last_published) return LOAM_NOT_READY;
+    frameCount++;
+    if (frameCount < stackFrameNum) return LOAM_NOT_READY;
+    frameCount = 0;
+    CUDA_OK(cudaSetDevice(device));
+    if (lo.stream != stream) {
+      CUDA_OK(cudaEventRecord(ev_dep, lo.stream));
+      CUDA_OK(cudaStreamWaitEvent(stream, ev_dep, 0));
+    }
+    LMState* st = d_state.p;
+    const int nb = 148;
+    float4* arena[2] = {d_arena[0][cur_arena].p, d_arena[1][cur_arena].p};
+    // K1
+    LMSetupArgs SA;
+    SA.st = st; SA.lo = lo.d_state.p; SA.cubes[0] = d_cubes[0].p; SA.cubes[1] = d_cubes[1].p;
+    LAUNCH("lm_setup", lm_setup, 1, 256, 0, stream, SA);
+    // K2
+    LMStackArgs KA;
+    KA.st = st; KA.in[0] = lo.d_corner_last.p; KA.in[1] = lo.d_surf_last.p; KA.out[0] = d_stack2[0].p; KA.out[1] = d_stack2[1].p;
+    LAUNCH("lm_stack_transform", lm_stack_transform, nb, 256, 0, stream, KA);
+    // K3: downSizeFilterCorner (0.2) / downSizeFilterSurf (0.4) on the incoming sweep
+    {
+      CloudKeyPair cp;
+      cp.njobs = 2;
+      for (int T = 0; T < 2; T++) {
+        CloudKeyJob& j = cp.j[T];
+        j.pts = d_stack2[T].p; j.n_ptr = &st->stackN2[T]; j.bbox = d_bbox[T].p; j.keys = d_skeys[T][0].p; j.vals = d_svals[T][0].p;
+        j.overflow = &st->vxOverflow[T]; j.leaf = T == 0 ? 0.2f : 0.4f;
+      }
+      LAUNCH("vx_bbox", vx_bbox, dim3(nb, 2), 256, 0, stream, cp);
+      LAUNCH("vx_cloud_keys", vx_cloud_keys, dim3(nb, 2), 256, 0, stream, cp);
+      LAUNCH("vx_rearm_bbox", vx_rearm_bbox, 1, 32, 0, stream, cp);
+      int r = radix_sort_pairs(sort_pair(false), cap, stream);
+      if (r != LOAM_OK) return r;
+      VoxelPair vp;
+      vp.njobs = 2;
+      for (int T = 0; T < 2; T++) {
+        VoxelJob& j = vp.j[T];
+        j.keys = d_skeys[T][0].p; j.vals = d_svals[T][0].p; j.pts = d_stack2[T].p; j.n_ptr = &st->stackN2[T];
+        j.block_heads = d_sheads[T].p; j.out = d_stack[T].p; j.out_base_ptr = nullptr; j.out_count = &st->stackN[T];
+        j.seg_count = nullptr; j.seg_shift = 0; j.nblk_cap = (cap + VX_TILE - 1) / VX_TILE + 1;
+      }
+      r = voxel_reduce_sorted(vp, cap, stream);
+      if (r != LOAM_OK) return r;
+    }
+    // K4
+    LMGatherArgs GA;
+    GA.st = st; GA.ecap = ecap;
+    for (int T = 0; T < 2; T++) { GA.cubes[T] = d_cubes[T].p; GA.arena[T] = arena[T]; GA.E[T] = d_E[T].p; }
+    LAUNCH("lm_gather_map", lm_gather_map, dim3(125, 2), 256, 0, stream, GA);
+    // K5: kdtreeCornerFromMap / kdtreeSurfFromMap -> grid index, cell 1.02 m
+    {
+      GridPair gp;
+      for (int T = 0; T < 2; T++) gp.g[T] = g_map[T].buf(d_E[T].p, &st->mapN[T], &st->optimize_enable, 1.02f);
+      int r = grid_build_pair(gp, 2 * nb, stream);
+      if (r != LOAM_OK) return r;
+    }
+    // K6
+    if (has_imu) {
+      *h_imu.p = imu;
+      CUDA_OK(cudaMemcpyAsync(d_imu.p, h_imu.p, sizeof(LMImu), cudaMemcpyHostToDevice, stream));
+    }
+    {
+      LMOptArgs OA;
+      OA.st = st;
+      for (int T = 0; T < 2; T++) { OA.stack[T] = d_stack[T].p; OA.map[T] = d_E[T].p; OA.grid[T] = g_map[T].view(); OA.nn_dbg[T] = d_nn[T].p; }
+      OA.partials = d_partials.p; OA.imu = d_imu.p; OA.has_imu = has_imu ? 1 : 0; OA.timeLaserOdometry = stamp; OA.max_iter = P.lm_max_iter;
+      void* args[] = {&OA};
+      if (g_profile) prof_begin(stream);
+      CUDA_OK(cudaLaunchCooperativeKernel((void*)lm_optimize, dim3(coop_blocks), dim3(LM_THREADS), args, 0, stream));
+      g_launches++;
+      if (g_profile) prof_end("lm_optimize", stream);
+    }
+    // K7: insert + per-cube refilter
+    {
+      LMInsertArgs IA;
+      IA.st = st;
+      for (int T = 0; T < 2; T++) { IA.stack[T] = d_stack[T].p; IA.ins_pts[T] = d_ins_pts[T].p; IA.ins_cube[T] = d_ins_cube[T].p; IA.touch_cnt[T] = d_touch[T].p; }
+      LAUNCH("lm_insert_ids", lm_insert_ids, nb, 256, 0, stream, IA);
+      LMPlanArgs PA;
+      PA.st = st; PA.ecap = ecap;
+      for (int T = 0; T < 2; T++) { PA.cubes[T] = d_cubes[T].p; PA.touch_cnt[T] = d_touch[T].p; PA.cube_rank[T] = d_rank[T].p; }
+      LAUNCH("lm_refilter_plan", lm_refilter_plan, 1, 1024, 0, stream, PA);
+      LMFillArgs FA;
+      FA.st = st;
+      for (int T = 0; T < 2; T++) {
+        FA.arena[T] = arena[T]; FA.E[T] = d_E[T].p; FA.ins_pts[T] = d_ins_pts[T].p; FA.ins_cube[T] = d_ins_cube[T].p;
+        FA.cube_rank[T] = d_rank[T].p; FA.keys[T] = d_ekeys[T][0].p; FA.vals[T] = d_evals[T][0].p;
+      }
+      LAUNCH("lm_refilter_fill", lm_refilter_fill, dim3(2 * nb, 2), 256, 0, stream, FA);
+      int r = radix_sort_pairs(sort_pair(true), ecap, stream);
+      if (r != LOAM_OK) return r;
+      VoxelPair vp;
+      vp.njobs = 2;
+      for (int T = 0; T < 2; T++) {
+        VoxelJob& j = vp.j[T];
+        j.keys = d_ekeys[T][0].p; j.vals = d_evals[T][0].p; j.pts = d_E[T].p; j.n_ptr = &st->En[T];
+        j.block_heads = d_eheads[T].p; j.out = arena[T]; j.out_base_ptr = &st->outOff[T]; j.out_count = &st->outCount[T];
+        j.seg_count = st->segCount[T]; j.seg_shift = 24; j.nblk_cap = (ecap + VX_TILE - 1) / VX_TILE + 1;
+      }
+      r = voxel_reduce_sorted(vp, ecap, stream);
+      if (r != LOAM_OK) return r;
+      LMCommitArgs CA;
+      CA.st = st;
+      for (int T = 0; T < 2; T++) { CA.cubes[T] = d_cubes[T].p; CA.touch_cnt[T] = d_touch[T].p; CA.cube_rank[T] = d_rank[T].p; }
+      LAUNCH("lm_refilter_commit", lm_refilter_commit, 1, 1024, 0, stream, CA);
+    }
+    mapFrameCount++;  // :1038-1040
+    last_surround = false;
+    if (mapFrameCount >= mapFrameNum) { mapFrameCount = 0; last_surround = true; }
+    // K8
+    LAUNCH("lm_registered", lm_registered, 2 * nb, 256, 0, stream, st, lo.d_full_end.p, &lo.d_state.p->n_full_end, d_registered.p);
+    CUDA_OK(cudaGetLastError());
+    return LOAM_OK;
+  }
+
+  int compact() {
+    LMCompactArgs CA;
+    CA.st = d_state.p;
+    for (int T = 0; T < 2; T++) {
+      CA.cubes[T] = d_cubes[T].p; CA.src[T] = d_arena[T][cur_arena].p; CA.dst[T] = d_arena[T][cur_arena ^ 1].p; CA.new_off[T] = d_newoff[T].p;
+    }
+    LAUNCH("lm_compact_plan", lm_compact_plan, 2, 1024, 0, stream, CA);
+    LAUNCH("lm_compact_copy", lm_compact_copy, dim3(296, 2), 256, 0, stream, CA);
+    CUDA_OK(cudaGetLastError());
+    cur_arena ^= 1;
+    return LOAM_OK;
+  }
+
+  int sync_state() {
+    CUDA_OK(cudaMemcpyAsync(h_state.p, d_state.p, sizeof(LMState), cudaMemcpyDeviceToHost, stream));
+    CUDA_OK(cudaStreamSynchronize(stream));
+    last_state = *h_state.p;
+    if (last_state.error) { set_error("laserMapping capacity exceeded (flags %d)", last_state.error); return LOAM_ERR_CAPACITY; }
+    if (last_state.bump[0] > arena_cap / 2 || last_state.bump[1] > arena_cap / 2) {
+      int r = compact();
+      if (r != LOAM_OK) return r;
+    }
+    return LOAM_OK;
+  }
+};
+
+// transformMaintenance.cpp, host only (north_star: "transformMaintenance stays on the host")
+struct TMHost {
+  float transformSum[6], transformIncre[6], transformMapped[6], transformBefMapped[6], transformAftMapped[6];  // :49-53
+  TMHost() {
+    for (int i = 0; i < 6; i++) transformSum[i] = transformIncre[i] = transformMapped[i] = transformBefMapped[i] = transformAftMapped[i] = 0;
+  }
+  // odomAftMappedHandler :182-203: pose arrives as a quaternion (decoded here), bef as twist floats
+  void on_mapping(const float aft[6], const float bef[6]) {
+    float a[6];
+    pm::odometry_msg_roundtrip(aft, a);
+    for (int i = 0; i < 6; i++) { transformAftMapped[i] = a[i]; transformBefMapped[i] = bef[i]; }
+  }
+  // laserOdometryHandler :147-180
+  void on_odometry(const float sum[6], float integrated[6]) {
+    pm::odometry_msg_roundtrip(sum, transformSum);
+    pm::transformAssociateToMap(transformSum, transformBefMapped, transformAftMapped, transformIncre, transformMapped);
+    for (int i = 0; i < 6; i++) integrated[i] = transformMapped[i];
+  }
+};
+
+}  // namespace loamgpu
