@@ -1,0 +1,366 @@
+#!/usr/bin/env python
+"""bench.py -- sweeps/s of the LOAM per-sweep pipeline (scanRegistration -> laserOdometry ->
+laserMapping -> transformMaintenance) on synthetic HDL-64E sweeps (BASELINE.json configs[1]).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's sm_100a path
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU code (oracle/_ref)
+
+One step = one sweep through the whole pipeline.  `value` = sweeps/s with the K sweeps already
+resident in HBM (no host synchronisation inside the timed region); `e2e` = the same through the
+public C-ABI call loam_pipeline_push() with HOST buffers (H2D of the sweep and D2H of the poses
+inside every step).  N > 1: one independent sequence per GPU (weak scaling, BASELINE config 5
+style); the only communication is one NCCL gather of the poses after the timed region.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import importlib
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+PKG = "loam_velodyne-1_b200"
+METRIC = "sweeps/s (odometry+mapping) on synthetic VLP-16 & HDL-64; p50 ms/sweep"
+PRESET = 2  # HDL-64E urban canyon, 64 rings x 2000 az
+WORKLOAD = "synthetic HDL-64E urban canyon, 64 rings x 2000 az (~128k pts/sweep), single stream per GPU"
+
+
+# ---------------------------------------------------------------------------------------------
+# multi-GPU plumbing (host logic; covered by tests/test_host_side.py with gloo)
+# ---------------------------------------------------------------------------------------------
+def shard_sequences(n_seq, rank, world):
+    """sequence s runs on rank s % world"""
+    return [s for s in range(n_seq) if s % world == rank]
+
+
+def gather_poses(local, n_seq, n_sweeps, rank, world, device="cuda"):
+    """one collective: every rank contributes a dense [n_seq, n_sweeps, 6] table that is zero outside
+    its own sequences; the sum over ranks is the full table (NCCL all_reduce over NVLink, gloo on CPU)"""
+    import torch
+    import torch.distributed as dist
+    t = torch.zeros((n_seq, n_sweeps, 6), dtype=torch.float32)
+    for s, p in local.items():
+        t[s] = torch.from_numpy(np.asarray(p, np.float32))
+    if world > 1:
+        t = t.to(device)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        t = t.cpu()
+    return t.numpy()
+
+
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows = []
+        self.proc = None
+        self.idx = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def algorithmic_bytes(kernel, s):
+    """ALGORITHMIC bytes PER LAUNCH of the kernels that can dominate a step (DESIGN.md
+    §5 states the per-unit figures).  s = mean per-sweep counters of the run (map / stack counters
+    are means over mapped sweeps, the launches that use them happen once per mapped sweep)."""
+    N, Ns, Nf, Nls, Nlf = s["n_full"], s["n_sharp"], s["n_flat"], s["n_less_sharp"], s["n_less_flat"]
+    Q = s["n_stack_corner"] + s["n_stack_surf"]
+    M = s["n_map_corner"] + s["n_map_surf"]
+    it_lo, it_lm = max(s["lo_iters"], 1.0), max(s["lm_iters"], 1.0)
+    if kernel == "lm_optimize":   # per iteration: each query reads itself (16) + its 5 neighbours (5*16)
+        return it_lm * Q * 96.0
+    if kernel == "lo_optimize":   # per iteration: feature (16) + tripod (2..3 x 16) + every accumulated row (32)
+        rows = (it_lo + 1) / 2.0 * (Ns + Nf)
+        return it_lo * ((Ns + Nf) * 16.0 + (2 * Ns + 3 * Nf) * 16.0 + rows * 32.0)
+    if kernel in ("rs_scatter", "rs_hist"):  # one radix pass over (key,val) pairs of both jobs: read 8 (+ write 8)
+        n = (Nls + Nlf + M + Q) / 2.0   # two sorts per mapped sweep (incoming sweep, map refilter), averaged
+        return n * (16.0 if kernel == "rs_scatter" else 4.0)
+    if kernel == "sr_curv_reject":
+        return N * 22.0 + N * 18.0
+    if kernel == "sr_lessflat":
+        return N * 17.0 + Nlf * 16.0
+    if kernel == "sr_sort_sectors":
+        return N * 8.0
+    if kernel in ("sr_ring_ori", "sr_scatter"):
+        return N * 16.0 if kernel == "sr_ring_ori" else N * 32.0
+    if kernel == "lo_transform_to_end":
+        return (Nls + Nlf + N / 2.0) * 32.0
+    if kernel == "lm_refilter_fill":
+        return (M + Q) * (16.0 + 16.0 + 8.0)
+    if kernel == "lm_gather_map":
+        return M * 32.0
+    if kernel in ("grid_count", "grid_scatter", "grid_bbox"):
+        return (Nls + Nlf + M) / 2.0 * 24.0
+    return None
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def gen_sweeps(seed, count):
+    synth = importlib.import_module(PKG + ".synth")
+    S = synth.Synth(PRESET, seed=seed)
+    out = []
+    for k in range(count):
+        xyz, st = S.sweep(k)
+        out.append((xyz, st))
+    return out
+
+
+def first_last(xyz):
+    fin = np.isfinite(xyz).all(axis=1)
+    idx = np.nonzero(fin)[0]
+    return np.concatenate([xyz[idx[0]], xyz[idx[-1]]]).astype(np.float32), int(idx[0])
+
+
+def cpu_baseline(sweeps, budget_s=20.0, max_sweeps=80):
+    """the reference's CPU pipeline on the host cores, bounded sample of the same workload"""
+    from oracle import checker
+    kind = "reference" if checker.available("reference") else "port"
+    C = checker.Checker(checker.make_params(PRESET), kind)
+    t0 = time.perf_counter()
+    done = 0
+    lat = []
+    for xyz, st in sweeps[:max_sweeps]:
+        t1 = time.perf_counter()
+        C.push(xyz, st)
+        lat.append(time.perf_counter() - t1)
+        done += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    wall = time.perf_counter() - t0
+    busy = C.busy_seconds()
+    C.close()
+    return {"value": done / wall, "unit": "sweeps/s", "cores": 1, "kind": kind,
+            "sample": f"first {done} sweeps of the same HDL-64E sequence, sr->lo->lm->tm sequentially on one host thread",
+            "p50_ms_per_sweep": 1e3 * statistics.median(lat),
+            "node_busy_s": {"sr": busy[0], "lo": busy[1], "lm": busy[2], "tm": busy[3]},
+            "pipelined_3proc_estimate_sweeps_per_s": done / max(busy[0], busy[1], busy[2], 1e-9),
+            "host": {"nproc": os.cpu_count()}}
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return 0
+    n = min(args.steps + args.warmup, 80)
+    sweeps = gen_sweeps(2345, n)
+    cb = cpu_baseline(sweeps, budget_s=120.0, max_sweeps=n)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "sweeps/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / cb["value"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "note": "reference CPU nodes (oracle/_ref when built, else the oracle port), in-process, ROS stripped"},
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": "sweeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-profile", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the sm_100a library has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    pkg = importlib.import_module(PKG)
+    W, K = max(args.warmup, 3), args.steps
+    total = W + K
+    sweeps = gen_sweeps(2345 + rank, total)          # one independent sequence per rank
+    npts = [x.shape[0] for x, _ in sweeps]
+
+    # ---------------- value: inputs resident in HBM, no host sync inside the timed region ------
+    dev = torch.device("cuda", local_rank)
+    resident = [torch.from_numpy(x).to(dev) for x, _ in sweeps]
+    aux = [first_last(x) for x, _ in sweeps]
+    P = pkg.make_params(PRESET, system_delay=0)
+    G = pkg.Pipeline(P, device=local_rank)
+    for k in range(W):
+        G.push_device(resident[k].data_ptr(), npts[k], aux[k][0], aux[k][1], sweeps[k][1])
+    G.collect()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = pkg.kernel_launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stream = torch.cuda.ExternalStream(G.stream(), device=dev)
+    t_wall0 = time.perf_counter()
+    ev0.record(stream)
+    for k in range(W, total):
+        G.push_device(resident[k].data_ptr(), npts[k], aux[k][0], aux[k][1], sweeps[k][1])
+    ev1.record(stream)
+    results = G.collect()
+    torch.cuda.synchronize()
+    t_wall = time.perf_counter() - t_wall0
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop()
+    launches = pkg.kernel_launch_count() - launches0
+    ms = ev0.elapsed_time(ev1)
+    ms_t = torch.tensor([ms, t_wall * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
+    ms_max = float(ms_t[0].item())
+    value = world * K / (ms_max * 1e-3)
+    stats = {}
+    for key in ("n_full", "n_sharp", "n_less_sharp", "n_flat", "n_less_flat", "lo_iters", "lm_iters", "n_map_corner", "n_map_surf", "n_stack_corner", "n_stack_surf"):
+        vals = [getattr(r, key) for r in results if r.sr_status == 0 and (not key.startswith(("lm_", "n_map", "n_stack")) or r.lm_status == 0)]
+        stats[key] = float(np.mean(vals)) if vals else 0.0
+    poses_local = {rank: np.array([r.transform_mapped[:] for r in results], np.float32)}
+    del G
+
+    # ---------------- e2e: public C-ABI call, host buffers, H2D + D2H inside every step ----------
+    G2 = pkg.Pipeline(P, device=local_rank)
+    pinned = [x for x, _ in sweeps]
+    for k in range(W):
+        G2.push(pinned[k], sweeps[k][1])
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    lat = []
+    t0 = time.perf_counter()
+    for k in range(W, total):
+        t1 = time.perf_counter()
+        r = G2.push(pinned[k], sweeps[k][1])
+        lat.append(time.perf_counter() - t1)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.barrier()
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_value = world * K / float(e2e_t.item())
+    d2h = ctypes_sizeof_record(pkg)
+    e2e = {"value": e2e_value, "unit": "sweeps/s", "h2d_bytes_per_step": int(np.mean(npts[W:]) * 12), "d2h_bytes_per_step": d2h,
+           "p50_ms_per_sweep": 1e3 * statistics.median(lat), "p99_ms_per_sweep": 1e3 * float(np.percentile(lat, 99)),
+           "api": "loam_pipeline_push (synchronous, pageable host buffer staged through pinned memory)"}
+
+    # ---------------- per-kernel device time (separate pass, CUDA events around every launch) ----
+    roofline = None
+    kernels = None
+    if not args.no_profile:
+        pkg.profile_enable(True)
+        for k in range(min(total, 60)):
+            G2.push(pinned[k % total], sweeps[k % total][1] + 1000.0)  # continue the sequence state; timing only
+        prof = pkg.profile_report()
+        pkg.profile_enable(False)
+        nsw = min(total, 60)
+        tot_ms = sum(v[1] for v in prof.values())
+        kernels = sorted(((name, v[0], v[1]) for name, v in prof.items()), key=lambda t: -t[2])
+        top = kernels[0]
+        peak, peak_src = measured_peak()
+        for name, calls, kms in kernels:   # dominant kernel for which an algorithmic byte count is defined
+            ab = algorithmic_bytes(name, stats)
+            if ab is not None:
+                per_launch = ab  # algorithmic_bytes() is defined per launch
+                avg_s = kms * 1e-3 / calls
+                achieved = per_launch / avg_s / 1e9
+                roofline = {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                            "traffic": None, "peak_source": peak_src, "avg_launch_us": avg_s * 1e6, "launches_profiled": calls,
+                            "share_of_device_time": kms / tot_ms,
+                            "note": "working set of one HDL-64 sweep (~10 MB) is L2-resident and the LM kernels are latency-bound; see DESIGN.md §5"}
+                break
+        kernels = [{"kernel": n, "calls": c, "ms": round(m, 4), "share": round(m / tot_ms, 4)} for n, c, m in kernels[:12]]
+    del G2
+
+    # ---------------- the one collective of the multi-sequence configuration ---------------------
+    table = gather_poses(poses_local, world, K, rank, world, device=dev)
+
+    cb = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cb = cpu_baseline(sweeps, budget_s=20.0, max_sweeps=80)
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": "sweeps/s", "n_gpus": world, "steps": K, "warmup": W,
+                "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "sequences": world, "sweeps_per_sequence": K, "points_per_sweep": int(np.mean(npts)),
+                           "parallelism": f"seq{world}", "l2": "inputs larger than L2: %d distinct sweeps (%.0f MB) resident in HBM, each read once" % (total, sum(npts) * 12 / 1e6),
+                           "timed_region": "K x (scanRegistration + laserOdometry + laserMapping every 2nd sweep + pose record), CUDA events on the pipeline stream, no host sync inside"},
+                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+                "wall_ms_incl_launch": float(ms_t[1].item()),
+                "mean_counts": stats, "roofline": roofline, "top_kernels": kernels, "cpu_baseline": cb,
+                "poses_gathered": [int(table.shape[0]), int(table.shape[1])]}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def ctypes_sizeof_record(pkg):
+    # PipeRecord (csrc/loam_pipeline.cuh): SRCounts 32 + 12*4 + 12*4 + 12 + 12*4 + 16 + 24
+    return 32 + 48 + 48 + 12 + 48 + 16 + 24
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -157,9 +157,27 @@ int loam_pipeline_imu(loam_pipeline* h, double stamp, const double quat[4], cons
 /* synchronous: uploads the sweep, runs the nodes, downloads the poses into *res */
 int loam_pipeline_push(loam_pipeline* h, const float* xyz, int n, int stride_bytes, double stamp,
                        loam_sweep_result* res);
+/* asynchronous form: push_async only enqueues (the host buffer is staged before it returns),
+ * collect() waits for everything enqueued so far and returns the per-sweep results in push order.
+ * push_device takes a sweep that is already resident in device memory as packed xyz floats;
+ * first_last_xyz = host copies of its first and last finite point (scanRegistration.cpp:230-232
+ * reads them on the host), first_index = index of the first finite point. */
+int loam_pipeline_push_async(loam_pipeline* h, const float* xyz, int n, int stride_bytes, double stamp);
+int loam_pipeline_push_device(loam_pipeline* h, const float* d_xyz, int n, const float first_last_xyz[6],
+                              int first_index, double stamp);
+int loam_pipeline_collect(loam_pipeline* h, loam_sweep_result* out, int cap, int* n);
+void* loam_pipeline_stream(loam_pipeline* h); /* the cudaStream_t all work of this handle runs on */
 loam_sr* loam_pipeline_sr(loam_pipeline* h);
 loam_lo* loam_pipeline_lo(loam_pipeline* h);
 loam_lm* loam_pipeline_lm(loam_pipeline* h);
+
+/* ---- test hooks: device versions of the building blocks, host pointers in and out ---- */
+/* fn: 0 sin 1 cos 2 atan 3 atan2(y,x) 4 asin 5 sqrt 6 x/y 7 x*y+x (unfused) -- loam/detmath.h on the device */
+int loam_debug_math(int fn, const float* x, const float* y, float* out, int n);
+/* op 0: QR solve (m x n, one rhs) 1: Jacobi eigen (values then row vectors) 2: LU inverse; `batch` systems */
+int loam_debug_linalg(int op, const float* A, const float* b, float* out, int m, int n, int batch);
+int loam_debug_sort_pairs(unsigned int* keys, unsigned int* vals, int n);
+int loam_debug_voxel_filter(const float* xyzi, int n, float leaf, float* out, int cap_out, int* n_out);
 
 /* number of kernel launches issued by this library on the calling process so far */
 long long loam_kernel_launch_count(void);

@@ -103,6 +103,11 @@ def lib():
     L.loam_tm_on_odometry.argtypes = [vp, vp, vp]
     L.loam_pipeline_imu.argtypes = [vp, cd, vp, vp]
     L.loam_pipeline_push.argtypes = [vp, vp, ci, ci, cd, ctypes.POINTER(SweepResult)]
+    L.loam_pipeline_push_async.argtypes = [vp, vp, ci, ci, cd]
+    L.loam_pipeline_push_device.argtypes = [vp, vp, ci, vp, ci, cd]
+    L.loam_pipeline_collect.argtypes = [vp, vp, ci, ctypes.POINTER(ci)]
+    L.loam_pipeline_stream.restype = vp
+    L.loam_pipeline_stream.argtypes = [vp]
     for f in ("sr", "lo", "lm"):
         fn = getattr(L, f"loam_pipeline_{f}")
         fn.restype = vp
@@ -306,6 +311,25 @@ class Pipeline(_Node):
         res = SweepResult()
         _check(self.L.loam_pipeline_push(self.h, xyz.ctypes.data, xyz.shape[0], xyz.strides[0], float(stamp), ctypes.byref(res)))
         return res
+
+
+    def push_async(self, xyz, stamp):
+        """xyz must stay alive only until this returns (it is staged into pinned memory)"""
+        xyz = np.ascontiguousarray(xyz, dtype=np.float32)
+        return _check(self.L.loam_pipeline_push_async(self.h, xyz.ctypes.data, xyz.shape[0], xyz.strides[0], float(stamp)))
+
+    def push_device(self, d_ptr, n, first_last_xyz, first_index, stamp):
+        fl = np.ascontiguousarray(first_last_xyz, dtype=np.float32)
+        return _check(self.L.loam_pipeline_push_device(self.h, ctypes.c_void_p(d_ptr), n, fl.ctypes.data, first_index, float(stamp)))
+
+    def collect(self, cap=1024):
+        arr = (SweepResult * cap)()
+        n = ctypes.c_int()
+        _check(self.L.loam_pipeline_collect(self.h, arr, cap, ctypes.byref(n)))
+        return [arr[i] for i in range(min(n.value, cap))]
+
+    def stream(self):
+        return self.L.loam_pipeline_stream(self.h)
 
 
 def _borrow(cls, h, cap, L):

@@ -86,6 +86,38 @@ struct PinnedBuf {
   ~PinnedBuf() { free(); }
 };
 
+// small ring of pinned staging slots for host->device parameter uploads that may still be in
+// flight when the host prepares the next one (asynchronous pipeline mode)
+template <typename T, int N>
+struct PinnedRing {
+  T* p[N];
+  cudaEvent_t ev[N];
+  int next = 0;
+  bool ok = false;
+  int alloc() {
+    for (int i = 0; i < N; i++) {
+      if (cudaMallocHost((void**)&p[i], sizeof(T)) != cudaSuccess) { set_error("cudaMallocHost failed"); return LOAM_ERR_CUDA; }
+      if (cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming) != cudaSuccess) return LOAM_ERR_CUDA;
+    }
+    ok = true;
+    return LOAM_OK;
+  }
+  // copies `v` to the device through the next free slot
+  int upload(T* dst, const T& v, cudaStream_t s) {
+    int i = next;
+    next = (next + 1) % N;
+    if (cudaEventSynchronize(ev[i]) != cudaSuccess) return LOAM_ERR_CUDA;
+    *p[i] = v;
+    if (cudaMemcpyAsync(dst, p[i], sizeof(T), cudaMemcpyHostToDevice, s) != cudaSuccess) return LOAM_ERR_CUDA;
+    if (cudaEventRecord(ev[i], s) != cudaSuccess) return LOAM_ERR_CUDA;
+    return LOAM_OK;
+  }
+  ~PinnedRing() {
+    if (!ok) return;
+    for (int i = 0; i < N; i++) { cudaFreeHost(p[i]); cudaEventDestroy(ev[i]); }
+  }
+};
+
 // order-preserving float <-> uint mapping for atomicMin/Max on floats
 __device__ __forceinline__ unsigned int float_flip(float f) {
   unsigned int u = __float_as_uint(f);

@@ -7,6 +7,7 @@
 #include "loam_lo.cuh"
 #include "loam_lm.cuh"
 #include "loam_pipeline.cuh"
+#include "debug_hooks.cuh"
 
 namespace loamgpu {
 

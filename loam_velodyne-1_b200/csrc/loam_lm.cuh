@@ -14,6 +14,7 @@ struct LMHandle {
   cudaEvent_t ev_dep = nullptr;
   int cap = 0, ecap = 0, arena_cap = 0, coop_blocks = 0;
   int cur_arena = 0;
+  int sweeps_since_compact = 0;
   static const int stackFrameNum = 1, mapFrameNum = 5;  // :51-52
   int frameCount = stackFrameNum - 1, mapFrameCount = mapFrameNum - 1;  // :404-405
   DevBuf<LMState> d_state;
@@ -28,7 +29,7 @@ struct LMHandle {
   DevBuf<double> d_partials;
   GridStorage g_map[2];
   PinnedBuf<LMState> h_state;
-  PinnedBuf<LMImu> h_imu;
+  PinnedRing<LMImu, 4> h_imu;
   LMImu imu;
   bool has_imu = false;
   LMState last_state;
@@ -77,7 +78,7 @@ struct LMHandle {
       }
     }
     r |= d_registered.alloc(cap); r |= d_partials.alloc_zero((size_t)2 * coop_blocks * LO_NRED, stream);
-    r |= h_state.alloc(1); r |= h_imu.alloc(1);
+    r |= h_state.alloc(1); r |= h_imu.alloc();
     if (r != LOAM_OK) return LOAM_ERR_CUDA;
     LMState init;
     memset(&init, 0, sizeof(init));
@@ -186,8 +187,7 @@ struct LMHandle {
     }
     // K6
     if (has_imu) {
-      *h_imu.p = imu;
-      CUDA_OK(cudaMemcpyAsync(d_imu.p, h_imu.p, sizeof(LMImu), cudaMemcpyHostToDevice, stream));
+      if (h_imu.upload(d_imu.p, imu, stream) != LOAM_OK) { set_error("imu upload failed"); return LOAM_ERR_CUDA; }
     }
     {
       LMOptArgs OA;
@@ -234,6 +234,10 @@ struct LMHandle {
       for (int T = 0; T < 2; T++) { CA.cubes[T] = d_cubes[T].p; CA.touch_cnt[T] = d_touch[T].p; CA.cube_rank[T] = d_rank[T].p; }
       LAUNCH("lm_refilter_commit", lm_refilter_commit, 1, 1024, 0, stream, CA);
     }
+    if (++sweeps_since_compact >= 8) {  // bounded garbage in the log-structured arena
+      int cr = compact();
+      if (cr != LOAM_OK) return cr;
+    }
     mapFrameCount++;  // :1038-1040
     last_surround = false;
     if (mapFrameCount >= mapFrameNum) { mapFrameCount = 0; last_surround = true; }
@@ -253,6 +257,7 @@ struct LMHandle {
     LAUNCH("lm_compact_copy", lm_compact_copy, dim3(296, 2), 256, 0, stream, CA);
     CUDA_OK(cudaGetLastError());
     cur_arena ^= 1;
+    sweeps_since_compact = 0;
     return LOAM_OK;
   }
 

@@ -1,16 +1,51 @@
 // loam_pipeline.cuh -- the four nodes wired as the reference's topic graph on
 // one device and one CUDA stream: sr -> lo -> tm.onOdometry -> (lm -> tm.onMapping).
+//
+// All per-sweep state lives in device memory and every kernel takes its sizes from device
+// counters, so a sweep is a fixed launch sequence with NO host round trip: push_async() only
+// enqueues, a one-thread kernel snapshots the poses/counters of the sweep into a device ring, and
+// collect() reads the ring back (one small D2H) and runs transformMaintenance on the host.
 #pragma once
+#include <deque>
 #include "loam_lm.cuh"
 
 namespace loamgpu {
 
+struct PipeRecord {
+  SRCounts cnt;
+  float imu_trans[12];
+  float transform[6], transformSum[6];
+  int lo_iters, lo_rows, lo_deg;
+  float aft[6], bef[6];
+  int lm_iters, lm_rows, lm_deg, lm_error;
+  int mapN[2], stackN[2], bump[2];
+};
+
+__global__ void pipe_record(PipeRecord* out, const SRCounts* cnt, const ImuState* imu, const LOState* lo, const LMState* lm, int with_lm) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  PipeRecord r;
+  r.cnt = *cnt;
+  lo_load_imu(imu, r.imu_trans);
+  for (int i = 0; i < 6; i++) { r.transform[i] = lo->transform[i]; r.transformSum[i] = lo->transformSum[i]; }
+  r.lo_iters = lo->iters; r.lo_rows = lo->rows; r.lo_deg = lo->isDegenerate;
+  for (int i = 0; i < 6; i++) { r.aft[i] = lm->transformAftMapped[i]; r.bef[i] = lm->transformBefMapped[i]; }
+  r.lm_iters = lm->iters; r.lm_rows = lm->rows; r.lm_deg = lm->isDegenerate; r.lm_error = with_lm ? lm->error : 0;
+  for (int T = 0; T < 2; T++) { r.mapN[T] = lm->mapN[T]; r.stackN[T] = lm->stackN[T]; r.bump[T] = lm->bump[T]; }
+  *out = r;
+}
+
 struct PipelineHandle {
+  static const int RING = 1024;
   SRHandle sr;
   LOHandle lo;
   LMHandle lm;
   TMHost tm;
   cudaStream_t stream = nullptr;
+  DevBuf<PipeRecord> d_ring;
+  PinnedBuf<PipeRecord> h_ring;
+  struct Pending { int slot; int sr_status, lo_status, lm_status; };
+  std::deque<Pending> pending;
+  int next_slot = 0;
   loam_sweep_result res;
 
   int init(const loam_params* p, int dev) {
@@ -22,6 +57,7 @@ struct PipelineHandle {
     if (r != LOAM_OK) return r;
     r = lm.init(p, dev, stream);
     if (r != LOAM_OK) return r;
+    if (d_ring.alloc(RING) != LOAM_OK || h_ring.alloc(RING) != LOAM_OK) return LOAM_ERR_CUDA;
     memset(&res, 0, sizeof(res));
     return LOAM_OK;
   }
@@ -33,57 +69,92 @@ struct PipelineHandle {
     return LOAM_OK;
   }
 
-  int push(const float* xyz, int n, int stride_bytes, double stamp, loam_sweep_result* out) {
-    loam_sweep_result& r = res;
-    r.sr_status = r.lo_status = r.lm_status = LOAM_NOT_READY;
-    int rc = sr.process(xyz, n, stride_bytes, stamp);
+  // enqueue one sweep.  src_device: xyz is packed device memory and aux = {first xyz, last xyz}
+  int push_async(const float* xyz, int n, int stride_bytes, double stamp, bool src_device, const float* aux, int first_idx) {
+    if ((int)pending.size() >= RING) { set_error("result ring full: call collect"); return LOAM_ERR_CAPACITY; }
+    Pending pd;
+    pd.slot = next_slot;
+    pd.sr_status = pd.lo_status = pd.lm_status = LOAM_NOT_READY;
+    int rc = src_device ? sr.process_resident(xyz, n, aux, aux + 3, first_idx, stamp) : sr.process(xyz, n, stride_bytes, stamp);
     if (rc < 0) return rc;
     if (rc == LOAM_OK) {
-      r.sr_status = LOAM_OK;
+      pd.sr_status = LOAM_OK;
       bool pub = false;
       int lrc = lo.process(sr, &pub);
       if (lrc < 0) return lrc;
-      int mrc = LOAM_NOT_READY;
+      pd.lo_status = lrc;
       if (lrc == LOAM_OK && pub) {
-        mrc = lm.process(lo, stamp);
+        int mrc = lm.process(lo, stamp);
         if (mrc < 0) return mrc;
+        pd.lm_status = mrc;
       }
-      // one synchronisation per sweep: counters + poses
-      CUDA_OK(cudaMemcpyAsync(sr.h_cnt.p, sr.d_cnt.p, sizeof(SRCounts), cudaMemcpyDeviceToHost, stream));
-      CUDA_OK(cudaMemcpyAsync(sr.h_imu_state.p, sr.imu_state_dev(), sizeof(ImuState), cudaMemcpyDeviceToHost, stream));
-      CUDA_OK(cudaMemcpyAsync(lo.h_state.p, lo.d_state.p, sizeof(LOState), cudaMemcpyDeviceToHost, stream));
-      if (mrc == LOAM_OK) CUDA_OK(cudaMemcpyAsync(lm.h_state.p, lm.d_state.p, sizeof(LMState), cudaMemcpyDeviceToHost, stream));
-      CUDA_OK(cudaStreamSynchronize(stream));
-      sr.last_counts = *sr.h_cnt.p;
-      if (sr.last_counts.error) { set_error("scanRegistration capacity exceeded (flags %d)", sr.last_counts.error); return LOAM_ERR_CAPACITY; }
-      lo.last_state = *lo.h_state.p;
-      lo.last_n_sharp = sr.last_counts.n_sharp; lo.last_n_flat = sr.last_counts.n_flat;
-      r.n_full = sr.last_counts.n_full; r.n_sharp = sr.last_counts.n_sharp; r.n_less_sharp = sr.last_counts.n_less_sharp;
-      r.n_flat = sr.last_counts.n_flat; r.n_less_flat = sr.last_counts.n_less_flat;
-      sr.imu_trans(r.imu_trans);
-      r.lo_iters = lo.last_state.iters; r.lo_rows = lo.last_state.rows; r.lo_degenerate = lo.last_state.isDegenerate;
-      for (int i = 0; i < 6; i++) { r.transform[i] = lo.last_state.transform[i]; r.transform_sum[i] = lo.last_state.transformSum[i]; }
-      if (lrc == LOAM_OK) {
-        r.lo_status = LOAM_OK;
-        tm.on_odometry(lo.last_state.transformSum, r.transform_mapped);
-        if (mrc == LOAM_OK) {
-          lm.last_state = *lm.h_state.p;
-          const LMState& m = lm.last_state;
-          if (m.error) { set_error("laserMapping capacity exceeded (flags %d)", m.error); return LOAM_ERR_CAPACITY; }
-          r.lm_status = LOAM_OK;
-          r.lm_iters = m.iters; r.lm_rows = m.rows; r.lm_degenerate = m.isDegenerate;
-          r.n_map_corner = m.mapN[0]; r.n_map_surf = m.mapN[1]; r.n_stack_corner = m.stackN[0]; r.n_stack_surf = m.stackN[1];
-          for (int i = 0; i < 6; i++) { r.transform_aft_mapped[i] = m.transformAftMapped[i]; r.transform_bef_mapped[i] = m.transformBefMapped[i]; }
-          tm.on_mapping(m.transformAftMapped, m.transformBefMapped);
-          if (m.bump[0] > lm.arena_cap / 2 || m.bump[1] > lm.arena_cap / 2) {
-            int cr = lm.compact();
-            if (cr != LOAM_OK) return cr;
+      LAUNCH("pipe_record", pipe_record, 1, 32, 0, stream, d_ring.p + pd.slot, sr.d_cnt.p, sr.imu_state_dev(), lo.d_state.p, lm.d_state.p,
+             pd.lm_status == LOAM_OK ? 1 : 0);
+      CUDA_OK(cudaMemcpyAsync(h_ring.p + pd.slot, d_ring.p + pd.slot, sizeof(PipeRecord), cudaMemcpyDeviceToHost, stream));
+    }
+    next_slot = (next_slot + 1) % RING;
+    pending.push_back(pd);
+    return rc;
+  }
+
+  // wait for everything enqueued so far; fills out[0..*n) in push order (transformMaintenance runs here)
+  int collect(loam_sweep_result* out, int cap, int* n) {
+    CUDA_OK(cudaStreamSynchronize(stream));
+    int k = 0;
+    while (!pending.empty()) {
+      Pending pd = pending.front();
+      pending.pop_front();
+      loam_sweep_result& r = res;
+      r.sr_status = pd.sr_status; r.lo_status = pd.lo_status; r.lm_status = pd.lm_status;
+      if (pd.sr_status == LOAM_OK) {
+        const PipeRecord& q = h_ring.p[pd.slot];
+        if (q.cnt.error) { set_error("scanRegistration capacity exceeded (flags %d)", q.cnt.error); return LOAM_ERR_CAPACITY; }
+        sr.last_counts = q.cnt;
+        lo.last_n_sharp = q.cnt.n_sharp; lo.last_n_flat = q.cnt.n_flat;
+        r.n_full = q.cnt.n_full; r.n_sharp = q.cnt.n_sharp; r.n_less_sharp = q.cnt.n_less_sharp;
+        r.n_flat = q.cnt.n_flat; r.n_less_flat = q.cnt.n_less_flat;
+        memcpy(r.imu_trans, q.imu_trans, sizeof(r.imu_trans));
+        r.lo_iters = q.lo_iters; r.lo_rows = q.lo_rows; r.lo_degenerate = q.lo_deg;
+        memcpy(r.transform, q.transform, sizeof(float) * 6);
+        memcpy(r.transform_sum, q.transformSum, sizeof(float) * 6);
+        memcpy(lo.last_state.transform, q.transform, sizeof(float) * 6);
+        memcpy(lo.last_state.transformSum, q.transformSum, sizeof(float) * 6);
+        lo.last_state.iters = q.lo_iters; lo.last_state.rows = q.lo_rows; lo.last_state.isDegenerate = q.lo_deg;
+        lo.last_state.n_corner_last = q.cnt.n_less_sharp; lo.last_state.n_surf_last = q.cnt.n_less_flat;
+        if (pd.lm_status == LOAM_OK) lo.last_state.n_full_end = q.cnt.n_full;
+        if (pd.lo_status == LOAM_OK) {
+          tm.on_odometry(q.transformSum, r.transform_mapped);
+          if (pd.lm_status == LOAM_OK) {
+            if (q.lm_error) { set_error("laserMapping capacity exceeded (flags %d)", q.lm_error); return LOAM_ERR_CAPACITY; }
+            r.lm_iters = q.lm_iters; r.lm_rows = q.lm_rows; r.lm_degenerate = q.lm_deg;
+            r.n_map_corner = q.mapN[0]; r.n_map_surf = q.mapN[1]; r.n_stack_corner = q.stackN[0]; r.n_stack_surf = q.stackN[1];
+            memcpy(r.transform_aft_mapped, q.aft, sizeof(float) * 6);
+            memcpy(r.transform_bef_mapped, q.bef, sizeof(float) * 6);
+            LMState& m = lm.last_state;
+            memcpy(m.transformAftMapped, q.aft, sizeof(float) * 6);
+            memcpy(m.transformBefMapped, q.bef, sizeof(float) * 6);
+            m.iters = q.lm_iters; m.rows = q.lm_rows; m.isDegenerate = q.lm_deg;
+            m.mapN[0] = q.mapN[0]; m.mapN[1] = q.mapN[1]; m.stackN[0] = q.stackN[0]; m.stackN[1] = q.stackN[1];
+            m.bump[0] = q.bump[0]; m.bump[1] = q.bump[1]; m.registeredN = q.cnt.n_full;
+            tm.on_mapping(q.aft, q.bef);
           }
         }
       }
+      if (out && k < cap) out[k] = r;
+      k++;
     }
-    if (out) *out = r;
-    return r.sr_status;
+    if (n) *n = k;
+    return LOAM_OK;
+  }
+
+  int push(const float* xyz, int n, int stride_bytes, double stamp, loam_sweep_result* out) {
+    int rc = push_async(xyz, n, stride_bytes, stamp, false, nullptr, 0);
+    if (rc < 0) return rc;
+    int got = 0;
+    int c = collect(nullptr, 0, &got);
+    if (c < 0) return c;
+    if (out) *out = res;
+    return res.sr_status;
   }
 };
 

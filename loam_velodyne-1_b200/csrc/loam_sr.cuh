@@ -19,7 +19,10 @@ struct SRHandle {
   int systemInitCount = 0;
   bool systemInited = false;
   // device buffers
-  DevBuf<float> d_raw;
+  DevBuf<float> d_raw2[2];
+  float* d_raw_cur = nullptr;
+  cudaEvent_t ev_raw[2] = {nullptr, nullptr};
+  int raw_sel = 0;
   DevBuf<short> d_ring;
   DevBuf<float> d_ori, d_reltime, d_curv;
   DevBuf<int> d_hist, d_ring_start, d_scan_start, d_scan_end, d_pos, d_sort_ind;
@@ -31,9 +34,10 @@ struct SRHandle {
   DevBuf<SRCounts> d_cnt;
   DevBuf<ImuSnapshot> d_imu;
   DevBuf<ImuState> d_imu_state;  // [2]
-  PinnedBuf<float> h_raw;
+  PinnedBuf<float> h_raw2[2];
   PinnedBuf<SRCounts> h_cnt;
-  PinnedBuf<ImuSnapshot> h_imu;
+  PinnedRing<ImuSnapshot, 4> h_imu;
+  PinnedRing<SRCounts, 4> h_cnt_init;
   PinnedBuf<ImuState> h_imu_state;
   int imu_parity = 0;
   // host IMU ring buffer
@@ -60,7 +64,7 @@ struct SRHandle {
     nblk_cap = (cap + SR_BLK - 1) / SR_BLK;
     int R = P.n_scans;
     int r = LOAM_OK;
-    r |= d_raw.alloc((size_t)cap * 3); r |= d_ring.alloc(cap); r |= d_ori.alloc(cap); r |= d_reltime.alloc(cap);
+    r |= d_raw2[0].alloc((size_t)cap * 3); r |= d_raw2[1].alloc((size_t)cap * 3); r |= d_ring.alloc(cap); r |= d_ori.alloc(cap); r |= d_reltime.alloc(cap);
     r |= d_curv.alloc_zero(cap, stream); r |= d_hist.alloc((size_t)R * nblk_cap); r |= d_ring_start.alloc(R + 1);
     r |= d_scan_start.alloc(R); r |= d_scan_end.alloc(R); r |= d_pos.alloc(cap); r |= d_sort_ind.alloc_zero(cap, stream);
     r |= d_picked.alloc_zero(cap + 16, stream); r |= d_gap.alloc_zero(cap + 16, stream); r |= d_steps.alloc(cap);
@@ -73,8 +77,9 @@ struct SRHandle {
     r |= d_full.alloc(cap); r |= d_sharp.alloc((size_t)R * SR_SHARP_PER_RING); r |= d_less_sharp.alloc((size_t)R * SR_LESS_SHARP_PER_RING);
     r |= d_flat.alloc((size_t)R * SR_FLAT_PER_RING); r |= d_less_flat.alloc(cap); r |= d_lessflat_tmp.alloc((size_t)R * SR_RING_CAP);
     r |= d_cnt.alloc_zero(1, stream); r |= d_imu.alloc(1); r |= d_imu_state.alloc_zero(2, stream);
-    r |= h_raw.alloc((size_t)cap * 3); r |= h_cnt.alloc(1); r |= h_imu.alloc(1); r |= h_imu_state.alloc(1);
+    r |= h_raw2[0].alloc((size_t)cap * 3); r |= h_raw2[1].alloc((size_t)cap * 3); r |= h_cnt.alloc(1); r |= h_imu.alloc(); r |= h_cnt_init.alloc(); r |= h_imu_state.alloc(1);
     if (r != LOAM_OK) return LOAM_ERR_CUDA;
+    for (int b = 0; b < 2; b++) CUDA_OK(cudaEventCreateWithFlags(&ev_raw[b], cudaEventDisableTiming));
     memset(&imu, 0, sizeof(imu));
     memset(imuAcc, 0, sizeof(imuAcc));
     imu.pointer_last = -1;
@@ -85,7 +90,10 @@ struct SRHandle {
     CUDA_OK(cudaStreamSynchronize(stream));
     return LOAM_OK;
   }
-  ~SRHandle() { if (own_stream && stream) cudaStreamDestroy(stream); }
+  ~SRHandle() {
+    for (int b = 0; b < 2; b++) if (ev_raw[b]) cudaEventDestroy(ev_raw[b]);
+    if (own_stream && stream) cudaStreamDestroy(stream);
+  }
 
   // imuHandler :638-660 + AccumulateIMUShift :173-209 (host, sequential)
   int on_imu(double stamp, const double quat[4], const float acc[3]) {
@@ -139,32 +147,63 @@ struct SRHandle {
     if (n <= 0 || !xyz || stride_bytes < 12 || (stride_bytes & 3)) { set_error("bad sweep"); return LOAM_ERR_ARG; }
     if (n > cap) { set_error("sweep of %d points exceeds max_points=%d", n, cap); return LOAM_ERR_CAPACITY; }
     CUDA_OK(cudaSetDevice(device));
-    // stage through pinned memory (packed xyz); first/last finite points give startOri/endOri
-    CUDA_OK(cudaStreamSynchronize(stream));  // previous sweep may still read h_raw / d_raw
+    // stage through one of two pinned buffers (the other may still be in flight)
+    const int b = raw_sel;
+    raw_sel ^= 1;
+    CUDA_OK(cudaEventSynchronize(ev_raw[b]));
+    float* hr = h_raw2[b].p;
     int sf = stride_bytes / 4;
+    if (sf == 3) memcpy(hr, xyz, sizeof(float) * 3 * (size_t)n);
+    else
+      for (int i = 0; i < n; i++) {
+        const float* p = xyz + (size_t)i * sf;
+        hr[3 * i] = p[0]; hr[3 * i + 1] = p[1]; hr[3 * i + 2] = p[2];
+      }
     int first = -1, lastf = -1;
     for (int i = 0; i < n; i++) {
-      const float* p = xyz + (size_t)i * sf;
-      h_raw.p[3 * i] = p[0]; h_raw.p[3 * i + 1] = p[1]; h_raw.p[3 * i + 2] = p[2];
-    }
-    for (int i = 0; i < n; i++) {
-      const float* p = h_raw.p + 3 * i;
+      const float* p = hr + 3 * i;
       if (isfinite(p[0]) && isfinite(p[1]) && isfinite(p[2])) { first = i; break; }
     }
     for (int i = n - 1; i >= 0; i--) {
-      const float* p = h_raw.p + 3 * i;
+      const float* p = hr + 3 * i;
       if (isfinite(p[0]) && isfinite(p[1]) && isfinite(p[2])) { lastf = i; break; }
     }
     if (first < 0) return LOAM_NOT_READY;
-    // :230-238
-    float startOri = -dm::atan2(h_raw.p[3 * first + 1], h_raw.p[3 * first]);
-    float endOri = -dm::atan2(h_raw.p[3 * lastf + 1], h_raw.p[3 * lastf]) + 2 * M_PI;
+    float startOri, endOri;
+    sweep_orientation(hr + 3 * first, hr + 3 * lastf, startOri, endOri);
+    d_raw_cur = d_raw2[b].p;
+    CUDA_OK(cudaMemcpyAsync(d_raw_cur, hr, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, stream));
+    int rc = process_device(n, first, startOri, endOri, stamp);
+    CUDA_OK(cudaEventRecord(ev_raw[b], stream));
+    return rc;
+  }
+
+  // :230-238
+  static void sweep_orientation(const float* p0, const float* pl, float& startOri, float& endOri) {
+    startOri = -dm::atan2(p0[1], p0[0]);
+    endOri = -dm::atan2(pl[1], pl[0]) + 2 * M_PI;
     if (endOri - startOri > 3 * M_PI) {
       endOri -= 2 * M_PI;
     } else if (endOri - startOri < M_PI) {
       endOri += 2 * M_PI;
     }
-    CUDA_OK(cudaMemcpyAsync(d_raw.p, h_raw.p, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, stream));
+  }
+
+  // same, for a sweep that is already resident in device memory (packed xyz).  first_xyz/last_xyz:
+  // host copies of the first / last finite point, first = index of the first finite point.
+  int process_resident(const float* d_xyz, int n, const float* first_xyz, const float* last_xyz, int first, double stamp) {
+    processed = false;
+    if (!systemInited) {
+      systemInitCount++;
+      if (systemInitCount >= P.system_delay) systemInited = true;
+      return LOAM_NOT_READY;
+    }
+    if (n <= 0 || !d_xyz) { set_error("bad sweep"); return LOAM_ERR_ARG; }
+    if (n > cap) { set_error("sweep of %d points exceeds max_points=%d", n, cap); return LOAM_ERR_CAPACITY; }
+    CUDA_OK(cudaSetDevice(device));
+    float startOri, endOri;
+    sweep_orientation(first_xyz, last_xyz, startOri, endOri);
+    d_raw_cur = const_cast<float*>(d_xyz);
     return process_device(n, first, startOri, endOri, stamp);
   }
 
@@ -175,15 +214,13 @@ struct SRHandle {
     memset(&init, 0, sizeof(init));
     init.h_min = INT_MAX;
     init.last_valid = -1;
-    *h_cnt.p = init;
-    CUDA_OK(cudaMemcpyAsync(d_cnt.p, h_cnt.p, sizeof(SRCounts), cudaMemcpyHostToDevice, stream));
-    LAUNCH("sr_ring_ori", sr_ring_ori, nblk, SR_BLK, 0, stream, d_raw.p, n, 3, Pd, startOri, d_ring.p, d_ori.p, d_hist.p, nblk, d_cnt.p);
+    if (h_cnt_init.upload(d_cnt.p, init, stream) != LOAM_OK) { set_error("counter upload failed"); return LOAM_ERR_CUDA; }
+    LAUNCH("sr_ring_ori", sr_ring_ori, nblk, SR_BLK, 0, stream, d_raw_cur, n, 3, Pd, startOri, d_ring.p, d_ori.p, d_hist.p, nblk, d_cnt.p);
     LAUNCH("sr_ring_scan", sr_ring_scan, 1, 1024, 0, stream, d_hist.p, nblk, R, d_ring_start.p, d_scan_start.p, d_scan_end.p, d_cnt.p, cap);
-    LAUNCH("sr_scatter", sr_scatter, nblk, SR_BLK, 0, stream, d_raw.p, n, 3, Pd, startOri, endOri, d_ring.p, d_ori.p, d_hist.p, nblk,
+    LAUNCH("sr_scatter", sr_scatter, nblk, SR_BLK, 0, stream, d_raw_cur, n, 3, Pd, startOri, endOri, d_ring.p, d_ori.p, d_hist.p, nblk,
            d_cnt.p, d_full.p, d_pos.p, d_reltime.p);
     if (has_imu && imu.pointer_last >= 0) {  // :286
-      *h_imu.p = imu;
-      CUDA_OK(cudaMemcpyAsync(d_imu.p, h_imu.p, sizeof(ImuSnapshot), cudaMemcpyHostToDevice, stream));
+      if (h_imu.upload(d_imu.p, imu, stream) != LOAM_OK) { set_error("imu upload failed"); return LOAM_ERR_CUDA; }
       ImuState* st_in = d_imu_state.p + imu_parity;
       ImuState* st_out = d_imu_state.p + (imu_parity ^ 1);
       CUDA_OK(cudaMemcpyAsync(st_out, st_in, sizeof(ImuState), cudaMemcpyDeviceToDevice, stream));

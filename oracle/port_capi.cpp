@@ -169,3 +169,71 @@ void chk_lo_set_state(void* hv, const float transform[6], const float transformS
 }
 
 }  // extern "C"
+
+// ---- building blocks exposed for unit tests (oracle/defs/*) ----
+extern "C" {
+// fn: 0 sin 1 cos 2 atan 3 atan2(y,x) 4 asin 5 sqrt 6 x/y 7 x*y+x ; the library's math (detmath or glibc)
+void chk_math(int fn, const float* x, const float* y, float* out, int n) {
+  for (int i = 0; i < n; i++) {
+    float r = 0.f;
+    switch (fn) {
+      case 0: r = omath::sin(x[i]); break;
+      case 1: r = omath::cos(x[i]); break;
+      case 2: r = omath::atan(x[i]); break;
+      case 3: r = omath::atan2(y[i], x[i]); break;
+      case 4: r = omath::asin(x[i]); break;
+      case 5: r = omath::sqrt(x[i]); break;
+      case 6: r = x[i] / y[i]; break;
+      case 7: r = x[i] * y[i] + x[i]; break;
+    }
+    out[i] = r;
+  }
+}
+void chk_linalg(int op, const float* A, const float* b, float* out, int m, int n, int batch) {
+  for (int t = 0; t < batch; t++) {
+    float a[36], bb[8], w[8], v[36];
+    for (int i = 0; i < m * n; i++) a[i] = A[(size_t)t * m * n + i];
+    if (op == 0) {
+      for (int i = 0; i < m; i++) bb[i] = b[(size_t)t * m + i];
+      int ok = cvl::qr_solve(a, m, n, bb, 1);
+      for (int i = 0; i < n; i++) out[(size_t)t * n + i] = ok ? bb[i] : 0.f;
+    } else if (op == 1) {
+      cvl::jacobi_eigen(a, w, v, n);
+      float* o = out + (size_t)t * (n + n * n);
+      for (int i = 0; i < n; i++) o[i] = w[i];
+      for (int i = 0; i < n * n; i++) o[n + i] = v[i];
+    } else if (op == 2) {
+      cvl::lu_inverse(a, v, n);
+      for (int i = 0; i < n * n; i++) out[(size_t)t * n * n + i] = v[i];
+    }
+  }
+}
+void chk_gemm(const float* A, const float* B, float* C, int m, int k, int n) { cvl::gemm(A, B, C, m, k, n); }
+int chk_voxel_filter(const float* xyzi, int n, float leaf, float* out, int cap) {
+  Cloud::Ptr in(new Cloud());
+  in->points.resize(n);
+  for (int i = 0; i < n; i++) { in->points[i].x = xyzi[4 * i]; in->points[i].y = xyzi[4 * i + 1]; in->points[i].z = xyzi[4 * i + 2]; in->points[i].intensity = xyzi[4 * i + 3]; }
+  pcl::VoxelGrid<PointType> f;
+  f.setLeafSize(leaf, leaf, leaf);
+  f.setInputCloud(in);
+  Cloud o;
+  f.filter(o);
+  return copy_cloud(o, out, cap);
+}
+// k-NN of each query in the cloud through the kd-tree: idx[q*k..], d2[q*k..]
+void chk_knn(const float* xyzi, int n, const float* queries, int nq, int k, int* idx, float* d2) {
+  Cloud::Ptr in(new Cloud());
+  in->points.resize(n);
+  for (int i = 0; i < n; i++) { in->points[i].x = xyzi[4 * i]; in->points[i].y = xyzi[4 * i + 1]; in->points[i].z = xyzi[4 * i + 2]; in->points[i].intensity = xyzi[4 * i + 3]; }
+  pcl::KdTreeFLANN<PointType> tree;
+  tree.setInputCloud(in);
+  std::vector<int> ii;
+  std::vector<float> dd;
+  for (int q = 0; q < nq; q++) {
+    PointType p;
+    p.x = queries[3 * q]; p.y = queries[3 * q + 1]; p.z = queries[3 * q + 2];
+    int got = tree.nearestKSearch(p, k, ii, dd);
+    for (int j = 0; j < k; j++) { idx[q * k + j] = j < got ? ii[j] : -1; d2[q * k + j] = j < got ? dd[j] : -1.f; }
+  }
+}
+}
