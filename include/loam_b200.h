@@ -179,6 +179,11 @@ int loam_debug_linalg(int op, const float* A, const float* b, float* out, int m,
 int loam_debug_sort_pairs(unsigned int* keys, unsigned int* vals, int n);
 int loam_debug_voxel_filter(const float* xyzi, int n, float leaf, float* out, int cap_out, int* n_out);
 
+/* phase clocks (SM cycles, clock64 of CTA 0) of the persistent LM kernels: which 0 = laserOdometry,
+ * 1 = laserMapping; slot 0 = number of stamps that follow */
+int loam_debug_phase_enable(int on);
+int loam_debug_phase_clocks(int which, long long* out, int n);
+
 /* number of kernel launches issued by this library on the calling process so far */
 long long loam_kernel_launch_count(void);
 /* per-kernel device time accumulated since the last reset (CUDA events; 0 when profiling is off) */

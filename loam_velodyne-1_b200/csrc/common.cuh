@@ -129,4 +129,13 @@ __device__ __forceinline__ float float_unflip(unsigned int u) {
 
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
 
+// phase clocks of the two persistent kernels (test hook, loam_debug_phase_clocks): when enabled,
+// thread 0 of CTA 0 stamps clock64() at the phase boundaries of every LM iteration
+constexpr int PHASE_CLK_N = 512;
+__device__ int g_phase_on = 0;
+__device__ long long g_phase_clk[2][PHASE_CLK_N];
+__device__ __forceinline__ void phase_stamp(int which, int& slot) {
+  if (slot >= 0 && slot < PHASE_CLK_N) g_phase_clk[which][slot++] = clock64();
+}
+
 }  // namespace loamgpu

@@ -23,7 +23,8 @@ __global__ void dbg_math_kernel(int fn, const float* x, const float* y, float* o
   out[i] = r;
 }
 
-// op 0: qr_solve (m x n, 1 rhs) -> out[n]; 1: jacobi_eigen (n x n) -> out[n + n*n]; 2: lu_inverse -> out[n*n]
+// op 0: qr_solve (m x n, 1 rhs) -> out[n]; 1: jacobi_eigen (n x n) -> out[n + n*n]; 2: lu_inverse -> out[n*n];
+// 3: qr_solve_fixed<6,6> / <5,3>; 4: jacobi_eigen3
 __global__ void dbg_linalg_kernel(int op, const float* A, const float* b, float* out, int m, int n, int batch) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= batch) return;
@@ -39,9 +40,20 @@ __global__ void dbg_linalg_kernel(int op, const float* A, const float* b, float*
     float* o = out + (size_t)t * (n + n * n);
     for (int i = 0; i < n; i++) o[i] = w[i];
     for (int i = 0; i < n * n; i++) o[n + i] = v[i];
-  } else {
+  } else if (op == 2) {
     la::lu_inverse(a, v, n);
     for (int i = 0; i < n * n; i++) out[(size_t)t * n * n + i] = v[i];
+  } else if (op == 3) {  // register-resident specialisations: same layout as op 0 / op 1
+    for (int i = 0; i < m; i++) bb[i] = b[(size_t)t * m + i];
+    int ok = 0;
+    if (m == 6 && n == 6) ok = la::qr_solve_fixed<6, 6>(a, bb);
+    else if (m == 5 && n == 3) ok = la::qr_solve_fixed<5, 3>(a, bb);
+    for (int i = 0; i < n; i++) out[(size_t)t * n + i] = ok ? bb[i] : 0.f;
+  } else if (op == 4 && n == 3) {
+    la::jacobi_eigen3(a, w, v);
+    float* o = out + (size_t)t * (n + n * n);
+    for (int i = 0; i < n; i++) o[i] = w[i];
+    for (int i = 0; i < n * n; i++) o[n + i] = v[i];
   }
 }
 

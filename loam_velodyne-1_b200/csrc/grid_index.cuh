@@ -22,13 +22,11 @@ struct GridDesc {
 struct GridBuf {         // passed by value to kernels
   GridDesc* desc;        // device
   unsigned int* bbox;    // 6 flipped floats: min xyz, max xyz
-  int* cell_count;       // max_cells
-  int* cell_start;       // max_cells
+  int2* cell;            // max_cells: {start, count}; the cells of one x-row are contiguous in sorted_pts
   int* cursor;           // 1
   int* pt_cell;          // cap
   int* pt_rank;          // cap
-  float4* sorted_pts;    // cap
-  int* sorted_idx;       // cap
+  float4* sorted_pts;    // cap: (x, y, z, original index as int bits)
   const float4* pts;     // source cloud
   const int* n_ptr;      // device count of the source cloud
   const int* enable;     // optional device flag (nullptr = always build)
@@ -39,23 +37,22 @@ struct GridBuf {         // passed by value to kernels
 
 struct GridView {        // what queries need
   const GridDesc* desc;
-  const int* cell_count;
-  const int* cell_start;
+  const int2* cell;
   const float4* sorted_pts;
-  const int* sorted_idx;
 };
 
 struct GridStorage {
   DevBuf<GridDesc> desc;
   DevBuf<unsigned int> bbox;
-  DevBuf<int> cell_count, cell_start, cursor, pt_cell, pt_rank, sorted_idx;
+  DevBuf<int2> cell;
+  DevBuf<int> cursor, pt_cell, pt_rank;
   DevBuf<float4> sorted_pts;
   int max_cells = 0, cap = 0;
   int alloc(int cap_points, int max_cells_, cudaStream_t s) {
     cap = cap_points; max_cells = max_cells_;
     int r = LOAM_OK;
-    r |= desc.alloc_zero(1, s); r |= bbox.alloc(6); r |= cell_count.alloc_zero(max_cells, s); r |= cell_start.alloc_zero(max_cells, s);
-    r |= cursor.alloc_zero(1, s); r |= pt_cell.alloc(cap); r |= pt_rank.alloc(cap); r |= sorted_idx.alloc(cap); r |= sorted_pts.alloc(cap);
+    r |= desc.alloc_zero(1, s); r |= bbox.alloc(6); r |= cell.alloc_zero(max_cells, s);
+    r |= cursor.alloc_zero(1, s); r |= pt_cell.alloc(cap); r |= pt_rank.alloc(cap); r |= sorted_pts.alloc(cap);
     if (r == LOAM_OK) {
       unsigned int init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
       if (cudaMemcpyAsync(bbox.p, init, sizeof(init), cudaMemcpyHostToDevice, s) != cudaSuccess) r = LOAM_ERR_CUDA;
@@ -65,14 +62,14 @@ struct GridStorage {
   }
   GridBuf buf(const float4* pts, const int* n_ptr, const int* enable, float h0) {
     GridBuf b;
-    b.desc = desc.p; b.bbox = bbox.p; b.cell_count = cell_count.p; b.cell_start = cell_start.p; b.cursor = cursor.p;
-    b.pt_cell = pt_cell.p; b.pt_rank = pt_rank.p; b.sorted_pts = sorted_pts.p; b.sorted_idx = sorted_idx.p;
+    b.desc = desc.p; b.bbox = bbox.p; b.cell = cell.p; b.cursor = cursor.p;
+    b.pt_cell = pt_cell.p; b.pt_rank = pt_rank.p; b.sorted_pts = sorted_pts.p;
     b.pts = pts; b.n_ptr = n_ptr; b.enable = enable; b.max_cells = max_cells; b.cap = cap; b.h0 = h0;
     return b;
   }
   GridView view() const {
     GridView v;
-    v.desc = desc.p; v.cell_count = cell_count.p; v.cell_start = cell_start.p; v.sorted_pts = sorted_pts.p; v.sorted_idx = sorted_idx.p;
+    v.desc = desc.p; v.cell = cell.p; v.sorted_pts = sorted_pts.p;
     return v;
   }
 };
@@ -132,12 +129,12 @@ __device__ __forceinline__ GridDesc grid_make_desc(const GridBuf& g) {
   return d;
 }
 
-// descriptor + zero the cell counters (every block recomputes the descriptor from the bbox)
+// descriptor + zero the cell table (every block recomputes the descriptor from the bbox)
 __global__ void __launch_bounds__(256) grid_setup(GridPair gp) {
   const GridBuf g = gp.g[blockIdx.y];
   if (!grid_enabled(g)) return;
   GridDesc d = grid_make_desc(g);
-  for (int c = blockIdx.x * 256 + threadIdx.x; c < d.ncells; c += gridDim.x * 256) g.cell_count[c] = 0;
+  for (int c = blockIdx.x * 256 + threadIdx.x; c < d.ncells; c += gridDim.x * 256) g.cell[c] = make_int2(0, 0);
   if (blockIdx.x == 0 && threadIdx.x == 0) { *g.desc = d; *g.cursor = 0; }
 }
 
@@ -151,17 +148,38 @@ __global__ void __launch_bounds__(256) grid_count(GridPair gp) {
     int cx = grid_cell_coord(p.x, d.ox, d.inv_h, d.nx), cy = grid_cell_coord(p.y, d.oy, d.inv_h, d.ny), cz = grid_cell_coord(p.z, d.oz, d.inv_h, d.nz);
     int c = (cz * d.ny + cy) * d.nx + cx;
     g.pt_cell[i] = c;
-    g.pt_rank[i] = atomicAdd(&g.cell_count[c], 1);
+    g.pt_rank[i] = atomicAdd(&g.cell[c].y, 1);
   }
 }
 
+// one warp per x-row (fixed y, z): the row's cells get consecutive slots, so a run of x-adjacent
+// cells is ONE contiguous range of sorted_pts and a query needs one header load per row end.
 __global__ void __launch_bounds__(256) grid_alloc(GridPair gp) {
   const GridBuf g = gp.g[blockIdx.y];
   if (!grid_enabled(g)) return;
-  const int ncells = g.desc->ncells;
-  for (int c = blockIdx.x * 256 + threadIdx.x; c < ncells; c += gridDim.x * 256) {
-    int k = g.cell_count[c];
-    g.cell_start[c] = k > 0 ? atomicAdd(g.cursor, k) : 0;
+  const GridDesc d = *g.desc;
+  const int lane = lane_id();
+  const int nrows = d.ny * d.nz;
+  for (int row = blockIdx.x * 8 + (threadIdx.x >> 5); row < nrows; row += gridDim.x * 8) {
+    int2* cells = g.cell + (size_t)row * d.nx;
+    int tot = 0;
+    for (int x = lane; x < d.nx; x += 32) tot += cells[x].y;
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+    if (tot == 0) continue;   // all starts stay 0, all counts 0: every range of this row is empty
+    int base = 0;
+    if (lane == 0) base = atomicAdd(g.cursor, tot);
+    int run = __shfl_sync(0xffffffffu, base, 0);
+    for (int x0 = 0; x0 < d.nx; x0 += 32) {
+      int x = x0 + lane;
+      int c = x < d.nx ? cells[x].y : 0;
+      int incl = c;
+      for (int o = 1; o < 32; o <<= 1) {
+        int y = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += y;
+      }
+      if (x < d.nx) cells[x].x = run + incl - c;
+      run += __shfl_sync(0xffffffffu, incl, 31);
+    }
   }
 }
 
@@ -170,9 +188,10 @@ __global__ void __launch_bounds__(256) grid_scatter(GridPair gp) {
   if (!grid_enabled(g)) return;
   const int n = g.desc->n_points;
   for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
-    int dst = g.cell_start[g.pt_cell[i]] + g.pt_rank[i];
-    g.sorted_pts[dst] = g.pts[i];
-    g.sorted_idx[dst] = i;
+    int dst = g.cell[g.pt_cell[i]].x + g.pt_rank[i];
+    float4 p = g.pts[i];
+    p.w = __int_as_float(i);
+    g.sorted_pts[dst] = p;
   }
 }
 
@@ -190,49 +209,131 @@ inline int grid_build_pair(GridPair gp, int nblocks, cudaStream_t stream) {
 // ---- queries -----------------------------------------------------------------------------
 __device__ __forceinline__ bool nn_less(float d, int i, float bd, int bi) { return d < bd || (d == bd && i < bi); }
 
+// The 3x3x3 block of cells around (cx,cy,cz) as 9 x-rows = 9 contiguous ranges of sorted_pts.
+// ONE round of header loads for the whole block: lane 2r loads the first cell of row r, lane
+// 2r+1 the last one.  Afterwards every lane holds all nine (begin, prefix) pairs in registers.
+struct GridRows9 {
+  int beg[9];
+  int pre[10];   // pre[r] = number of candidates in rows < r; pre[9] = total
+};
+// W = lanes cooperating on one query (32 or 16); gl = lane index inside the group
+template <int W>
+__device__ __forceinline__ void grid_rows9(const GridView& g, const GridDesc& d, int cx, int cy, int cz, GridRows9& R) {
+  const int gl = lane_id() & (W - 1);
+  const unsigned int gmask = (W == 32) ? 0xffffffffu : (((1u << W) - 1u) << (lane_id() & ~(W - 1)));
+  const int x0 = max(cx - 1, 0), x1 = min(cx + 1, d.nx - 1);
+  int vb = 0, ve = 0;
+  if (gl < 9 && x0 <= x1) {
+    const int y = cy + (gl % 3) - 1, z = cz + (gl / 3) - 1;
+    if (y >= 0 && y < d.ny && z >= 0 && z < d.nz) {
+      const int2* row = g.cell + (size_t)(z * d.ny + y) * d.nx;
+      int2 c0 = __ldg(&row[x0]);
+      int2 c1 = __ldg(&row[x1]);
+      vb = c0.x; ve = c1.x + c1.y;
+    }
+  }
+  R.pre[0] = 0;
+#pragma unroll
+  for (int k = 0; k < 9; k++) {
+    int b = __shfl_sync(gmask, vb, k, W);
+    int en = __shfl_sync(gmask, ve, k, W);
+    R.beg[k] = b;
+    R.pre[k + 1] = R.pre[k] + (en - b);
+  }
+}
+// position in sorted_pts of flat candidate t (0 <= t < pre[9])
+__device__ __forceinline__ int grid_rows9_pos(const GridRows9& R, int t) {
+  int pos = R.beg[0] + t;
+#pragma unroll
+  for (int k = 1; k < 9; k++)
+    if (t >= R.pre[k]) pos = R.beg[k] + (t - R.pre[k]);
+  return pos;
+}
+
 // exact 1-NN, warp cooperative.  All lanes return the same (idx, d2); idx = -1 if the cloud is
 // empty or nothing lies within sqrt(maxd2).  Tie-break: lowest original index.
+// Stage 1 examines the 27 cells around the (clamped) query cell with one batch of header loads and
+// independent point loads; almost every query ends there.  Stage 2 (rare) walks further
+// Chebyshev shells cell by cell.
 __device__ __forceinline__ void grid_nn1_warp(const GridView& g, float qx, float qy, float qz, float maxd2, int& out_idx, float& out_d2) {
   const GridDesc d = *g.desc;
   float bd = 3.0e38f;
   int bi = 0x7fffffff;
   if (d.valid) {
     int cx = (int)floorf((qx - d.ox) * d.inv_h), cy = (int)floorf((qy - d.oy) * d.inv_h), cz = (int)floorf((qz - d.oz) * d.inv_h);
-    // the query may lie outside the grid: clamp its cell and account for the gap in the bound
+    // the query may lie outside the grid: clamp its cell (the true distance to any unexamined
+    // point is then even larger than the bound used below)
     int qcx = min(max(cx, 0), d.nx - 1), qcy = min(max(cy, 0), d.ny - 1), qcz = min(max(cz, 0), d.nz - 1);
     const float maxr = sqrtf(maxd2);
     const int lane = lane_id();
-    for (int k = 0;; k++) {
+    {
+      GridRows9 R;
+      grid_rows9<32>(g, d, qcx, qcy, qcz, R);
+      const int total = R.pre[9];
+      for (int t0 = lane; t0 < total; t0 += 128) {
+        float4 pc[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const int t = t0 + u * 32;
+          pc[u] = g.sorted_pts[grid_rows9_pos(R, t < total ? t : 0)];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          if (t0 + u * 32 >= total) break;
+          const float4 p = pc[u];
+          float dx = qx - p.x, dy = qy - p.y, dz = qz - p.z;
+          float dd = 0.f;
+          dd += dx * dx; dd += dy * dy; dd += dz * dz;
+          int id = __float_as_int(p.w);
+          if (nn_less(dd, id, bd, bi)) { bd = dd; bi = id; }
+        }
+      }
+    }
+    for (int k = 1;; k++) {
       int x0 = max(qcx - k, 0), x1 = min(qcx + k, d.nx - 1);
       int y0 = max(qcy - k, 0), y1 = min(qcy + k, d.ny - 1);
       int z0 = max(qcz - k, 0), z1 = min(qcz + k, d.nz - 1);
-      for (int z = z0; z <= z1; z++)
-        for (int y = y0; y <= y1; y++)
-          for (int x = x0; x <= x1; x++) {
-            int cheb = max(max(abs(x - qcx), abs(y - qcy)), abs(z - qcz));
-            if (cheb != k) continue;
-            int c = (z * d.ny + y) * d.nx + x;
-            int cnt = g.cell_count[c];
-            if (cnt == 0) continue;
-            int st = g.cell_start[c];
-            for (int t = lane; t < cnt; t += 32) {
-              float4 p = g.sorted_pts[st + t];
-              float dx = qx - p.x, dy = qy - p.y, dz = qz - p.z;
-              float dd = 0.f;
-              dd += dx * dx; dd += dy * dy; dd += dz * dz;
-              int id = g.sorted_idx[st + t];
-              if (nn_less(dd, id, bd, bi)) { bd = dd; bi = id; }
+      if (k >= 2) {
+        // shell k, one lane per (y, z) row of the (2k+1)^2 square: a face row is one contiguous
+        // x-range, an interior row contributes only its two end cells
+        const int side = 2 * k + 1;
+        for (int r0 = 0; r0 < side * side; r0 += 32) {
+          const int r = r0 + lane;
+          int b0 = 0, n0 = 0, b1 = 0, n1 = 0;
+          if (r < side * side) {
+            const int dy = r % side - k, dz = r / side - k;
+            const int y = qcy + dy, z = qcz + dz;
+            if (y >= 0 && y < d.ny && z >= 0 && z < d.nz) {
+              const int2* row = g.cell + (size_t)(z * d.ny + y) * d.nx;
+              const bool face = (abs(dy) == k) || (abs(dz) == k);
+              if (face) {
+                int2 c0 = __ldg(&row[x0]);
+                int2 c1 = __ldg(&row[x1]);
+                b0 = c0.x; n0 = c1.x + c1.y - c0.x;
+              } else {
+                if (qcx - k >= 0) { int2 c0 = __ldg(&row[qcx - k]); b0 = c0.x; n0 = c0.y; }
+                if (qcx + k < d.nx) { int2 c1 = __ldg(&row[qcx + k]); b1 = c1.x; n1 = c1.y; }
+              }
             }
           }
+          for (int t = 0; t < n0 + n1; t++) {
+            float4 p = g.sorted_pts[t < n0 ? b0 + t : b1 + (t - n0)];
+            float dx = qx - p.x, dy = qy - p.y, dz = qz - p.z;
+            float dd = 0.f;
+            dd += dx * dx; dd += dy * dy; dd += dz * dz;
+            int id = __float_as_int(p.w);
+            if (nn_less(dd, id, bd, bi)) { bd = dd; bi = id; }
+          }
+        }
+      }
       // warp-wide best so far
       float wb = bd;
       for (int o = 16; o > 0; o >>= 1) wb = fminf(wb, __shfl_xor_sync(0xffffffffu, wb, o));
-      // every unexamined point is farther than k*h - slack along some axis from the CLAMPED cell;
-      // if the query is outside the grid the true distance is even larger.
+      // every unexamined point is farther than k*h - slack along some axis from the CLAMPED cell
       float bound = (float)k * d.h - 0.01f;
       bool covered = (x0 == 0 && x1 == d.nx - 1 && y0 == 0 && y1 == d.ny - 1 && z0 == 0 && z1 == d.nz - 1);
       if (covered) break;
-      if (k >= 1 && bound > 0.f && (wb < bound * bound || bound > maxr)) break;
+      if (bound > 0.f && (wb < bound * bound || bound > maxr)) break;
     }
     for (int o = 16; o > 0; o >>= 1) {
       float od = __shfl_xor_sync(0xffffffffu, bd, o);

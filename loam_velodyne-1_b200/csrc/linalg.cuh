@@ -171,6 +171,171 @@ LOAM_HD void jacobi_eigen(float* A, float* W, float* V, int n) {
   }
 }
 
+// ---- register-resident specialisations (device hot paths) -------------------------------------
+// Same operations in the same order as the generic routines above (bit-identical results,
+// checked by tests/test_gpu_parity.py::test_device_linalg_fixed_equals_generic); every loop bound
+// is a compile-time constant so the arrays live in registers instead of local memory.
+template <int M, int N>
+LOAM_HD int qr_solve_fixed(float* A, float* b) {   // one right-hand side
+  const float eps = FLT_EPSILON * 10;
+  float hf[N];
+#pragma unroll
+  for (int l = 0; l < N; l++) {
+    float vl[M];
+    float vn = 0.f;
+#pragma unroll
+    for (int i = 0; i < M - l; i++) {
+      vl[i] = A[(l + i) * N + l];
+      vn += vl[i] * vl[i];
+    }
+    float tmpV = vl[0];
+    vl[0] = vl[0] + (float)((vl[0] >= 0.f) - (vl[0] < 0.f)) * loam::dm::sqrt(vn);
+    vn = loam::dm::sqrt(vn + vl[0] * vl[0] - tmpV * tmpV);
+#pragma unroll
+    for (int i = 0; i < M - l; i++) vl[i] /= vn;
+#pragma unroll
+    for (int j = l; j < N; j++) {
+      float vA = 0.f;
+#pragma unroll
+      for (int i = l; i < M; i++) vA += vl[i - l] * A[i * N + j];
+#pragma unroll
+      for (int i = l; i < M; i++) A[i * N + j] -= 2 * vl[i - l] * vA;
+    }
+    hf[l] = vl[0] * vl[0];
+#pragma unroll
+    for (int i = 1; i < M - l; i++) A[(l + i) * N + l] = vl[i] / vl[0];
+  }
+#pragma unroll
+  for (int l = 0; l < N; l++) {
+    float vl[M];
+    vl[0] = 1.f;
+#pragma unroll
+    for (int j = 1; j < M - l; j++) vl[j] = A[(j + l) * N + l];
+    float vB = 0.f;
+#pragma unroll
+    for (int i = l; i < M; i++) vB += vl[i - l] * b[i];
+#pragma unroll
+    for (int i = l; i < M; i++) b[i] -= 2 * vl[i - l] * vB * hf[l];
+  }
+  int ok = 1;
+#pragma unroll
+  for (int i = N - 1; i >= 0; i--) {
+    if (ok) {
+#pragma unroll
+      for (int j = N - 1; j > i; j--) b[i] -= b[j] * A[i * N + j];
+      if (fabsf(A[i * N + i]) < eps) ok = 0;
+      else b[i] /= A[i * N + i];
+    }
+  }
+  return ok;
+}
+
+// 3x3 symmetric Jacobi with the matrix in registers.  Only the strict upper triangle is ever read
+// by the generic routine; element access by (runtime row, runtime col) is a 3-way select.
+struct Sym3 {
+  float a01, a02, a12;
+  LOAM_HD float get(int r, int c) const { return r == 0 ? (c == 1 ? a01 : a02) : a12; }
+  LOAM_HD void set(int r, int c, float v) { if (r == 0) { if (c == 1) a01 = v; else a02 = v; } else a12 = v; }
+};
+LOAM_HD void jacobi_eigen3(const float* Ain, float* W, float* V) {
+  const float eps = FLT_EPSILON;
+  Sym3 A;
+  A.a01 = Ain[1]; A.a02 = Ain[2]; A.a12 = Ain[5];
+  float w0 = Ain[0], w1 = Ain[4], w2 = Ain[8];
+  float v[9] = {1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f};
+  // indR[0] in {1,2}, indR[1] = 2, indC[1] = 0, indC[2] in {0,1}
+  int indR0 = 1;
+  if (fabsf(A.a01) < fabsf(A.a02)) indR0 = 2;
+  int indC2 = 0;
+  if (fabsf(A.a02) < fabsf(A.a12)) indC2 = 1;
+  for (int iters = 0; iters < 270; iters++) {
+    int k = 0;
+    float mv = fabsf(A.get(0, indR0));
+    { float val = fabsf(A.a12); if (mv < val) mv = val, k = 1; }
+    int l = k == 0 ? indR0 : 2;
+    { float val = fabsf(A.a01); if (mv < val) mv = val, k = 0, l = 1; }
+    { float val = fabsf(A.get(indC2, 2)); if (mv < val) mv = val, k = indC2, l = 2; }
+    float p = A.get(k, l);
+    if (fabsf(p) <= eps) break;
+    float wk = k == 0 ? w0 : w1;           // k in {0,1}
+    float wl = l == 1 ? w1 : w2;           // l in {1,2}
+    float y = (float)((wl - wk) * 0.5);
+    float t = fabsf(y) + hypot_cv(p, y);
+    float s = hypot_cv(p, t);
+    float c = t / s;
+    s = p / s;
+    t = (p / t) * p;
+    if (y < 0) s = -s, t = -t;
+    A.set(k, l, 0.f);
+    wk -= t; wl += t;
+    if (k == 0) w0 = wk; else w1 = wk;
+    if (l == 1) w1 = wl; else w2 = wl;
+    float a0, b0;
+    // the one remaining index m (not k, not l): exactly one of the three generic loops runs once
+    if (k == 0 && l == 1) {        // i = 2 > l : rot(A[k][2], A[l][2])
+      a0 = A.a02; b0 = A.a12; A.a02 = a0 * c - b0 * s; A.a12 = a0 * s + b0 * c;
+    } else if (k == 0 && l == 2) { // i = 1 in (k,l) : rot(A[k][1], A[1][l])
+      a0 = A.a01; b0 = A.a12; A.a01 = a0 * c - b0 * s; A.a12 = a0 * s + b0 * c;
+    } else {                       // k == 1, l == 2; i = 0 < k : rot(A[0][k], A[0][l])
+      a0 = A.a01; b0 = A.a02; A.a01 = a0 * c - b0 * s; A.a02 = a0 * s + b0 * c;
+    }
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      float vk = k == 0 ? v[i] : v[3 + i];
+      float vl_ = l == 1 ? v[3 + i] : v[6 + i];
+      float nk = vk * c - vl_ * s, nl = vk * s + vl_ * c;
+      if (k == 0) v[i] = nk; else v[3 + i] = nk;
+      if (l == 1) v[3 + i] = nl; else v[6 + i] = nl;
+    }
+    // recompute indR / indC of rows/cols k and l (the only ones with a choice are indR[0], indC[2])
+    if (k == 0) { indR0 = 1; if (fabsf(A.a01) < fabsf(A.a02)) indR0 = 2; }
+    if (l == 2) { indC2 = 0; if (fabsf(A.a02) < fabsf(A.a12)) indC2 = 1; }
+  }
+  W[0] = w0; W[1] = w1; W[2] = w2;
+#pragma unroll
+  for (int i = 0; i < 9; i++) V[i] = v[i];
+  // selection sort, descending (same swaps as the generic routine)
+#pragma unroll
+  for (int k = 0; k < 2; k++) {
+    int m = k;
+#pragma unroll
+    for (int i = k + 1; i < 3; i++)
+      if (W[m] < W[i]) m = i;
+    if (k != m) {
+      float tw = W[m]; W[m] = W[k]; W[k] = tw;
+#pragma unroll
+      for (int i = 0; i < 3; i++) {
+        float tv = V[3 * m + i]; V[3 * m + i] = V[3 * k + i]; V[3 * k + i] = tv;
+      }
+    }
+  }
+}
+
+// true when every eigenvalue of the symmetric 6x6 matrix A is provably > tau: LDL^T of A - tau*I
+// in fp64 has only positive pivots.  Used to skip the Jacobi eigen-decomposition of the
+// degeneracy test when its outcome ("not degenerate") is certain.
+LOAM_HD bool spd6_above(const float* A, double tau) {
+  double L[36];
+#pragma unroll
+  for (int i = 0; i < 36; i++) L[i] = (double)A[i];
+#pragma unroll
+  for (int i = 0; i < 6; i++) L[i * 6 + i] -= tau;
+  bool ok = true;
+#pragma unroll
+  for (int j = 0; j < 6; j++) {
+    double dj = L[j * 6 + j];
+    if (!(dj > 0.0)) ok = false;
+    double inv = ok ? 1.0 / dj : 0.0;
+#pragma unroll
+    for (int i = j + 1; i < 6; i++) {
+      double f = L[i * 6 + j] * inv;
+#pragma unroll
+      for (int k = j + 1; k <= i; k++) L[i * 6 + k] -= f * L[k * 6 + j];
+    }
+  }
+  return ok;
+}
+
 // LU inverse with partial pivoting (hal::LU32f on [A | I]).  A overwritten; returns 0 if singular
 // (then inv is all zeros, as cv::invert does).
 LOAM_HD int lu_inverse(float* A, float* inv, int m) {

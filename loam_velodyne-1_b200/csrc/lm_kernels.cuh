@@ -283,59 +283,77 @@ __global__ void __launch_bounds__(256) lm_gather_map(LMGatherArgs A) {
 }
 
 // ---- exact 5-NN inside radius 1 (the only case the reference accepts, :719,:826) ------------
-// Returns true when the 5th neighbour has d2 < 1.0; idx/d2 ascending by (d2, index).
-__device__ __forceinline__ bool lm_knn5_warp(const GridView& g, float qx, float qy, float qz, int* idx5, float* d5) {
-  const GridDesc d = *g.desc;
+// A group of W lanes (half a warp) cooperates on one query.  Returns true when the 5th neighbour
+// has d2 < 1.0; neighbours ascending by (d2, index).  out[r] = (x, y, z, original index bits) of
+// neighbour r, written by the lane that owns it (out is shared memory).  One batch of cell-header
+// loads (grid_rows9), then every candidate load is independent: the dependent-load depth per
+// query is 2, not 3 x 27.  The 5-way merge uses the warp-reduce unit (redux.sync) on the distance
+// bits (non-negative floats order like unsigned ints), ties resolved by a second reduce on the index.
+template <int W>
+__device__ __forceinline__ bool lm_knn5_group(const GridView& g, const GridDesc& d, float qx, float qy, float qz, float4* out) {
   const int lane = lane_id();
-  float ld[5]; int li[5];
+  const int gl = lane & (W - 1);
+  const unsigned int gmask = (W == 32) ? 0xffffffffu : (((1u << W) - 1u) << (lane & ~(W - 1)));
+  float ld[5]; int li[5]; float lx[5], ly[5], lz[5];
 #pragma unroll
-  for (int k = 0; k < 5; k++) { ld[k] = 3.0e38f; li[k] = 0x7fffffff; }
+  for (int k = 0; k < 5; k++) { ld[k] = 3.0e38f; li[k] = 0x7fffffff; lx[k] = ly[k] = lz[k] = 0.f; }
+  int total = 0;
   if (d.valid) {
     int cx = (int)floorf((qx - d.ox) * d.inv_h), cy = (int)floorf((qy - d.oy) * d.inv_h), cz = (int)floorf((qz - d.oz) * d.inv_h);
     // cell size >= 1.02 m: every point with d2 < 1 lies in the 3x3x3 block around the query cell
-    for (int z = max(cz - 1, 0); z <= min(cz + 1, d.nz - 1); z++)
-      for (int y = max(cy - 1, 0); y <= min(cy + 1, d.ny - 1); y++)
-        for (int x = max(cx - 1, 0); x <= min(cx + 1, d.nx - 1); x++) {
-          int c = (z * d.ny + y) * d.nx + x;
-          int cnt = g.cell_count[c];
-          if (cnt == 0) continue;
-          int st = g.cell_start[c];
-          for (int t = lane; t < cnt; t += 32) {
-            float4 p = g.sorted_pts[st + t];
-            float dx = qx - p.x, dy = qy - p.y, dz = qz - p.z;
-            float dd = 0.f;
-            dd += dx * dx; dd += dy * dy; dd += dz * dz;
-            int id = g.sorted_idx[st + t];
-            if (nn_less(dd, id, ld[4], li[4])) {
-              ld[4] = dd; li[4] = id;
+    GridRows9 R;
+    grid_rows9<W>(g, d, cx, cy, cz, R);
+    total = R.pre[9];
+    if (total >= 5) {
+      // four independent candidate loads in flight per lane before the first one is consumed
+      for (int t0 = gl; t0 < total; t0 += 4 * W) {
+        float4 pc[4];
 #pragma unroll
-              for (int k = 4; k > 0; k--) {
-                if (nn_less(ld[k], li[k], ld[k - 1], li[k - 1])) {
-                  float td = ld[k]; ld[k] = ld[k - 1]; ld[k - 1] = td;
-                  int ti = li[k]; li[k] = li[k - 1]; li[k - 1] = ti;
-                }
+        for (int u = 0; u < 4; u++) {
+          const int t = t0 + u * W;
+          pc[u] = g.sorted_pts[grid_rows9_pos(R, t < total ? t : 0)];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          if (t0 + u * W >= total) break;
+          const float4 p = pc[u];
+          float dx = qx - p.x, dy = qy - p.y, dz = qz - p.z;
+          float dd = 0.f;
+          dd += dx * dx; dd += dy * dy; dd += dz * dz;
+          int id = __float_as_int(p.w);
+          if (nn_less(dd, id, ld[4], li[4])) {
+            ld[4] = dd; li[4] = id; lx[4] = p.x; ly[4] = p.y; lz[4] = p.z;
+#pragma unroll
+            for (int k = 4; k > 0; k--) {
+              if (nn_less(ld[k], li[k], ld[k - 1], li[k - 1])) {
+                float td = ld[k]; ld[k] = ld[k - 1]; ld[k - 1] = td;
+                int ti = li[k]; li[k] = li[k - 1]; li[k - 1] = ti;
+                float tx = lx[k]; lx[k] = lx[k - 1]; lx[k - 1] = tx;
+                float ty = ly[k]; ly[k] = ly[k - 1]; ly[k - 1] = ty;
+                float tz = lz[k]; lz[k] = lz[k - 1]; lz[k - 1] = tz;
               }
             }
           }
         }
+      }
+    }
   }
-  // merge the 32 sorted lists: five rounds of warp arg-min, the winner pops its head
+  if (total < 5) return false;   // uniform inside the group
+  // merge the W sorted lists: five rounds, the winner pops its head
+  unsigned int bdu = 0; int bi = 0;
 #pragma unroll
   for (int r = 0; r < 5; r++) {
-    float bd = ld[0]; int bi = li[0];
-    for (int o = 16; o > 0; o >>= 1) {
-      float od = __shfl_xor_sync(0xffffffffu, bd, o);
-      int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-      if (nn_less(od, oi, bd, bi)) { bd = od; bi = oi; }
-    }
-    idx5[r] = bi; d5[r] = bd;
-    if (li[0] == bi && ld[0] == bd && bi != 0x7fffffff) {
+    bdu = __reduce_min_sync(gmask, __float_as_uint(ld[0]));
+    const bool tie = __float_as_uint(ld[0]) == bdu;
+    bi = (int)__reduce_min_sync(gmask, tie ? (unsigned int)li[0] : 0x7fffffffu);
+    if (tie && li[0] == bi && bi != 0x7fffffff) {   // indices are unique: exactly one owner
+      out[r] = make_float4(lx[0], ly[0], lz[0], __int_as_float(bi));
 #pragma unroll
-      for (int k = 0; k < 4; k++) { ld[k] = ld[k + 1]; li[k] = li[k + 1]; }
+      for (int k = 0; k < 4; k++) { ld[k] = ld[k + 1]; li[k] = li[k + 1]; lx[k] = lx[k + 1]; ly[k] = ly[k + 1]; lz[k] = lz[k + 1]; }
       ld[4] = 3.0e38f; li[4] = 0x7fffffff;
     }
   }
-  return idx5[4] != 0x7fffffff && d5[4] < 1.0;
+  return bi != 0x7fffffff && __uint_as_float(bdu) < 1.0;
 }
 
 }  // namespace loamgpu

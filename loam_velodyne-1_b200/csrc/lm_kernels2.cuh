@@ -20,26 +20,28 @@ struct LMOptArgs {
 };
 
 // corner: 5-NN mean, 3x3 covariance, eigen line test, point-to-line residual (:719-818)
-__device__ __forceinline__ bool lm_corner_fit(const float4* map, const int* idx, const float4 pointSel, float4& coeff) {
+__device__ __forceinline__ bool lm_corner_fit(const float4* nb, const float4 pointSel, float4& coeff) {
   float cx = 0; float cy = 0; float cz = 0;
+#pragma unroll
   for (int j = 0; j < 5; j++) {
-    cx += map[idx[j]].x;
-    cy += map[idx[j]].y;
-    cz += map[idx[j]].z;
+    cx += nb[j].x;
+    cy += nb[j].y;
+    cz += nb[j].z;
   }
   cx /= 5; cy /= 5; cz /= 5;
   float a11 = 0; float a12 = 0; float a13 = 0; float a22 = 0; float a23 = 0; float a33 = 0;
+#pragma unroll
   for (int j = 0; j < 5; j++) {
-    float ax = map[idx[j]].x - cx;
-    float ay = map[idx[j]].y - cy;
-    float az = map[idx[j]].z - cz;
+    float ax = nb[j].x - cx;
+    float ay = nb[j].y - cy;
+    float az = nb[j].z - cz;
     a11 += ax * ax; a12 += ax * ay; a13 += ax * az;
     a22 += ay * ay; a23 += ay * az; a33 += az * az;
   }
   a11 /= 5; a12 /= 5; a13 /= 5; a22 /= 5; a23 /= 5; a33 /= 5;
   float A1[9] = {a11, a12, a13, a12, a22, a23, a13, a23, a33};
   float D1[3], V1[9];
-  la::jacobi_eigen(A1, D1, V1, 3);
+  la::jacobi_eigen3(A1, D1, V1);
   if (!(D1[0] > 3 * D1[1])) return false;
   float x0 = pointSel.x; float y0 = pointSel.y; float z0 = pointSel.z;
   float x1 = cx + 0.1 * V1[0];
@@ -71,15 +73,16 @@ __device__ __forceinline__ bool lm_corner_fit(const float4* map, const int* idx,
 }
 
 // surf: 5x3 QR plane fit, 0.2 m validity, point-to-plane residual (:826-875)
-__device__ __forceinline__ bool lm_surf_fit(const float4* map, const int* idx, const float4 pointSel, float4& coeff) {
+__device__ __forceinline__ bool lm_surf_fit(const float4* nb, const float4 pointSel, float4& coeff) {
   float A0[15], B0[5];
+#pragma unroll
   for (int j = 0; j < 5; j++) {
-    A0[j * 3 + 0] = map[idx[j]].x;
-    A0[j * 3 + 1] = map[idx[j]].y;
-    A0[j * 3 + 2] = map[idx[j]].z;
+    A0[j * 3 + 0] = nb[j].x;
+    A0[j * 3 + 1] = nb[j].y;
+    A0[j * 3 + 2] = nb[j].z;
     B0[j] = -1.f;
   }
-  int ok = la::qr_solve(A0, 5, 3, B0, 1);
+  int ok = la::qr_solve_fixed<5, 3>(A0, B0);
   float pa = ok ? B0[0] : 0.f;
   float pb = ok ? B0[1] : 0.f;
   float pc = ok ? B0[2] : 0.f;
@@ -87,8 +90,9 @@ __device__ __forceinline__ bool lm_surf_fit(const float4* map, const int* idx, c
   float ps = dm::sqrt(pa * pa + pb * pb + pc * pc);
   pa /= ps; pb /= ps; pc /= ps; pd /= ps;
   bool planeValid = true;
+#pragma unroll
   for (int j = 0; j < 5; j++) {
-    if (dm::fabs(pa * map[idx[j]].x + pb * map[idx[j]].y + pc * map[idx[j]].z + pd) > 0.2) {
+    if (dm::fabs(pa * nb[j].x + pb * nb[j].y + pc * nb[j].z + pd) > 0.2) {
       planeValid = false;
       break;
     }
@@ -104,7 +108,7 @@ __device__ __forceinline__ bool lm_surf_fit(const float4* map, const int* idx, c
 }
 
 // Jacobian row :898-920
-__device__ __forceinline__ void lm_row_accumulate(const float4 pointOri, const float4 coeffv, const LMTrig& g, double* acc) {
+__device__ __forceinline__ void lm_row(const float4 pointOri, const float4 coeffv, const LMTrig& g, float* a, float& b) {
   float srx = g.srx, crx = g.crx, sry = g.sry, cry = g.cry, srz = g.srz, crz = g.crz;
   struct { float x, y, z; } coeff = {coeffv.x, coeffv.y, coeffv.z};
   float arx = (crx*sry*srz*pointOri.x + crx*crz*sry*pointOri.y - srx*sry*pointOri.z) * coeff.x
@@ -117,16 +121,8 @@ __device__ __forceinline__ void lm_row_accumulate(const float4 pointOri, const f
   float arz = ((crz*srx*sry - cry*srz)*pointOri.x + (-cry*crz-srx*sry*srz)*pointOri.y)*coeff.x
             + (crx*crz*pointOri.x - crx*srz*pointOri.y) * coeff.y
             + ((sry*srz + cry*crz*srx)*pointOri.x + (crz*sry-cry*srx*srz)*pointOri.y)*coeff.z;
-  float a[6] = {arx, ary, arz, coeff.x, coeff.y, coeff.z};
-  float b = -coeffv.w;
-  int k = 0;
-#pragma unroll
-  for (int i = 0; i < 6; i++)
-#pragma unroll
-    for (int j = i; j < 6; j++) acc[k++] += (double)a[i] * (double)a[j];
-#pragma unroll
-  for (int i = 0; i < 6; i++) acc[21 + i] += (double)a[i] * (double)b;
-  acc[27] += 1.0;
+  a[0] = arx; a[1] = ary; a[2] = arz; a[3] = coeff.x; a[4] = coeff.y; a[5] = coeff.z;
+  b = -coeffv.w;
 }
 
 // transformUpdate :199-232
@@ -160,18 +156,29 @@ __device__ __forceinline__ void lm_transform_update(LMState* st, float* T, const
   }
 }
 
-// K6: the whole LM loop :706-978 as one cooperative kernel (one warp per query)
-__global__ void __launch_bounds__(LM_THREADS) lm_optimize(LMOptArgs A) {
+// K6: the whole LM loop :706-978 as one cooperative kernel.  Every CTA owns a contiguous slice of
+// the queries.  Per iteration: (A) one warp per query: 5-NN on the grid index, neighbours parked
+// in shared memory; (B) one THREAD per query: line / plane fit and Jacobian row (32 fits per warp
+// in flight instead of one on lane 0); (C) 28 threads sum the CTA's rows in query order in fp64;
+// then the per-CTA partials are exchanged through one grid barrier and every CTA redundantly
+// finishes the sum (ascending CTA order) and the 6x6 solve, so no broadcast is needed.
+constexpr int LM_CH = 256;   // queries per CTA per pass
+__global__ void __launch_bounds__(LM_THREADS, 1) lm_optimize(LMOptArgs A) {
   cg::grid_group grid = cg::this_grid();
   __shared__ float s_T[6];
   __shared__ LMTrig s_trig;
   __shared__ float s_matP[36];
   __shared__ int s_deg, s_stop, s_rows;
-  __shared__ double s_red[LM_WARPS][LO_NRED];
+  __shared__ double s_g[PS_GROUPS][LO_NRED];
   __shared__ double s_tot[LO_NRED];
+  __shared__ float4 s_nb[LM_CH + 1][5];   // +1: scratch slot for an idle half-warp
+  __shared__ float s_row[LM_CH][8];          // a[0..5], b, valid
+  __shared__ unsigned char s_found[LM_CH];
   const int lane = lane_id(), warp = threadIdx.x >> 5;
-  const int gwarp = blockIdx.x * LM_WARPS + warp, nwarps = gridDim.x * LM_WARPS;
   LMState* st = A.st;
+  int clk = (blockIdx.x == 0 && threadIdx.x == 0 && g_phase_on) ? 1 : -1;
+#define PS() do { if (clk >= 0) phase_stamp(1, clk); } while (0)
+  PS();
   if (threadIdx.x == 0) {
     for (int i = 0; i < 6; i++) s_T[i] = st->transformTobeMapped[i];
     for (int i = 0; i < 36; i++) s_matP[i] = st->matP[i];
@@ -180,52 +187,72 @@ __global__ void __launch_bounds__(LM_THREADS) lm_optimize(LMOptArgs A) {
   }
   __syncthreads();
   const int Qc = st->stackN[0], Qs = st->stackN[1];
+  const int Q = Qc + Qs;
+  // CTA b owns queries b, b + G, b + 2G, ... : corner and surf queries (different fit cost, different
+  // map density) are spread evenly over the CTAs
+  const int G = (int)gridDim.x;
+  const int nmine = (Q > (int)blockIdx.x) ? (Q - (int)blockIdx.x + G - 1) / G : 0;
   int iters_done = 0;
   const bool enabled = st->optimize_enable != 0;
   if (enabled) {
+    const GridDesc gd0 = *A.grid[0].desc, gd1 = *A.grid[1].desc;
     for (int iterCount = 0; iterCount < A.max_iter; iterCount++) {
       iters_done = iterCount + 1;
       if (threadIdx.x == 0) s_trig = lm_trig(s_T);
       __syncthreads();
+      PS();  // 0: trig done
       const LMTrig g = s_trig;
-      double acc[LO_NRED];
-#pragma unroll
-      for (int k = 0; k < LO_NRED; k++) acc[k] = 0.0;
-      for (int q = gwarp; q < Qc + Qs; q += nwarps) {
-        const int T = q < Qc ? 0 : 1;
-        const int k = T ? q - Qc : q;
-        const float4 pointOri = A.stack[T][k];
-        const float4 pointSel = lm_to_map(pointOri, g, s_T);
-        int idx5[5]; float d5[5];
-        bool found = lm_knn5_warp(A.grid[T], pointSel.x, pointSel.y, pointSel.z, idx5, d5);
-        if (lane < 5) A.nn_dbg[T][(size_t)k * 5 + lane] = found ? idx5[lane] : -1;
-        if (lane == 0 && found) {
-          float4 coeff;
-          bool valid = T == 0 ? lm_corner_fit(A.map[0], idx5, pointSel, coeff) : lm_surf_fit(A.map[1], idx5, pointSel, coeff);
-          if (valid) lm_row_accumulate(pointOri, coeff, g, acc);
+      double acc = 0.0;
+      for (int c0 = 0; c0 < nmine; c0 += LM_CH) {
+        const int nq = min(LM_CH, nmine - c0);
+        // ---- (A) 5-NN, half a warp per query ----
+        for (int i = warp * 2 + (lane >> 4); i < nq + (nq & 1); i += LM_WARPS * 2) {
+          const bool act = i < nq;   // both halves of a warp run the same trip count
+          const int q = (int)blockIdx.x + (c0 + (act ? i : 0)) * G;
+          const int T = q < Qc ? 0 : 1;
+          const int k = T ? q - Qc : q;
+          const float4 pointSel = lm_to_map(A.stack[T][k], g, s_T);
+          bool found = lm_knn5_group<16>(A.grid[T], T ? gd1 : gd0, pointSel.x, pointSel.y, pointSel.z, s_nb[act ? i : LM_CH]);
+          if (act && (lane & 15) == 0) s_found[i] = found ? 1 : 0;
         }
-      }
+        __syncthreads();
+        if (c0 == 0) PS();  // 1: kNN done
+        // ---- (B) fit + Jacobian row, one thread per query ----
+        for (int i = threadIdx.x; i < nq; i += LM_THREADS) {
+          const int q = (int)blockIdx.x + (c0 + i) * G;
+          const int T = q < Qc ? 0 : 1;
+          const int k = T ? q - Qc : q;
+          const bool found = s_found[i] != 0;
+          float valid = 0.f;
+          if (found) {
+            const float4 pointOri = A.stack[T][k];
+            const float4 pointSel = lm_to_map(pointOri, g, s_T);
+            float4 coeff;
+            bool ok = T == 0 ? lm_corner_fit(s_nb[i], pointSel, coeff) : lm_surf_fit(s_nb[i], pointSel, coeff);
+            if (ok) {
+              float a[6], b;
+              lm_row(pointOri, coeff, g, a, b);
 #pragma unroll
-      for (int k = 0; k < LO_NRED; k++) {
-        double v = acc[k];
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if (lane == 0) s_red[warp][k] = v;
+              for (int j = 0; j < 6; j++) s_row[i][j] = a[j];
+              s_row[i][6] = b;
+              valid = 1.f;
+            }
+          }
+          s_row[i][7] = valid;
+          int* dbg = A.nn_dbg[T] + (size_t)k * 5;
+#pragma unroll
+          for (int j = 0; j < 5; j++) dbg[j] = found ? __float_as_int(s_nb[i][j].w) : -1;
+        }
+        __syncthreads();
+        if (c0 == 0) PS();  // 2: fits done
+        // ---- (C) the CTA's share of AtA / AtB ----
+        red_rows(s_row, nq, acc);
+        __syncthreads();
       }
-      __syncthreads();
+      PS();  // 3: CTA rows summed
       double* part = A.partials + (size_t)(iterCount & 1) * gridDim.x * LO_NRED;
-      if (threadIdx.x < LO_NRED) {
-        double v = 0.0;
-        for (int w = 0; w < LM_WARPS; w++) v += s_red[w][threadIdx.x];
-        part[(size_t)blockIdx.x * LO_NRED + threadIdx.x] = v;
-      }
-      __threadfence();
-      grid.sync();
-      if (threadIdx.x < LO_NRED) {
-        double v = 0.0;
-        for (int b = 0; b < (int)gridDim.x; b++) v += __ldcg(&part[(size_t)b * LO_NRED + threadIdx.x]);
-        s_tot[threadIdx.x] = v;
-      }
-      __syncthreads();
+      red_finish(grid, acc, part, s_g, s_tot, 1, clk);  // stamps 4 (before barrier), 5 (after)
+      PS();  // 6: partials summed
       if (threadIdx.x == 0) {
         s_stop = 0;
         int laserCloudSelNum = (int)s_tot[27];
@@ -238,6 +265,7 @@ __global__ void __launch_bounds__(LM_THREADS) lm_optimize(LMOptArgs A) {
         }
       }
       __syncthreads();
+      PS();  // 7: solve done
       if (s_stop) break;
     }
   }
@@ -254,6 +282,8 @@ __global__ void __launch_bounds__(LM_THREADS) lm_optimize(LMOptArgs A) {
     st->iters = iters_done;
     st->rows = s_rows;
   }
+  if (clk >= 0) g_phase_clk[1][0] = clk - 1;
+#undef PS
 }
 
 // ---- map update ------------------------------------------------------------------------------

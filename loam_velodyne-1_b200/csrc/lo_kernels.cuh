@@ -46,6 +46,9 @@ struct LOArgs {
   unsigned char* row_valid;     // [max_iter][fcap]
   double* partials;             // [2][gridDim][LO_NRED]
   const ImuState* imu;          // imuTrans of this sweep
+  const int* corner_roff;       // [n_scans + 1] first index of every ring inside corner_last
+  const int* surf_roff;         // same for surf_last
+  int n_scans;
   int fcap;
   int max_iter;
 };
@@ -154,46 +157,65 @@ __device__ __forceinline__ void warp_argmin(float& d, int& ord, int& idx) {
   }
 }
 
-// corner correspondence :478-527 for one feature (warp cooperative)
-__device__ void lo_corner_search(const LOArgs& A, const float4 sel, int n_sharp, int n_last, int& ind1, int& ind2) {
+// ring of position i in a ring-major cloud: largest r with roff[r] <= i (roff has R+1 entries).
+// The "last" clouds are ring-major by construction (scanRegistration emits ring -> sector -> pick
+// order / ring -> voxel order) and int(intensity) of every point equals its ring, so this is the
+// same value as the reference's int(laserCloud*Last->points[i].intensity) without a dependent load.
+__device__ __forceinline__ int lo_ring_of(const int* roff, int R, int i) {
+  int lo = 0, hi = R - 1;
+  while (lo < hi) {
+    int mid = (lo + hi + 1) >> 1;
+    if (roff[mid] <= i) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+// corner correspondence :478-527 for one feature (warp cooperative).  The reference's two linear
+// scans stop at the first point whose ring leaves (c-2.5, c+2.5); with the ring offset table the
+// window is known up front, so every load below is independent (no load -> ballot -> load chain).
+__device__ void lo_corner_search(const LOArgs& A, const int* roff, int R, const float4 sel, int n_sharp, int n_last, int& ind1, int& ind2) {
   const int lane = lane_id();
   int bi; float bd;
   grid_nn1_warp(A.corner_grid, sel.x, sel.y, sel.z, 25.f, bi, bd);
   int closestPointInd = -1, minPointInd2 = -1;
   if (bi >= 0 && bd < 25) {
     closestPointInd = bi;
-    int closestPointScan = int(A.corner_last[closestPointInd].w);
+    const int c = lo_ring_of(roff, R, bi);   // closestPointScan
     float best = 25.f; int bord = 0x7fffffff, bidx = -1;
-    int jend = min(n_sharp, n_last);  // forward bound is cornerPointsSharpNum (:486), kept
-    bool stop = false;
-    for (int base = closestPointInd + 1; base < jend && !stop; base += 32) {
-      int j = base + lane;
-      bool in = j < jend;
-      float4 pj = in ? A.corner_last[j] : make_float4(0, 0, 0, 0);
-      bool brk = in && (int(pj.w) > closestPointScan + 2.5);
-      unsigned int bm = __ballot_sync(0xffffffffu, brk);
-      int firstbrk = bm ? __ffs(bm) - 1 : 32;
-      if (in && lane < firstbrk && int(pj.w) > closestPointScan) {
-        float dd = lo_sqdist(pj, sel);
-        int ord = j - (closestPointInd + 1);
-        if (dd < best || (dd == best && ord < bord)) { best = dd; bord = ord; bidx = j; }
+    const int jend = min(n_sharp, n_last);  // forward bound is cornerPointsSharpNum (:486), kept
+    // forward: j > closest, ring in (c, c+2.5]  <=>  roff[c+1] <= j < roff[c+3]
+    {
+      const int a0 = max(bi + 1, roff[min(c + 1, R)]), b0 = min(jend, roff[min(c + 3, R)]);
+      for (int j0 = a0 + lane; j0 < b0; j0 += 128) {
+        float4 pc[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) pc[u] = __ldg(&A.corner_last[min(j0 + 32 * u, b0 - 1)]);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const int j = j0 + 32 * u;
+          if (j >= b0) break;
+          float dd = lo_sqdist(pc[u], sel);
+          int ord = j - (bi + 1);
+          if (dd < best || (dd == best && ord < bord)) { best = dd; bord = ord; bidx = j; }
+        }
       }
-      if (bm) stop = true;
     }
-    stop = false;
-    for (int base = closestPointInd - 1; base >= 0 && !stop; base -= 32) {
-      int j = base - lane;
-      bool in = j >= 0;
-      float4 pj = in ? A.corner_last[j] : make_float4(0, 0, 0, 0);
-      bool brk = in && (int(pj.w) < closestPointScan - 2.5);
-      unsigned int bm = __ballot_sync(0xffffffffu, brk);
-      int firstbrk = bm ? __ffs(bm) - 1 : 32;
-      if (in && lane < firstbrk && int(pj.w) < closestPointScan) {
-        float dd = lo_sqdist(pj, sel);
-        int ord = 0x40000000 + (closestPointInd - 1 - j);
-        if (dd < best || (dd == best && ord < bord)) { best = dd; bord = ord; bidx = j; }
+    // backward: j < closest, ring in [c-2.5, c)  <=>  roff[c-2] <= j < roff[c]
+    {
+      const int a0 = roff[max(c - 2, 0)], b0 = min(bi, roff[c]);
+      for (int j0 = b0 - 1 - lane; j0 >= a0; j0 -= 128) {
+        float4 pc[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) pc[u] = __ldg(&A.corner_last[max(j0 - 32 * u, a0)]);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const int j = j0 - 32 * u;
+          if (j < a0) break;
+          float dd = lo_sqdist(pc[u], sel);
+          int ord = 0x40000000 + (bi - 1 - j);
+          if (dd < best || (dd == best && ord < bord)) { best = dd; bord = ord; bidx = j; }
+        }
       }
-      if (bm) stop = true;
     }
     warp_argmin(best, bord, bidx);
     if (best < 25.f) minPointInd2 = bidx;
@@ -203,54 +225,58 @@ __device__ void lo_corner_search(const LOArgs& A, const float4 sel, int n_sharp,
 }
 
 // surf correspondence :590-650
-__device__ void lo_surf_search(const LOArgs& A, const float4 sel, int n_flat, int n_last, int& ind1, int& ind2, int& ind3) {
+__device__ void lo_surf_search(const LOArgs& A, const int* roff, int R, const float4 sel, int n_flat, int n_last, int& ind1, int& ind2, int& ind3) {
   const int lane = lane_id();
   int bi; float bd;
   grid_nn1_warp(A.surf_grid, sel.x, sel.y, sel.z, 25.f, bi, bd);
   int closestPointInd = -1, minPointInd2 = -1, minPointInd3 = -1;
   if (bi >= 0 && bd < 25) {
     closestPointInd = bi;
-    int closestPointScan = int(A.surf_last[closestPointInd].w);
+    const int c = lo_ring_of(roff, R, bi);
     float best2 = 25.f, best3 = 25.f;
     int ord2 = 0x7fffffff, ord3 = 0x7fffffff, idx2 = -1, idx3 = -1;
-    int jend = min(n_flat, n_last);  // forward bound is surfPointsFlatNum (:598), kept
-    bool stop = false;
-    for (int base = closestPointInd + 1; base < jend && !stop; base += 32) {
-      int j = base + lane;
-      bool in = j < jend;
-      float4 pj = in ? A.surf_last[j] : make_float4(0, 0, 0, 0);
-      bool brk = in && (int(pj.w) > closestPointScan + 2.5);
-      unsigned int bm = __ballot_sync(0xffffffffu, brk);
-      int firstbrk = bm ? __ffs(bm) - 1 : 32;
-      if (in && lane < firstbrk) {
-        float dd = lo_sqdist(pj, sel);
-        int ord = j - (closestPointInd + 1);
-        if (int(pj.w) <= closestPointScan) {
+    const int jend = min(n_flat, n_last);  // forward bound is surfPointsFlatNum (:598), kept
+    // forward: ring <= c (same ring) feeds minPointInd2, ring in (c, c+2.5] feeds minPointInd3
+    {
+      const int a0 = bi + 1, b0 = min(jend, roff[min(c + 3, R)]), split = roff[min(c + 1, R)];
+      for (int j0 = a0 + lane; j0 < b0; j0 += 128) {
+        float4 pc[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) pc[u] = __ldg(&A.surf_last[min(j0 + 32 * u, b0 - 1)]);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+        const int j = j0 + 32 * u;
+        if (j >= b0) break;
+        float dd = lo_sqdist(pc[u], sel);
+        int ord = j - (bi + 1);
+        if (j < split) {
           if (dd < best2 || (dd == best2 && ord < ord2)) { best2 = dd; ord2 = ord; idx2 = j; }
         } else {
           if (dd < best3 || (dd == best3 && ord < ord3)) { best3 = dd; ord3 = ord; idx3 = j; }
         }
+        }
       }
-      if (bm) stop = true;
     }
-    stop = false;
-    for (int base = closestPointInd - 1; base >= 0 && !stop; base -= 32) {
-      int j = base - lane;
-      bool in = j >= 0;
-      float4 pj = in ? A.surf_last[j] : make_float4(0, 0, 0, 0);
-      bool brk = in && (int(pj.w) < closestPointScan - 2.5);
-      unsigned int bm = __ballot_sync(0xffffffffu, brk);
-      int firstbrk = bm ? __ffs(bm) - 1 : 32;
-      if (in && lane < firstbrk) {
-        float dd = lo_sqdist(pj, sel);
-        int ord = 0x40000000 + (closestPointInd - 1 - j);
-        if (int(pj.w) >= closestPointScan) {
+    // backward: ring >= c (same ring) feeds minPointInd2, ring in [c-2.5, c) feeds minPointInd3
+    {
+      const int a0 = roff[max(c - 2, 0)], split = roff[c];
+      for (int j0 = bi - 1 - lane; j0 >= a0; j0 -= 128) {
+        float4 pc[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) pc[u] = __ldg(&A.surf_last[max(j0 - 32 * u, a0)]);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+        const int j = j0 - 32 * u;
+        if (j < a0) break;
+        float dd = lo_sqdist(pc[u], sel);
+        int ord = 0x40000000 + (bi - 1 - j);
+        if (j >= split) {
           if (dd < best2 || (dd == best2 && ord < ord2)) { best2 = dd; ord2 = ord; idx2 = j; }
         } else {
           if (dd < best3 || (dd == best3 && ord < ord3)) { best3 = dd; ord3 = ord; idx3 = j; }
         }
+        }
       }
-      if (bm) stop = true;
     }
     warp_argmin(best2, ord2, idx2);
     warp_argmin(best3, ord3, idx3);
@@ -314,9 +340,9 @@ __device__ __forceinline__ bool lo_surf_residual(const float4 pointSel, const fl
   return (s > 0.1 && pd2 != 0);
 }
 
-// one Jacobian row :709-763 -> accumulate into acc[28] (upper triangle of AtA, AtB, count)
-__device__ __forceinline__ void lo_row_accumulate(const float4 pointOri, const float4 coeffv, const float* tr6 /*srx,crx,sry,cry,srz,crz*/,
-                                                  const float* transform, double* acc) {
+// one Jacobian row :709-763 -> a[6], b
+__device__ __forceinline__ void lo_row(const float4 pointOri, const float4 coeffv, const float* tr6 /*srx,crx,sry,cry,srz,crz*/,
+                                       const float* transform, float* a, float& b) {
   float s = 1;
   float srx = tr6[0], crx = tr6[1], sry = tr6[2], cry = tr6[3], srz = tr6[4], crz = tr6[5];
   float tx = s * transform[3];
@@ -349,16 +375,8 @@ __device__ __forceinline__ void lo_row_accumulate(const float4 pointOri, const f
             - s*(sry*srz - cry*crz*srx) * coeff.z;
   float atz = s*crx*sry * coeff.x - s*srx * coeff.y - s*crx*cry * coeff.z;
   float d2 = coeffv.w;
-  float b = -0.05 * d2;
-  float a[6] = {arx, ary, arz, atx, aty, atz};
-  int k = 0;
-#pragma unroll
-  for (int i = 0; i < 6; i++)
-#pragma unroll
-    for (int j = i; j < 6; j++) acc[k++] += (double)a[i] * (double)a[j];
-#pragma unroll
-  for (int i = 0; i < 6; i++) acc[21 + i] += (double)a[i] * (double)b;
-  acc[27] += 1.0;
+  b = -0.05 * d2;
+  a[0] = arx; a[1] = ary; a[2] = arz; a[3] = atx; a[4] = aty; a[5] = atz;
 }
 
 }  // namespace loamgpu

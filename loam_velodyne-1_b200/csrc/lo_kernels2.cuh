@@ -8,37 +8,54 @@ namespace loamgpu {
 // (iteration 0) eigen-degeneracy analysis, projection.  laserOdometry.cpp:765-797 /
 // laserMapping.cpp:922-954.  tot[0..20] upper triangle of AtA, tot[21..26] AtB.
 __device__ __forceinline__ void lm_solve_step(const double* tot, bool first_iter, float eig_thresh, int* isDegenerate, float* matP, float* X) {
-  float AtA[36], AtB[6], A2[36];
-  int k = 0;
-  for (int i = 0; i < 6; i++)
-    for (int j = i; j < 6; j++) {
-      float v = (float)tot[k++];
-      AtA[i * 6 + j] = v;
-      AtA[j * 6 + i] = v;
-    }
-  for (int i = 0; i < 6; i++) AtB[i] = (float)tot[21 + i];
+  float AtA[36], A2[36], b2[6];
+  {
+    int k = 0;
+#pragma unroll
+    for (int i = 0; i < 6; i++)
+#pragma unroll
+      for (int j = i; j < 6; j++) {
+        float v = (float)tot[k++];
+        AtA[i * 6 + j] = v;
+        AtA[j * 6 + i] = v;
+      }
+  }
+#pragma unroll
+  for (int i = 0; i < 6; i++) b2[i] = (float)tot[21 + i];
+#pragma unroll
   for (int i = 0; i < 36; i++) A2[i] = AtA[i];
-  float b2[6];
-  for (int i = 0; i < 6; i++) b2[i] = AtB[i];
-  int ok = la::qr_solve(A2, 6, 6, b2, 1);
+  int ok = la::qr_solve_fixed<6, 6>(A2, b2);
+#pragma unroll
   for (int i = 0; i < 6; i++) X[i] = ok ? b2[i] : 0.f;
   if (first_iter) {
-    float E[6], V[36], V2[36], Vc[36], Vinv[36];
-    for (int i = 0; i < 36; i++) A2[i] = AtA[i];
-    la::jacobi_eigen(A2, E, V, 6);
-    for (int i = 0; i < 36; i++) V2[i] = V[i];
-    *isDegenerate = 0;
-    for (int i = 5; i >= 0; i--) {
-      if (E[i] < eig_thresh) {
-        for (int j = 0; j < 6; j++) V2[i * 6 + j] = 0;
-        *isDegenerate = 1;
-      } else {
-        break;
+    // cv::eigen + threshold scan only decides isDegenerate (and matP, which is read only when
+    // isDegenerate is set).  If A - tau*I is positive definite with tau comfortably above the
+    // threshold (margin >> the fp32 Jacobi's eigenvalue error ~ 1e-6 * trace), every computed
+    // eigenvalue is >= threshold and the outcome is known without the decomposition.
+    double trace = 0.0;
+#pragma unroll
+    for (int i = 0; i < 6; i++) trace += (double)AtA[i * 6 + i];
+    if (la::spd6_above(AtA, (double)eig_thresh + 1.0e-4 * trace)) {
+      *isDegenerate = 0;
+      for (int i = 0; i < 36; i++) matP[i] = (i % 7 == 0) ? 1.f : 0.f;
+    } else {
+      float E[6], V[36], V2[36], Vc[36], Vinv[36];
+      for (int i = 0; i < 36; i++) A2[i] = AtA[i];
+      la::jacobi_eigen(A2, E, V, 6);
+      for (int i = 0; i < 36; i++) V2[i] = V[i];
+      *isDegenerate = 0;
+      for (int i = 5; i >= 0; i--) {
+        if (E[i] < eig_thresh) {
+          for (int j = 0; j < 6; j++) V2[i * 6 + j] = 0;
+          *isDegenerate = 1;
+        } else {
+          break;
+        }
       }
+      for (int i = 0; i < 36; i++) Vc[i] = V[i];
+      la::lu_inverse(Vc, Vinv, 6);
+      la::gemm(Vinv, V2, matP, 6, 6, 6);
     }
-    for (int i = 0; i < 36; i++) Vc[i] = V[i];
-    la::lu_inverse(Vc, Vinv, 6);
-    la::gemm(Vinv, V2, matP, 6, 6, 6);
   }
   if (*isDegenerate) {
     float X2[6];
@@ -80,20 +97,111 @@ __device__ __forceinline__ void lo_integrate(LOState* st, const float* transform
   transformSum[3] = tx; transformSum[4] = ty; transformSum[5] = tz;
 }
 
-// The whole per-sweep LM loop :458-856 as one cooperative kernel.
-__global__ void __launch_bounds__(LO_THREADS) lo_optimize(LOArgs A) {
+// ---- deterministic reductions shared by lo_optimize and lm_optimize ---------------------------
+// rows: [n][8] floats = a[0..5], b, valid.  28 sums (21 upper AtA, 6 AtB, row count) in fp64.
+constexpr int RED_GROUPS = 8;
+__device__ __forceinline__ void red_entry(int e, int& ri, int& rj) {
+  ri = 0; rj = 0;
+  if (e < 21) {
+    int k = e, i = 0;
+    while (k >= 6 - i) { k -= 6 - i; i++; }
+    ri = i; rj = i + k;
+  } else if (e < 27) { ri = e - 21; rj = 6; }
+}
+// thread (e = t % 28, grp = t / 28), t < 28 * RED_GROUPS, adds rows grp*len .. (grp+1)*len-1 of
+// this pass to its running sum `acc` (ascending row order inside a group)
+__device__ __forceinline__ void red_rows(const float (*rows)[8], int n, double& acc) {
+  const int t = threadIdx.x;
+  if (t >= LO_NRED * RED_GROUPS) return;
+  const int e = t % LO_NRED, grp = t / LO_NRED;
+  int ri, rj;
+  red_entry(e, ri, rj);
+  const int len = (n + RED_GROUPS - 1) / RED_GROUPS;
+  const int r0 = grp * len, r1 = min(n, r0 + len);
+  for (int r = r0; r < r1; r++) {
+    if (rows[r][7] != 0.f) {
+      if (e < 27) acc += (double)rows[r][ri] * (double)rows[r][rj];
+      else acc += 1.0;
+    }
+  }
+}
+// same for rows laid out [warp][32] of which only slots < used per warp can be valid; group grp
+// covers warps grp*wpg .. grp*wpg+wpg-1
+__device__ __forceinline__ void red_rows_warped(const float (*rows)[8], int nwarps, int used, double& acc) {
+  const int t = threadIdx.x;
+  if (t >= LO_NRED * RED_GROUPS) return;
+  const int e = t % LO_NRED, grp = t / LO_NRED;
+  int ri, rj;
+  red_entry(e, ri, rj);
+  const int wpg = (nwarps + RED_GROUPS - 1) / RED_GROUPS;
+  for (int w = grp * wpg; w < min(nwarps, (grp + 1) * wpg); w++)
+    for (int l = 0; l < used; l++) {
+      const float* row = rows[w * 32 + l];
+      if (row[7] != 0.f) {
+        if (e < 27) acc += (double)row[ri] * (double)row[rj];
+        else acc += 1.0;
+      }
+    }
+}
+// CTA total = groups in ascending order -> partials[blockIdx]; one grid barrier; every CTA then
+// sums all partials (16 interleaved lanes per entry, then ascending) into s_tot[28].
+constexpr int PS_GROUPS = 16;
+__device__ __forceinline__ void red_finish(cg::grid_group& grid, double acc, double* part, double (*s_g)[LO_NRED], double* s_tot, int which, int& clk) {
+  const int t = threadIdx.x;
+  if (t < LO_NRED * RED_GROUPS) s_g[t / LO_NRED][t % LO_NRED] = acc;
+  __syncthreads();
+  if (t < LO_NRED) {
+    double v = 0.0;
+#pragma unroll
+    for (int g = 0; g < RED_GROUPS; g++) v += s_g[g][t];
+    part[(size_t)blockIdx.x * LO_NRED + t] = v;
+  }
+  __threadfence();
+  if (clk >= 0) phase_stamp(which, clk);
+  grid.sync();
+  if (clk >= 0) phase_stamp(which, clk);
+  if (t < LO_NRED * PS_GROUPS) {
+    const int e = t % LO_NRED, g = t / LO_NRED;
+    double v = 0.0;
+    for (int b = g; b < (int)gridDim.x; b += PS_GROUPS) v += __ldcg(&part[(size_t)b * LO_NRED + e]);
+    s_g[g][e] = v;
+  }
+  __syncthreads();
+  if (t < LO_NRED) {
+    double v = 0.0;
+#pragma unroll
+    for (int g = 0; g < PS_GROUPS; g++) v += s_g[g][t];
+    s_tot[t] = v;
+  }
+  __syncthreads();
+}
+
+// The whole per-sweep LM loop :458-856 as one cooperative kernel.  Every CTA owns a contiguous
+// slice of the features, one warp per feature.
+__global__ void __launch_bounds__(LO_THREADS, 1) lo_optimize(LOArgs A) {
   cg::grid_group grid = cg::this_grid();
   __shared__ float s_tr[6];
   __shared__ float s_trig[6];
   __shared__ float s_imu[12];
   __shared__ float s_matP[36];
   __shared__ int s_deg, s_stop;
-  __shared__ double s_red[LO_WARPS][LO_NRED];
+  __shared__ double s_g[PS_GROUPS][LO_NRED];
   __shared__ double s_tot[LO_NRED];
   __shared__ int s_rows;
+  __shared__ int s_roff[2][SR_MAX_RINGS + 1];
+  __shared__ float s_row[LO_WARPS * 32][8];     // one row per (feature of this pass, iteration slab)
+  __shared__ float4 s_tri[LO_WARPS][3];         // tripod of the warp's first-pass feature
+  __shared__ int s_triok[LO_WARPS];
   const int lane = lane_id(), warp = threadIdx.x >> 5;
-  const int gwarp = blockIdx.x * LO_WARPS + warp, nwarps = gridDim.x * LO_WARPS;
   LOState* st = A.st;
+  int clk = (blockIdx.x == 0 && threadIdx.x == 0 && g_phase_on) ? 1 : -1;
+#define PS() do { if (clk >= 0) phase_stamp(0, clk); } while (0)
+  PS();
+  const int R = A.n_scans;
+  for (int i = threadIdx.x; i < 2 * (R + 1); i += LO_THREADS) {
+    int T = i / (R + 1), r = i % (R + 1);
+    s_roff[T][r] = T ? A.surf_roff[r] : A.corner_roff[r];
+  }
   if (threadIdx.x == 0) {
     lo_load_imu(A.imu, s_imu);
     const float scanPeriod = 0.1;
@@ -109,85 +217,100 @@ __global__ void __launch_bounds__(LO_THREADS) lo_optimize(LOArgs A) {
   const int n_sharp = A.cnt->n_sharp, n_flat = A.cnt->n_flat;
   const int F = n_sharp + n_flat;
   const int n_corner_last = st->n_corner_last, n_surf_last = st->n_surf_last;
+  const int per = (F + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int f_lo = min((int)blockIdx.x * per, F), f_hi = min(f_lo + per, F);
   int iters_done = 0;
   if (st->cornerLastNum > 10 && st->surfLastNum > 100) {  // :465
     for (int iterCount = 0; iterCount < A.max_iter; iterCount++) {
       iters_done = iterCount + 1;
       const bool refresh = (iterCount % 5 == 0);
-      // ---- features: transform, (search), residual -> row slab of this iteration ----
-      for (int f = gwarp; f < F; f += nwarps) {
-        const bool is_corner = f < n_sharp;
-        const float4 pt = is_corner ? A.sharp[f] : A.flat[f - n_sharp];
-        const float4 sel = lo_transform_to_start(pt, s_tr);
-        bool valid = false;
-        float4 coeff = make_float4(0, 0, 0, 0);
-        if (is_corner) {
-          int i1, i2;
-          if (refresh) {
-            lo_corner_search(A, sel, n_sharp, n_corner_last, i1, i2);
-            if (lane == 0) { A.corner_ind1[f] = i1; A.corner_ind2[f] = i2; }
-          } else {
-            i1 = A.corner_ind1[f]; i2 = A.corner_ind2[f];
-          }
-          if (lane == 0 && i2 >= 0) valid = lo_corner_residual(sel, A.corner_last[i1], A.corner_last[i2], iterCount, coeff);
-        } else {
-          int g = f - n_sharp;
-          int i1, i2, i3;
-          if (refresh) {
-            lo_surf_search(A, sel, n_flat, n_surf_last, i1, i2, i3);
-            if (lane == 0) { A.surf_ind1[g] = i1; A.surf_ind2[g] = i2; A.surf_ind3[g] = i3; }
-          } else {
-            i1 = A.surf_ind1[g]; i2 = A.surf_ind2[g]; i3 = A.surf_ind3[g];
-          }
-          if (lane == 0 && i2 >= 0 && i3 >= 0)
-            valid = lo_surf_residual(sel, A.surf_last[i1], A.surf_last[i2], A.surf_last[i3], iterCount, coeff);
-        }
-        if (lane == 0) {
-          A.coeff[(size_t)iterCount * A.fcap + f] = coeff;
-          A.row_valid[(size_t)iterCount * A.fcap + f] = valid ? 1 : 0;
-        }
-      }
-      __syncwarp();
-      // ---- Jacobian of every row accumulated so far (rows are NOT cleared per iteration) ----
       if (threadIdx.x == 0) {
         s_trig[0] = dm::sin(s_tr[0]); s_trig[1] = dm::cos(s_tr[0]);
         s_trig[2] = dm::sin(s_tr[1]); s_trig[3] = dm::cos(s_tr[1]);
         s_trig[4] = dm::sin(s_tr[2]); s_trig[5] = dm::cos(s_tr[2]);
       }
       __syncthreads();
-      double acc[LO_NRED];
+      double acc = 0.0;
+      for (int c0 = f_lo; c0 < f_hi; c0 += LO_WARPS) {
+        const int f = c0 + warp;
+        const bool first_pass = (c0 == f_lo);
+        s_row[warp * 32 + lane][7] = 0.f;
+        if (f < f_hi) {
+          // ---- transform, (search), residual -> row slab of this iteration ----
+          const bool is_corner = f < n_sharp;
+          const float4 pt = is_corner ? A.sharp[f] : A.flat[f - n_sharp];
+          const float4 sel = lo_transform_to_start(pt, s_tr);
+          bool valid = false;
+          float4 coeff = make_float4(0, 0, 0, 0);
+          if (is_corner) {
+            int i1 = -1, i2 = -1;
+            float4 t1, t2;
+            bool have = false;
+            if (refresh) {
+              lo_corner_search(A, s_roff[0], R, sel, n_sharp, n_corner_last, i1, i2);
+              if (lane == 0) { A.corner_ind1[f] = i1; A.corner_ind2[f] = i2; }
+            } else if (first_pass) {
+              have = true;
+              i2 = s_triok[warp] ? 0 : -1;
+              t1 = s_tri[warp][0]; t2 = s_tri[warp][1];
+            } else {
+              i1 = A.corner_ind1[f]; i2 = A.corner_ind2[f];
+            }
+            if (lane == 0) {
+              if (!have && i2 >= 0) { t1 = A.corner_last[i1]; t2 = A.corner_last[i2]; }
+              if (refresh && first_pass) { s_triok[warp] = i2 >= 0 ? 1 : 0; if (i2 >= 0) { s_tri[warp][0] = t1; s_tri[warp][1] = t2; } }
+              if (i2 >= 0) valid = lo_corner_residual(sel, t1, t2, iterCount, coeff);
+            }
+          } else {
+            int g = f - n_sharp;
+            int i1 = -1, i2 = -1, i3 = -1;
+            float4 t1, t2, t3;
+            bool have = false;
+            if (refresh) {
+              lo_surf_search(A, s_roff[1], R, sel, n_flat, n_surf_last, i1, i2, i3);
+              if (lane == 0) { A.surf_ind1[g] = i1; A.surf_ind2[g] = i2; A.surf_ind3[g] = i3; }
+            } else if (first_pass) {
+              have = true;
+              i2 = i3 = s_triok[warp] ? 0 : -1;
+              t1 = s_tri[warp][0]; t2 = s_tri[warp][1]; t3 = s_tri[warp][2];
+            } else {
+              i1 = A.surf_ind1[g]; i2 = A.surf_ind2[g]; i3 = A.surf_ind3[g];
+            }
+            if (lane == 0) {
+              const bool ok = i2 >= 0 && i3 >= 0;
+              if (!have && ok) { t1 = A.surf_last[i1]; t2 = A.surf_last[i2]; t3 = A.surf_last[i3]; }
+              if (refresh && first_pass) { s_triok[warp] = ok ? 1 : 0; if (ok) { s_tri[warp][0] = t1; s_tri[warp][1] = t2; s_tri[warp][2] = t3; } }
+              if (ok) valid = lo_surf_residual(sel, t1, t2, t3, iterCount, coeff);
+            }
+          }
+          if (lane == 0) {
+            A.coeff[(size_t)iterCount * A.fcap + f] = coeff;
+            A.row_valid[(size_t)iterCount * A.fcap + f] = valid ? 1 : 0;
+          }
+          __syncwarp();
+          // ---- Jacobian of every row accumulated so far (rows are NOT cleared per iteration):
+          // lane k re-evaluates the row this feature produced in iteration k ----
+          if (lane <= iterCount) {
+            size_t slot = (size_t)lane * A.fcap + f;
+            if (A.row_valid[slot]) {
+              float a[6], b;
+              lo_row(pt, A.coeff[slot], s_trig, s_tr, a, b);
+              float* row = s_row[warp * 32 + lane];
 #pragma unroll
-      for (int k = 0; k < LO_NRED; k++) acc[k] = 0.0;
-      for (int f = gwarp; f < F; f += nwarps) {
-        if (lane <= iterCount) {
-          size_t slot = (size_t)lane * A.fcap + f;
-          if (A.row_valid[slot]) {
-            const float4 pt = f < n_sharp ? A.sharp[f] : A.flat[f - n_sharp];
-            lo_row_accumulate(pt, A.coeff[slot], s_trig, s_tr, acc);
+              for (int j = 0; j < 6; j++) row[j] = a[j];
+              row[6] = b;
+              row[7] = 1.f;
+            }
           }
         }
+        __syncthreads();
+        if (first_pass) PS();  // 0: features + rows of the first pass done
+        red_rows_warped(s_row, LO_WARPS, iterCount + 1, acc);
+        __syncthreads();
       }
-#pragma unroll
-      for (int k = 0; k < LO_NRED; k++) {
-        double v = acc[k];
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if (lane == 0) s_red[warp][k] = v;
-      }
-      __syncthreads();
       double* part = A.partials + (size_t)(iterCount & 1) * gridDim.x * LO_NRED;
-      if (threadIdx.x < LO_NRED) {
-        double v = 0.0;
-        for (int w = 0; w < LO_WARPS; w++) v += s_red[w][threadIdx.x];
-        part[(size_t)blockIdx.x * LO_NRED + threadIdx.x] = v;
-      }
-      __threadfence();
-      grid.sync();
-      if (threadIdx.x < LO_NRED) {
-        double v = 0.0;
-        for (int b = 0; b < (int)gridDim.x; b++) v += __ldcg(&part[(size_t)b * LO_NRED + threadIdx.x]);
-        s_tot[threadIdx.x] = v;
-      }
-      __syncthreads();
+      red_finish(grid, acc, part, s_g, s_tot, 0, clk);   // stamps 1 (before barrier), 2 (after)
+      PS();  // 3: partials summed
       if (threadIdx.x == 0) {
         s_stop = 0;
         int pointSelNum = (int)s_tot[27];
@@ -203,6 +326,7 @@ __global__ void __launch_bounds__(LO_THREADS) lo_optimize(LOArgs A) {
         }
       }
       __syncthreads();
+      PS();  // 4: solve done
       if (s_stop) break;
     }
   }
@@ -214,6 +338,8 @@ __global__ void __launch_bounds__(LO_THREADS) lo_optimize(LOArgs A) {
     st->iters = iters_done;
     st->rows = s_rows;
   }
+  if (clk >= 0) g_phase_clk[0][0] = clk - 1;
+#undef PS
 }
 
 // TransformToEnd over less-sharp -> corner_last, less-flat -> surf_last, (optionally) full ->
@@ -245,7 +371,16 @@ __global__ void __launch_bounds__(256) lo_transform_to_end_kernel(ToEndArgs A) {
 
 // bookkeeping after the swap (:901-903); mode 1 = first sweep (:427-456: plain adoption of the
 // clouds, transformSum seeded from the IMU, the *LastNum counters are NOT touched)
-__global__ void lo_finish(LOState* st, const SRCounts* cnt, const ImuState* imu, int first_sweep, int do_full) {
+__global__ void lo_finish(LOState* st, const SRCounts* cnt, const ImuState* imu, int first_sweep, int do_full,
+                          const int* ring_counts, int n_scans, int* corner_roff, int* surf_roff) {
+  // ring offset tables of the clouds that just became corner_last / surf_last (ring-major)
+  if (blockIdx.x == 0 && threadIdx.x < 2) {
+    int* roff = threadIdx.x ? surf_roff : corner_roff;
+    const int col = threadIdx.x ? 3 : 1;
+    int run = 0;
+    for (int r = 0; r < n_scans; r++) { roff[r] = run; run += ring_counts[r * 4 + col]; }
+    roff[n_scans] = run;
+  }
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   st->n_corner_last = cnt->n_less_sharp;
   st->n_surf_last = cnt->n_less_flat;

@@ -56,6 +56,19 @@ static int download_array(const T* dev, int count, T* out, int cap, int* n, cuda
 
 using namespace loamgpu;
 
+// test hook: phase clocks of lo_optimize (which = 0) / lm_optimize (1); see common.cuh
+extern "C" int loam_debug_phase_enable(int on) {
+  CUDA_OK(cudaMemcpyToSymbol(g_phase_on, &on, sizeof(int)));
+  return LOAM_OK;
+}
+extern "C" int loam_debug_phase_clocks(int which, long long* out, int n) {
+  if (which < 0 || which > 1 || !out || n < 0) return LOAM_ERR_ARG;
+  if (n > PHASE_CLK_N) n = PHASE_CLK_N;
+  CUDA_OK(cudaDeviceSynchronize());
+  CUDA_OK(cudaMemcpyFromSymbol(out, g_phase_clk, sizeof(long long) * n, sizeof(long long) * PHASE_CLK_N * which));
+  return LOAM_OK;
+}
+
 struct loam_sr { SRHandle h; };
 struct loam_lo { LOHandle h; };
 struct loam_lm { LMHandle h; };

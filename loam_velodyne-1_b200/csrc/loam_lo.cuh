@@ -18,7 +18,7 @@ struct LOHandle {
   DevBuf<LOState> d_state;
   DevBuf<float4> d_corner_last, d_surf_last, d_full_end, d_coeff;
   DevBuf<unsigned char> d_row_valid;
-  DevBuf<int> d_c1, d_c2, d_s1, d_s2, d_s3;
+  DevBuf<int> d_c1, d_c2, d_s1, d_s2, d_s3, d_corner_roff, d_surf_roff;
   DevBuf<double> d_partials;
   GridStorage g_corner, g_surf;
   PinnedBuf<LOState> h_state;
@@ -48,6 +48,7 @@ struct LOHandle {
     r |= d_c1.alloc_zero(fcap, stream); r |= d_c2.alloc_zero(fcap, stream);
     r |= d_s1.alloc_zero(fcap, stream); r |= d_s2.alloc_zero(fcap, stream); r |= d_s3.alloc_zero(fcap, stream);
     r |= d_partials.alloc_zero((size_t)2 * coop_blocks * LO_NRED, stream);
+    r |= d_corner_roff.alloc_zero(SR_MAX_RINGS + 1, stream); r |= d_surf_roff.alloc_zero(SR_MAX_RINGS + 1, stream);
     r |= g_corner.alloc(cap, 1 << 21, stream); r |= g_surf.alloc(cap, 1 << 21, stream);
     r |= h_state.alloc(1);
     if (r != LOAM_OK) return LOAM_ERR_CUDA;
@@ -76,7 +77,7 @@ struct LOHandle {
     const int nb = 148;
     if (!systemInited) {  // :427-456
       LAUNCH("lo_adopt_first", lo_adopt_first, nb, 256, 0, stream, sr.d_cnt.p, sr.d_less_sharp.p, sr.d_less_flat.p, d_corner_last.p, d_surf_last.p);
-      LAUNCH("lo_finish", lo_finish, 1, 32, 0, stream, d_state.p, sr.d_cnt.p, imu, 1, 0);
+      LAUNCH("lo_finish", lo_finish, 1, 32, 0, stream, d_state.p, sr.d_cnt.p, imu, 1, 0, sr.d_ring_counts.p, P.n_scans, d_corner_roff.p, d_surf_roff.p);
       int r = grid_build_pair(gp, nb, stream);
       if (r != LOAM_OK) return r;
       systemInited = true;
@@ -89,6 +90,7 @@ struct LOHandle {
     A.corner_grid = g_corner.view(); A.surf_grid = g_surf.view();
     A.corner_ind1 = d_c1.p; A.corner_ind2 = d_c2.p; A.surf_ind1 = d_s1.p; A.surf_ind2 = d_s2.p; A.surf_ind3 = d_s3.p;
     A.coeff = d_coeff.p; A.row_valid = d_row_valid.p; A.partials = d_partials.p; A.imu = imu;
+    A.corner_roff = d_corner_roff.p; A.surf_roff = d_surf_roff.p; A.n_scans = P.n_scans;
     A.fcap = fcap; A.max_iter = P.lo_max_iter;
     {
       void* args[] = {&A};
@@ -104,7 +106,7 @@ struct LOHandle {
     T.less_sharp = sr.d_less_sharp.p; T.less_flat = sr.d_less_flat.p; T.full = sr.d_full.p;
     T.corner_last = d_corner_last.p; T.surf_last = d_surf_last.p; T.full_end = d_full_end.p; T.do_full = do_full;
     LAUNCH("lo_transform_to_end", lo_transform_to_end_kernel, 2 * nb, 256, 0, stream, T);
-    LAUNCH("lo_finish", lo_finish, 1, 32, 0, stream, d_state.p, sr.d_cnt.p, imu, 0, do_full);
+    LAUNCH("lo_finish", lo_finish, 1, 32, 0, stream, d_state.p, sr.d_cnt.p, imu, 0, do_full, sr.d_ring_counts.p, P.n_scans, d_corner_roff.p, d_surf_roff.p);
     int r = grid_build_pair(gp, nb, stream);
     if (r != LOAM_OK) return r;
     if (do_full) { frameCount = 0; *published = true; }  // :910-911

@@ -46,7 +46,7 @@ def test_device_linalg_equals_opencv_golden(pkg):
     def run(op, A, b, m, n):
         A = np.ascontiguousarray(A, np.float32)
         batch = A.shape[0]
-        outw = n if op == 0 else (n + n * n if op == 1 else n * n)
+        outw = n if op in (0, 3) else (n + n * n if op in (1, 4) else n * n)
         out = np.zeros((batch, outw), np.float32)
         bb = np.ascontiguousarray(b, np.float32) if b is not None else np.zeros((batch, m), np.float32)
         assert L.loam_debug_linalg(op, A.ctypes.data, bb.ctypes.data, out.ctypes.data, m, n, batch) == 0
@@ -59,6 +59,19 @@ def test_device_linalg_equals_opencv_golden(pkg):
         assert biteq(o[:, :n], G[f"eig{n}_w"])
         assert biteq(o[:, n:].reshape(-1, n, n), G[f"eig{n}_v"])
     assert biteq(run(2, G["inv6_A"], None, 6, 6).reshape(-1, 6, 6), G["inv6_inv"])
+    # the register-resident specialisations used on the hot paths give the same bits
+    assert biteq(run(3, G["qr6_A"], G["qr6_b"], 6, 6), G["qr6_x"])
+    assert biteq(run(3, G["qr53_A"], -np.ones((200, 5), np.float32), 5, 3), G["qr53_x"])
+    o = run(4, G["eig3_A"], None, 3, 3)
+    assert biteq(o[:, :3], G["eig3_w"])
+    assert biteq(o[:, 3:].reshape(-1, 3, 3), G["eig3_v"])
+    # near-degenerate 3x3 inputs (repeated / zero eigenvalues) exercise the pivot bookkeeping
+    rng = np.random.default_rng(7)
+    B = rng.standard_normal((500, 3, 1)).astype(np.float32) * rng.uniform(0.01, 3.0, (500, 1, 1)).astype(np.float32)
+    A3 = (B @ B.transpose(0, 2, 1)).astype(np.float32)
+    A3[::3] += np.eye(3, dtype=np.float32) * 1e-3
+    A3[5::7] = 0
+    assert biteq(run(4, A3, None, 3, 3), run(1, A3, None, 3, 3))
 
 
 @pytest.mark.parametrize("n", [0, 1, 31, 4096, 4097, 100_003, 1_500_000])
