@@ -184,6 +184,10 @@ int loam_debug_voxel_filter(const float* xyzi, int n, float leaf, float* out, in
 int loam_debug_phase_enable(int on);
 int loam_debug_phase_clocks(int which, long long* out, int n);
 
+/* map-update statistics of the last mapped sweep, 2 x 8 ints (corner, surf): merge cubes, general-path
+ * cubes, append-only cubes, max old points, max new points, points written, -, cubes gone dirty */
+int loam_debug_lm_counters(loam_lm* h, int* out, int n);
+
 /* number of kernel launches issued by this library on the calling process so far */
 long long loam_kernel_launch_count(void);
 /* per-kernel device time accumulated since the last reset (CUDA events; 0 when profiling is off) */

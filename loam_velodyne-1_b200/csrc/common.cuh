@@ -129,11 +129,28 @@ __device__ __forceinline__ float float_unflip(unsigned int u) {
 
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
 
+// lanes of the warp holding the same 8-bit digit (0 for idle lanes): eight ballots.  match.any
+// serialises over the distinct values of the warp (~0.3 us with random digits on sm_100), this
+// does not.
+__device__ __forceinline__ unsigned int warp_match8(int d, bool in) {
+  unsigned int m = __ballot_sync(0xffffffffu, in);
+#pragma unroll
+  for (int b = 0; b < 8; b++) {
+    const bool bit = (d >> b) & 1;
+    const unsigned int bal = __ballot_sync(0xffffffffu, bit);
+    m &= bit ? bal : ~bal;
+  }
+  return in ? m : 0u;
+}
+
 // phase clocks of the two persistent kernels (test hook, loam_debug_phase_clocks): when enabled,
 // thread 0 of CTA 0 stamps clock64() at the phase boundaries of every LM iteration
 constexpr int PHASE_CLK_N = 512;
 __device__ int g_phase_on = 0;
 __device__ long long g_phase_clk[2][PHASE_CLK_N];
+__device__ long long g_rf_clk[2 * 250 * 8];   // lm_refilter_cube: 8 stamps per (type, rank)
+__device__ long long g_dbg_clk[64];           // ad-hoc stamps of single-CTA kernels (dev only)
+#define DBG_STAMP(slot) do { if (g_phase_on && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_dbg_clk[slot] = clock64(); } while (0)
 __device__ __forceinline__ void phase_stamp(int which, int& slot) {
   if (slot >= 0 && slot < PHASE_CLK_N) g_phase_clk[which][slot++] = clock64();
 }

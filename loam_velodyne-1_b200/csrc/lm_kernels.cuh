@@ -21,7 +21,7 @@ constexpr int PROC_MAX = 250;                            // cubes rewritten per 
 constexpr int LM_THREADS = 512;
 constexpr int LM_WARPS = LM_THREADS / 32;
 
-struct CubeDesc { int off; int cnt; };
+struct CubeDesc { int off; int cnt; int dirty; int pad; };   // dirty: not known to be one point per voxel in voxel order (lm_refilter.cuh)
 
 struct LMImu {   // host-maintained ring buffer, laserMapping.cpp:102-108,323-335
   double time[IMU_Q];
@@ -53,13 +53,13 @@ struct LMState {
   // refilter plan (part 2)
   int nproc[2];
   int procCube[2][PROC_MAX];
-  int procInOff[2][PROC_MAX + 1];       // start of each processed cube's old points inside E
-  int procOldOff[2][PROC_MAX];
-  int procOldCnt[2][PROC_MAX];
-  int En[2];                            // number of elements in E (old points + all stack points)
-  int outOff[2];                        // where this sweep's block starts in the arena
-  int outCount[2];                      // points written by the refilter
-  int segCount[2][256];                 // output points per processed cube
+  int procMode[2][PROC_MAX];            // 1 = valid cube (refiltered), 0 = only appended to
+  int procNewCnt[2][PROC_MAX];          // new points of this sweep per processed cube
+  int procNewOff[2][PROC_MAX + 1];      // their start inside the sorted new-point list
+  int newSel[2];                        // which ping-pong buffer holds the sorted new-point list
+  int scratchBump[2];                   // general-path scratch allocation of this sweep
+  int rfStat[2][8];                     // last sweep: [0] merge cubes [1] general cubes [2] append cubes [3] max n_old
+                                        // [4] max n_new [5] points written [6] new-only voxels [7] cubes gone dirty
   int surroundN;                        // surround cloud size (LM-14)
   int surroundIn;
   int registeredN;                      // size of the registered full-resolution cloud
@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
           }
           int c0[3];
           c0[a] = 0; c0[(a + 1) % 3] = u; c0[(a + 2) % 3] = v;
-          cubes[c0[0] + CUBE_W * c0[1] + CUBE_W * CUBE_H * c0[2]].cnt = 0;
+          { CubeDesc& cd = cubes[c0[0] + CUBE_W * c0[1] + CUBE_W * CUBE_H * c0[2]]; cd.cnt = 0; cd.dirty = 0; }
         } else {
           for (int t = 0; t < n - 1; t++) {
             int cc[3], cp[3];
@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
           }
           int c0[3];
           c0[a] = n - 1; c0[(a + 1) % 3] = u; c0[(a + 2) % 3] = v;
-          cubes[c0[0] + CUBE_W * c0[1] + CUBE_W * CUBE_H * c0[2]].cnt = 0;
+          { CubeDesc& cd = cubes[c0[0] + CUBE_W * c0[1] + CUBE_W * CUBE_H * c0[2]]; cd.cnt = 0; cd.dirty = 0; }
         }
       }
     }
@@ -224,23 +224,46 @@ __global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
     s_ind[threadIdx.x] = in ? i + CUBE_W * j + CUBE_W * CUBE_H * k : -1;
   }
   __syncthreads();
+  __shared__ int s_vlist[125], s_nv;
+  __shared__ int s_cnt[2][128];
   if (threadIdx.x == 0) {
     int nv = 0, ns = 0;
     for (int q = 0; q < 125; q++) {  // (i, j, k) loop order == q order
       if (!s_in[q]) continue;
-      if (s_fov[q]) st->validInd[nv++] = s_ind[q];
+      if (s_fov[q]) { s_vlist[nv] = s_ind[q]; st->validInd[nv++] = s_ind[q]; }
       st->surroundInd[ns++] = s_ind[q];
     }
     st->validNum = nv; st->surroundNum = ns;
-    for (int T = 0; T < 2; T++) {
-      int off = 0;
-      for (int v = 0; v < nv; v++) { st->gatherOff[T][v] = off; off += A.cubes[T][st->validInd[v]].cnt; }
-      st->gatherOff[T][nv] = off;
-      st->mapN[T] = off;
-    }
-    st->optimize_enable = (st->mapN[0] > 10 && st->mapN[1] > 100) ? 1 : 0;  // :706
+    s_nv = nv;
     st->iters = 0; st->rows = 0;
   }
+  __syncthreads();
+  // offsets of the valid cubes inside the local map: the cube sizes are fetched in parallel
+  // (a serial loop here is 250 dependent global loads on the critical path of every mapped sweep)
+  const int nv = s_nv;
+  if (threadIdx.x < 250) {
+    const int T = threadIdx.x / 125, v = threadIdx.x % 125;
+    s_cnt[T][v] = v < nv ? A.cubes[T][s_vlist[v]].cnt : 0;
+  }
+  __syncthreads();
+  if (threadIdx.x < 64) {   // warp T scans its 125 counts
+    const int T = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int run = 0;
+    for (int v0 = 0; v0 < 128; v0 += 32) {
+      const int v = v0 + lane;
+      const int c = v < 125 ? s_cnt[T][v] : 0;
+      int x = c;
+      for (int o = 1; o < 32; o <<= 1) {
+        int y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
+      }
+      if (v < nv) st->gatherOff[T][v] = run + x - c;
+      run += __shfl_sync(0xffffffffu, x, 31);
+    }
+    if (lane == 0) { st->gatherOff[T][nv] = run; st->mapN[T] = run; s_cnt[T][127] = run; }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) st->optimize_enable = (s_cnt[0][127] > 10 && s_cnt[1][127] > 100) ? 1 : 0;  // :706
 }
 
 // K2: incoming clouds to the map with the predicted pose and back (:424-434, :683-691)

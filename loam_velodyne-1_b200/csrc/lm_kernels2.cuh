@@ -3,6 +3,7 @@
 #pragma once
 #include "lm_kernels.cuh"
 #include "sort_voxel.cuh"
+#include "lm_refilter.cuh"
 
 namespace loamgpu {
 
@@ -286,200 +287,7 @@ __global__ void __launch_bounds__(LM_THREADS, 1) lm_optimize(LMOptArgs A) {
 #undef PS
 }
 
-// ---- map update ------------------------------------------------------------------------------
-struct LMInsertArgs {
-  LMState* st;
-  const float4* stack[2];
-  float4* ins_pts[2];
-  int* ins_cube[2];
-  int* touch_cnt[2];
-};
-// K7a: stack points to the map with the refined pose and their cube (:980-1016)
-__global__ void __launch_bounds__(256) lm_insert_ids(LMInsertArgs A) {
-  const LMState* st = A.st;
-  __shared__ LMTrig s_g;
-  __shared__ float s_T[6];
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < 6; i++) s_T[i] = st->transformTobeMapped[i];
-    s_g = lm_trig(s_T);
-  }
-  __syncthreads();
-  const LMTrig g = s_g;
-  const int n0 = st->stackN[0], n1 = st->stackN[1];
-  for (int i = blockIdx.x * 256 + threadIdx.x; i < n0 + n1; i += gridDim.x * 256) {
-    int T = i < n0 ? 0 : 1;
-    int k = T ? i - n0 : i;
-    float4 pointSel = lm_to_map(A.stack[T][k], g, s_T);
-    int cubeI = lm_cube_coord(pointSel.x, st->cenW), cubeJ = lm_cube_coord(pointSel.y, st->cenH), cubeK = lm_cube_coord(pointSel.z, st->cenD);
-    int cube = -1;
-    if (cubeI >= 0 && cubeI < CUBE_W && cubeJ >= 0 && cubeJ < CUBE_H && cubeK >= 0 && cubeK < CUBE_D) {
-      cube = cubeI + CUBE_W * cubeJ + CUBE_W * CUBE_H * cubeK;
-      atomicAdd(&A.touch_cnt[T][cube], 1);
-    }
-    A.ins_pts[T][k] = pointSel;
-    A.ins_cube[T][k] = cube;
-  }
-}
-
-struct LMPlanArgs {
-  LMState* st;
-  CubeDesc* cubes[2];
-  int* touch_cnt[2];
-  int* cube_rank[2];
-  int ecap;
-};
-// K7b: one block.  Which cubes get rewritten this sweep and where their points sit inside E:
-// ranks 0..validNum-1 = the valid cubes (their old points ARE the local map, already in E),
-// then every other cube that received points (ascending cube index).
-__global__ void __launch_bounds__(1024) lm_refilter_plan(LMPlanArgs A) {
-  LMState* st = A.st;
-  __shared__ int s_scan[32];
-  __shared__ int s_carry;
-  for (int T = 0; T < 2; T++) {
-    const int nv = st->validNum;
-    for (int r = threadIdx.x; r < nv; r += 1024) {
-      int c = st->validInd[r];
-      A.cube_rank[T][c] = r;
-      st->procCube[T][r] = c;
-    }
-    for (int r = threadIdx.x; r < 256; r += 1024) st->segCount[T][r] = 0;
-    if (threadIdx.x == 0) s_carry = nv;
-    __syncthreads();
-    for (int base = 0; base < CUBE_NUM; base += 1024) {
-      int c = base + threadIdx.x;
-      int flag = (c < CUBE_NUM && A.touch_cnt[T][c] > 0 && A.cube_rank[T][c] < 0) ? 1 : 0;
-      int x = flag;
-      for (int o = 1; o < 32; o <<= 1) {
-        int y = __shfl_up_sync(0xffffffffu, x, o);
-        if (lane_id() >= o) x += y;
-      }
-      if (lane_id() == 31) s_scan[threadIdx.x >> 5] = x;
-      __syncthreads();
-      if (threadIdx.x < 32) {
-        int w = s_scan[threadIdx.x], s = w;
-        for (int o = 1; o < 32; o <<= 1) {
-          int y = __shfl_up_sync(0xffffffffu, s, o);
-          if (lane_id() >= o) s += y;
-        }
-        s_scan[threadIdx.x] = s - w;
-      }
-      __syncthreads();
-      int r = s_carry + s_scan[threadIdx.x >> 5] + x - flag;
-      if (flag) {
-        if (r < PROC_MAX) { A.cube_rank[T][c] = r; st->procCube[T][r] = c; }
-        else atomicOr(&st->error, 2);
-      }
-      __syncthreads();
-      if (threadIdx.x == 1023) s_carry = r + flag;
-      __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-      int np = min(s_carry, PROC_MAX);
-      st->nproc[T] = np;
-      int off = 0;
-      for (int r = 0; r < np; r++) {
-        CubeDesc d = A.cubes[T][st->procCube[T][r]];
-        st->procInOff[T][r] = off;
-        st->procOldOff[T][r] = d.off;
-        st->procOldCnt[T][r] = d.cnt;
-        off += d.cnt;
-      }
-      st->procInOff[T][np] = off;
-      int En = off + st->stackN[T];
-      st->outOff[T] = st->bump[T];
-      if (En > A.ecap) { atomicOr(&st->error, 8); En = 0; }
-      if (st->bump[T] + En > st->arenaCap) { atomicOr(&st->error, 1); En = 0; }
-      st->En[T] = En;
-    }
-    __syncthreads();
-  }
-}
-
-struct LMFillArgs {
-  LMState* st;
-  const float4* arena[2];
-  float4* E[2];
-  const float4* ins_pts[2];
-  const int* ins_cube[2];
-  const int* cube_rank[2];
-  unsigned int* keys[2];
-  unsigned int* vals[2];
-};
-// voxel coordinate of a map point relative to its cube, 8 bits per axis
-__device__ __forceinline__ unsigned int lm_voxel_key(const float4 p, int cube, const LMState* st, int T, int* error) {
-  const float inv = T == 0 ? (1.0f / 0.2f) : (1.0f / 0.4f);   // 5.0f / 2.5f exactly, as PCL computes 1/leaf
-  const int cells = T == 0 ? 250 : 125;
-  int ci = cube % CUBE_W, cj = (cube / CUBE_W) % CUBE_H, ck = cube / (CUBE_W * CUBE_H);
-  int bi = (ci - st->cenW) * cells - (cells + 1) / 2 - 1;
-  int bj = (cj - st->cenH) * cells - (cells + 1) / 2 - 1;
-  int bk = (ck - st->cenD) * cells - (cells + 1) / 2 - 1;
-  int gx = (int)floorf(p.x * inv) - bi, gy = (int)floorf(p.y * inv) - bj, gz = (int)floorf(p.z * inv) - bk;
-  if ((gx | gy | gz) & ~255) {
-    atomicOr(error, 4);
-    gx = min(max(gx, 0), 255); gy = min(max(gy, 0), 255); gz = min(max(gz, 0), 255);
-  }
-  return ((unsigned int)gz << 16) | ((unsigned int)gy << 8) | (unsigned int)gx;  // PCL order: idx = i + j*dx + k*dx*dy
-}
-// K7c: build E = [old points of the processed cubes][stack points in stack order] with sort keys
-__global__ void __launch_bounds__(256) lm_refilter_fill(LMFillArgs A) {
-  LMState* st = A.st;
-  const int T = blockIdx.y;
-  const int En = st->En[T];
-  const int np = st->nproc[T], nv = st->validNum;
-  const int total_old = st->procInOff[T][np];
-  for (int e = blockIdx.x * 256 + threadIdx.x; e < En; e += gridDim.x * 256) {
-    unsigned int key;
-    if (e < total_old) {
-      int lo = 0, hi = np - 1;  // last r with procInOff[r] <= e
-      while (lo < hi) {
-        int mid = (lo + hi + 1) >> 1;
-        if (st->procInOff[T][mid] <= e) lo = mid; else hi = mid - 1;
-      }
-      int r = lo;
-      int k = e - st->procInOff[T][r];
-      float4 p;
-      if (r < nv) p = A.E[T][e];  // already gathered as the local map
-      else { p = A.arena[T][st->procOldOff[T][r] + k]; A.E[T][e] = p; }
-      if (r < nv) key = ((unsigned int)r << 24) | lm_voxel_key(p, st->procCube[T][r], st, T, &st->error);
-      else key = ((unsigned int)r << 24) | (unsigned int)k;            // not refiltered: keep all, keep order
-    } else {
-      int i = e - total_old;
-      float4 p = A.ins_pts[T][i];
-      A.E[T][e] = p;
-      int cube = A.ins_cube[T][i];
-      int r = cube >= 0 ? A.cube_rank[T][cube] : -1;
-      if (r < 0) key = 0xffffffffu;                                      // outside the 21x11x21 window: dropped (:991-996)
-      else if (r < nv) key = ((unsigned int)r << 24) | lm_voxel_key(p, cube, st, T, &st->error);
-      else key = ((unsigned int)r << 24) | (unsigned int)(st->procOldCnt[T][r] + i);
-    }
-    A.keys[T][e] = key;
-    A.vals[T][e] = (unsigned int)e;
-  }
-}
-
-struct LMCommitArgs {
-  LMState* st;
-  CubeDesc* cubes[2];
-  int* touch_cnt[2];
-  int* cube_rank[2];
-};
-// K7e: new descriptors for the rewritten cubes; release the scratch tables
-__global__ void __launch_bounds__(1024) lm_refilter_commit(LMCommitArgs A) {
-  LMState* st = A.st;
-  for (int T = 0; T < 2; T++) {
-    if (threadIdx.x == 0 && st->En[T] > 0) {
-      int off = st->outOff[T];
-      for (int r = 0; r < st->nproc[T]; r++) {
-        CubeDesc d;
-        d.off = off; d.cnt = st->segCount[T][r];
-        A.cubes[T][st->procCube[T][r]] = d;
-        off += d.cnt;
-      }
-      st->bump[T] = off;
-    }
-    for (int c = threadIdx.x; c < CUBE_NUM; c += 1024) { A.touch_cnt[T][c] = 0; A.cube_rank[T][c] = -1; }
-  }
-}
+// ---- map update: lm_refilter.cuh ----
 
 // K8: registered full-resolution cloud (:1060-1063)
 __global__ void __launch_bounds__(256) lm_registered(LMState* st, const float4* in, const int* n_ptr, float4* out) {

@@ -239,12 +239,12 @@ __device__ void lo_surf_search(const LOArgs& A, const int* roff, int R, const fl
     // forward: ring <= c (same ring) feeds minPointInd2, ring in (c, c+2.5] feeds minPointInd3
     {
       const int a0 = bi + 1, b0 = min(jend, roff[min(c + 3, R)]), split = roff[min(c + 1, R)];
-      for (int j0 = a0 + lane; j0 < b0; j0 += 128) {
-        float4 pc[4];
+      for (int j0 = a0 + lane; j0 < b0; j0 += 256) {
+        float4 pc[8];
 #pragma unroll
-        for (int u = 0; u < 4; u++) pc[u] = __ldg(&A.surf_last[min(j0 + 32 * u, b0 - 1)]);
+        for (int u = 0; u < 8; u++) pc[u] = __ldg(&A.surf_last[min(j0 + 32 * u, b0 - 1)]);
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < 8; u++) {
         const int j = j0 + 32 * u;
         if (j >= b0) break;
         float dd = lo_sqdist(pc[u], sel);
@@ -260,12 +260,12 @@ __device__ void lo_surf_search(const LOArgs& A, const int* roff, int R, const fl
     // backward: ring >= c (same ring) feeds minPointInd2, ring in [c-2.5, c) feeds minPointInd3
     {
       const int a0 = roff[max(c - 2, 0)], split = roff[c];
-      for (int j0 = bi - 1 - lane; j0 >= a0; j0 -= 128) {
-        float4 pc[4];
+      for (int j0 = bi - 1 - lane; j0 >= a0; j0 -= 256) {
+        float4 pc[8];
 #pragma unroll
-        for (int u = 0; u < 4; u++) pc[u] = __ldg(&A.surf_last[max(j0 - 32 * u, a0)]);
+        for (int u = 0; u < 8; u++) pc[u] = __ldg(&A.surf_last[max(j0 - 32 * u, a0)]);
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < 8; u++) {
         const int j = j0 - 32 * u;
         if (j < a0) break;
         float dd = lo_sqdist(pc[u], sel);

@@ -374,12 +374,25 @@ __global__ void __launch_bounds__(256) lo_transform_to_end_kernel(ToEndArgs A) {
 __global__ void lo_finish(LOState* st, const SRCounts* cnt, const ImuState* imu, int first_sweep, int do_full,
                           const int* ring_counts, int n_scans, int* corner_roff, int* surf_roff) {
   // ring offset tables of the clouds that just became corner_last / surf_last (ring-major)
-  if (blockIdx.x == 0 && threadIdx.x < 2) {
-    int* roff = threadIdx.x ? surf_roff : corner_roff;
-    const int col = threadIdx.x ? 3 : 1;
-    int run = 0;
-    for (int r = 0; r < n_scans; r++) { roff[r] = run; run += ring_counts[r * 4 + col]; }
-    roff[n_scans] = run;
+  {
+    const int lane = threadIdx.x & 31;   // launched with one warp
+    for (int T = 0; T < 2; T++) {
+      int* roff = T ? surf_roff : corner_roff;
+      const int col = T ? 3 : 1;
+      int run = 0;
+      for (int r0 = 0; r0 < n_scans; r0 += 32) {
+        const int r = r0 + lane;
+        const int c = r < n_scans ? ring_counts[r * 4 + col] : 0;
+        int x = c;
+        for (int o = 1; o < 32; o <<= 1) {
+          int y = __shfl_up_sync(0xffffffffu, x, o);
+          if (lane >= o) x += y;
+        }
+        if (r < n_scans) roff[r] = run + x - c;
+        run += __shfl_sync(0xffffffffu, x, 31);
+      }
+      if (lane == 0) roff[n_scans] = run;
+    }
   }
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   st->n_corner_last = cnt->n_less_sharp;

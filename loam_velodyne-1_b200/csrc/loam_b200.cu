@@ -62,9 +62,20 @@ extern "C" int loam_debug_phase_enable(int on) {
   return LOAM_OK;
 }
 extern "C" int loam_debug_phase_clocks(int which, long long* out, int n) {
-  if (which < 0 || which > 1 || !out || n < 0) return LOAM_ERR_ARG;
-  if (n > PHASE_CLK_N) n = PHASE_CLK_N;
+  if (which == 3) {
+    if (n > 64) n = 64;
+    CUDA_OK(cudaDeviceSynchronize());
+    CUDA_OK(cudaMemcpyFromSymbol(out, g_dbg_clk, sizeof(long long) * n, 0));
+    return LOAM_OK;
+  }
+  if (which < 0 || which > 2 || !out || n < 0) return LOAM_ERR_ARG;
   CUDA_OK(cudaDeviceSynchronize());
+  if (which == 2) {
+    if (n > 2 * 250 * 8) n = 2 * 250 * 8;
+    CUDA_OK(cudaMemcpyFromSymbol(out, g_rf_clk, sizeof(long long) * n, 0));
+    return LOAM_OK;
+  }
+  if (n > PHASE_CLK_N) n = PHASE_CLK_N;
   CUDA_OK(cudaMemcpyFromSymbol(out, g_phase_clk, sizeof(long long) * n, sizeof(long long) * PHASE_CLK_N * which));
   return LOAM_OK;
 }

@@ -24,8 +24,9 @@ struct LMHandle {
   DevBuf<float4> d_arena[2][2];        // [type][A/B]
   DevBuf<float4> d_stack2[2], d_stack[2], d_E[2], d_ins_pts[2], d_registered, d_surround;
   DevBuf<int> d_ins_cube[2], d_nn[2];
-  DevBuf<unsigned int> d_skeys[2][2], d_svals[2][2], d_ekeys[2][2], d_evals[2][2], d_bbox[2];
-  DevBuf<int> d_shist[2], d_ehist[2], d_sdig[2], d_edig[2], d_sheads[2], d_eheads[2];
+  DevBuf<unsigned int> d_ins_key[2], d_nk[2][2], d_nv[2][2], d_sk[2][2], d_sv[2][2];
+  DevBuf<unsigned int> d_skeys[2][2], d_svals[2][2], d_bbox[2];
+  DevBuf<int> d_shist[2], d_sdig[2], d_sheads[2];
   DevBuf<double> d_partials;
   GridStorage g_map[2];
   PinnedBuf<LMState> h_state;
@@ -53,6 +54,7 @@ struct LMHandle {
     int per_sm = 0;
     CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lm_optimize, LM_THREADS, 0));
     if (per_sm < 1) { set_error("lm_optimize cannot be made resident"); return LOAM_ERR_CUDA; }
+    CUDA_OK(cudaFuncSetAttribute(lm_refilter_cube, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_SMEM));
     int r = LOAM_OK;
     r |= d_state.alloc_zero(1, stream); r |= d_imu.alloc_zero(1, stream);
     int snblk = (cap + RS_TILE - 1) / RS_TILE + 1, enblk = (ecap + RS_TILE - 1) / RS_TILE + 1;
@@ -63,12 +65,14 @@ struct LMHandle {
       r |= d_arena[T][0].alloc(arena_cap); r |= d_arena[T][1].alloc(arena_cap);
       r |= d_stack2[T].alloc(cap); r |= d_stack[T].alloc(cap); r |= d_E[T].alloc(ecap); r |= d_ins_pts[T].alloc(cap);
       r |= d_ins_cube[T].alloc(cap); r |= d_nn[T].alloc((size_t)cap * 5);
+      r |= d_ins_key[T].alloc(cap);
+      for (int k = 0; k < 2; k++) { r |= d_nk[T][k].alloc(cap); r |= d_nv[T][k].alloc(cap); r |= d_sk[T][k].alloc(ecap); r |= d_sv[T][k].alloc(ecap); }
       for (int k = 0; k < 2; k++) {
-        r |= d_skeys[T][k].alloc(cap); r |= d_svals[T][k].alloc(cap); r |= d_ekeys[T][k].alloc(ecap); r |= d_evals[T][k].alloc(ecap);
+        r |= d_skeys[T][k].alloc(cap); r |= d_svals[T][k].alloc(cap);
       }
       r |= d_bbox[T].alloc(6);
-      r |= d_shist[T].alloc((size_t)256 * snblk); r |= d_ehist[T].alloc((size_t)256 * enblk);
-      r |= d_sdig[T].alloc(256); r |= d_edig[T].alloc(256); r |= d_sheads[T].alloc(svblk); r |= d_eheads[T].alloc(evblk);
+      r |= d_shist[T].alloc((size_t)256 * snblk);
+      r |= d_sdig[T].alloc(256); r |= d_sheads[T].alloc(svblk);
       r |= g_map[T].alloc(ecap, 1 << 22, stream);
       if (r == LOAM_OK) {
         if (cudaMemsetAsync(d_rank[T].p, 0xff, sizeof(int) * CUBE_NUM, stream) != cudaSuccess) r = LOAM_ERR_CUDA;
@@ -110,18 +114,13 @@ struct LMHandle {
     return LOAM_OK;
   }
 
-  SortPair sort_pair(bool forE) {
+  SortPair sort_pair() {
     SortPair sp;
     sp.njobs = 2;
     for (int T = 0; T < 2; T++) {
       SortJob& j = sp.j[T];
-      if (forE) {
-        j.keys[0] = d_ekeys[T][0].p; j.keys[1] = d_ekeys[T][1].p; j.vals[0] = d_evals[T][0].p; j.vals[1] = d_evals[T][1].p;
-        j.hist = d_ehist[T].p; j.digit_total = d_edig[T].p; j.n_ptr = &d_state.p->En[T]; j.nblk_cap = (ecap + RS_TILE - 1) / RS_TILE + 1;
-      } else {
-        j.keys[0] = d_skeys[T][0].p; j.keys[1] = d_skeys[T][1].p; j.vals[0] = d_svals[T][0].p; j.vals[1] = d_svals[T][1].p;
-        j.hist = d_shist[T].p; j.digit_total = d_sdig[T].p; j.n_ptr = &d_state.p->stackN2[T]; j.nblk_cap = (cap + RS_TILE - 1) / RS_TILE + 1;
-      }
+      j.keys[0] = d_skeys[T][0].p; j.keys[1] = d_skeys[T][1].p; j.vals[0] = d_svals[T][0].p; j.vals[1] = d_svals[T][1].p;
+      j.hist = d_shist[T].p; j.digit_total = d_sdig[T].p; j.n_ptr = &d_state.p->stackN2[T]; j.nblk_cap = (cap + RS_TILE - 1) / RS_TILE + 1;
     }
     return sp;
   }
@@ -160,7 +159,7 @@ struct LMHandle {
       LAUNCH("vx_bbox", vx_bbox, dim3(nb, 2), 256, 0, stream, cp);
       LAUNCH("vx_cloud_keys", vx_cloud_keys, dim3(nb, 2), 256, 0, stream, cp);
       LAUNCH("vx_rearm_bbox", vx_rearm_bbox, 1, 32, 0, stream, cp);
-      int r = radix_sort_pairs(sort_pair(false), cap, stream);
+      int r = radix_sort_pairs(sort_pair(), cap, stream);
       if (r != LOAM_OK) return r;
       VoxelPair vp;
       vp.njobs = 2;
@@ -200,39 +199,31 @@ struct LMHandle {
       g_launches++;
       if (g_profile) prof_end("lm_optimize", stream);
     }
-    // K7: insert + per-cube refilter
+    // K7: insert + per-cube refilter (lm_refilter.cuh)
     {
       LMInsertArgs IA;
       IA.st = st;
-      for (int T = 0; T < 2; T++) { IA.stack[T] = d_stack[T].p; IA.ins_pts[T] = d_ins_pts[T].p; IA.ins_cube[T] = d_ins_cube[T].p; IA.touch_cnt[T] = d_touch[T].p; }
+      for (int T = 0; T < 2; T++) { IA.stack[T] = d_stack[T].p; IA.ins_pts[T] = d_ins_pts[T].p; IA.ins_cube[T] = d_ins_cube[T].p; IA.ins_key[T] = d_ins_key[T].p; IA.touch_cnt[T] = d_touch[T].p; }
       LAUNCH("lm_insert_ids", lm_insert_ids, nb, 256, 0, stream, IA);
       LMPlanArgs PA;
-      PA.st = st; PA.ecap = ecap;
+      PA.st = st;
       for (int T = 0; T < 2; T++) { PA.cubes[T] = d_cubes[T].p; PA.touch_cnt[T] = d_touch[T].p; PA.cube_rank[T] = d_rank[T].p; }
-      LAUNCH("lm_refilter_plan", lm_refilter_plan, 1, 1024, 0, stream, PA);
-      LMFillArgs FA;
-      FA.st = st;
+      LAUNCH("lm_refilter_plan", lm_refilter_plan, 2, 1024, 0, stream, PA);
+      LMSortNewArgs NA;
+      NA.st = st;
       for (int T = 0; T < 2; T++) {
-        FA.arena[T] = arena[T]; FA.E[T] = d_E[T].p; FA.ins_pts[T] = d_ins_pts[T].p; FA.ins_cube[T] = d_ins_cube[T].p;
-        FA.cube_rank[T] = d_rank[T].p; FA.keys[T] = d_ekeys[T][0].p; FA.vals[T] = d_evals[T][0].p;
+        NA.ins_cube[T] = d_ins_cube[T].p; NA.ins_key[T] = d_ins_key[T].p; NA.cube_rank[T] = d_rank[T].p;
+        for (int k = 0; k < 2; k++) { NA.nk[T][k] = d_nk[T][k].p; NA.nv[T][k] = d_nv[T][k].p; }
       }
-      LAUNCH("lm_refilter_fill", lm_refilter_fill, dim3(2 * nb, 2), 256, 0, stream, FA);
-      int r = radix_sort_pairs(sort_pair(true), ecap, stream);
-      if (r != LOAM_OK) return r;
-      VoxelPair vp;
-      vp.njobs = 2;
+      LAUNCH("lm_sort_new", lm_sort_new, 2, 1024, 0, stream, NA);
+      LMCubeArgs CA;
+      CA.st = st; CA.scap = ecap;
       for (int T = 0; T < 2; T++) {
-        VoxelJob& j = vp.j[T];
-        j.keys = d_ekeys[T][0].p; j.vals = d_evals[T][0].p; j.pts = d_E[T].p; j.n_ptr = &st->En[T];
-        j.block_heads = d_eheads[T].p; j.out = arena[T]; j.out_base_ptr = &st->outOff[T]; j.out_count = &st->outCount[T];
-        j.seg_count = st->segCount[T]; j.seg_shift = 24; j.nblk_cap = (ecap + VX_TILE - 1) / VX_TILE + 1;
+        CA.cubes[T] = d_cubes[T].p; CA.arena[T] = arena[T]; CA.ins_pts[T] = d_ins_pts[T].p;
+        CA.touch_cnt[T] = d_touch[T].p; CA.cube_rank[T] = d_rank[T].p;
+        for (int k = 0; k < 2; k++) { CA.nk[T][k] = d_nk[T][k].p; CA.nv[T][k] = d_nv[T][k].p; CA.sk[T][k] = d_sk[T][k].p; CA.sv[T][k] = d_sv[T][k].p; }
       }
-      r = voxel_reduce_sorted(vp, ecap, stream);
-      if (r != LOAM_OK) return r;
-      LMCommitArgs CA;
-      CA.st = st;
-      for (int T = 0; T < 2; T++) { CA.cubes[T] = d_cubes[T].p; CA.touch_cnt[T] = d_touch[T].p; CA.cube_rank[T] = d_rank[T].p; }
-      LAUNCH("lm_refilter_commit", lm_refilter_commit, 1, 1024, 0, stream, CA);
+      LAUNCH("lm_refilter_cube", lm_refilter_cube, dim3(PROC_MAX, 2), RF_THREADS, RF_SMEM, stream, CA);
     }
     if (++sweeps_since_compact >= 8) {  // bounded garbage in the log-structured arena
       int cr = compact();

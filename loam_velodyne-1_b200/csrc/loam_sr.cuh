@@ -217,7 +217,7 @@ struct SRHandle {
     if (h_cnt_init.upload(d_cnt.p, init, stream) != LOAM_OK) { set_error("counter upload failed"); return LOAM_ERR_CUDA; }
     LAUNCH("sr_ring_ori", sr_ring_ori, nblk, SR_BLK, 0, stream, d_raw_cur, n, 3, Pd, startOri, d_ring.p, d_ori.p, d_hist.p, nblk, d_cnt.p);
     LAUNCH("sr_ring_scan", sr_ring_scan, 1, 1024, 0, stream, d_hist.p, nblk, R, d_ring_start.p, d_scan_start.p, d_scan_end.p, d_cnt.p, cap);
-    LAUNCH("sr_scatter", sr_scatter, nblk, SR_BLK, 0, stream, d_raw_cur, n, 3, Pd, startOri, endOri, d_ring.p, d_ori.p, d_hist.p, nblk,
+    LAUNCH("sr_scatter", sr_scatter, nblk, SR_BLK, 0, stream, d_raw_cur, n, 3, Pd, startOri, endOri, d_ring.p, d_ori.p, d_hist.p, d_ring_start.p, nblk,
            d_cnt.p, d_full.p, d_pos.p, d_reltime.p);
     if (has_imu && imu.pointer_last >= 0) {  // :286
       if (h_imu.upload(d_imu.p, imu, stream) != LOAM_OK) { set_error("imu upload failed"); return LOAM_ERR_CUDA; }
@@ -232,7 +232,7 @@ struct SRHandle {
     int crblocks = (n + CR_TILE - 1) / CR_TILE;
     LAUNCH("sr_curv_reject", sr_curv_reject, crblocks, CR_TILE, 0, stream, d_full.p, d_cnt.p, d_curv.p, d_sort_ind.p, d_picked.p, d_label.p, d_gap.p);
     LAUNCH("sr_sort_sectors", sr_sort_sectors, dim3(6, R), 512, 0, stream, d_curv.p, d_sort_ind.p, d_scan_start.p, d_scan_end.p, d_cnt.p);
-    LAUNCH("sr_select", sr_select, R, 32, 0, stream, d_curv.p, d_sort_ind.p, d_scan_start.p, d_scan_end.p, d_ring_start.p, d_gap.p,
+    LAUNCH("sr_select", sr_select, R, SEL_THREADS, 0, stream, d_curv.p, d_sort_ind.p, d_scan_start.p, d_scan_end.p, d_ring_start.p, d_gap.p,
            d_picked.p, d_label.p, d_sharp_ring.p, d_less_sharp_ring.p, d_flat_ring.p, d_ring_counts.p, d_cnt.p);
     size_t smem = (sizeof(unsigned long long) + sizeof(float4)) * SR_RING_CAP;
     LAUNCH("sr_lessflat", sr_lessflat, R, 1024, smem, stream, d_full.p, d_label.p, d_scan_start.p, d_scan_end.p, d_lessflat_tmp.p, d_ring_counts.p, d_cnt.p);

@@ -121,8 +121,8 @@ __global__ void __launch_bounds__(RS_THREADS) rs_scatter(SortPair sp, int pass) 
     bool in = i < n;
     key[s] = in ? kin[i] : 0xffffffffu;
     val[s] = in ? vin[i] : 0u;
-    int d = in ? (int)((key[s] >> (8 * pass)) & 255) : 256 + lane;  // out-of-range lanes never match
-    unsigned int m = __match_any_sync(0xffffffffu, d);
+    int d = (int)((key[s] >> (8 * pass)) & 255);
+    unsigned int m = warp_match8(d, in);
     int r = __popc(m & ((1u << lane) - 1u));
     if (in) {
       rank[s] = cnt[warp][d] + r;

@@ -133,62 +133,76 @@ __global__ void __launch_bounds__(SR_BLK) sr_ring_ori(const float* __restrict__ 
   for (int r = threadIdx.x; r < P.n_scans; r += SR_BLK) hist[r * nblk + blockIdx.x] = sh[r];
 }
 
-// K-B: single block.  exclusive scan of hist in ring-major order (= stable ring bucketing,
-// :350-357), ring_start[], cloudSize, and scanStartInd/scanEndInd exactly as the loop :359-393
-// derives them from ring changes inside [5, cloudSize-6].
+// K-B: single block.  Stable ring bucketing (:350-357): one warp per ring scans that ring's
+// per-block counts (exclusive, relative to the ring), the ring totals give ring_start[] and
+// cloudSize; scanStartInd/scanEndInd exactly as the loop :359-393 derives them from ring changes
+// inside [5, cloudSize-6].  sr_scatter adds ring_start[ring] to the relative offsets.
 __global__ void __launch_bounds__(1024) sr_ring_scan(int* __restrict__ hist, int nblk, int n_scans,
                                                      int* __restrict__ ring_start, int* __restrict__ scan_start,
                                                      int* __restrict__ scan_end, SRCounts* cnt, int max_points) {
-  __shared__ int warp_tot[32];
-  __shared__ int carry;
-  int total_items = n_scans * nblk;
-  if (threadIdx.x == 0) carry = 0;
-  __syncthreads();
-  for (int base = 0; base < total_items; base += 1024) {
-    int idx = base + threadIdx.x;
-    int v = idx < total_items ? hist[idx] : 0;
-    int x = v;
-    for (int o = 1; o < 32; o <<= 1) {
-      int y = __shfl_up_sync(0xffffffffu, x, o);
-      if (lane_id() >= o) x += y;
-    }
-    if (lane_id() == 31) warp_tot[threadIdx.x >> 5] = x;
-    __syncthreads();
-    if (threadIdx.x < 32) {
-      int w = warp_tot[threadIdx.x];
-      int s = w;
-      for (int o = 1; o < 32; o <<= 1) {
-        int y = __shfl_up_sync(0xffffffffu, s, o);
-        if (lane_id() >= o) s += y;
+  __shared__ int s_tot[SR_MAX_RINGS];
+  __shared__ int s_start[SR_MAX_RINGS + 1];
+  const int lane = lane_id(), warp = threadIdx.x >> 5;
+  for (int r = warp; r < n_scans; r += 32) {
+    int* row = hist + (size_t)r * nblk;
+    int run = 0;
+    for (int b0 = 0; b0 < nblk; b0 += 128) {   // four independent loads per lane in flight
+      int v[4], x[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) { int i = b0 + u * 32 + lane; v[u] = i < nblk ? row[i] : 0; }
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        x[u] = v[u];
+        for (int o = 1; o < 32; o <<= 1) {
+          int y = __shfl_up_sync(0xffffffffu, x[u], o);
+          if (lane >= o) x[u] += y;
+        }
       }
-      warp_tot[threadIdx.x] = s - w;  // exclusive
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        int i = b0 + u * 32 + lane;
+        if (i < nblk) row[i] = run + x[u] - v[u];
+        run += __shfl_sync(0xffffffffu, x[u], 31);
+      }
     }
-    __syncthreads();
-    int excl = carry + warp_tot[threadIdx.x >> 5] + x - v;
-    if (idx < total_items) {
-      hist[idx] = excl;
-      if (idx % nblk == 0) ring_start[idx / nblk] = excl;
-    }
-    __syncthreads();
-    if (threadIdx.x == 1023) carry = excl + v;
-    __syncthreads();
+    if (lane == 0) s_tot[r] = run;
   }
+  __syncthreads();
+  if (warp == 0) {
+    int run = 0;
+    for (int r0 = 0; r0 < n_scans; r0 += 32) {
+      int r = r0 + lane;
+      int v = r < n_scans ? s_tot[r] : 0;
+      int x = v;
+      for (int o = 1; o < 32; o <<= 1) {
+        int y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
+      }
+      if (r < n_scans) { s_start[r] = run + x - v; ring_start[r] = run + x - v; }
+      run += __shfl_sync(0xffffffffu, x, 31);
+    }
+    if (lane == 0) { s_start[n_scans] = run; ring_start[n_scans] = run; }
+  }
+  __syncthreads();
+  const int cloudSize = s_start[n_scans];
+  for (int r = threadIdx.x; r < n_scans; r += 1024) { scan_start[r] = 0; scan_end[r] = 0; }
+  __syncthreads();
+  // every ring r > 0 that owns a position inside [5, cloudSize-6] starts a scan (:383-390) and
+  // closes the scan of ring r-1 (the ring id the reference tracks is simply "previous ring + 1")
+  for (int r = threadIdx.x; r < n_scans; r += 1024) {
+    int f = s_start[r], c = s_start[r + 1] - f;
+    if (c <= 0 || r == 0) continue;
+    int lo = f > 5 ? f : 5;
+    int hi = f + c - 1 < cloudSize - 6 ? f + c - 1 : cloudSize - 6;
+    if (lo <= hi) {
+      scan_start[r] = lo + 5;
+      scan_end[r - 1] = lo - 5;
+    }
+  }
+  __syncthreads();
   if (threadIdx.x == 0) {
-    int cloudSize = carry;
-    ring_start[n_scans] = cloudSize;
     cnt->n_full = cloudSize;
     if (cloudSize > max_points) cnt->error |= 4;
-    for (int r = 0; r < n_scans; r++) { scan_start[r] = 0; scan_end[r] = 0; }
-    for (int r = 0; r < n_scans; r++) {
-      int f = ring_start[r], c = ring_start[r + 1] - f;
-      if (c <= 0) continue;
-      int lo = f > 5 ? f : 5;
-      int hi = f + c - 1 < cloudSize - 6 ? f + c - 1 : cloudSize - 6;
-      if (lo <= hi && r > 0) {  // :383-390 (scanCount > 0 && scanCount < N_SCANS)
-        scan_start[r] = lo + 5;
-        scan_end[r - 1] = lo - 5;
-      }
-    }
     scan_start[0] = 5;                     // :392
     scan_end[n_scans - 1] = cloudSize - 5; // :393
   }
@@ -198,8 +212,8 @@ __global__ void __launch_bounds__(1024) sr_ring_scan(int* __restrict__ hist, int
 __global__ void __launch_bounds__(SR_BLK) sr_scatter(const float* __restrict__ raw, int n, int stride_floats,
                                                      SRParamsDev P, float startOri, float endOri,
                                                      const short* __restrict__ ring, const float* __restrict__ ori_raw,
-                                                     const int* __restrict__ base, int nblk, const SRCounts* cnt,
-                                                     float4* __restrict__ full, int* __restrict__ pos_out,
+                                                     const int* __restrict__ base, const int* __restrict__ ring_start, int nblk,
+                                                     const SRCounts* cnt, float4* __restrict__ full, int* __restrict__ pos_out,
                                                      float* __restrict__ reltime_out) {
   __shared__ unsigned short wcount[SR_BLK / 32][SR_MAX_RINGS];
   for (int k = threadIdx.x; k < (SR_BLK / 32) * SR_MAX_RINGS; k += SR_BLK) (&wcount[0][0])[k] = 0;
@@ -215,7 +229,7 @@ __global__ void __launch_bounds__(SR_BLK) sr_scatter(const float* __restrict__ r
   if (rid >= 0) {
     int off = 0;
     for (int w = 0; w < warp; w++) off += wcount[w][rid];
-    int pos = base[rid * nblk + blockIdx.x] + off + rank_in_warp;
+    int pos = ring_start[rid] + base[rid * nblk + blockIdx.x] + off + rank_in_warp;
     const float* p = raw + (size_t)i * stride_floats;
     float px = p[1], py = p[2], pz = p[0];
     float ori = ori_raw[i];

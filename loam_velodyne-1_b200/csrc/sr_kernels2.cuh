@@ -147,111 +147,162 @@ __global__ void __launch_bounds__(512) sr_sort_sectors(const float* __restrict__
   for (int k = threadIdx.x; k < m; k += 512) sort_ind[sp + k] = (int)(keys[k] & 0xffffffffu);
 }
 
-// K-G: one warp per ring.  Greedy selection :476-566 with the suppression flags shared by the six
+// K-G: one CTA per ring.  Greedy selection :476-566 with the suppression flags shared by the six
 // sectors of the ring (they spill up to 5 positions across sector boundaries, App. A.1 §14).
-__global__ void __launch_bounds__(32) sr_select(const float* __restrict__ curvature, const int* __restrict__ sort_ind,
-                                                const int* __restrict__ scan_start, const int* __restrict__ scan_end,
-                                                const int* __restrict__ ring_start, const unsigned char* __restrict__ gapflag,
-                                                unsigned char* __restrict__ picked, signed char* __restrict__ label,
-                                                int* __restrict__ sharp_idx, int* __restrict__ less_sharp_idx,
-                                                int* __restrict__ flat_idx, int* __restrict__ ring_counts,
-                                                const SRCounts* __restrict__ cnt) {
+// The picks of a ring are strictly sequential, so the whole working set of the ring is staged in
+// shared memory first (sorted (curvature, index) pairs, picked flags, a running count of the
+// "gap" flags) and warp 0 then runs the greedy scans without touching global memory:
+//   position j is suppressed by a pick p  <=>  |j - p| <= 5 and no gap flag lies between them
+//                                         <=>  |j - p| <= 5 and seg[j] == seg[p]   (seg = prefix count of gap flags)
+// which every lane evaluates locally for its own candidate after the pick is broadcast.
+constexpr int SEL_THREADS = 256;
+constexpr int SEL_CAP = SR_RING_CAP + 32;   // ring window: [scanStart - 5, scanEnd + 5)
+__global__ void __launch_bounds__(SEL_THREADS) sr_select(const float* __restrict__ curvature, const int* __restrict__ sort_ind,
+                                                         const int* __restrict__ scan_start, const int* __restrict__ scan_end,
+                                                         const int* __restrict__ ring_start, const unsigned char* __restrict__ gapflag,
+                                                         unsigned char* __restrict__ picked, signed char* __restrict__ label,
+                                                         int* __restrict__ sharp_idx, int* __restrict__ less_sharp_idx,
+                                                         int* __restrict__ flat_idx, int* __restrict__ ring_counts,
+                                                         SRCounts* __restrict__ cnt) {
+  __shared__ unsigned char s_picked[SEL_CAP];
+  __shared__ unsigned short s_seg[SEL_CAP];
+  __shared__ int s_ind[SEL_CAP];      // sorted order, window-relative
+  __shared__ float s_curv[SEL_CAP];   // curvature in sorted order
+  __shared__ int s_wsum[SEL_THREADS / 32];
+  __shared__ int s_carry;
   const int ring = blockIdx.x;
-  const int lane = threadIdx.x;
+  const int lane = threadIdx.x & 31;
   const int nfull = cnt->n_full;
-  int n_sharp = 0, n_less = 0, n_flat = 0;
+  const int S = scan_start[ring], E = scan_end[ring];
   int* my_sharp = sharp_idx + ring * SR_SHARP_PER_RING;
   int* my_less = less_sharp_idx + ring * SR_LESS_SHARP_PER_RING;
   int* my_flat = flat_idx + ring * SR_FLAT_PER_RING;
-  for (int j = 0; j < 6; j++) {
-    int sp, ep;
-    sector_bounds(scan_start, scan_end, ring, j, sp, ep);
-    if (sp < 0 || ep >= nfull || ep < sp) continue;
-    // ---- corners: k = ep .. sp ----
-    int largest = 0;
-    bool done = false;
-    for (int base = ep; base >= sp && !done; base -= 32) {
-      int k = base - lane;
-      bool valid = k >= sp;
-      int ind = valid ? sort_ind[k] : 0;
-      float c = valid ? curvature[ind] : 0.f;
-      bool cand = valid && (c > 0.1);
-      unsigned int stop = __ballot_sync(0xffffffffu, valid && !(c > 0.1));
-      while (true) {
-        bool ok = cand && picked[ind] == 0;
-        unsigned int mk = __ballot_sync(0xffffffffu, ok);
-        if (mk == 0) break;
-        int L = __ffs(mk) - 1;
-        int pind = __shfl_sync(0xffffffffu, ind, L);
-        largest++;
-        if (largest <= 2) {
-          if (lane == 0) { label[pind] = 2; my_sharp[n_sharp] = pind; my_less[n_less] = pind; }
-          n_sharp++; n_less++;
-        } else if (largest <= 20) {
-          if (lane == 0) { label[pind] = 1; my_less[n_less] = pind; }
-          n_less++;
-        } else {
-          done = true;
-          break;
-        }
-        if (lane == 0) {
-          picked[pind] = 1;
-          for (int l = 1; l <= 5; l++) {
-            if (gapflag[pind + l]) break;   // gap between pind+l-1 and pind+l
-            picked[pind + l] = 1;
+  const int w0 = max(S - 5, 0), w1 = min(E + 5, nfull);   // window of positions this ring can touch
+  const int wn = w1 - w0;
+  if (E <= S || wn <= 0 || S < 0) {   // no sector holds a point (:463-464 give ep < sp)
+    if (threadIdx.x == 0) { ring_counts[ring * 4 + 0] = 0; ring_counts[ring * 4 + 1] = 0; ring_counts[ring * 4 + 2] = 0; }
+    return;
+  }
+  if (wn > SEL_CAP) {
+    if (threadIdx.x == 0) { atomicOr(&cnt->error, 2); ring_counts[ring * 4 + 0] = 0; ring_counts[ring * 4 + 1] = 0; ring_counts[ring * 4 + 2] = 0; }
+    return;
+  }
+  // ---- stage: picked flags, prefix count of gap flags, sorted (index, curvature) ----
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  for (int base = 0; base < wn; base += SEL_THREADS) {
+    const int k = base + threadIdx.x;
+    int gf = 0;
+    if (k < wn) {
+      s_picked[k] = picked[w0 + k];
+      gf = (k > 0 && gapflag[w0 + k]) ? 1 : 0;   // gap between w0+k-1 and w0+k
+    }
+    int x = gf;
+    for (int o = 1; o < 32; o <<= 1) {
+      int y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) s_wsum[threadIdx.x >> 5] = x;
+    __syncthreads();
+    int off = s_carry;
+    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) off += s_wsum[w];
+    if (k < wn) s_seg[k] = (unsigned short)(off + x);
+    __syncthreads();
+    if (threadIdx.x == SEL_THREADS - 1) s_carry = off + x;
+    __syncthreads();
+  }
+  for (int k = S + threadIdx.x; k < min(E, nfull); k += SEL_THREADS) {   // sectors tile [S, E-1]
+    const int ind = sort_ind[k];
+    s_ind[k - w0] = ind - w0;
+    s_curv[k - w0] = curvature[ind];
+  }
+  __syncthreads();
+  // ---- greedy scans, warp 0 ----
+  if (threadIdx.x < 32) {
+    int n_sharp = 0, n_less = 0, n_flat = 0;
+    for (int j = 0; j < 6; j++) {
+      int sp, ep;
+      sector_bounds(scan_start, scan_end, ring, j, sp, ep);
+      if (sp < 0 || ep >= nfull || ep < sp) continue;
+      // ---- corners: k = ep .. sp ----
+      int largest = 0;
+      bool done = false;
+      for (int base = ep; base >= sp && !done; base -= 32) {
+        const int k = base - lane;
+        const bool valid = k >= sp;
+        const int ind = valid ? s_ind[k - w0] : 0;
+        const float c = valid ? s_curv[k - w0] : 0.f;
+        const int seg = s_seg[ind];
+        bool ok = valid && (c > 0.1) && s_picked[ind] == 0;
+        const unsigned int stop = __ballot_sync(0xffffffffu, valid && !(c > 0.1));
+        while (true) {
+          const unsigned int mk = __ballot_sync(0xffffffffu, ok);
+          if (mk == 0) break;
+          const int L = __ffs(mk) - 1;
+          const int pind = __shfl_sync(0xffffffffu, ind, L);
+          const int pseg = __shfl_sync(0xffffffffu, seg, L);
+          largest++;
+          if (largest <= 2) {
+            if (lane == 0) { label[w0 + pind] = 2; my_sharp[n_sharp] = w0 + pind; my_less[n_less] = w0 + pind; }
+            n_sharp++; n_less++;
+          } else if (largest <= 20) {
+            if (lane == 0) { label[w0 + pind] = 1; my_less[n_less] = w0 + pind; }
+            n_less++;
+          } else {
+            done = true;
+            break;
           }
-          for (int l = -1; l >= -5; l--) {
-            if (gapflag[pind + l + 1]) break;  // gap between pind+l and pind+l+1
-            picked[pind + l] = 1;
+          if (lane < 11) {   // :495-520, positions pind-5 .. pind+5
+            const int q = pind - 5 + lane;
+            if (q >= 0 && q < wn && s_seg[q] == pseg) s_picked[q] = 1;
           }
+          if (abs(ind - pind) <= 5 && seg == pseg) ok = false;
+          if (lane <= L) ok = false;
         }
         __syncwarp();
-        cand = cand && lane > L;
+        if (stop) done = true;  // ascending sort: everything further down has c <= 0.1
       }
-      if (stop) done = true;  // ascending sort: everything further down has c <= 0.1
-    }
-    // ---- flat: k = sp .. ep ----
-    int smallest = 0;
-    done = false;
-    for (int base = sp; base <= ep && !done; base += 32) {
-      int k = base + lane;
-      bool valid = k <= ep;
-      int ind = valid ? sort_ind[k] : 0;
-      float c = valid ? curvature[ind] : 0.f;
-      bool cand = valid && (c < 0.1);
-      unsigned int stop = __ballot_sync(0xffffffffu, valid && !(c < 0.1));
-      while (true) {
-        bool ok = cand && picked[ind] == 0;
-        unsigned int mk = __ballot_sync(0xffffffffu, ok);
-        if (mk == 0) break;
-        int L = __ffs(mk) - 1;
-        int pind = __shfl_sync(0xffffffffu, ind, L);
-        if (lane == 0) { label[pind] = -1; my_flat[n_flat] = pind; }
-        n_flat++;
-        smallest++;
-        if (smallest >= 4) { done = true; break; }  // :534-536 breaks BEFORE marking
-        if (lane == 0) {
-          picked[pind] = 1;
-          for (int l = 1; l <= 5; l++) {
-            if (gapflag[pind + l]) break;
-            picked[pind + l] = 1;
+      // ---- flat: k = sp .. ep ----
+      int smallest = 0;
+      done = false;
+      for (int base = sp; base <= ep && !done; base += 32) {
+        const int k = base + lane;
+        const bool valid = k <= ep;
+        const int ind = valid ? s_ind[k - w0] : 0;
+        const float c = valid ? s_curv[k - w0] : 0.f;
+        const int seg = s_seg[ind];
+        bool ok = valid && (c < 0.1) && s_picked[ind] == 0;
+        const unsigned int stop = __ballot_sync(0xffffffffu, valid && !(c < 0.1));
+        while (true) {
+          const unsigned int mk = __ballot_sync(0xffffffffu, ok);
+          if (mk == 0) break;
+          const int L = __ffs(mk) - 1;
+          const int pind = __shfl_sync(0xffffffffu, ind, L);
+          const int pseg = __shfl_sync(0xffffffffu, seg, L);
+          if (lane == 0) { label[w0 + pind] = -1; my_flat[n_flat] = w0 + pind; }
+          n_flat++;
+          smallest++;
+          if (smallest >= 4) { done = true; break; }  // :534-536 breaks BEFORE marking
+          if (lane < 11) {
+            const int q = pind - 5 + lane;
+            if (q >= 0 && q < wn && s_seg[q] == pseg) s_picked[q] = 1;
           }
-          for (int l = -1; l >= -5; l--) {
-            if (gapflag[pind + l + 1]) break;
-            picked[pind + l] = 1;
-          }
+          if (abs(ind - pind) <= 5 && seg == pseg) ok = false;
+          if (lane <= L) ok = false;
         }
         __syncwarp();
-        cand = cand && lane > L;
+        if (stop) done = true;
       }
-      if (stop) done = true;
+    }
+    if (lane == 0) {
+      ring_counts[ring * 4 + 0] = n_sharp;
+      ring_counts[ring * 4 + 1] = n_less;
+      ring_counts[ring * 4 + 2] = n_flat;
     }
   }
-  if (lane == 0) {
-    ring_counts[ring * 4 + 0] = n_sharp;
-    ring_counts[ring * 4 + 1] = n_less;
-    ring_counts[ring * 4 + 2] = n_flat;
-  }
+  __syncthreads();
+  // cloudNeighborPicked after selection (only ever raised; windows of different rings are disjoint)
+  for (int k = threadIdx.x; k < wn; k += SEL_THREADS) if (s_picked[k]) picked[w0 + k] = 1;
 }
 
 // K-H: one block per ring.  surfPointsLessFlatScan = positions k in [scanStart, scanEnd-1] with

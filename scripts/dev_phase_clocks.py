@@ -18,6 +18,30 @@ for k in range(nsw):
     r = G.push(xyz, st)
     if k < nsw - 4:
         continue
+    if r.lm_status == 0:
+        cnt = np.zeros(16, np.int32)
+        L.loam_debug_lm_counters.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+        L.loam_debug_lm_counters(G.lm.h, cnt.ctypes.data, 16)
+        print(f"sweep {k} refilter corner {cnt[:8].tolist()} surf {cnt[8:].tolist()}  map {r.n_map_corner}/{r.n_map_surf} stack {r.n_stack_corner}/{r.n_stack_surf}")
+    if r.lm_status == 0:
+        rf = np.zeros(2 * 250 * 8, np.int64)
+        L.loam_debug_phase_clocks(2, rf.ctypes.data, rf.size)
+        rf = rf.reshape(2, 250, 8)
+        for T in range(2):
+            for rr in range(250):
+                t = rf[T, rr]
+                if t[0] == 0 or t[4] == 0:
+                    continue
+                n_old, n_new = int(t[7] >> 32), int(t[7] & 0xffffffff)
+                if n_old < 2000:
+                    continue
+                st_ = [(t[k] - t[0]) / 1.965e3 if t[k] else -1 for k in range(1, 5)]
+                print(f"   rf T{T} r{rr} n_old={n_old} n_new={n_new} passA={st_[0]:.1f} scan+alloc={st_[1]:.1f} passB={st_[2]:.1f} end={st_[3]:.1f} us")
+    if r.lm_status == 0:
+        dc = np.zeros(64, np.int64)
+        L.loam_debug_phase_clocks(3, dc.ctypes.data, 64)
+        us = lambda a, b: (dc[b] - dc[a]) / 1.965e3
+        print(f"   sort_new: build={us(0,1):.1f} sort={us(1,2):.1f}  pass0: walk1={us(8,9):.1f} prefix={us(9,10):.1f} walk2={us(10,11):.1f}")
     for which, tag in ((0, "LO"), (1, "LM")):
         if which == 1 and r.lm_status != 0:
             continue
