@@ -359,7 +359,7 @@ def main():
 
 def ctypes_sizeof_record(pkg):
     # PipeRecord (csrc/loam_pipeline.cuh): SRCounts 32 + 12*4 + 12*4 + 12 + 12*4 + 16 + 24
-    return 32 + 48 + 48 + 12 + 48 + 16 + 24
+    return 32 + 48 + 48 + 12 + 48 + 16 + 24 + 8
 
 
 if __name__ == "__main__":

@@ -245,8 +245,8 @@ class LaserMapping(_Node):
     def process(self, lo, stamp):
         return _check(self.L.loam_lm_process(self.h, lo.h, float(stamp)))
 
-    def cloud(self, which):
-        return self._dl(self.L.loam_lm_download, which, np.float32, 4)
+    def cloud(self, which, cap=None):
+        return self._dl(self.L.loam_lm_download, which, np.float32, 4, cap=cap)
 
     def ints(self, which):
         return self._dl(self.L.loam_lm_download_ints, which, np.int32, 1, cap=5 * self.cap)

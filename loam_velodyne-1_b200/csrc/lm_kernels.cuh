@@ -61,7 +61,8 @@ struct LMState {
   int rfStat[2][8];                     // last sweep: [0] merge cubes [1] general cubes [2] append cubes [3] max n_old
                                         // [4] max n_new [5] points written [6] new-only voxels [7] cubes gone dirty
   int surroundN;                        // surround cloud size (LM-14)
-  int surroundIn;
+  int surroundIn;                       // size of the gathered (unfiltered) surround cloud
+  int surroundOff[250];                 // start of every (cube, type) segment inside it
   int registeredN;                      // size of the registered full-resolution cloud
   int vxOverflow[4];
 };

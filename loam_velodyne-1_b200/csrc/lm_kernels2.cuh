@@ -304,6 +304,57 @@ __global__ void __launch_bounds__(256) lm_registered(LMState* st, const float4* 
   for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) out[i] = lm_to_map(in[i], g, s_T);
 }
 
+// ---- LM-14: surround map every mapFrameNum-th mapped sweep (:1042-1057) ----------------------
+// laserCloudSurround2 = for every surround cube (i, j, k order): corner points then surf points;
+// laserCloudSurround = downSizeFilterCorner (0.2 m) of that, a whole-cloud pcl::VoxelGrid.
+struct LMSurroundArgs {
+  LMState* st;
+  const CubeDesc* cubes[2];
+  const float4* arena[2];
+  float4* S;           // gathered cloud
+  int scap;
+};
+// one block: segment offsets (cube sizes fetched in parallel, one scan)
+__global__ void __launch_bounds__(256) lm_surround_plan(LMSurroundArgs A) {
+  LMState* st = A.st;
+  __shared__ int s_cnt[256];
+  const int ns = st->surroundNum;
+  // element 2*i = corner cube i, 2*i+1 = surf cube i
+  const int e = threadIdx.x;
+  int c = 0;
+  if (e < 2 * ns && e < 250) c = A.cubes[e & 1][st->surroundInd[e >> 1]].cnt;
+  s_cnt[e] = c;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    int run = 0;
+    for (int b = 0; b < 256; b += 32) {
+      int v = s_cnt[b + lane], x = v;
+      for (int o = 1; o < 32; o <<= 1) {
+        int y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
+      }
+      s_cnt[b + lane] = run + x - v;
+      run += __shfl_sync(0xffffffffu, x, 31);
+    }
+    if (lane == 0) {
+      if (run > A.scap) { atomicOr(&st->error, 8); run = 0; }
+      st->surroundIn = run;
+    }
+  }
+  __syncthreads();
+  if (e < 250) st->surroundOff[e] = s_cnt[e];
+}
+__global__ void __launch_bounds__(256) lm_surround_gather(LMSurroundArgs A) {
+  const LMState* st = A.st;
+  const int e = blockIdx.x;
+  if (e >= 2 * st->surroundNum || st->surroundIn == 0) return;
+  const CubeDesc d = A.cubes[e & 1][st->surroundInd[e >> 1]];
+  const float4* src = A.arena[e & 1] + d.off;
+  float4* dst = A.S + st->surroundOff[e];
+  for (int k = threadIdx.x; k < d.cnt; k += 256) dst[k] = src[k];
+}
+
 // arena compaction: copy every live cube segment into the other arena (host-triggered)
 struct LMCompactArgs {
   LMState* st;

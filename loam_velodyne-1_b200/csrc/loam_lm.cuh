@@ -26,7 +26,9 @@ struct LMHandle {
   DevBuf<int> d_ins_cube[2], d_nn[2];
   DevBuf<unsigned int> d_ins_key[2], d_nk[2][2], d_nv[2][2], d_sk[2][2], d_sv[2][2];
   DevBuf<unsigned int> d_skeys[2][2], d_svals[2][2], d_bbox[2];
-  DevBuf<int> d_shist[2], d_sdig[2], d_sheads[2];
+  DevBuf<int> d_shist[2], d_sdig[2], d_sheads[2], d_uhist, d_udig, d_uheads;
+  DevBuf<unsigned int> d_ukeys[2], d_uvals[2], d_ubbox;
+  DevBuf<float4> d_S;
   DevBuf<double> d_partials;
   GridStorage g_map[2];
   PinnedBuf<LMState> h_state;
@@ -80,6 +82,14 @@ struct LMHandle {
         if (cudaMemcpyAsync(d_bbox[T].p, init, sizeof(init), cudaMemcpyHostToDevice, stream) != cudaSuccess) r = LOAM_ERR_CUDA;
         cudaStreamSynchronize(stream);
       }
+    }
+    r |= d_S.alloc(ecap); r |= d_surround.alloc(ecap); r |= d_ubbox.alloc(6);
+    for (int k = 0; k < 2; k++) { r |= d_ukeys[k].alloc(ecap); r |= d_uvals[k].alloc(ecap); }
+    r |= d_uhist.alloc((size_t)256 * enblk); r |= d_udig.alloc(256); r |= d_uheads.alloc(evblk);
+    if (r == LOAM_OK) {
+      unsigned int binit[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+      if (cudaMemcpyAsync(d_ubbox.p, binit, sizeof(binit), cudaMemcpyHostToDevice, stream) != cudaSuccess) r = LOAM_ERR_CUDA;
+      cudaStreamSynchronize(stream);
     }
     r |= d_registered.alloc(cap); r |= d_partials.alloc_zero((size_t)2 * coop_blocks * LO_NRED, stream);
     r |= h_state.alloc(1); r |= h_imu.alloc();
@@ -231,11 +241,51 @@ struct LMHandle {
     }
     mapFrameCount++;  // :1038-1040
     last_surround = false;
-    if (mapFrameCount >= mapFrameNum) { mapFrameCount = 0; last_surround = true; }
+    if (mapFrameCount >= mapFrameNum) {
+      mapFrameCount = 0;
+      last_surround = true;
+      int sr_ = surround();
+      if (sr_ != LOAM_OK) return sr_;
+    }
     // K8
     LAUNCH("lm_registered", lm_registered, 2 * nb, 256, 0, stream, st, lo.d_full_end.p, &lo.d_state.p->n_full_end, d_registered.p);
     CUDA_OK(cudaGetLastError());
     return LOAM_OK;
+  }
+
+  // LM-14 (:1042-1057): gather the surround cubes, whole-cloud VoxelGrid(0.2)
+  int surround() {
+    LMState* st = d_state.p;
+    LMSurroundArgs SA;
+    SA.st = st; SA.S = d_S.p; SA.scap = ecap;
+    for (int T = 0; T < 2; T++) { SA.cubes[T] = d_cubes[T].p; SA.arena[T] = d_arena[T][cur_arena].p; }
+    LAUNCH("lm_surround_plan", lm_surround_plan, 1, 256, 0, stream, SA);
+    LAUNCH("lm_surround_gather", lm_surround_gather, 250, 256, 0, stream, SA);
+    CloudKeyPair cp;
+    cp.njobs = 1;
+    CloudKeyJob& cj = cp.j[0];
+    cj.pts = d_S.p; cj.n_ptr = &st->surroundIn; cj.bbox = d_ubbox.p; cj.keys = d_ukeys[0].p; cj.vals = d_uvals[0].p;
+    cj.overflow = &st->vxOverflow[2]; cj.leaf = 0.2f;
+    cp.j[1] = cj;
+    LAUNCH("vx_bbox", vx_bbox, dim3(296, 1), 256, 0, stream, cp);
+    LAUNCH("vx_cloud_keys", vx_cloud_keys, dim3(296, 1), 256, 0, stream, cp);
+    LAUNCH("vx_rearm_bbox", vx_rearm_bbox, 1, 32, 0, stream, cp);
+    SortPair sp;
+    sp.njobs = 1;
+    SortJob& sj = sp.j[0];
+    sj.keys[0] = d_ukeys[0].p; sj.keys[1] = d_ukeys[1].p; sj.vals[0] = d_uvals[0].p; sj.vals[1] = d_uvals[1].p;
+    sj.hist = d_uhist.p; sj.digit_total = d_udig.p; sj.n_ptr = &st->surroundIn; sj.nblk_cap = (ecap + RS_TILE - 1) / RS_TILE + 1;
+    sp.j[1] = sj;
+    int r = radix_sort_pairs(sp, ecap, stream);
+    if (r != LOAM_OK) return r;
+    VoxelPair vp;
+    vp.njobs = 1;
+    VoxelJob& vj = vp.j[0];
+    vj.keys = d_ukeys[0].p; vj.vals = d_uvals[0].p; vj.pts = d_S.p; vj.n_ptr = &st->surroundIn;
+    vj.block_heads = d_uheads.p; vj.out = d_surround.p; vj.out_base_ptr = nullptr; vj.out_count = &st->surroundN;
+    vj.seg_count = nullptr; vj.seg_shift = 0; vj.nblk_cap = (ecap + VX_TILE - 1) / VX_TILE + 1;
+    vp.j[1] = vj;
+    return voxel_reduce_sorted(vp, ecap, stream);
   }
 
   int compact() {

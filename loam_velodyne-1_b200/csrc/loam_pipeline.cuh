@@ -19,6 +19,7 @@ struct PipeRecord {
   float aft[6], bef[6];
   int lm_iters, lm_rows, lm_deg, lm_error;
   int mapN[2], stackN[2], bump[2];
+  int surroundN, pad;
 };
 
 __global__ void pipe_record(PipeRecord* out, const SRCounts* cnt, const ImuState* imu, const LOState* lo, const LMState* lm, int with_lm) {
@@ -31,6 +32,7 @@ __global__ void pipe_record(PipeRecord* out, const SRCounts* cnt, const ImuState
   for (int i = 0; i < 6; i++) { r.aft[i] = lm->transformAftMapped[i]; r.bef[i] = lm->transformBefMapped[i]; }
   r.lm_iters = lm->iters; r.lm_rows = lm->rows; r.lm_deg = lm->isDegenerate; r.lm_error = with_lm ? lm->error : 0;
   for (int T = 0; T < 2; T++) { r.mapN[T] = lm->mapN[T]; r.stackN[T] = lm->stackN[T]; r.bump[T] = lm->bump[T]; }
+  r.surroundN = lm->surroundN; r.pad = 0;
   *out = r;
 }
 
@@ -135,7 +137,7 @@ struct PipelineHandle {
             memcpy(m.transformBefMapped, q.bef, sizeof(float) * 6);
             m.iters = q.lm_iters; m.rows = q.lm_rows; m.isDegenerate = q.lm_deg;
             m.mapN[0] = q.mapN[0]; m.mapN[1] = q.mapN[1]; m.stackN[0] = q.stackN[0]; m.stackN[1] = q.stackN[1];
-            m.bump[0] = q.bump[0]; m.bump[1] = q.bump[1]; m.registeredN = q.cnt.n_full;
+            m.bump[0] = q.bump[0]; m.bump[1] = q.bump[1]; m.registeredN = q.cnt.n_full; m.surroundN = q.surroundN;
             tm.on_mapping(q.aft, q.bef);
           }
         }
