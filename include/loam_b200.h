@@ -178,6 +178,8 @@ int loam_debug_math(int fn, const float* x, const float* y, float* out, int n);
 int loam_debug_linalg(int op, const float* A, const float* b, float* out, int m, int n, int batch);
 int loam_debug_sort_pairs(unsigned int* keys, unsigned int* vals, int n);
 int loam_debug_voxel_filter(const float* xyzi, int n, float leaf, float* out, int cap_out, int* n_out);
+/* same filter through the one-kernel cooperative path laserMapping uses for the incoming sweep */
+int loam_debug_voxel_filter_coop(const float* xyzi, int n, float leaf, float* out, int cap_out, int* n_out);
 
 /* phase clocks (SM cycles, clock64 of CTA 0) of the persistent LM kernels: which 0 = laserOdometry,
  * 1 = laserMapping; slot 0 = number of stamps that follow */

@@ -2,6 +2,7 @@
 // the host-only transformMaintenance node (transformMaintenance.cpp).
 #pragma once
 #include "lm_kernels2.cuh"
+#include "vx_coop.cuh"
 #include "loam_lo.cuh"
 
 namespace loamgpu {
@@ -28,7 +29,8 @@ struct LMHandle {
   DevBuf<unsigned int> d_skeys[2][2], d_svals[2][2], d_bbox[2];
   DevBuf<int> d_shist[2], d_sdig[2], d_sheads[2], d_uhist, d_udig, d_uheads;
   DevBuf<unsigned int> d_ukeys[2], d_uvals[2], d_ubbox;
-  DevBuf<float4> d_S;
+  DevBuf<float4> d_S, d_ssorted[2];
+  int vc_tile_cap = 0;
   DevBuf<double> d_partials;
   GridStorage g_map[2];
   PinnedBuf<LMState> h_state;
@@ -73,7 +75,8 @@ struct LMHandle {
         r |= d_skeys[T][k].alloc(cap); r |= d_svals[T][k].alloc(cap);
       }
       r |= d_bbox[T].alloc(6);
-      r |= d_shist[T].alloc((size_t)256 * snblk);
+      vc_tile_cap = (cap + VC_TILE - 1) / VC_TILE + 1;
+      r |= d_shist[T].alloc((size_t)256 * vc_tile_cap); r |= d_ssorted[T].alloc(cap);
       r |= d_sdig[T].alloc(256); r |= d_sheads[T].alloc(svblk);
       r |= g_map[T].alloc(ecap, 1 << 22, stream);
       if (r == LOAM_OK) {
@@ -157,30 +160,21 @@ struct LMHandle {
     LMStackArgs KA;
     KA.st = st; KA.in[0] = lo.d_corner_last.p; KA.in[1] = lo.d_surf_last.p; KA.out[0] = d_stack2[0].p; KA.out[1] = d_stack2[1].p;
     LAUNCH("lm_stack_transform", lm_stack_transform, nb, 256, 0, stream, KA);
-    // K3: downSizeFilterCorner (0.2) / downSizeFilterSurf (0.4) on the incoming sweep
+    // K3: downSizeFilterCorner (0.2) / downSizeFilterSurf (0.4) on the incoming sweep: one cooperative kernel
     {
-      CloudKeyPair cp;
-      cp.njobs = 2;
+      VxCoopArgs VA;
       for (int T = 0; T < 2; T++) {
-        CloudKeyJob& j = cp.j[T];
-        j.pts = d_stack2[T].p; j.n_ptr = &st->stackN2[T]; j.bbox = d_bbox[T].p; j.keys = d_skeys[T][0].p; j.vals = d_svals[T][0].p;
-        j.overflow = &st->vxOverflow[T]; j.leaf = T == 0 ? 0.2f : 0.4f;
+        VxCoopJob& j = VA.j[T];
+        j.pts = d_stack2[T].p; j.n_ptr = &st->stackN2[T]; j.bbox = d_bbox[T].p;
+        j.keys[0] = d_skeys[T][0].p; j.keys[1] = d_skeys[T][1].p; j.vals[0] = d_svals[T][0].p; j.vals[1] = d_svals[T][1].p;
+        j.hist = d_shist[T].p; j.heads = d_sheads[T].p; j.sorted = d_ssorted[T].p; j.out = d_stack[T].p; j.out_count = &st->stackN[T];
+        j.overflow = &st->vxOverflow[T]; j.leaf = T == 0 ? 0.2f : 0.4f; j.tile_cap = vc_tile_cap;
       }
-      LAUNCH("vx_bbox", vx_bbox, dim3(nb, 2), 256, 0, stream, cp);
-      LAUNCH("vx_cloud_keys", vx_cloud_keys, dim3(nb, 2), 256, 0, stream, cp);
-      LAUNCH("vx_rearm_bbox", vx_rearm_bbox, 1, 32, 0, stream, cp);
-      int r = radix_sort_pairs(sort_pair(), cap, stream);
-      if (r != LOAM_OK) return r;
-      VoxelPair vp;
-      vp.njobs = 2;
-      for (int T = 0; T < 2; T++) {
-        VoxelJob& j = vp.j[T];
-        j.keys = d_skeys[T][0].p; j.vals = d_svals[T][0].p; j.pts = d_stack2[T].p; j.n_ptr = &st->stackN2[T];
-        j.block_heads = d_sheads[T].p; j.out = d_stack[T].p; j.out_base_ptr = nullptr; j.out_count = &st->stackN[T];
-        j.seg_count = nullptr; j.seg_shift = 0; j.nblk_cap = (cap + VX_TILE - 1) / VX_TILE + 1;
-      }
-      r = voxel_reduce_sorted(vp, cap, stream);
-      if (r != LOAM_OK) return r;
+      void* args[] = {&VA};
+      if (g_profile) prof_begin(stream);
+      CUDA_OK(cudaLaunchCooperativeKernel((void*)vx_filter_coop, dim3(32, 2), dim3(VC_THREADS), args, 0, stream));
+      g_launches++;
+      if (g_profile) prof_end("vx_filter_coop", stream);
     }
     // K4
     LMGatherArgs GA;

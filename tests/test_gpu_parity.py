@@ -107,6 +107,22 @@ def test_device_voxel_filter_equals_pcl_definition(pkg, checker, leaf, n):
     assert L.loam_debug_voxel_filter(pts.ctypes.data, n, leaf, out.ctypes.data, n, ctypes.byref(cnt)) == 0
     assert cnt.value == m
     assert biteq(out[:m], ref[:m])
+    # the one-kernel cooperative variant (laserMapping's incoming-sweep filters) gives the same bits,
+    # also with non-finite points in the input (dropped, like removeNaN + VoxelGrid)
+    L.loam_debug_voxel_filter_coop.argtypes = L.loam_debug_voxel_filter.argtypes
+    outc = np.zeros((n, 4), np.float32)
+    cntc = ctypes.c_int()
+    assert L.loam_debug_voxel_filter_coop(pts.ctypes.data, n, leaf, outc.ctypes.data, n, ctypes.byref(cntc)) == 0
+    assert cntc.value == m and biteq(outc[:m], ref[:m])
+    if n > 100:
+        bad = pts.copy()
+        bad[::97, 0] = np.nan
+        for fn in (L.loam_debug_voxel_filter, L.loam_debug_voxel_filter_coop):
+            oa = np.zeros((n, 4), np.float32); ca = ctypes.c_int()
+            assert fn(bad.ctypes.data, n, leaf, oa.ctypes.data, n, ctypes.byref(ca)) == 0
+            good = np.ascontiguousarray(bad[np.isfinite(bad[:, 0])])
+            mg = Lo.chk_voxel_filter(good.ctypes.data, good.shape[0], leaf, ref.ctypes.data, n)
+            assert ca.value == mg and biteq(oa[:mg], ref[:mg])
     # idempotence on the output is NOT guaranteed by PCL (centroids can cross cell borders), but the
     # output must be sorted by voxel index, i.e. filtering it again never increases the size
     cnt2 = ctypes.c_int()
