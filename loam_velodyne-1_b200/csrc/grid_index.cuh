@@ -101,10 +101,18 @@ __global__ void __launch_bounds__(256) grid_bbox(GridPair gp) {
       mx[a] = fmaxf(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
     }
   }
-  if (lane_id() == 0 && mn[0] <= mx[0]) {
-    for (int a = 0; a < 3; a++) {
-      atomicMin(&g.bbox[a], float_flip(mn[a]));
-      atomicMax(&g.bbox[3 + a], float_flip(mx[a]));
+  // one set of atomics per CTA (per-warp atomics on six addresses serialise for ~10 us)
+  __shared__ float s_mn[8][3], s_mx[8][3];
+  const int warp = threadIdx.x >> 5;
+  if (lane_id() == 0) for (int a = 0; a < 3; a++) { s_mn[warp][a] = mn[a]; s_mx[warp][a] = mx[a]; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    const int a = threadIdx.x;
+    float lo = s_mn[0][a], hi = s_mx[0][a];
+    for (int w = 1; w < 8; w++) { lo = fminf(lo, s_mn[w][a]); hi = fmaxf(hi, s_mx[w][a]); }
+    if (lo <= hi) {
+      atomicMin(&g.bbox[a], float_flip(lo));
+      atomicMax(&g.bbox[3 + a], float_flip(hi));
     }
   }
 }

@@ -301,9 +301,18 @@ __global__ void __launch_bounds__(256) lm_gather_map(LMGatherArgs A) {
   if (v >= st->validNum) return;
   CubeDesc d = A.cubes[T][st->validInd[v]];
   int dst = st->gatherOff[T][v];
-  if (dst + d.cnt > A.ecap) { if (threadIdx.x == 0) atomicOr(&A.st->error, 8); return; }
+  if (dst + d.cnt > A.ecap) { if (threadIdx.x == 0 && blockIdx.z == 0) atomicOr(&A.st->error, 8); return; }
   const float4* src = A.arena[T] + d.off;
-  for (int k = threadIdx.x; k < d.cnt; k += 256) A.E[T][dst + k] = src[k];
+  // blockIdx.z splits a cube into slices; four independent loads per thread in flight
+  const int per = (d.cnt + (int)gridDim.z - 1) / (int)gridDim.z;
+  const int k0 = blockIdx.z * per, k1 = min(d.cnt, k0 + per);
+  for (int k = k0 + threadIdx.x; k < k1; k += 4 * 256) {
+    float4 p[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) p[u] = src[min(k + u * 256, k1 - 1)];
+#pragma unroll
+    for (int u = 0; u < 4; u++) if (k + u * 256 < k1) A.E[T][dst + k + u * 256] = p[u];
+  }
 }
 
 // ---- exact 5-NN inside radius 1 (the only case the reference accepts, :719,:826) ------------

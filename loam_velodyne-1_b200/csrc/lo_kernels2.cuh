@@ -217,8 +217,10 @@ __global__ void __launch_bounds__(LO_THREADS, 1) lo_optimize(LOArgs A) {
   const int n_sharp = A.cnt->n_sharp, n_flat = A.cnt->n_flat;
   const int F = n_sharp + n_flat;
   const int n_corner_last = st->n_corner_last, n_surf_last = st->n_surf_last;
+  // every CTA owns a contiguous slice of the features (the critical path is the single most
+  // expensive feature, so spreading features over CTAs does not help)
   const int per = (F + (int)gridDim.x - 1) / (int)gridDim.x;
-  const int f_lo = min((int)blockIdx.x * per, F), f_hi = min(f_lo + per, F);
+  const int f_lo = min((int)blockIdx.x * per, F), nmine = min(f_lo + per, F) - f_lo;
   int iters_done = 0;
   if (st->cornerLastNum > 10 && st->surfLastNum > 100) {  // :465
     for (int iterCount = 0; iterCount < A.max_iter; iterCount++) {
@@ -231,11 +233,13 @@ __global__ void __launch_bounds__(LO_THREADS, 1) lo_optimize(LOArgs A) {
       }
       __syncthreads();
       double acc = 0.0;
-      for (int c0 = f_lo; c0 < f_hi; c0 += LO_WARPS) {
-        const int f = c0 + warp;
-        const bool first_pass = (c0 == f_lo);
+      long long dbg_t0 = 0;
+      if (iterCount == 0 && g_phase_on && threadIdx.x == 0) dbg_t0 = clock64();
+      for (int j0 = 0; j0 < nmine; j0 += LO_WARPS) {
+        const int f = f_lo + j0 + warp;
+        const bool first_pass = (j0 == 0);
         s_row[warp * 32 + lane][7] = 0.f;
-        if (f < f_hi) {
+        if (j0 + warp < nmine) {
           // ---- transform, (search), residual -> row slab of this iteration ----
           const bool is_corner = f < n_sharp;
           const float4 pt = is_corner ? A.sharp[f] : A.flat[f - n_sharp];
@@ -305,6 +309,7 @@ __global__ void __launch_bounds__(LO_THREADS, 1) lo_optimize(LOArgs A) {
         }
         __syncthreads();
         if (first_pass) PS();  // 0: features + rows of the first pass done
+        if (first_pass && iterCount == 0 && g_phase_on && threadIdx.x == 0) g_dbg_clk[64 + blockIdx.x] = clock64() - dbg_t0;
         red_rows_warped(s_row, LO_WARPS, iterCount + 1, acc);
         __syncthreads();
       }

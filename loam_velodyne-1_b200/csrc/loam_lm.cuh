@@ -180,7 +180,7 @@ struct LMHandle {
     LMGatherArgs GA;
     GA.st = st; GA.ecap = ecap;
     for (int T = 0; T < 2; T++) { GA.cubes[T] = d_cubes[T].p; GA.arena[T] = arena[T]; GA.E[T] = d_E[T].p; }
-    LAUNCH("lm_gather_map", lm_gather_map, dim3(125, 2), 256, 0, stream, GA);
+    LAUNCH("lm_gather_map", lm_gather_map, dim3(125, 2, 8), 256, 0, stream, GA);
     // K5: kdtreeCornerFromMap / kdtreeSurfFromMap -> grid index, cell 1.02 m
     {
       GridPair gp;

@@ -42,6 +42,11 @@ for k in range(nsw):
         L.loam_debug_phase_clocks(3, dc.ctypes.data, 64)
         us = lambda a, b: (dc[b] - dc[a]) / 1.965e3
         print(f"   sort_new: build={us(0,1):.1f} sort={us(1,2):.1f}  pass0: walk1={us(8,9):.1f} prefix={us(9,10):.1f} walk2={us(10,11):.1f}")
+    dc = np.zeros(512, np.int64)
+    L.loam_debug_phase_clocks(3, dc.ctypes.data, 512)
+    ft = dc[64:64 + 148] / 1.965e3
+    print(f"   sr_select ring0: stage={(dc[21]-dc[20])/1.965e3:.1f} select={(dc[22]-dc[21])/1.965e3:.1f} us")
+    print("   LO it0 per-CTA feature phase us: " + " ".join(f"{v:.0f}" for v in ft))
     for which, tag in ((0, "LO"), (1, "LM")):
         if which == 1 and r.lm_status != 0:
             continue
