@@ -157,8 +157,11 @@ int loam_pipeline_imu(loam_pipeline* h, double stamp, const double quat[4], cons
 /* synchronous: uploads the sweep, runs the nodes, downloads the poses into *res */
 int loam_pipeline_push(loam_pipeline* h, const float* xyz, int n, int stride_bytes, double stamp,
                        loam_sweep_result* res);
-/* asynchronous form: push_async only enqueues (the host buffer is staged before it returns),
- * collect() waits for everything enqueued so far and returns the per-sweep results in push order.
+/* asynchronous form: push_async only enqueues.  A pageable (or strided) host buffer is staged
+ * into pinned memory before it returns; a CUDA-pinned packed buffer (cudaHostAlloc /
+ * cudaHostRegister, stride_bytes == 12) is read in place by the copy engine and must stay
+ * unchanged until collect().  The H2D transfer runs on its own stream and overlaps the kernels
+ * of the previous sweep.  collect() waits for everything enqueued so far and returns the per-sweep results in push order.
  * push_device takes a sweep that is already resident in device memory as packed xyz floats;
  * first_last_xyz = host copies of its first and last finite point (scanRegistration.cpp:230-232
  * reads them on the host), first_index = index of the first finite point. */

@@ -314,7 +314,7 @@ class Pipeline(_Node):
 
 
     def push_async(self, xyz, stamp):
-        """xyz must stay alive only until this returns (it is staged into pinned memory)"""
+        """pageable xyz is staged before this returns; CUDA-pinned packed xyz is read in place until collect()"""
         xyz = np.ascontiguousarray(xyz, dtype=np.float32)
         return _check(self.L.loam_pipeline_push_async(self.h, xyz.ctypes.data, xyz.shape[0], xyz.strides[0], float(stamp)))
 

@@ -149,7 +149,7 @@ constexpr int PHASE_CLK_N = 512;
 __device__ int g_phase_on = 0;
 __device__ long long g_phase_clk[2][PHASE_CLK_N];
 __device__ long long g_rf_clk[2 * 250 * 8];   // lm_refilter_cube: 8 stamps per (type, rank)
-__device__ long long g_dbg_clk[512];           // ad-hoc stamps of single-CTA kernels (dev only)
+__device__ long long g_dbg_clk[1024];           // ad-hoc stamps of single-CTA kernels (dev only)
 #define DBG_STAMP(slot) do { if (g_phase_on && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_dbg_clk[slot] = clock64(); } while (0)
 __device__ __forceinline__ void phase_stamp(int which, int& slot) {
   if (slot >= 0 && slot < PHASE_CLK_N) g_phase_clk[which][slot++] = clock64();

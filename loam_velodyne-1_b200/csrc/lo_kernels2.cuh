@@ -243,7 +243,9 @@ __global__ void __launch_bounds__(LO_THREADS, 1) lo_optimize(LOArgs A) {
           // ---- transform, (search), residual -> row slab of this iteration ----
           const bool is_corner = f < n_sharp;
           const float4 pt = is_corner ? A.sharp[f] : A.flat[f - n_sharp];
+          if (refresh && g_phase_on && threadIdx.x == 0) g_dbg_clk[256 + blockIdx.x] = clock64();
           const float4 sel = lo_transform_to_start(pt, s_tr);
+          if (refresh && g_phase_on && threadIdx.x == 0) g_dbg_clk[832 + blockIdx.x] = clock64();
           bool valid = false;
           float4 coeff = make_float4(0, 0, 0, 0);
           if (is_corner) {
@@ -287,6 +289,7 @@ __global__ void __launch_bounds__(LO_THREADS, 1) lo_optimize(LOArgs A) {
               if (ok) valid = lo_surf_residual(sel, t1, t2, t3, iterCount, coeff);
             }
           }
+          if (refresh && g_phase_on && threadIdx.x == 0) g_dbg_clk[640 + blockIdx.x] = clock64();
           if (lane == 0) {
             A.coeff[(size_t)iterCount * A.fcap + f] = coeff;
             A.row_valid[(size_t)iterCount * A.fcap + f] = valid ? 1 : 0;

@@ -63,7 +63,7 @@ extern "C" int loam_debug_phase_enable(int on) {
 }
 extern "C" int loam_debug_phase_clocks(int which, long long* out, int n) {
   if (which == 3) {
-    if (n > 512) n = 512;
+    if (n > 1024) n = 1024;
     CUDA_OK(cudaDeviceSynchronize());
     CUDA_OK(cudaMemcpyFromSymbol(out, g_dbg_clk, sizeof(long long) * n, 0));
     return LOAM_OK;

@@ -1,5 +1,7 @@
 // loam_pipeline.cuh -- the four nodes wired as the reference's topic graph on
-// one device and one CUDA stream: sr -> lo -> tm.onOdometry -> (lm -> tm.onMapping).
+// one device: sr -> lo -> tm.onOdometry -> (lm -> tm.onMapping).  Like the reference's separate
+// ROS nodes, the stages of consecutive sweeps overlap: scanRegistration of sweep k+1 runs on its
+// own stream while laserOdometry / laserMapping of sweep k run on the pipeline stream.
 //
 // All per-sweep state lives in device memory and every kernel takes its sizes from device
 // counters, so a sweep is a fixed launch sequence with NO host round trip: push_async() only
@@ -42,7 +44,8 @@ struct PipelineHandle {
   LOHandle lo;
   LMHandle lm;
   TMHost tm;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr;      // laserOdometry, laserMapping, pose record
+  cudaStream_t sr_stream = nullptr;   // scanRegistration of the NEXT sweep runs beside them (banked outputs, loam_sr.cuh)
   DevBuf<PipeRecord> d_ring;
   PinnedBuf<PipeRecord> h_ring;
   struct Pending { int slot; int sr_status, lo_status, lm_status; };
@@ -53,7 +56,8 @@ struct PipelineHandle {
   int init(const loam_params* p, int dev) {
     CUDA_OK(cudaSetDevice(dev));
     CUDA_OK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-    int r = sr.init(p, dev, stream);
+    CUDA_OK(cudaStreamCreateWithFlags(&sr_stream, cudaStreamNonBlocking));
+    int r = sr.init(p, dev, sr_stream);
     if (r != LOAM_OK) return r;
     r = lo.init(p, dev, stream);
     if (r != LOAM_OK) return r;
@@ -63,7 +67,11 @@ struct PipelineHandle {
     memset(&res, 0, sizeof(res));
     return LOAM_OK;
   }
-  ~PipelineHandle() { if (stream) { cudaStreamSynchronize(stream); } }
+  ~PipelineHandle() {
+    if (sr.copy_stream) cudaStreamSynchronize(sr.copy_stream);
+    if (sr_stream) { cudaStreamSynchronize(sr_stream); cudaStreamDestroy(sr_stream); }
+    if (stream) { cudaStreamSynchronize(stream); cudaStreamDestroy(stream); }
+  }
 
   int imu(double stamp, const double quat[4], const float acc[3]) {
     sr.on_imu(stamp, quat, acc);
@@ -93,6 +101,8 @@ struct PipelineHandle {
       LAUNCH("pipe_record", pipe_record, 1, 32, 0, stream, d_ring.p + pd.slot, sr.d_cnt.p, sr.imu_state_dev(), lo.d_state.p, lm.d_state.p,
              pd.lm_status == LOAM_OK ? 1 : 0);
       CUDA_OK(cudaMemcpyAsync(h_ring.p + pd.slot, d_ring.p + pd.slot, sizeof(PipeRecord), cudaMemcpyDeviceToHost, stream));
+      int rr = sr.release_bank(stream);
+      if (rr < 0) return rr;
     }
     next_slot = (next_slot + 1) % RING;
     pending.push_back(pd);

@@ -19,22 +19,53 @@ struct SRHandle {
   int systemInitCount = 0;
   bool systemInited = false;
   // device buffers
-  DevBuf<float> d_raw2[2];
+  // incoming sweeps: RAW_DEPTH device/pinned buffer pairs filled by a separate copy stream, so the
+  // H2D transfer of sweep k+1 overlaps the kernels of sweep k (ev_copied: copy -> compute,
+  // ev_free: compute -> copy, both also guard the reuse of the pinned staging buffer)
+  static const int RAW_DEPTH = 4;
+  DevBuf<float> d_raw2[RAW_DEPTH];
   float* d_raw_cur = nullptr;
-  cudaEvent_t ev_raw[2] = {nullptr, nullptr};
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_copied[RAW_DEPTH] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_free[RAW_DEPTH] = {nullptr, nullptr, nullptr, nullptr};
   int raw_sel = 0;
   DevBuf<short> d_ring;
   DevBuf<float> d_ori, d_reltime, d_curv;
   DevBuf<int> d_hist, d_ring_start, d_scan_start, d_scan_end, d_pos, d_sort_ind;
   DevBuf<unsigned char> d_picked, d_gap, d_steps;
   DevBuf<signed char> d_label;
-  DevBuf<int> d_sharp_ring, d_less_sharp_ring, d_flat_ring, d_ring_counts, d_blockmax;
+  DevBuf<int> d_sharp_ring, d_less_sharp_ring, d_flat_ring, d_blockmax;
   DevBuf<int> d_sharp_idx, d_less_sharp_idx, d_flat_idx;
-  DevBuf<float4> d_full, d_sharp, d_less_sharp, d_flat, d_less_flat, d_lessflat_tmp;
-  DevBuf<SRCounts> d_cnt;
+  DevBuf<float4> d_lessflat_tmp;
+  // What the node publishes (the five clouds :584-612, their counters, per-ring counts) lives in
+  // two banks, so that sweep k+1 can be registered on this node's stream while the consumers of
+  // sweep k (laserOdometry, the pose record) still read bank k&1 on another stream.  d_full ...
+  // d_cnt are views of the bank of the most recent sweep.
+  struct Bank {
+    DevBuf<float4> full, sharp, less_sharp, flat, less_flat;
+    DevBuf<SRCounts> cnt;
+    DevBuf<int> ring_counts;
+    cudaEvent_t released = nullptr;   // recorded by the consumer when it is done with the bank
+  } bank[2];
+  int cur_bank = 0;
+  template <typename T> struct View { T* p = nullptr; };
+  View<float4> d_full, d_sharp, d_less_sharp, d_flat, d_less_flat;
+  View<SRCounts> d_cnt;
+  View<int> d_ring_counts;
+  void select_bank(int b) {
+    cur_bank = b;
+    Bank& k = bank[b];
+    d_full.p = k.full.p; d_sharp.p = k.sharp.p; d_less_sharp.p = k.less_sharp.p; d_flat.p = k.flat.p; d_less_flat.p = k.less_flat.p;
+    d_cnt.p = k.cnt.p; d_ring_counts.p = k.ring_counts.p;
+  }
+  // called by the consumer of the current bank after its last read has been enqueued on `s`
+  int release_bank(cudaStream_t s) {
+    if (s != stream) CUDA_OK(cudaEventRecord(bank[cur_bank].released, s));
+    return LOAM_OK;
+  }
   DevBuf<ImuSnapshot> d_imu;
   DevBuf<ImuState> d_imu_state;  // [2]
-  PinnedBuf<float> h_raw2[2];
+  PinnedBuf<float> h_raw2[RAW_DEPTH];
   PinnedBuf<SRCounts> h_cnt;
   PinnedRing<ImuSnapshot, 4> h_imu;
   PinnedRing<SRCounts, 4> h_cnt_init;
@@ -64,22 +95,34 @@ struct SRHandle {
     nblk_cap = (cap + SR_BLK - 1) / SR_BLK;
     int R = P.n_scans;
     int r = LOAM_OK;
-    r |= d_raw2[0].alloc((size_t)cap * 3); r |= d_raw2[1].alloc((size_t)cap * 3); r |= d_ring.alloc(cap); r |= d_ori.alloc(cap); r |= d_reltime.alloc(cap);
+    for (int b = 0; b < RAW_DEPTH; b++) { r |= d_raw2[b].alloc((size_t)cap * 3); r |= h_raw2[b].alloc((size_t)cap * 3); }
+    r |= d_ring.alloc(cap); r |= d_ori.alloc(cap); r |= d_reltime.alloc(cap);
     r |= d_curv.alloc_zero(cap, stream); r |= d_hist.alloc((size_t)R * nblk_cap); r |= d_ring_start.alloc(R + 1);
     r |= d_scan_start.alloc(R); r |= d_scan_end.alloc(R); r |= d_pos.alloc(cap); r |= d_sort_ind.alloc_zero(cap, stream);
     r |= d_picked.alloc_zero(cap + 16, stream); r |= d_gap.alloc_zero(cap + 16, stream); r |= d_steps.alloc(cap);
     r |= d_label.alloc_zero(cap, stream);
     r |= d_sharp_ring.alloc((size_t)R * SR_SHARP_PER_RING); r |= d_less_sharp_ring.alloc((size_t)R * SR_LESS_SHARP_PER_RING);
-    r |= d_flat_ring.alloc((size_t)R * SR_FLAT_PER_RING); r |= d_ring_counts.alloc_zero((size_t)R * 4, stream);
+    r |= d_flat_ring.alloc((size_t)R * SR_FLAT_PER_RING);
     r |= d_blockmax.alloc(nblk_cap);
     r |= d_sharp_idx.alloc((size_t)R * SR_SHARP_PER_RING); r |= d_less_sharp_idx.alloc((size_t)R * SR_LESS_SHARP_PER_RING);
     r |= d_flat_idx.alloc((size_t)R * SR_FLAT_PER_RING);
-    r |= d_full.alloc(cap); r |= d_sharp.alloc((size_t)R * SR_SHARP_PER_RING); r |= d_less_sharp.alloc((size_t)R * SR_LESS_SHARP_PER_RING);
-    r |= d_flat.alloc((size_t)R * SR_FLAT_PER_RING); r |= d_less_flat.alloc(cap); r |= d_lessflat_tmp.alloc((size_t)R * SR_RING_CAP);
-    r |= d_cnt.alloc_zero(1, stream); r |= d_imu.alloc(1); r |= d_imu_state.alloc_zero(2, stream);
-    r |= h_raw2[0].alloc((size_t)cap * 3); r |= h_raw2[1].alloc((size_t)cap * 3); r |= h_cnt.alloc(1); r |= h_imu.alloc(); r |= h_cnt_init.alloc(); r |= h_imu_state.alloc(1);
+    for (int b = 0; b < 2; b++) {
+      Bank& k = bank[b];
+      r |= k.full.alloc(cap); r |= k.sharp.alloc((size_t)R * SR_SHARP_PER_RING); r |= k.less_sharp.alloc((size_t)R * SR_LESS_SHARP_PER_RING);
+      r |= k.flat.alloc((size_t)R * SR_FLAT_PER_RING); r |= k.less_flat.alloc(cap);
+      r |= k.cnt.alloc_zero(1, stream); r |= k.ring_counts.alloc_zero((size_t)R * 4, stream);
+      if (cudaEventCreateWithFlags(&k.released, cudaEventDisableTiming) != cudaSuccess) r = LOAM_ERR_CUDA;
+    }
+    select_bank(0);
+    r |= d_lessflat_tmp.alloc((size_t)R * SR_RING_CAP);
+    r |= d_imu.alloc(1); r |= d_imu_state.alloc_zero(2, stream);
+    r |= h_cnt.alloc(1); r |= h_imu.alloc(); r |= h_cnt_init.alloc(); r |= h_imu_state.alloc(1);
     if (r != LOAM_OK) return LOAM_ERR_CUDA;
-    for (int b = 0; b < 2; b++) CUDA_OK(cudaEventCreateWithFlags(&ev_raw[b], cudaEventDisableTiming));
+    CUDA_OK(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
+    for (int b = 0; b < RAW_DEPTH; b++) {
+      CUDA_OK(cudaEventCreateWithFlags(&ev_copied[b], cudaEventDisableTiming));
+      CUDA_OK(cudaEventCreateWithFlags(&ev_free[b], cudaEventDisableTiming));
+    }
     memset(&imu, 0, sizeof(imu));
     memset(imuAcc, 0, sizeof(imuAcc));
     imu.pointer_last = -1;
@@ -91,7 +134,12 @@ struct SRHandle {
     return LOAM_OK;
   }
   ~SRHandle() {
-    for (int b = 0; b < 2; b++) if (ev_raw[b]) cudaEventDestroy(ev_raw[b]);
+    if (copy_stream) { cudaStreamSynchronize(copy_stream); cudaStreamDestroy(copy_stream); }
+    for (int b = 0; b < 2; b++) if (bank[b].released) cudaEventDestroy(bank[b].released);
+    for (int b = 0; b < RAW_DEPTH; b++) {
+      if (ev_copied[b]) cudaEventDestroy(ev_copied[b]);
+      if (ev_free[b]) cudaEventDestroy(ev_free[b]);
+    }
     if (own_stream && stream) cudaStreamDestroy(stream);
   }
 
@@ -147,18 +195,29 @@ struct SRHandle {
     if (n <= 0 || !xyz || stride_bytes < 12 || (stride_bytes & 3)) { set_error("bad sweep"); return LOAM_ERR_ARG; }
     if (n > cap) { set_error("sweep of %d points exceeds max_points=%d", n, cap); return LOAM_ERR_CAPACITY; }
     CUDA_OK(cudaSetDevice(device));
-    // stage through one of two pinned buffers (the other may still be in flight)
+    // A CUDA-pinned, packed (stride 12) caller buffer is read by the DMA engine in place (the caller
+    // keeps it unchanged until collect() / the synchronous call returns); anything else is staged
+    // through one of RAW_DEPTH pinned buffers.
     const int b = raw_sel;
-    raw_sel ^= 1;
-    CUDA_OK(cudaEventSynchronize(ev_raw[b]));
-    float* hr = h_raw2[b].p;
-    int sf = stride_bytes / 4;
-    if (sf == 3) memcpy(hr, xyz, sizeof(float) * 3 * (size_t)n);
-    else
-      for (int i = 0; i < n; i++) {
-        const float* p = xyz + (size_t)i * sf;
-        hr[3 * i] = p[0]; hr[3 * i + 1] = p[1]; hr[3 * i + 2] = p[2];
-      }
+    raw_sel = (raw_sel + 1) % RAW_DEPTH;
+    const int sf = stride_bytes / 4;
+    const float* hr = nullptr;
+    if (sf == 3) {
+      cudaPointerAttributes at;
+      if (cudaPointerGetAttributes(&at, xyz) == cudaSuccess && at.type == cudaMemoryTypeHost) hr = xyz;
+      else cudaGetLastError();
+    }
+    if (!hr) {
+      CUDA_OK(cudaEventSynchronize(ev_copied[b]));   // previous transfer out of this staging buffer is done
+      float* st = h_raw2[b].p;
+      if (sf == 3) memcpy(st, xyz, sizeof(float) * 3 * (size_t)n);
+      else
+        for (int i = 0; i < n; i++) {
+          const float* p = xyz + (size_t)i * sf;
+          st[3 * i] = p[0]; st[3 * i + 1] = p[1]; st[3 * i + 2] = p[2];
+        }
+      hr = st;
+    }
     int first = -1, lastf = -1;
     for (int i = 0; i < n; i++) {
       const float* p = hr + 3 * i;
@@ -172,9 +231,12 @@ struct SRHandle {
     float startOri, endOri;
     sweep_orientation(hr + 3 * first, hr + 3 * lastf, startOri, endOri);
     d_raw_cur = d_raw2[b].p;
-    CUDA_OK(cudaMemcpyAsync(d_raw_cur, hr, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, stream));
+    CUDA_OK(cudaStreamWaitEvent(copy_stream, ev_free[b], 0));   // kernels that read d_raw2[b] RAW_DEPTH sweeps ago
+    CUDA_OK(cudaMemcpyAsync(d_raw_cur, hr, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, copy_stream));
+    CUDA_OK(cudaEventRecord(ev_copied[b], copy_stream));
+    CUDA_OK(cudaStreamWaitEvent(stream, ev_copied[b], 0));
     int rc = process_device(n, first, startOri, endOri, stamp);
-    CUDA_OK(cudaEventRecord(ev_raw[b], stream));
+    CUDA_OK(cudaEventRecord(ev_free[b], stream));
     return rc;
   }
 
@@ -210,6 +272,8 @@ struct SRHandle {
   int process_device(int n, int first, float startOri, float endOri, double stamp) {
     const int R = P.n_scans;
     const int nblk = (n + SR_BLK - 1) / SR_BLK;
+    select_bank(cur_bank ^ 1);
+    CUDA_OK(cudaStreamWaitEvent(stream, bank[cur_bank].released, 0));   // consumers of the sweep before last
     SRCounts init;
     memset(&init, 0, sizeof(init));
     init.h_min = INT_MAX;

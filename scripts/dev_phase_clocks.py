@@ -42,9 +42,12 @@ for k in range(nsw):
         L.loam_debug_phase_clocks(3, dc.ctypes.data, 64)
         us = lambda a, b: (dc[b] - dc[a]) / 1.965e3
         print(f"   sort_new: build={us(0,1):.1f} sort={us(1,2):.1f}  pass0: walk1={us(8,9):.1f} prefix={us(9,10):.1f} walk2={us(10,11):.1f}")
-    dc = np.zeros(512, np.int64)
-    L.loam_debug_phase_clocks(3, dc.ctypes.data, 512)
+    dc = np.zeros(1024, np.int64)
+    L.loam_debug_phase_clocks(3, dc.ctypes.data, 1024)
     ft = dc[64:64 + 148] / 1.965e3
+    for b in (0, 20, 60, 80, 100, 120, 130, 140):
+        t0_, t1_, t2_, t3_ = dc[256 + b], dc[832 + b], dc[448 + b], dc[640 + b]
+        print(f"   LO last-search CTA{b} warp0: transform={(t1_-t0_)/1.965e3:.1f} nn1={(t2_-t1_)/1.965e3:.1f} window+residual={(t3_-t2_)/1.965e3:.1f} us")
     print(f"   sr_select ring0: stage={(dc[21]-dc[20])/1.965e3:.1f} select={(dc[22]-dc[21])/1.965e3:.1f} us")
     print("   LO it0 per-CTA feature phase us: " + " ".join(f"{v:.0f}" for v in ft))
     for which, tag in ((0, "LO"), (1, "LM")):
