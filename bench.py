@@ -258,6 +258,7 @@ def main():
     ev0.record(stream)
     for k in range(W, total):
         G.push_device(resident[k].data_ptr(), npts[k], aux[k][0], aux[k][1], sweeps[k][1])
+    G.join()            # the pipeline stream waits for the registration / mapping streams: ev1 covers all work
     ev1.record(stream)
     results = G.collect()
     torch.cuda.synchronize()
@@ -370,7 +371,7 @@ def main():
                 "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "sequences": world, "sweeps_per_sequence": K, "points_per_sweep": int(np.mean(npts)),
                            "parallelism": f"seq{world}", "l2": "inputs larger than L2: %d distinct sweeps (%.0f MB) resident in HBM, each read once" % (total, sum(npts) * 12 / 1e6),
-                           "timed_region": "K x (scanRegistration + laserOdometry + laserMapping every 2nd sweep + pose record), CUDA events on the pipeline stream, no host sync inside"},
+                           "timed_region": "K x (scanRegistration + laserOdometry + laserMapping every 2nd sweep + pose record); stages of consecutive sweeps overlap on 3 streams (+ copy stream) like the reference's nodes; CUDA events on the pipeline stream after a device-side join of all streams, no host sync inside"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
                 "wall_ms_incl_launch": float(ms_t[1].item()),
                 "mean_counts": stats, "roofline": roofline, "top_kernels": kernels, "cpu_baseline": cb,

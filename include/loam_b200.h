@@ -169,7 +169,13 @@ int loam_pipeline_push_async(loam_pipeline* h, const float* xyz, int n, int stri
 int loam_pipeline_push_device(loam_pipeline* h, const float* d_xyz, int n, const float first_last_xyz[6],
                               int first_index, double stamp);
 int loam_pipeline_collect(loam_pipeline* h, loam_sweep_result* out, int cap, int* n);
-void* loam_pipeline_stream(loam_pipeline* h); /* the cudaStream_t all work of this handle runs on */
+/* The stages of consecutive sweeps overlap on internal streams (registration of sweep k+1 and
+ * mapping of sweep k-1 beside the odometry of sweep k).  loam_pipeline_stream() is the odometry
+ * stream; loam_pipeline_join() makes it wait (on the device, no host synchronisation) for all work
+ * enqueued so far on the other streams, so that an event recorded on it afterwards covers
+ * everything pushed before. */
+void* loam_pipeline_stream(loam_pipeline* h);
+int loam_pipeline_join(loam_pipeline* h);
 loam_sr* loam_pipeline_sr(loam_pipeline* h);
 loam_lo* loam_pipeline_lo(loam_pipeline* h);
 loam_lm* loam_pipeline_lm(loam_pipeline* h);

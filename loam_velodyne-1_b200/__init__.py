@@ -108,6 +108,7 @@ def lib():
     L.loam_pipeline_collect.argtypes = [vp, vp, ci, ctypes.POINTER(ci)]
     L.loam_pipeline_stream.restype = vp
     L.loam_pipeline_stream.argtypes = [vp]
+    L.loam_pipeline_join.argtypes = [vp]
     for f in ("sr", "lo", "lm"):
         fn = getattr(L, f"loam_pipeline_{f}")
         fn.restype = vp
@@ -330,6 +331,10 @@ class Pipeline(_Node):
 
     def stream(self):
         return self.L.loam_pipeline_stream(self.h)
+
+    def join(self):
+        """device-side: the stream() waits for the registration / mapping streams"""
+        _check(self.L.loam_pipeline_join(self.h))
 
 
 def _borrow(cls, h, cap, L):

@@ -116,6 +116,26 @@ __device__ __forceinline__ int lm_cube_coord(float v, int cen) {
   return c;
 }
 
+// topic hand-over laserOdometry -> laserMapping (see LMHandle::Input): copies the three clouds and
+// the odometry state of this sweep into an input bank
+struct LMHandoffArgs {
+  const LOState* lo;
+  const float4* src[3];
+  float4* dst[3];
+  LOState* lo_out;
+  int cap;
+};
+__global__ void __launch_bounds__(256) lm_handoff(LMHandoffArgs A) {
+  const int n0 = min(A.lo->n_corner_last, A.cap), n1 = min(A.lo->n_surf_last, A.cap), n2 = min(A.lo->n_full_end, A.cap);
+  const int total = n0 + n1 + n2;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
+    if (i < n0) A.dst[0][i] = A.src[0][i];
+    else if (i < n0 + n1) A.dst[1][i - n0] = A.src[1][i - n0];
+    else A.dst[2][i - n0 - n1] = A.src[2][i - n0 - n1];
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) *A.lo_out = *A.lo;
+}
+
 struct LMSetupArgs {
   LMState* st;
   const LOState* lo;        // transformSum of this sweep, cloud sizes

@@ -40,6 +40,16 @@ struct LMHandle {
   LMState last_state;
   bool last_surround = false;
   int last_n_registered = 0;
+  // What the node receives from laserOdometry (/laser_cloud_corner_last, _surf_last,
+  // /velodyne_cloud_3, /laser_odom_to_init).  When the odometry runs on another stream the
+  // messages are copied into one of two input banks (lm_handoff, enqueued on the odometry's
+  // stream), so the odometry of the next sweeps runs beside this sweep's mapping -- the topic
+  // queue between the reference's two nodes.
+  struct Input { const LOState* lo; const float4* corner_last; const float4* surf_last; const float4* full_end; };
+  DevBuf<LOState> d_in_state[2];
+  DevBuf<float4> d_in_corner[2], d_in_surf[2], d_in_full[2];
+  cudaEvent_t ev_in_ready[2] = {nullptr, nullptr}, ev_in_done[2] = {nullptr, nullptr};
+  int in_bank = 0;
 
   int init(const loam_params* p, int dev, cudaStream_t s) {
     P = *p;
@@ -96,6 +106,11 @@ struct LMHandle {
     }
     r |= d_registered.alloc(cap); r |= d_partials.alloc_zero((size_t)2 * coop_blocks * LO_NRED, stream);
     r |= h_state.alloc(1); r |= h_imu.alloc();
+    for (int b = 0; b < 2; b++) {
+      r |= d_in_state[b].alloc_zero(1, stream); r |= d_in_corner[b].alloc(cap); r |= d_in_surf[b].alloc(cap); r |= d_in_full[b].alloc(cap);
+      if (cudaEventCreateWithFlags(&ev_in_ready[b], cudaEventDisableTiming) != cudaSuccess) r = LOAM_ERR_CUDA;
+      if (cudaEventCreateWithFlags(&ev_in_done[b], cudaEventDisableTiming) != cudaSuccess) r = LOAM_ERR_CUDA;
+    }
     if (r != LOAM_OK) return LOAM_ERR_CUDA;
     LMState init;
     memset(&init, 0, sizeof(init));
@@ -111,6 +126,10 @@ struct LMHandle {
   }
   ~LMHandle() {
     if (ev_dep) cudaEventDestroy(ev_dep);
+    for (int b = 0; b < 2; b++) {
+      if (ev_in_ready[b]) cudaEventDestroy(ev_in_ready[b]);
+      if (ev_in_done[b]) cudaEventDestroy(ev_in_done[b]);
+    }
     if (own_stream && stream) cudaStreamDestroy(stream);
   }
 
@@ -145,20 +164,37 @@ struct LMHandle {
     if (frameCount < stackFrameNum) return LOAM_NOT_READY;
     frameCount = 0;
     CUDA_OK(cudaSetDevice(device));
+    Input in;
+    in.lo = lo.d_state.p; in.corner_last = lo.d_corner_last.p; in.surf_last = lo.d_surf_last.p; in.full_end = lo.d_full_end.p;
+    int bank = -1;
     if (lo.stream != stream) {
-      CUDA_OK(cudaEventRecord(ev_dep, lo.stream));
-      CUDA_OK(cudaStreamWaitEvent(stream, ev_dep, 0));
+      bank = in_bank;
+      in_bank ^= 1;
+      CUDA_OK(cudaStreamWaitEvent(lo.stream, ev_in_done[bank], 0));   // the mapping pass that last read this bank
+      LMHandoffArgs HA;
+      HA.lo = in.lo; HA.src[0] = in.corner_last; HA.src[1] = in.surf_last; HA.src[2] = in.full_end;
+      HA.dst[0] = d_in_corner[bank].p; HA.dst[1] = d_in_surf[bank].p; HA.dst[2] = d_in_full[bank].p; HA.lo_out = d_in_state[bank].p; HA.cap = cap;
+      LAUNCH("lm_handoff", lm_handoff, 148, 256, 0, lo.stream, HA);
+      CUDA_OK(cudaEventRecord(ev_in_ready[bank], lo.stream));
+      CUDA_OK(cudaStreamWaitEvent(stream, ev_in_ready[bank], 0));
+      in.lo = d_in_state[bank].p; in.corner_last = d_in_corner[bank].p; in.surf_last = d_in_surf[bank].p; in.full_end = d_in_full[bank].p;
     }
+    int rc = run(in, stamp);
+    if (bank >= 0) CUDA_OK(cudaEventRecord(ev_in_done[bank], stream));
+    return rc;
+  }
+
+  int run(const Input& in, double stamp) {
     LMState* st = d_state.p;
     const int nb = 148;
     float4* arena[2] = {d_arena[0][cur_arena].p, d_arena[1][cur_arena].p};
     // K1
     LMSetupArgs SA;
-    SA.st = st; SA.lo = lo.d_state.p; SA.cubes[0] = d_cubes[0].p; SA.cubes[1] = d_cubes[1].p;
+    SA.st = st; SA.lo = in.lo; SA.cubes[0] = d_cubes[0].p; SA.cubes[1] = d_cubes[1].p;
     LAUNCH("lm_setup", lm_setup, 1, 256, 0, stream, SA);
     // K2
     LMStackArgs KA;
-    KA.st = st; KA.in[0] = lo.d_corner_last.p; KA.in[1] = lo.d_surf_last.p; KA.out[0] = d_stack2[0].p; KA.out[1] = d_stack2[1].p;
+    KA.st = st; KA.in[0] = in.corner_last; KA.in[1] = in.surf_last; KA.out[0] = d_stack2[0].p; KA.out[1] = d_stack2[1].p;
     LAUNCH("lm_stack_transform", lm_stack_transform, nb, 256, 0, stream, KA);
     // K3: downSizeFilterCorner (0.2) / downSizeFilterSurf (0.4) on the incoming sweep: one cooperative kernel
     {
@@ -242,7 +278,7 @@ struct LMHandle {
       if (sr_ != LOAM_OK) return sr_;
     }
     // K8
-    LAUNCH("lm_registered", lm_registered, 2 * nb, 256, 0, stream, st, lo.d_full_end.p, &lo.d_state.p->n_full_end, d_registered.p);
+    LAUNCH("lm_registered", lm_registered, 2 * nb, 256, 0, stream, st, in.full_end, &in.lo->n_full_end, d_registered.p);
     CUDA_OK(cudaGetLastError());
     return LOAM_OK;
   }

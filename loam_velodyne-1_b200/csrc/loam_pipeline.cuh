@@ -24,18 +24,27 @@ struct PipeRecord {
   int surroundN, pad;
 };
 
-__global__ void pipe_record(PipeRecord* out, const SRCounts* cnt, const ImuState* imu, const LOState* lo, const LMState* lm, int with_lm) {
+// odometry part of a sweep's record (pipeline stream) ...
+__global__ void pipe_record(PipeRecord* out, const SRCounts* cnt, const ImuState* imu, const LOState* lo) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   PipeRecord r;
   r.cnt = *cnt;
   lo_load_imu(imu, r.imu_trans);
   for (int i = 0; i < 6; i++) { r.transform[i] = lo->transform[i]; r.transformSum[i] = lo->transformSum[i]; }
   r.lo_iters = lo->iters; r.lo_rows = lo->rows; r.lo_deg = lo->isDegenerate;
-  for (int i = 0; i < 6; i++) { r.aft[i] = lm->transformAftMapped[i]; r.bef[i] = lm->transformBefMapped[i]; }
-  r.lm_iters = lm->iters; r.lm_rows = lm->rows; r.lm_deg = lm->isDegenerate; r.lm_error = with_lm ? lm->error : 0;
-  for (int T = 0; T < 2; T++) { r.mapN[T] = lm->mapN[T]; r.stackN[T] = lm->stackN[T]; r.bump[T] = lm->bump[T]; }
-  r.surroundN = lm->surroundN; r.pad = 0;
+  for (int i = 0; i < 6; i++) { r.aft[i] = 0.f; r.bef[i] = 0.f; }
+  r.lm_iters = 0; r.lm_rows = 0; r.lm_deg = 0; r.lm_error = 0;
+  for (int T = 0; T < 2; T++) { r.mapN[T] = 0; r.stackN[T] = 0; r.bump[T] = 0; }
+  r.surroundN = 0; r.pad = 0;
   *out = r;
+}
+// ... and its mapping part, appended on the mapping stream when the sweep was mapped
+__global__ void pipe_record_lm(PipeRecord* out, const LMState* lm) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  for (int i = 0; i < 6; i++) { out->aft[i] = lm->transformAftMapped[i]; out->bef[i] = lm->transformBefMapped[i]; }
+  out->lm_iters = lm->iters; out->lm_rows = lm->rows; out->lm_deg = lm->isDegenerate; out->lm_error = lm->error;
+  for (int T = 0; T < 2; T++) { out->mapN[T] = lm->mapN[T]; out->stackN[T] = lm->stackN[T]; out->bump[T] = lm->bump[T]; }
+  out->surroundN = lm->surroundN;
 }
 
 struct PipelineHandle {
@@ -44,8 +53,10 @@ struct PipelineHandle {
   LOHandle lo;
   LMHandle lm;
   TMHost tm;
-  cudaStream_t stream = nullptr;      // laserOdometry, laserMapping, pose record
+  cudaStream_t stream = nullptr;      // laserOdometry, pose record
   cudaStream_t sr_stream = nullptr;   // scanRegistration of the NEXT sweep runs beside them (banked outputs, loam_sr.cuh)
+  cudaStream_t lm_stream = nullptr;   // laserMapping of sweep k runs beside the odometry of sweeps k+1, k+2 (input banks, loam_lm.cuh)
+  cudaEvent_t ev_join[2] = {nullptr, nullptr};
   DevBuf<PipeRecord> d_ring;
   PinnedBuf<PipeRecord> h_ring;
   struct Pending { int slot; int sr_status, lo_status, lm_status; };
@@ -61,7 +72,9 @@ struct PipelineHandle {
     if (r != LOAM_OK) return r;
     r = lo.init(p, dev, stream);
     if (r != LOAM_OK) return r;
-    r = lm.init(p, dev, stream);
+    CUDA_OK(cudaStreamCreateWithFlags(&lm_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; i++) CUDA_OK(cudaEventCreateWithFlags(&ev_join[i], cudaEventDisableTiming));
+    r = lm.init(p, dev, lm_stream);
     if (r != LOAM_OK) return r;
     if (d_ring.alloc(RING) != LOAM_OK || h_ring.alloc(RING) != LOAM_OK) return LOAM_ERR_CUDA;
     memset(&res, 0, sizeof(res));
@@ -70,7 +83,18 @@ struct PipelineHandle {
   ~PipelineHandle() {
     if (sr.copy_stream) cudaStreamSynchronize(sr.copy_stream);
     if (sr_stream) { cudaStreamSynchronize(sr_stream); cudaStreamDestroy(sr_stream); }
+    if (lm_stream) { cudaStreamSynchronize(lm_stream); cudaStreamDestroy(lm_stream); }
     if (stream) { cudaStreamSynchronize(stream); cudaStreamDestroy(stream); }
+    for (int i = 0; i < 2; i++) if (ev_join[i]) cudaEventDestroy(ev_join[i]);
+  }
+
+  // make the pipeline stream wait for everything enqueued so far on the other streams (no host sync)
+  int join() {
+    CUDA_OK(cudaEventRecord(ev_join[0], sr_stream));
+    CUDA_OK(cudaEventRecord(ev_join[1], lm_stream));
+    CUDA_OK(cudaStreamWaitEvent(stream, ev_join[0], 0));
+    CUDA_OK(cudaStreamWaitEvent(stream, ev_join[1], 0));
+    return LOAM_OK;
   }
 
   int imu(double stamp, const double quat[4], const float acc[3]) {
@@ -93,16 +117,22 @@ struct PipelineHandle {
       int lrc = lo.process(sr, &pub);
       if (lrc < 0) return lrc;
       pd.lo_status = lrc;
+      // record + release of the scanRegistration bank BEFORE the mapping is enqueued: the next
+      // sweeps' registration / odometry do not wait for it
+      LAUNCH("pipe_record", pipe_record, 1, 32, 0, stream, d_ring.p + pd.slot, sr.d_cnt.p, sr.imu_state_dev(), lo.d_state.p);
+      int rr = sr.release_bank(stream);
+      if (rr < 0) return rr;
       if (lrc == LOAM_OK && pub) {
         int mrc = lm.process(lo, stamp);
         if (mrc < 0) return mrc;
         pd.lm_status = mrc;
       }
-      LAUNCH("pipe_record", pipe_record, 1, 32, 0, stream, d_ring.p + pd.slot, sr.d_cnt.p, sr.imu_state_dev(), lo.d_state.p, lm.d_state.p,
-             pd.lm_status == LOAM_OK ? 1 : 0);
-      CUDA_OK(cudaMemcpyAsync(h_ring.p + pd.slot, d_ring.p + pd.slot, sizeof(PipeRecord), cudaMemcpyDeviceToHost, stream));
-      int rr = sr.release_bank(stream);
-      if (rr < 0) return rr;
+      if (pd.lm_status == LOAM_OK) {
+        LAUNCH("pipe_record_lm", pipe_record_lm, 1, 32, 0, lm_stream, d_ring.p + pd.slot, lm.d_state.p);
+        CUDA_OK(cudaMemcpyAsync(h_ring.p + pd.slot, d_ring.p + pd.slot, sizeof(PipeRecord), cudaMemcpyDeviceToHost, lm_stream));
+      } else {
+        CUDA_OK(cudaMemcpyAsync(h_ring.p + pd.slot, d_ring.p + pd.slot, sizeof(PipeRecord), cudaMemcpyDeviceToHost, stream));
+      }
     }
     next_slot = (next_slot + 1) % RING;
     pending.push_back(pd);
@@ -112,6 +142,7 @@ struct PipelineHandle {
   // wait for everything enqueued so far; fills out[0..*n) in push order (transformMaintenance runs here)
   int collect(loam_sweep_result* out, int cap, int* n) {
     CUDA_OK(cudaStreamSynchronize(stream));
+    CUDA_OK(cudaStreamSynchronize(lm_stream));
     int k = 0;
     while (!pending.empty()) {
       Pending pd = pending.front();
