@@ -199,6 +199,13 @@ int loam_debug_phase_clocks(int which, long long* out, int n);
  * cubes, append-only cubes, max old points, max new points, points written, -, cubes gone dirty */
 int loam_debug_lm_counters(loam_lm* h, int* out, int n);
 
+/* timeline of the pipeline's streams: while enabled, every launch is bracketed by one-thread
+ * kernels that write %globaltimer on the launch's stream (nothing is synchronised);
+ * on = 3 stamps only the begin and end of every node pass (light enough not to disturb the
+ * overlap).  loam_debug_trace_dump writes "kernel,stream,start_ns,end_ns" rows and returns their number */
+int loam_debug_trace_enable(int on);
+int loam_debug_trace_dump(const char* path);
+
 /* number of kernel launches issued by this library on the calling process so far */
 long long loam_kernel_launch_count(void);
 /* per-kernel device time accumulated since the last reset (CUDA events; 0 when profiling is off) */

@@ -21,12 +21,13 @@ namespace dm = loam::dm;
 
 void set_error(const char* fmt, ...);
 extern long long g_launches;
-extern bool g_profile;
+extern int g_profile;   // 0 off, 1 per-kernel CUDA events (serialising), 2 timeline stamps around every launch (non-serialising), 3 stamps at node boundaries only
 
 struct ProfEntry { double ms = 0; long long calls = 0; };
 std::map<std::string, ProfEntry>& prof_table();
 void prof_begin(cudaStream_t s);
 void prof_end(const char* name, cudaStream_t s);
+void prof_node(const char* name, cudaStream_t s, bool begin);   // mode 3: stamps at node boundaries only
 
 #define CUDA_OK(expr)                                                                     \
   do {                                                                                    \
@@ -41,10 +42,10 @@ void prof_end(const char* name, cudaStream_t s);
 // gpu_launches) and, in profile mode, brackets the launch with CUDA events on its own stream
 #define LAUNCH(name, kern, grid, block, smem, stream, ...)                 \
   do {                                                                     \
-    if (loamgpu::g_profile) loamgpu::prof_begin(stream);                   \
+    if (loamgpu::g_profile && loamgpu::g_profile != 3) loamgpu::prof_begin(stream); \
     kern<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);              \
     loamgpu::g_launches++;                                                 \
-    if (loamgpu::g_profile) loamgpu::prof_end(name, stream);               \
+    if (loamgpu::g_profile && loamgpu::g_profile != 3) loamgpu::prof_end(name, stream); \
   } while (0)
 
 template <typename T>
@@ -86,6 +87,11 @@ struct PinnedBuf {
   ~PinnedBuf() { free(); }
 };
 
+// word copy executed by one CTA; src may be pinned host memory (zero-copy read over PCIe/C2C)
+__global__ void __launch_bounds__(128) pinned_fetch(unsigned int* __restrict__ dst, const unsigned int* __restrict__ src, int nwords) {
+  for (int i = threadIdx.x; i < nwords; i += 128) dst[i] = src[i];
+}
+
 // small ring of pinned staging slots for host->device parameter uploads that may still be in
 // flight when the host prepares the next one (asynchronous pipeline mode)
 template <typename T, int N>
@@ -108,7 +114,12 @@ struct PinnedRing {
     next = (next + 1) % N;
     if (cudaEventSynchronize(ev[i]) != cudaSuccess) return LOAM_ERR_CUDA;
     *p[i] = v;
-    if (cudaMemcpyAsync(dst, p[i], sizeof(T), cudaMemcpyHostToDevice, s) != cudaSuccess) return LOAM_ERR_CUDA;
+    // a kernel reads the pinned slot instead of a copy-engine transfer: the copy engines execute
+    // their queue in order, so a small H2D that has to wait for its stream (e.g. the mapping
+    // stream, which runs a sweep or two behind) would hold back the next sweeps' point transfers
+    static_assert(sizeof(T) % 4 == 0, "word-sized parameter blocks only");
+    pinned_fetch<<<1, 128, 0, s>>>((unsigned int*)dst, (const unsigned int*)p[i], (int)(sizeof(T) / 4));
+    g_launches++;
     if (cudaEventRecord(ev[i], s) != cudaSuccess) return LOAM_ERR_CUDA;
     return LOAM_OK;
   }

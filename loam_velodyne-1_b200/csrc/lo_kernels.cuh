@@ -16,7 +16,7 @@
 namespace loamgpu {
 namespace cg = cooperative_groups;
 
-constexpr int LO_THREADS = 512;
+constexpr int LO_THREADS = 256;   // half an SM's registers: lm_optimize (or other streams' kernels) runs beside it
 constexpr int LO_WARPS = LO_THREADS / 32;
 constexpr int LO_NRED = 28;  // 21 (AtA upper) + 6 (AtB) + 1 (row count)
 

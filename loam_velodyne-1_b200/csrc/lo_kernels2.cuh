@@ -160,8 +160,8 @@ __device__ __forceinline__ void red_finish(cg::grid_group& grid, double acc, dou
   if (clk >= 0) phase_stamp(which, clk);
   grid.sync();
   if (clk >= 0) phase_stamp(which, clk);
-  if (t < LO_NRED * PS_GROUPS) {
-    const int e = t % LO_NRED, g = t / LO_NRED;
+  for (int u = t; u < LO_NRED * PS_GROUPS; u += blockDim.x) {
+    const int e = u % LO_NRED, g = u / LO_NRED;
     double v = 0.0;
     for (int b = g; b < (int)gridDim.x; b += PS_GROUPS) v += __ldcg(&part[(size_t)b * LO_NRED + e]);
     s_g[g][e] = v;
@@ -178,7 +178,7 @@ __device__ __forceinline__ void red_finish(cg::grid_group& grid, double acc, dou
 
 // The whole per-sweep LM loop :458-856 as one cooperative kernel.  Every CTA owns a contiguous
 // slice of the features, one warp per feature.
-__global__ void __launch_bounds__(LO_THREADS, 1) lo_optimize(LOArgs A) {
+__global__ void __launch_bounds__(LO_THREADS, 2) lo_optimize(LOArgs A) {
   cg::grid_group grid = cg::this_grid();
   __shared__ float s_tr[6];
   __shared__ float s_trig[6];

@@ -12,7 +12,7 @@
 namespace loamgpu {
 
 long long g_launches = 0;
-bool g_profile = false;
+int g_profile = 0;
 static thread_local char g_err[512] = "";
 static cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;
 
@@ -27,11 +27,53 @@ std::map<std::string, ProfEntry>& prof_table() {
   static std::map<std::string, ProfEntry> t;
   return t;
 }
+// mode 2: a one-thread kernel writes %globaltimer before and after every launch on the launch's own
+// stream; nothing is synchronised, so the stamps show how the streams really overlap
+__global__ void trace_stamp(unsigned long long* out) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  *out = t;
+}
+struct TraceRec { const char* name; void* stream; int i0, i1; };
+static unsigned long long* g_trace_buf = nullptr;
+static const int TRACE_CAP = 1 << 17;
+static int g_trace_n = 0, g_trace_i0 = -1;
+static std::vector<TraceRec> g_trace_recs;
+
+void prof_node(const char* name, cudaStream_t s, bool begin) {
+  if (g_profile != 3 || !g_trace_buf || g_trace_n + 1 > TRACE_CAP) return;
+  static std::map<std::string, int> open_idx;
+  const int i = g_trace_n++;
+  trace_stamp<<<1, 1, 0, s>>>(g_trace_buf + i);
+  if (begin) { open_idx[name] = i; return; }
+  TraceRec r;
+  r.name = name; r.stream = (void*)s; r.i0 = open_idx.count(name) ? open_idx[name] : i; r.i1 = i;
+  g_trace_recs.push_back(r);
+}
 void prof_begin(cudaStream_t s) {
+  if (g_profile == 3) return;
+  if (g_profile == 2) {
+    g_trace_i0 = -1;
+    if (g_trace_buf && g_trace_n + 2 <= TRACE_CAP) {
+      g_trace_i0 = g_trace_n++;
+      trace_stamp<<<1, 1, 0, s>>>(g_trace_buf + g_trace_i0);
+    }
+    return;
+  }
   if (!g_ev0) { cudaEventCreate(&g_ev0); cudaEventCreate(&g_ev1); }
   cudaEventRecord(g_ev0, s);
 }
 void prof_end(const char* name, cudaStream_t s) {
+  if (g_profile == 3) return;
+  if (g_profile == 2) {
+    if (g_trace_i0 >= 0) {
+      TraceRec r;
+      r.name = name; r.stream = (void*)s; r.i0 = g_trace_i0; r.i1 = g_trace_n++;
+      trace_stamp<<<1, 1, 0, s>>>(g_trace_buf + r.i1);
+      g_trace_recs.push_back(r);
+    }
+    return;
+  }
   cudaEventRecord(g_ev1, s);
   cudaEventSynchronize(g_ev1);
   float ms = 0;
@@ -107,9 +149,29 @@ int loam_params_preset(loam_params* p, int preset) {
 const char* loam_last_error(void) { return g_err; }
 long long loam_kernel_launch_count(void) { return g_launches; }
 int loam_profile_enable(int on) {
-  g_profile = on != 0;
+  g_profile = on != 0 ? 1 : 0;
   prof_table().clear();
   return LOAM_OK;
+}
+int loam_debug_trace_enable(int on) {
+  if (on && !g_trace_buf) CUDA_OK(cudaMalloc((void**)&g_trace_buf, sizeof(unsigned long long) * TRACE_CAP));
+  CUDA_OK(cudaDeviceSynchronize());
+  g_trace_n = 0;
+  g_trace_recs.clear();
+  g_profile = on == 3 ? 3 : (on ? 2 : 0);
+  return LOAM_OK;
+}
+int loam_debug_trace_dump(const char* path) {
+  if (!path || !g_trace_buf) { set_error("trace is not enabled"); return LOAM_ERR_ARG; }
+  CUDA_OK(cudaDeviceSynchronize());
+  std::vector<unsigned long long> t((size_t)g_trace_n + 1);
+  if (g_trace_n > 0) CUDA_OK(cudaMemcpy(t.data(), g_trace_buf, sizeof(unsigned long long) * g_trace_n, cudaMemcpyDeviceToHost));
+  FILE* f = fopen(path, "w");
+  if (!f) { set_error("cannot open %s", path); return LOAM_ERR_ARG; }
+  fprintf(f, "kernel,stream,start_ns,end_ns\n");
+  for (const TraceRec& r : g_trace_recs) fprintf(f, "%s,%p,%llu,%llu\n", r.name, r.stream, t[r.i0], t[r.i1]);
+  fclose(f);
+  return (int)g_trace_recs.size();
 }
 int loam_profile_report(char* buf, int cap) {
   std::string s;

@@ -179,6 +179,7 @@ struct LMHandle {
       CUDA_OK(cudaStreamWaitEvent(stream, ev_in_ready[bank], 0));
       in.lo = d_in_state[bank].p; in.corner_last = d_in_corner[bank].p; in.surf_last = d_in_surf[bank].p; in.full_end = d_in_full[bank].p;
     }
+    if (g_profile == 3) prof_node("laserMapping", stream, true);
     int rc = run(in, stamp);
     if (bank >= 0) CUDA_OK(cudaEventRecord(ev_in_done[bank], stream));
     return rc;

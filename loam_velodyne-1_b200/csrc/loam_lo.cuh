@@ -70,6 +70,7 @@ struct LOHandle {
       CUDA_OK(cudaEventRecord(ev_dep, sr.stream));
       CUDA_OK(cudaStreamWaitEvent(stream, ev_dep, 0));
     }
+    if (g_profile == 3) prof_node("laserOdometry", stream, true);
     const ImuState* imu = sr.imu_state_dev();
     GridPair gp;
     gp.g[0] = g_corner.buf(d_corner_last.p, &d_state.p->n_corner_last, &d_state.p->index_enable, 1.0f);

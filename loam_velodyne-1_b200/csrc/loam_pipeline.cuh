@@ -57,7 +57,8 @@ struct PipelineHandle {
   cudaStream_t sr_stream = nullptr;   // scanRegistration of the NEXT sweep runs beside them (banked outputs, loam_sr.cuh)
   cudaStream_t lm_stream = nullptr;   // laserMapping of sweep k runs beside the odometry of sweeps k+1, k+2 (input banks, loam_lm.cuh)
   cudaEvent_t ev_join[2] = {nullptr, nullptr};
-  DevBuf<PipeRecord> d_ring;
+  // result ring in pinned host memory, written by pipe_record / pipe_record_lm directly (no copy
+  // engine: a D2H queued behind the mapping stream would stall the records of the next sweeps)
   PinnedBuf<PipeRecord> h_ring;
   struct Pending { int slot; int sr_status, lo_status, lm_status; };
   std::deque<Pending> pending;
@@ -76,7 +77,7 @@ struct PipelineHandle {
     for (int i = 0; i < 2; i++) CUDA_OK(cudaEventCreateWithFlags(&ev_join[i], cudaEventDisableTiming));
     r = lm.init(p, dev, lm_stream);
     if (r != LOAM_OK) return r;
-    if (d_ring.alloc(RING) != LOAM_OK || h_ring.alloc(RING) != LOAM_OK) return LOAM_ERR_CUDA;
+    if (h_ring.alloc(RING) != LOAM_OK) return LOAM_ERR_CUDA;
     memset(&res, 0, sizeof(res));
     return LOAM_OK;
   }
@@ -111,27 +112,27 @@ struct PipelineHandle {
     pd.sr_status = pd.lo_status = pd.lm_status = LOAM_NOT_READY;
     int rc = src_device ? sr.process_resident(xyz, n, aux, aux + 3, first_idx, stamp) : sr.process(xyz, n, stride_bytes, stamp);
     if (rc < 0) return rc;
+    if (g_profile == 3) prof_node("scanRegistration", sr_stream, false);
     if (rc == LOAM_OK) {
       pd.sr_status = LOAM_OK;
       bool pub = false;
       int lrc = lo.process(sr, &pub);
       if (lrc < 0) return lrc;
+      if (g_profile == 3) prof_node("laserOdometry", stream, false);
       pd.lo_status = lrc;
       // record + release of the scanRegistration bank BEFORE the mapping is enqueued: the next
       // sweeps' registration / odometry do not wait for it
-      LAUNCH("pipe_record", pipe_record, 1, 32, 0, stream, d_ring.p + pd.slot, sr.d_cnt.p, sr.imu_state_dev(), lo.d_state.p);
+      LAUNCH("pipe_record", pipe_record, 1, 32, 0, stream, h_ring.p + pd.slot, sr.d_cnt.p, sr.imu_state_dev(), lo.d_state.p);
       int rr = sr.release_bank(stream);
       if (rr < 0) return rr;
       if (lrc == LOAM_OK && pub) {
         int mrc = lm.process(lo, stamp);
         if (mrc < 0) return mrc;
+        if (g_profile == 3) prof_node("laserMapping", lm_stream, false);
         pd.lm_status = mrc;
       }
       if (pd.lm_status == LOAM_OK) {
-        LAUNCH("pipe_record_lm", pipe_record_lm, 1, 32, 0, lm_stream, d_ring.p + pd.slot, lm.d_state.p);
-        CUDA_OK(cudaMemcpyAsync(h_ring.p + pd.slot, d_ring.p + pd.slot, sizeof(PipeRecord), cudaMemcpyDeviceToHost, lm_stream));
-      } else {
-        CUDA_OK(cudaMemcpyAsync(h_ring.p + pd.slot, d_ring.p + pd.slot, sizeof(PipeRecord), cudaMemcpyDeviceToHost, stream));
+        LAUNCH("pipe_record_lm", pipe_record_lm, 1, 32, 0, lm_stream, h_ring.p + pd.slot, lm.d_state.p);
       }
     }
     next_slot = (next_slot + 1) % RING;

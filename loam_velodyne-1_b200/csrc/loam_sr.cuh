@@ -274,6 +274,7 @@ struct SRHandle {
     const int nblk = (n + SR_BLK - 1) / SR_BLK;
     select_bank(cur_bank ^ 1);
     CUDA_OK(cudaStreamWaitEvent(stream, bank[cur_bank].released, 0));   // consumers of the sweep before last
+    if (g_profile == 3) prof_node("scanRegistration", stream, true);
     SRCounts init;
     memset(&init, 0, sizeof(init));
     init.h_min = INT_MAX;

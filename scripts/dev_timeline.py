@@ -1,0 +1,52 @@
+"""dev tool: stream timeline of the free-running pipeline (loam_debug_trace_*): which kernels overlap,
+how long each stream is busy per sweep, and where the pipeline stream idles.
+
+    python scripts/dev_timeline.py [preset] [n_sweeps] [out.csv] [mode]   # mode 2 = every launch, 3 = node passes only
+"""
+import ctypes, importlib, os, sys
+from collections import defaultdict
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+pkg = importlib.import_module("loam_velodyne-1_b200")
+synth = importlib.import_module("loam_velodyne-1_b200.synth")
+L = pkg.lib()
+L.loam_debug_trace_enable.argtypes = [ctypes.c_int]
+L.loam_debug_trace_dump.argtypes = [ctypes.c_char_p]
+preset = int(sys.argv[1]) if len(sys.argv) > 1 else 2
+nsw = int(sys.argv[2]) if len(sys.argv) > 2 else 40
+out = sys.argv[3] if len(sys.argv) > 3 else os.path.join(ROOT, "gpurun_out", "timeline.csv")
+mode = int(sys.argv[4]) if len(sys.argv) > 4 else 2
+S = synth.Synth(preset)
+sweeps = [S.sweep(k) for k in range(nsw + 20)]
+G = pkg.Pipeline(pkg.make_params(preset, system_delay=0), device=0)
+for k in range(20):
+    G.push_async(*sweeps[k])
+G.collect()
+L.loam_debug_trace_enable(mode)
+for k in range(20, 20 + nsw):
+    G.push_async(*sweeps[k])
+G.collect()
+n = L.loam_debug_trace_dump(out.encode())
+L.loam_debug_trace_enable(0)
+rows = [l.strip().split(",") for l in open(out)][1:]
+ev = [(r[0], r[1], int(r[2]), int(r[3])) for r in rows]
+t0 = min(e[2] for e in ev)
+t1 = max(e[3] for e in ev)
+span = (t1 - t0) / 1e3
+print(f"{n} launches, {nsw} sweeps, span {span:.0f} us = {span / nsw:.1f} us/sweep (stamp kernels included)")
+streams = sorted(set(e[1] for e in ev))
+for s in streams:
+    es = [e for e in ev if e[1] == s]
+    busy = sum(e[3] - e[2] for e in es) / 1e3
+    names = defaultdict(float)
+    for e in es:
+        names[e[0]] += (e[3] - e[2]) / 1e3
+    top = sorted(names.items(), key=lambda kv: -kv[1])[:8]
+    print(f"stream {s}: busy {busy:.0f} us ({100 * busy / span:.0f}%)  " + "  ".join(f"{k}={v / nsw:.1f}" for k, v in top))
+# one steady-state period (two sweeps) as text: kernels in start order with stream tag
+mid = t0 + (t1 - t0) // 2
+tag = {s: "ABCD"[i] for i, s in enumerate(streams)}
+sel = sorted([e for e in ev if mid <= e[2] < mid + (3_000_000 if mode == 3 else 1_000_000) and e[3] - e[2] >= 4000], key=lambda e: e[2])
+for e in sel:
+    print(f"  {(e[2] - mid) / 1e3:8.1f} -> {(e[3] - mid) / 1e3:8.1f}  ({(e[3] - e[2]) / 1e3:6.1f} us)  " + "                    " * "ABCD".index(tag[e[1]]) + e[0])
