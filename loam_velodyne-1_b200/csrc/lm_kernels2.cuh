@@ -164,7 +164,7 @@ __device__ __forceinline__ void lm_transform_update(LMState* st, float* T, const
 // then the per-CTA partials are exchanged through one grid barrier and every CTA redundantly
 // finishes the sum (ascending CTA order) and the 6x6 solve, so no broadcast is needed.
 constexpr int LM_CH = 256;   // queries per CTA per pass
-__global__ void __launch_bounds__(LM_THREADS, 2) lm_optimize(LMOptArgs A) {
+__global__ void __launch_bounds__(LM_THREADS, 1) lm_optimize(LMOptArgs A) {
   cg::grid_group grid = cg::this_grid();
   __shared__ float s_T[6];
   __shared__ LMTrig s_trig;

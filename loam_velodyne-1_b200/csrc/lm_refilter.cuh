@@ -260,8 +260,60 @@ __device__ __forceinline__ void rf_lower_bound_multi(const unsigned int* a, int 
   }
 }
 
-// K7d: one CTA per rewritten cube (blockIdx.x = rank in the plan, blockIdx.y = feature type)
-__global__ void __launch_bounds__(RF_THREADS, 1) lm_refilter_cube(LMCubeArgs A) {
+// Lower bounds for the 4 x 32 keys a warp holds in one merge step.  Consecutive lanes hold
+// consecutive old points, so key[u] ascends with the lane: eight lanes run the full binary
+// searches that bracket the four ranges (first and last lane of every u; `lowkey[u]` <= the key of
+// lane 0 replaces the lower end when the caller also wants that position), then every lane searches
+// its own keys inside a bracket that is a handful of elements wide.  One 13-step probe sequence
+// with 8 active lanes per warp instead of four with 32: the merge passes are bound by the shared
+// memory pipe of the one SM that owns the cube.
+__device__ __forceinline__ void rf_lower_bound_warp4(const unsigned int* a, int n, const unsigned int* key, const unsigned int* lowkey,
+                                                     int* pos, int* lowpos) {
+  const unsigned int full = 0xffffffffu;
+  const int lane = lane_id();
+  unsigned int mine = 0;
+#pragma unroll
+  for (int u = 0; u < 4; u++) {
+    const unsigned int k_lo = lowkey ? __shfl_sync(full, lowkey[u], 0) : __shfl_sync(full, key[u], 0);
+    const unsigned int k_hi = __shfl_sync(full, key[u], 31);
+    if (lane == u) mine = k_lo;
+    if (lane == 4 + u) mine = k_hi;
+  }
+  int p = 0;
+  if (lane < 8) {
+    int lo = 0, hi = n;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (a[mid] < mine) lo = mid + 1; else hi = mid;
+    }
+    p = lo;
+  }
+#pragma unroll
+  for (int u = 0; u < 4; u++) {
+    int lo = __shfl_sync(full, p, u);
+    int hi = __shfl_sync(full, p, 4 + u);
+    if (lowpos) lowpos[u] = lo;
+    const unsigned int k = key[u];
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (a[mid] < k) lo = mid + 1; else hi = mid;
+    }
+    pos[u] = lo;
+  }
+}
+
+// K7d: one CLUSTER of RF_SLICES CTAs per rewritten cube (r = rank in the plan, T = feature type).
+// The merge path is sliced over the cluster: CTA s owns the old points [n_old*s/S, n_old*(s+1)/S)
+// and the new points whose voxel lies between the first old voxel of its slice and of the next
+// one (sorted lists: both are contiguous ranges).  The slices exchange three ints through
+// distributed shared memory (premise violated, new-only voxel count, dirty) and CTA 0 allocates
+// the output.  The work of a cube grows with the map (tens of thousands of old points in the
+// cubes around the sensor) and is bound by shared-memory probes and dependent L2 loads of ONE SM;
+// the cluster spreads it over eight.  Append-only cubes and the general path run on CTA 0 alone.
+constexpr int RF_SLICES = 8;
+__device__ __forceinline__ void rf_cube(const LMCubeArgs& A, const int T, const int r) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const int srank = (int)cluster.block_rank();
   extern __shared__ __align__(16) unsigned char rf_smem[];
   float4* s_npt = (float4*)rf_smem;                               // RF_NEW_CAP  the new points, sorted by (voxel, stack order)
   unsigned int* s_nkey = (unsigned int*)(s_npt + RF_NEW_CAP);     // RF_NEW_CAP  their voxel keys
@@ -272,9 +324,10 @@ __global__ void __launch_bounds__(RF_THREADS, 1) lm_refilter_cube(LMCubeArgs A) 
   CtaRadixSmem& S = *(CtaRadixSmem*)rf_smem;                      // general path (aliases the arrays above)
   __shared__ int s_ws[RF_THREADS / 32];
   __shared__ int s_base, s_dirty, s_sbase;
+  __shared__ int s_x[4];          // read by the other CTAs of the cluster: bad, n_no, base, dirty
+  __shared__ unsigned int s_kb[2];
+  __shared__ int s_jb[2];
   LMState* st = A.st;
-  const int T = blockIdx.y, r = blockIdx.x;
-  if (r >= st->nproc[T]) return;
   const int cube = st->procCube[T][r];
   const int mode = st->procMode[T][r];
   const int n_new = st->procNewCnt[T][r];
@@ -289,13 +342,188 @@ __global__ void __launch_bounds__(RF_THREADS, 1) lm_refilter_cube(LMCubeArgs A) 
   const int cenW = st->cenW, cenH = st->cenH, cenD = st->cenD;
   if (threadIdx.x == 0) s_dirty = 0;
   __syncthreads();
-  long long* clk = (threadIdx.x == 0 && g_phase_on) ? g_rf_clk + ((size_t)T * PROC_MAX + r) * 8 : nullptr;
+  long long* clk = (threadIdx.x == 0 && srank == 0 && g_phase_on) ? g_rf_clk + ((size_t)T * PROC_MAX + r) * 8 : nullptr;
 #define RS(k) do { if (clk) clk[k] = clock64(); } while (0)
   if (clk) { for (int k = 0; k < 8; k++) clk[k] = 0; clk[7] = ((long long)n_old << 32) | (unsigned int)n_new; }
   RS(0);
   int n_out = 0;
-  bool general = (mode == 1) && (desc.dirty != 0 || n_new > RF_NEW_CAP);
+  bool general = (mode == 1) && (desc.dirty != 0 || n_new > RF_NEW_CAP);   // cluster-uniform
 
+  if (mode == 1 && !general) {
+    // ---- merge path, slice `srank` ----
+    const int i_a = (int)((long long)n_old * srank / RF_SLICES), i_b = (int)((long long)n_old * (srank + 1) / RF_SLICES);
+    // all new keys (the slice bounds are found in them), flags cleared
+    for (int j = threadIdx.x; j < n_new; j += RF_THREADS) { s_nkey[j] = nkeys[j] & 0x00ffffffu; s_found[j] = 0; }
+    if (threadIdx.x < 2) {
+      // voxel range of the slice: [first old voxel of this slice, first old voxel of the next one)
+      const int i = threadIdx.x == 0 ? i_a : i_b;
+      unsigned int k;
+      if (threadIdx.x == 0 && srank == 0) k = 0u;
+      else if (i >= n_old) k = 0xffffffffu;
+      else k = lm_voxel_key(old[i], cube, cenW, cenH, cenD, T, &st->error);
+      s_kb[threadIdx.x] = k;
+    }
+    __syncthreads();
+    if (threadIdx.x < 2) s_jb[threadIdx.x] = rf_lower_bound(s_nkey, n_new, s_kb[threadIdx.x]);
+    __syncthreads();
+    const int j_a = s_jb[0], j_b = max(s_jb[0], s_jb[1]);
+    // staging of the slice's new points: index loads, then point loads, four in flight per thread
+    for (int j0 = j_a + threadIdx.x; j0 < j_b; j0 += 4 * RF_THREADS) {
+      unsigned int vv[4];
+      float4 pp[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) vv[u] = nvals[min(j0 + u * RF_THREADS, j_b - 1)];
+#pragma unroll
+      for (int u = 0; u < 4; u++) pp[u] = ins_pts[vv[u]];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int j = j0 + u * RF_THREADS;
+        if (j < j_b) s_npt[j] = pp[u];
+      }
+    }
+    __syncthreads();
+    RS(5);
+    // Pass A over the slice's old points: are they strictly ascending (premise, including the
+    // step across the slice boundary), and which voxels of the new list already hold an old point
+    int bad = 0;
+    for (int ib = i_a; ib < i_b; ib += 4 * RF_THREADS) {   // warp-uniform trip count (shuffles inside)
+      const int i0 = ib + threadIdx.x;
+      unsigned int key[4];
+      int jpos[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int i = i0 + u * RF_THREADS;
+        key[u] = 0xffffffffu;
+        if (i < i_b) {
+          // both loads are independent and issued up front (a shuffle from lane - 1 would leave
+          // lane 0 with a dependent global load per step)
+          const float4 pc = old[i], pp = old[i > 0 ? i - 1 : 0];
+          key[u] = lm_voxel_key(pc, cube, cenW, cenH, cenD, T, &st->error);
+          if (i > 0 && key[u] <= lm_voxel_key(pp, cube, cenW, cenH, cenD, T, &st->error)) bad = 1;
+        }
+      }
+      rf_lower_bound_warp4(s_nkey, n_new, key, nullptr, jpos, nullptr);
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+        if (i0 + u * RF_THREADS < i_b && jpos[u] < n_new && s_nkey[jpos[u]] == key[u]) s_found[jpos[u]] = 1;   // first new point of that voxel
+    }
+    bad = __syncthreads_or(bad);
+    RS(1);
+    // voxels that hold only new points: segment heads of the slice's new range without an old point
+    int n_no = 0;
+    for (int base = j_a; base < j_b; base += RF_THREADS) {
+      const int j = base + threadIdx.x;
+      int flag = 0;
+      if (j < j_b) flag = ((j == 0 || s_nkey[j - 1] != s_nkey[j]) && !s_found[j]) ? 1 : 0;
+      int tot;
+      const int rank = n_no + rf_block_scan(flag, s_ws, &tot);
+      if (flag) { s_nokey[rank] = s_nkey[j]; s_nopos[rank] = j; }
+      n_no += tot;
+    }
+    RS(6);
+    for (int q = threadIdx.x; q < n_no; q += RF_THREADS) s_oldbefore[q] = i_b;
+    if (threadIdx.x == 0) { s_x[0] = bad; s_x[1] = n_no; s_x[3] = 0; }
+    cluster.sync();
+    int pre_no = 0, tot_no = 0, any_bad = 0;
+#pragma unroll
+    for (int t = 0; t < RF_SLICES; t++) {
+      const int* x = cluster.map_shared_rank(s_x, t);
+      const int b = x[0], c = x[1];
+      any_bad |= b;
+      if (t < srank) pre_no += c;
+      tot_no += c;
+    }
+    if (any_bad) {
+      general = true;      // cluster-uniform; CTA 0 sorts the whole cube below
+      cluster.sync();      // everyone has read s_x before a CTA that returns rewrites it for its next cube
+    } else {
+      n_out = n_old + tot_no;
+      if (srank == 0 && threadIdx.x == 0) {
+        int b = atomicAdd(&st->bump[T], n_out);
+        if (b + n_out > st->arenaCap) { atomicOr(&st->error, 1); b = -1; }
+        s_x[2] = b;
+      }
+      cluster.sync();
+      RS(2);
+      const int base = *cluster.map_shared_rank(&s_x[2], 0);
+      int dirty = 0;
+      if (base >= 0) {
+        float4* out = arena + base + pre_no;
+        // Pass B: every old point moves up by the number of new-only voxels in front of it and
+        // absorbs the new points of its own voxel (old first, then stack order: the reference's
+        // input order)
+        for (int ib = i_a; ib < i_b; ib += 4 * RF_THREADS) {
+          const int i0 = ib + threadIdx.x;
+          float4 p[4];
+          unsigned int key[8];   // [0..3] this point, [4..7] its predecessor (inside the slice)
+          int c[8], jpos[4];
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            const int i = i0 + u * RF_THREADS;
+            key[u] = 0xffffffffu; key[4 + u] = 0u;
+            if (i < i_b) {
+              p[u] = old[i];
+              const float4 pp = old[i > 0 ? i - 1 : 0];
+              key[u] = lm_voxel_key(p[u], cube, cenW, cenH, cenD, T, &st->error);
+              key[4 + u] = i > i_a ? lm_voxel_key(pp, cube, cenW, cenH, cenD, T, &st->error) : 0u;
+            }
+          }
+          rf_lower_bound_warp4(s_nokey, n_no, key, key + 4, c, c + 4);
+          // the predecessor of lane > 0 is the previous lane's point; lane 0 got its own from the bracket
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            const int up = __shfl_up_sync(0xffffffffu, c[u], 1);
+            if (lane_id() > 0) c[4 + u] = up;
+          }
+          rf_lower_bound_warp4(s_nkey, n_new, key, nullptr, jpos, nullptr);
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            const int i = i0 + u * RF_THREADS;
+            if (i >= i_b) break;
+            // new-only voxels between the predecessor and this point sit right in front of it
+            const int cprev = i > i_a ? c[4 + u] : 0;
+            for (int q = cprev; q < c[u]; q++) s_oldbefore[q] = i;
+            int j = jpos[u];
+            float4 po = p[u];
+            if (j < n_new && s_nkey[j] == key[u]) {
+              RFCentroid cen;
+              cen.init();
+              cen.add(po);
+              for (; j < n_new && s_nkey[j] == key[u]; j++) cen.add(s_npt[j]);
+              po = cen.get();
+              if (lm_voxel_key(po, cube, cenW, cenH, cenD, T, &st->error) != key[u]) dirty = 1;
+            }
+            out[i + c[u]] = po;
+          }
+        }
+        __syncthreads();
+        RS(3);
+        for (int q = threadIdx.x; q < n_no; q += RF_THREADS) {
+          const unsigned int key = s_nokey[q];
+          RFCentroid cen;
+          cen.init();
+          for (int j = s_nopos[q]; j < n_new && s_nkey[j] == key; j++) cen.add(s_npt[j]);
+          const float4 p = cen.get();
+          if (lm_voxel_key(p, cube, cenW, cenH, cenD, T, &st->error) != key) dirty = 1;
+          out[s_oldbefore[q] + q] = p;
+        }
+      }
+      dirty = __syncthreads_or(dirty);
+      if (threadIdx.x == 0) s_x[3] = dirty;
+      cluster.sync();
+      if (srank == 0 && threadIdx.x == 0) {
+        int d_any = 0;
+        for (int t = 0; t < RF_SLICES; t++) d_any |= cluster.map_shared_rank(s_x, t)[3];
+        s_dirty = d_any;
+        if (base >= 0) { CubeDesc d; d.off = base; d.cnt = n_out; d.dirty = d_any; d.pad = 0; A.cubes[T][cube] = d; }
+      }
+      cluster.sync();      // s_x stays valid until CTA 0 has read it
+      if (srank != 0) return;
+      goto done;
+    }
+  }
+  // append-only cubes and the general path: CTA 0 of the cluster alone
+  if (srank != 0) return;
   if (mode == 0) {
     // ---- cube outside the valid set: the reference only appends (:1000-1016), in stack order.
     // Marked dirty so the first refilter after it becomes valid sorts everything. ----
@@ -310,120 +538,6 @@ __global__ void __launch_bounds__(RF_THREADS, 1) lm_refilter_cube(LMCubeArgs A) 
     for (int i = threadIdx.x; i < n_old; i += RF_THREADS) arena[s_base + i] = old[i];
     for (int j = threadIdx.x; j < n_new; j += RF_THREADS) arena[s_base + n_old + j] = ins_pts[nvals[j]];
     if (threadIdx.x == 0) { CubeDesc d; d.off = s_base; d.cnt = n_out; d.dirty = 1; d.pad = 0; A.cubes[T][cube] = d; }
-    goto done;
-  }
-
-  if (!general) {
-    // ---- merge path.  Pass A over the old points: are they strictly ascending (premise), and
-    // which voxels of the new list already hold an old point ----
-    for (int j = threadIdx.x; j < n_new; j += RF_THREADS) {
-      s_nkey[j] = nkeys[j] & 0x00ffffffu;
-      s_npt[j] = ins_pts[nvals[j]];
-      s_found[j] = 0;
-    }
-    __syncthreads();
-    int bad = 0;
-    for (int i0 = threadIdx.x; i0 < n_old; i0 += 4 * RF_THREADS) {
-      unsigned int key[4];
-      int jpos[4];
-#pragma unroll
-      for (int u = 0; u < 4; u++) {
-        const int i = i0 + u * RF_THREADS;
-        key[u] = 0xffffffffu;
-        if (i < n_old) {
-          // both loads are independent and issued up front (a shuffle from lane - 1 would leave
-          // lane 0 with a dependent global load per step)
-          const float4 pc = old[i], pp = old[i > 0 ? i - 1 : 0];
-          key[u] = lm_voxel_key(pc, cube, cenW, cenH, cenD, T, &st->error);
-          if (i > 0 && key[u] <= lm_voxel_key(pp, cube, cenW, cenH, cenD, T, &st->error)) bad = 1;
-        }
-      }
-      rf_lower_bound_multi<4>(s_nkey, n_new, key, jpos);
-#pragma unroll
-      for (int u = 0; u < 4; u++)
-        if (i0 + u * RF_THREADS < n_old && jpos[u] < n_new && s_nkey[jpos[u]] == key[u]) s_found[jpos[u]] = 1;   // first new point of that voxel
-    }
-    if (__syncthreads_or(bad)) general = true;
-    RS(1);
-  }
-
-  if (!general) {
-    // voxels that hold only new points: segment heads of the new list without an old point
-    int n_no = 0;
-    for (int base = 0; base < n_new; base += RF_THREADS) {
-      const int j = base + threadIdx.x;
-      int flag = 0;
-      if (j < n_new) flag = ((j == 0 || s_nkey[j - 1] != s_nkey[j]) && !s_found[j]) ? 1 : 0;
-      int tot;
-      const int rank = n_no + rf_block_scan(flag, s_ws, &tot);
-      if (flag) { s_nokey[rank] = s_nkey[j]; s_nopos[rank] = j; }
-      n_no += tot;
-    }
-    for (int q = threadIdx.x; q < n_no; q += RF_THREADS) s_oldbefore[q] = n_old;
-    n_out = n_old + n_no;
-    if (threadIdx.x == 0) {
-      int b = atomicAdd(&st->bump[T], n_out);
-      if (b + n_out > st->arenaCap) { atomicOr(&st->error, 1); b = -1; }
-      s_base = b;
-    }
-    __syncthreads();
-    RS(2);
-    if (s_base < 0) goto done;
-    float4* out = arena + s_base;
-    int dirty = 0;
-    // Pass B: every old point moves up by the number of new-only voxels in front of it and absorbs
-    // the new points of its own voxel (old first, then stack order: the reference's input order)
-    for (int i0 = threadIdx.x; i0 < n_old; i0 += 4 * RF_THREADS) {
-      float4 p[4];
-      unsigned int key[8];   // [0..3] this point, [4..7] its predecessor
-      int c[8], jpos[4];
-#pragma unroll
-      for (int u = 0; u < 4; u++) {
-        const int i = i0 + u * RF_THREADS;
-        key[u] = 0xffffffffu; key[4 + u] = 0u;
-        if (i < n_old) {
-          p[u] = old[i];
-          const float4 pp = old[i > 0 ? i - 1 : 0];
-          key[u] = lm_voxel_key(p[u], cube, cenW, cenH, cenD, T, &st->error);
-          key[4 + u] = i > 0 ? lm_voxel_key(pp, cube, cenW, cenH, cenD, T, &st->error) : 0u;
-        }
-      }
-      rf_lower_bound_multi<8>(s_nokey, n_no, key, c);
-      rf_lower_bound_multi<4>(s_nkey, n_new, key, jpos);
-#pragma unroll
-      for (int u = 0; u < 4; u++) {
-        const int i = i0 + u * RF_THREADS;
-        if (i >= n_old) break;
-        // new-only voxels between the predecessor and this point sit right in front of it
-        const int cprev = i > 0 ? c[4 + u] : 0;
-        for (int q = cprev; q < c[u]; q++) s_oldbefore[q] = i;
-        int j = jpos[u];
-        float4 po = p[u];
-        if (j < n_new && s_nkey[j] == key[u]) {
-          RFCentroid cen;
-          cen.init();
-          cen.add(po);
-          for (; j < n_new && s_nkey[j] == key[u]; j++) cen.add(s_npt[j]);
-          po = cen.get();
-          if (lm_voxel_key(po, cube, cenW, cenH, cenD, T, &st->error) != key[u]) dirty = 1;
-        }
-        out[i + c[u]] = po;
-      }
-    }
-    __syncthreads();
-    RS(3);
-    for (int q = threadIdx.x; q < n_no; q += RF_THREADS) {
-      const unsigned int key = s_nokey[q];
-      RFCentroid cen;
-      cen.init();
-      for (int j = s_nopos[q]; j < n_new && s_nkey[j] == key; j++) cen.add(s_npt[j]);
-      const float4 p = cen.get();
-      if (lm_voxel_key(p, cube, cenW, cenH, cenD, T, &st->error) != key) dirty = 1;
-      out[s_oldbefore[q] + q] = p;
-    }
-    if (dirty) s_dirty = 1;
-    __syncthreads();
-    if (threadIdx.x == 0) { CubeDesc d; d.off = s_base; d.cnt = n_out; d.dirty = s_dirty; d.pad = 0; A.cubes[T][cube] = d; }
     goto done;
   }
 
@@ -500,6 +614,16 @@ done:
     atomicMax(&st->rfStat[T][3], n_old); atomicMax(&st->rfStat[T][4], n_new);
     atomicAdd(&st->rfStat[T][5], n_out);
     if (s_dirty) atomicAdd(&st->rfStat[T][7], 1);
+  }
+}
+// one wave of clusters; a cluster walks the plan with stride (number of clusters)
+constexpr int RF_GRID = 8 * RF_SLICES;
+__global__ void __cluster_dims__(RF_SLICES, 1, 1) __launch_bounds__(RF_THREADS, 1) lm_refilter_cube(LMCubeArgs A) {
+  const int T = blockIdx.y;
+  const int np = A.st->nproc[T];
+  for (int r = blockIdx.x / RF_SLICES; r < np; r += gridDim.x / RF_SLICES) {
+    rf_cube(A, T, r);
+    __syncthreads();
   }
 }
 

@@ -264,7 +264,7 @@ struct LMHandle {
         CA.touch_cnt[T] = d_touch[T].p; CA.cube_rank[T] = d_rank[T].p;
         for (int k = 0; k < 2; k++) { CA.nk[T][k] = d_nk[T][k].p; CA.nv[T][k] = d_nv[T][k].p; CA.sk[T][k] = d_sk[T][k].p; CA.sv[T][k] = d_sv[T][k].p; }
       }
-      LAUNCH("lm_refilter_cube", lm_refilter_cube, dim3(PROC_MAX, 2), RF_THREADS, RF_SMEM, stream, CA);
+      LAUNCH("lm_refilter_cube", lm_refilter_cube, dim3(RF_GRID, 2), RF_THREADS, RF_SMEM, stream, CA);
     }
     if (++sweeps_since_compact >= 8) {  // bounded garbage in the log-structured arena
       int cr = compact();

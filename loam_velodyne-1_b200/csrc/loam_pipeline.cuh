@@ -73,7 +73,12 @@ struct PipelineHandle {
     if (r != LOAM_OK) return r;
     r = lo.init(p, dev, stream);
     if (r != LOAM_OK) return r;
-    CUDA_OK(cudaStreamCreateWithFlags(&lm_stream, cudaStreamNonBlocking));
+    {
+      // the mapping chain is the longest of the three: its kernels are scheduled first
+      int lo_pri = 0, hi_pri = 0;
+      CUDA_OK(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
+      CUDA_OK(cudaStreamCreateWithPriority(&lm_stream, cudaStreamNonBlocking, hi_pri));
+    }
     for (int i = 0; i < 2; i++) CUDA_OK(cudaEventCreateWithFlags(&ev_join[i], cudaEventDisableTiming));
     r = lm.init(p, dev, lm_stream);
     if (r != LOAM_OK) return r;

@@ -35,8 +35,8 @@ for k in range(nsw):
                 n_old, n_new = int(t[7] >> 32), int(t[7] & 0xffffffff)
                 if n_old < 2000:
                     continue
-                st_ = [(t[k] - t[0]) / 1.965e3 if t[k] else -1 for k in range(1, 5)]
-                print(f"   rf T{T} r{rr} n_old={n_old} n_new={n_new} passA={st_[0]:.1f} scan+alloc={st_[1]:.1f} passB={st_[2]:.1f} end={st_[3]:.1f} us")
+                st_ = [(t[k] - t[0]) / 1.965e3 if t[k] else -1 for k in range(1, 7)]
+                print(f"   rf T{T} r{rr} n_old={n_old} n_new={n_new} stage={st_[4]:.1f} passA={st_[0]:.1f} nolist={st_[5]:.1f} scan+alloc={st_[1]:.1f} passB={st_[2]:.1f} end={st_[3]:.1f} us")
     if r.lm_status == 0:
         dc = np.zeros(64, np.int64)
         L.loam_debug_phase_clocks(3, dc.ctypes.data, 64)
