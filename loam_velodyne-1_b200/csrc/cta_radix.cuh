@@ -121,12 +121,18 @@ __device__ __forceinline__ void cta_radix_pass_reg(const unsigned int* __restric
   }
   for (int k = threadIdx.x; k < nwarps * 256; k += blockDim.x) (&S.cnt[0][0])[k] = 0;
   __syncthreads();
+  // walk the chunk once: rank of every element among the equal digits of this warp seen so far
+  // (stable), per-warp digit counts as a by-product
+  int rk[ITEMS];
 #pragma unroll
   for (int u = 0; u < ITEMS; u++) {
     const bool in = c0 + u * 32 + lane < c1;
     const int d = (int)((key[u] >> shift) & 255u);
     const unsigned int m = warp_match8(d, in);
-    if (in && (m & ((1u << lane) - 1u)) == 0) S.cnt[warp][d] += __popc(m);
+    const int r = __popc(m & ((1u << lane) - 1u));
+    rk[u] = in ? S.cnt[warp][d] + r : -1;
+    __syncwarp();
+    if (in && r == 0) S.cnt[warp][d] += __popc(m);
     __syncwarp();
   }
   __syncthreads();
@@ -153,16 +159,11 @@ __device__ __forceinline__ void cta_radix_pass_reg(const unsigned int* __restric
   __syncthreads();
 #pragma unroll
   for (int u = 0; u < ITEMS; u++) {
-    const bool in = c0 + u * 32 + lane < c1;
-    const int d = (int)((key[u] >> shift) & 255u);
-    const unsigned int m = warp_match8(d, in);
-    const int r = __popc(m & ((1u << lane) - 1u));
-    int dst = 0;
-    if (in) dst = S.tot[d] + S.cnt[warp][d] + r;
-    __syncwarp();
-    if (in && r == 0) S.cnt[warp][d] += __popc(m);
-    __syncwarp();
-    if (in) { kout[dst] = key[u]; vout[dst] = val[u]; }
+    if (rk[u] >= 0) {
+      const int d = (int)((key[u] >> shift) & 255u);
+      const int dst = S.tot[d] + S.cnt[warp][d] + rk[u];
+      kout[dst] = key[u]; vout[dst] = val[u];
+    }
   }
   __threadfence_block();
   __syncthreads();
