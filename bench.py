@@ -132,13 +132,29 @@ def algorithmic_bytes(kernel, s):
         return N * 16.0 if kernel == "sr_ring_ori" else N * 32.0
     if kernel == "lo_transform_to_end":
         return (Nls + Nlf + N / 2.0) * 32.0
-    if kernel == "lm_refilter_fill":
-        return (M + Q) * (16.0 + 16.0 + 8.0)
+    if kernel == "lm_refilter_cube":   # touched cubes are rewritten: old point read + written (upper bound: the whole local map), new point + its key/index
+        return M * 32.0 + Q * 24.0
+    if kernel == "lm_sort_new":        # four 8-bit passes over (key, index) pairs, read + write
+        return Q * 16.0 * 4
+    if kernel == "vx_filter_coop":     # incoming clouds: bbox read, key pass, three radix passes over pairs, payload gather, centroids
+        return (Nls + Nlf) * (16.0 + 16.0 + 8.0 + 3 * 24.0 + 32.0 + 20.0) + Q * 16.0
+    if kernel == "sr_select":          # curvature, sort index, picked/label flags per point + the emitted features
+        return N * (4.0 + 4.0 + 2.0 + 2.0) + (Ns + Nls + Nf) * 4.0
     if kernel == "lm_gather_map":
         return M * 32.0
     if kernel in ("grid_count", "grid_scatter", "grid_bbox"):
         return (Nls + Nlf + M) / 2.0 * 24.0
     return None
+
+
+def measured_traffic(kernel):
+    """dram bytes per launch of `kernel` from the committed `ncu --set full` capture, if any"""
+    p = os.path.join(ROOT, "profiles", "r01_ncu_full_summary.json")
+    try:
+        d = json.load(open(p))
+        return float(d[kernel]["dram_bytes_per_launch"])
+    except Exception:
+        return None
 
 
 def measured_peak():
@@ -351,11 +367,11 @@ def main():
                 avg_s = kms * 1e-3 / calls
                 achieved = per_launch / avg_s / 1e9
                 roofline = {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                            "traffic": None, "peak_source": peak_src, "avg_launch_us": avg_s * 1e6, "launches_profiled": calls,
+                            "traffic": measured_traffic(name), "peak_source": peak_src, "avg_launch_us": avg_s * 1e6, "launches_profiled": calls,
                             "share_of_device_time": kms / tot_ms,
                             "note": "working set of one HDL-64 sweep (~10 MB) is L2-resident and the LM kernels are latency-bound; see DESIGN.md §5"}
                 break
-        kernels = [{"kernel": n, "calls": c, "ms": round(m, 4), "share": round(m / tot_ms, 4)} for n, c, m in kernels[:12]]
+        kernels = [{"kernel": n, "calls": c, "ms": round(m, 4), "share": round(m / tot_ms, 4)} for n, c, m in kernels[:16]]
     del G2
 
     # ---------------- the one collective of the multi-sequence configuration ---------------------
