@@ -246,6 +246,8 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the sm_100a library has no CPU fallback")
     torch.cuda.set_device(local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"     # keep NCCL's version banner off stdout (one JSON line)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     pkg = importlib.import_module(PKG)
     W, K = max(args.warmup, 3), args.steps
