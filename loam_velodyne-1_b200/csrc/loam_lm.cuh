@@ -13,6 +13,11 @@ struct LMHandle {
   cudaStream_t stream = nullptr;
   bool own_stream = false;
   cudaEvent_t ev_dep = nullptr;
+  // side stream for the branches of a pass that do not depend on each other: the local-map gather +
+  // index build (K4, K5) beside the incoming-sweep filters (K2, K3), and the registered cloud (K8)
+  // beside the map update (K7)
+  cudaStream_t aux = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_aux = nullptr;
   int cap = 0, ecap = 0, arena_cap = 0, coop_blocks = 0;
   int cur_arena = 0;
   int sweeps_since_compact = 0;
@@ -60,6 +65,13 @@ struct LMHandle {
     if (prop.major < 10) { set_error("device %d is not sm_100", dev); return LOAM_ERR_CUDA; }
     if (s) stream = s; else { CUDA_OK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking)); own_stream = true; }
     CUDA_OK(cudaEventCreateWithFlags(&ev_dep, cudaEventDisableTiming));
+    {
+      int pri = 0;
+      CUDA_OK(cudaStreamGetPriority(stream, &pri));
+      CUDA_OK(cudaStreamCreateWithPriority(&aux, cudaStreamNonBlocking, pri));
+      CUDA_OK(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+      CUDA_OK(cudaEventCreateWithFlags(&ev_aux, cudaEventDisableTiming));
+    }
     cap = P.max_points;
     arena_cap = P.map_arena_points > 0 ? P.map_arena_points : (8 << 20);
     ecap = arena_cap / 4;
@@ -126,6 +138,9 @@ struct LMHandle {
   }
   ~LMHandle() {
     if (ev_dep) cudaEventDestroy(ev_dep);
+    if (aux) { cudaStreamSynchronize(aux); cudaStreamDestroy(aux); }
+    if (ev_fork) cudaEventDestroy(ev_fork);
+    if (ev_aux) cudaEventDestroy(ev_aux);
     for (int b = 0; b < 2; b++) {
       if (ev_in_ready[b]) cudaEventDestroy(ev_in_ready[b]);
       if (ev_in_done[b]) cudaEventDestroy(ev_in_done[b]);
@@ -193,6 +208,8 @@ struct LMHandle {
     LMSetupArgs SA;
     SA.st = st; SA.lo = in.lo; SA.cubes[0] = d_cubes[0].p; SA.cubes[1] = d_cubes[1].p;
     LAUNCH("lm_setup", lm_setup, 1, 256, 0, stream, SA);
+    CUDA_OK(cudaEventRecord(ev_fork, stream));
+    CUDA_OK(cudaStreamWaitEvent(aux, ev_fork, 0));
     // K2
     LMStackArgs KA;
     KA.st = st; KA.in[0] = in.corner_last; KA.in[1] = in.surf_last; KA.out[0] = d_stack2[0].p; KA.out[1] = d_stack2[1].p;
@@ -217,13 +234,15 @@ struct LMHandle {
     LMGatherArgs GA;
     GA.st = st; GA.ecap = ecap;
     for (int T = 0; T < 2; T++) { GA.cubes[T] = d_cubes[T].p; GA.arena[T] = arena[T]; GA.E[T] = d_E[T].p; }
-    LAUNCH("lm_gather_map", lm_gather_map, dim3(125, 2, 8), 256, 0, stream, GA);
+    LAUNCH("lm_gather_map", lm_gather_map, dim3(125, 2, 8), 256, 0, aux, GA);
     // K5: kdtreeCornerFromMap / kdtreeSurfFromMap -> grid index, cell 1.02 m
     {
       GridPair gp;
       for (int T = 0; T < 2; T++) gp.g[T] = g_map[T].buf(d_E[T].p, &st->mapN[T], &st->optimize_enable, 1.02f);
-      int r = grid_build_pair(gp, 2 * nb, stream);
+      int r = grid_build_pair(gp, 2 * nb, aux);
       if (r != LOAM_OK) return r;
+      CUDA_OK(cudaEventRecord(ev_aux, aux));
+      CUDA_OK(cudaStreamWaitEvent(stream, ev_aux, 0));
     }
     // K6
     if (has_imu) {
@@ -240,6 +259,11 @@ struct LMHandle {
       g_launches++;
       if (g_profile) prof_end("lm_optimize", stream);
     }
+    // K8 on the side stream: needs only the refined pose
+    CUDA_OK(cudaEventRecord(ev_fork, stream));
+    CUDA_OK(cudaStreamWaitEvent(aux, ev_fork, 0));
+    LAUNCH("lm_registered", lm_registered, 2 * nb, 256, 0, aux, st, in.full_end, &in.lo->n_full_end, d_registered.p);
+    CUDA_OK(cudaEventRecord(ev_aux, aux));
     // K7: insert + per-cube refilter (lm_refilter.cuh)
     {
       LMInsertArgs IA;
@@ -278,8 +302,7 @@ struct LMHandle {
       int sr_ = surround();
       if (sr_ != LOAM_OK) return sr_;
     }
-    // K8
-    LAUNCH("lm_registered", lm_registered, 2 * nb, 256, 0, stream, st, in.full_end, &in.lo->n_full_end, d_registered.p);
+    CUDA_OK(cudaStreamWaitEvent(stream, ev_aux, 0));   // join the side stream: the pass is complete on `stream`
     CUDA_OK(cudaGetLastError());
     return LOAM_OK;
   }
