@@ -224,13 +224,14 @@ struct GridRows9 {
   int beg[9];
   int pre[10];   // pre[r] = number of candidates in rows < r; pre[9] = total
 };
-// W = lanes cooperating on one query (32 or 16); gl = lane index inside the group
+// W = lanes cooperating on one query (32, 16 or 8); gl = lane index inside the group.  With W = 8
+// lane 0 also loads the ninth row.
 template <int W>
 __device__ __forceinline__ void grid_rows9(const GridView& g, const GridDesc& d, int cx, int cy, int cz, GridRows9& R) {
   const int gl = lane_id() & (W - 1);
   const unsigned int gmask = (W == 32) ? 0xffffffffu : (((1u << W) - 1u) << (lane_id() & ~(W - 1)));
   const int x0 = max(cx - 1, 0), x1 = min(cx + 1, d.nx - 1);
-  int vb = 0, ve = 0;
+  int vb = 0, ve = 0, vb8 = 0, ve8 = 0;
   if (gl < 9 && x0 <= x1) {
     const int y = cy + (gl % 3) - 1, z = cz + (gl / 3) - 1;
     if (y >= 0 && y < d.ny && z >= 0 && z < d.nz) {
@@ -240,11 +241,21 @@ __device__ __forceinline__ void grid_rows9(const GridView& g, const GridDesc& d,
       vb = c0.x; ve = c1.x + c1.y;
     }
   }
+  if (W == 8 && gl == 0 && x0 <= x1) {
+    const int y = cy + 1, z = cz + 1;   // row 8
+    if (y >= 0 && y < d.ny && z >= 0 && z < d.nz) {
+      const int2* row = g.cell + (size_t)(z * d.ny + y) * d.nx;
+      int2 c0 = __ldg(&row[x0]);
+      int2 c1 = __ldg(&row[x1]);
+      vb8 = c0.x; ve8 = c1.x + c1.y;
+    }
+  }
   R.pre[0] = 0;
 #pragma unroll
   for (int k = 0; k < 9; k++) {
-    int b = __shfl_sync(gmask, vb, k, W);
-    int en = __shfl_sync(gmask, ve, k, W);
+    int b, en;
+    if (W == 8 && k == 8) { b = __shfl_sync(gmask, vb8, 0, W); en = __shfl_sync(gmask, ve8, 0, W); }
+    else { b = __shfl_sync(gmask, vb, k, W); en = __shfl_sync(gmask, ve, k, W); }
     R.beg[k] = b;
     R.pre[k + 1] = R.pre[k] + (en - b);
   }

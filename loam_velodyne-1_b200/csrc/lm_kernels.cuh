@@ -18,7 +18,7 @@ namespace loamgpu {
 constexpr int CUBE_W = 21, CUBE_H = 11, CUBE_D = 21;     // laserMapping.cpp:67-69
 constexpr int CUBE_NUM = CUBE_W * CUBE_H * CUBE_D;       // :70
 constexpr int PROC_MAX = 250;                            // cubes rewritten per mapped sweep
-constexpr int LM_THREADS = 512;   // the mapping chain bounds the pipeline's throughput: it gets the whole SM
+constexpr int LM_THREADS = 256;   // half an SM: lo_optimize and the other streams run beside it
 constexpr int LM_WARPS = LM_THREADS / 32;
 
 struct CubeDesc { int off; int cnt; int dirty; int pad; };   // dirty: not known to be one point per voxel in voxel order (lm_refilter.cuh)
