@@ -185,6 +185,70 @@ __global__ void __launch_bounds__(1024, 1) lm_sort_new(LMSortNewArgs A) {
   if (threadIdx.x == 0) st->newSel[T] = sel;
 }
 
+// K7c': the same list built per cube instead of by one global sort.  CTA (r, T) pulls the points
+// of plan entry r out of the stack (stable compaction: stack order), sorts them by voxel in shared
+// memory when the cube is going to be merged (three 8-bit passes over a few thousand pairs) and
+// writes them at procNewOff[r].  Cubes are independent, so the sorts run side by side on different
+// SMs; the one global 4-pass sort of all new points was 50 us of the mapping chain.  Append-only
+// cubes and cubes with more new points than the merge path holds stay in stack order (the general
+// path sorts everything again, stably).
+constexpr int BN_THREADS = 512;
+constexpr int BN_GRID = 16;
+constexpr size_t BN_SMEM = (size_t)RF_NEW_CAP * 16 + sizeof(CtaRadixSmem);
+__global__ void __launch_bounds__(BN_THREADS, 1) lm_bucket_new(LMSortNewArgs A) {
+  extern __shared__ __align__(16) unsigned char bn_smem[];
+  unsigned int* k0 = (unsigned int*)bn_smem;
+  unsigned int* v0 = k0 + RF_NEW_CAP;
+  unsigned int* k1 = v0 + RF_NEW_CAP;
+  unsigned int* v1 = k1 + RF_NEW_CAP;
+  CtaRadixSmem& S = *(CtaRadixSmem*)(v1 + RF_NEW_CAP);
+  __shared__ int s_ws[BN_THREADS / 32];
+  LMState* st = A.st;
+  const int T = blockIdx.y;
+  const int n = st->stackN[T];
+  const int np = st->nproc[T];
+  if (blockIdx.x == 0 && threadIdx.x == 0) st->newSel[T] = 0;
+  const int per = (n + BN_THREADS - 1) / BN_THREADS;          // contiguous chunk per thread: stable
+  const int c0 = min(n, (int)threadIdx.x * per), c1 = min(n, c0 + per);
+  for (int r = blockIdx.x; r < np; r += gridDim.x) {
+    const int cube = st->procCube[T][r];
+    const int n_new = st->procNewCnt[T][r];
+    const bool sorted = st->procMode[T][r] != 0 && n_new <= RF_NEW_CAP;
+    unsigned int* gk = A.nk[T][0] + st->procNewOff[T][r];
+    unsigned int* gv = A.nv[T][0] + st->procNewOff[T][r];
+    int cnt = 0;
+    for (int k = c0; k < c1; k++) cnt += (A.ins_cube[T][k] == cube) ? 1 : 0;
+    // exclusive prefix over the CTA
+    int x = cnt;
+    for (int o = 1; o < 32; o <<= 1) {
+      int y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane_id() >= o) x += y;
+    }
+    __syncthreads();
+    if (lane_id() == 31) s_ws[threadIdx.x >> 5] = x;
+    __syncthreads();
+    int pos = x - cnt;
+    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) pos += s_ws[w];
+    unsigned int* dk = sorted ? k0 : gk;
+    unsigned int* dv = sorted ? v0 : gv;
+    for (int k = c0; k < c1; k++) {
+      if (A.ins_cube[T][k] == cube) {
+        dk[pos] = ((unsigned int)r << 24) | (st->procMode[T][r] ? A.ins_key[T][k] : 0u);
+        dv[pos] = (unsigned int)k;
+        pos++;
+      }
+    }
+    __syncthreads();
+    if (sorted) {
+      const int res = cta_radix_sort(k0, v0, k1, v1, n_new, 3, S);
+      const unsigned int* sk = res ? k1 : k0;
+      const unsigned int* sv = res ? v1 : v0;
+      for (int j = threadIdx.x; j < n_new; j += BN_THREADS) { gk[j] = sk[j]; gv[j] = sv[j]; }
+    }
+    __syncthreads();
+  }
+}
+
 // running fp32 centroid, PCL 1.7 VoxelGrid::applyFilter: centroid = 0; centroid += p ...; /= count
 struct RFCentroid {
   float c0, c1, c2, c3;

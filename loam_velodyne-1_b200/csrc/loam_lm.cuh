@@ -81,6 +81,7 @@ struct LMHandle {
     CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lm_optimize, LM_THREADS, 0));
     if (per_sm < 1) { set_error("lm_optimize cannot be made resident"); return LOAM_ERR_CUDA; }
     CUDA_OK(cudaFuncSetAttribute(lm_refilter_cube, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_SMEM));
+    CUDA_OK(cudaFuncSetAttribute(lm_bucket_new, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BN_SMEM));
     int r = LOAM_OK;
     r |= d_state.alloc_zero(1, stream); r |= d_imu.alloc_zero(1, stream);
     int snblk = (cap + RS_TILE - 1) / RS_TILE + 1, enblk = (ecap + RS_TILE - 1) / RS_TILE + 1;
@@ -280,7 +281,7 @@ struct LMHandle {
         NA.ins_cube[T] = d_ins_cube[T].p; NA.ins_key[T] = d_ins_key[T].p; NA.cube_rank[T] = d_rank[T].p;
         for (int k = 0; k < 2; k++) { NA.nk[T][k] = d_nk[T][k].p; NA.nv[T][k] = d_nv[T][k].p; }
       }
-      LAUNCH("lm_sort_new", lm_sort_new, 2, 1024, 0, stream, NA);
+      LAUNCH("lm_bucket_new", lm_bucket_new, dim3(BN_GRID, 2), BN_THREADS, BN_SMEM, stream, NA);
       LMCubeArgs CA;
       CA.st = st; CA.scap = ecap;
       for (int T = 0; T < 2; T++) {
