@@ -82,6 +82,7 @@ struct LMHandle {
     if (per_sm < 1) { set_error("lm_optimize cannot be made resident"); return LOAM_ERR_CUDA; }
     CUDA_OK(cudaFuncSetAttribute(lm_refilter_cube, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_SMEM));
     CUDA_OK(cudaFuncSetAttribute(lm_bucket_new, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BN_SMEM));
+    CUDA_OK(cudaFuncSetAttribute(vx_filter_coop, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     int r = LOAM_OK;
     r |= d_state.alloc_zero(1, stream); r |= d_imu.alloc_zero(1, stream);
     int snblk = (cap + RS_TILE - 1) / RS_TILE + 1, enblk = (ecap + RS_TILE - 1) / RS_TILE + 1;
@@ -225,11 +226,7 @@ struct LMHandle {
         j.hist = d_shist[T].p; j.heads = d_sheads[T].p; j.sorted = d_ssorted[T].p; j.out = d_stack[T].p; j.out_count = &st->stackN[T];
         j.overflow = &st->vxOverflow[T]; j.leaf = T == 0 ? 0.2f : 0.4f; j.tile_cap = vc_tile_cap;
       }
-      void* args[] = {&VA};
-      if (g_profile) prof_begin(stream);
-      CUDA_OK(cudaLaunchCooperativeKernel((void*)vx_filter_coop, dim3(32, 2), dim3(VC_THREADS), args, 0, stream));
-      g_launches++;
-      if (g_profile) prof_end("vx_filter_coop", stream);
+      LAUNCH("vx_filter_coop", vx_filter_coop, dim3(VC_CLUSTER, 2), VC_THREADS, 0, stream, VA);
     }
     // K4
     LMGatherArgs GA;

@@ -1,7 +1,8 @@
-// vx_coop.cuh -- pcl::VoxelGrid of a whole cloud as ONE cooperative kernel:
+// vx_coop.cuh -- pcl::VoxelGrid of a whole cloud as ONE kernel:
 // bounding box -> voxel keys -> stable LSD radix sort (only as many 8-bit passes as the key range
-// needs) -> segment heads -> centroids, phases separated by grid-wide barriers instead of kernel
-// boundaries.  Used for the incoming-sweep filters of laserMapping (laserMapping.cpp:693-701,
+// needs) -> segment heads -> centroids.  One thread-block CLUSTER of VC_CLUSTER CTAs per job; the
+// phases are separated by cluster barriers (~0.2 us, hardware) instead of kernel boundaries or
+// grid-wide barriers (~2.5 us each, nine of them per filter).  Used for the incoming-sweep filters of laserMapping (laserMapping.cpp:693-701,
 // downSizeFilterCorner 0.2 m / downSizeFilterSurf 0.4 m): two jobs of 5e3 .. 5e4 points per
 // mapped sweep, for which the 18-launch device-wide path (sort_voxel.cuh) is launch/latency bound.
 // Semantics are identical to sort_voxel.cuh: cell = (int)(floor(p * inv_leaf) - (float)min_b),
@@ -19,6 +20,7 @@ constexpr int VC_THREADS = 256;
 constexpr int VC_ITEMS = 8;
 constexpr int VC_TILE = VC_THREADS * VC_ITEMS;   // 2048 elements per tile
 constexpr int VC_WARPS = VC_THREADS / 32;
+constexpr int VC_CLUSTER = 16;                   // CTAs per job (non-portable cluster size: cudaFuncAttributeNonPortableClusterSizeAllowed)
 
 struct VxCoopJob {
   const float4* pts;
@@ -78,8 +80,8 @@ __device__ __forceinline__ VcKeyParams vc_key_params(const VxCoopJob& J, int n) 
   return K;
 }
 
-__global__ void __launch_bounds__(VC_THREADS) vx_filter_coop(VxCoopArgs A) {
-  cg::grid_group grid = cg::this_grid();
+__global__ void __cluster_dims__(VC_CLUSTER, 1, 1) __launch_bounds__(VC_THREADS) vx_filter_coop(VxCoopArgs A) {
+  cg::cluster_group grid = cg::this_cluster();   // gridDim.x == VC_CLUSTER: the cluster is the job's whole "grid"
   const VxCoopJob J = A.j[blockIdx.y];
   const int G = gridDim.x;
   int n = *J.n_ptr;
@@ -112,13 +114,7 @@ __global__ void __launch_bounds__(VC_THREADS) vx_filter_coop(VxCoopArgs A) {
   grid.sync();
   // ---- voxel keys ----
   const VcKeyParams K = vc_key_params(J, n);
-  int passes_all = K.passes;   // every CTA of the grid must pass the same number of barriers
-  {
-    const VxCoopJob& O = A.j[blockIdx.y ^ 1];
-    int no = *O.n_ptr;
-    if ((no + VC_TILE - 1) / VC_TILE > O.tile_cap) no = 0;
-    if (gridDim.y > 1) passes_all = max(passes_all, vc_key_params(O, no).passes);
-  }
+  const int passes_all = K.passes;   // the jobs run in separate clusters: no common barrier count needed
   {
     const float inv = 1.0f / J.leaf;
     if (blockIdx.x == 0 && threadIdx.x == 0) *J.overflow = K.overflow;
