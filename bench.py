@@ -31,6 +31,15 @@ PKG = "loam_velodyne-1_b200"
 METRIC = "sweeps/s (odometry+mapping) on synthetic VLP-16 & HDL-64; p50 ms/sweep"
 PRESET = 2  # HDL-64E urban canyon, 64 rings x 2000 az
 WORKLOAD = "synthetic HDL-64E urban canyon, 64 rings x 2000 az (~128k pts/sweep), single stream per GPU"
+# --workload: the default is BASELINE.json configs[1] (the configuration the metric is quoted on); the
+# others are the remaining configs, run on request and kept under profiles/ (not the driver's line)
+WORKLOADS = {
+    "hdl64": (2, 2345, WORKLOAD),
+    "vlp16": (1, 1234, "synthetic VLP-16 corridor, 16 rings x 1800 az (~28.8k pts/sweep), single stream per GPU (configs[0] on the GPU)"),
+    "ring128": (4, 3456, "synthetic 128-ring lidar, 128 x 2048 (~262k pts/sweep) with 200 Hz IMU deskew, single stream per GPU (configs[3])"),
+    "mapstress": (2, 2345, "mapping only: HDL-64 laserOdometry output replayed against a pre-populated 21x21x11-cube local map (~1M map pts, 0.2/0.4 m voxels), 5-NN + line/plane fits + LM (configs[2])"),
+    "seq64": (1, 1000, "64 independent synthetic VLP-16 sequences (seeds 1000..1063), sequence-parallel over the GPUs, concurrent streams per GPU (configs[4])"),
+}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -167,14 +176,23 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def gen_sweeps(seed, count):
+def gen_sweeps(seed, count, preset=None):
     synth = importlib.import_module(PKG + ".synth")
-    S = synth.Synth(PRESET, seed=seed)
+    S = synth.Synth(PRESET if preset is None else preset, seed=seed)
     out = []
     for k in range(count):
         xyz, st = S.sweep(k)
         out.append((xyz, st))
     return out
+
+
+def gen_imu(seed, count, preset):
+    """per sweep k: the 20 IMU samples (200 Hz) that arrive before sweep k+1 (empty without an IMU)"""
+    synth = importlib.import_module(PKG + ".synth")
+    S = synth.Synth(preset, seed=seed)
+    if not S.has_imu:
+        return [[] for _ in range(count)]
+    return [[S.imu(j) for j in range(k * 20, (k + 1) * 20)] for k in range(count)]
 
 
 def first_last(xyz):
@@ -183,15 +201,17 @@ def first_last(xyz):
     return np.concatenate([xyz[idx[0]], xyz[idx[-1]]]).astype(np.float32), int(idx[0])
 
 
-def cpu_baseline(sweeps, budget_s=20.0, max_sweeps=80):
+def cpu_baseline(sweeps, budget_s=20.0, max_sweeps=80, preset=None, imu=None, label="HDL-64E"):
     """the reference's CPU pipeline on the host cores, bounded sample of the same workload"""
     from oracle import checker
     kind = "reference" if checker.available("reference") else "port"
-    C = checker.Checker(checker.make_params(PRESET), kind)
+    C = checker.Checker(checker.make_params(PRESET if preset is None else preset), kind)
     t0 = time.perf_counter()
     done = 0
     lat = []
-    for xyz, st in sweeps[:max_sweeps]:
+    for k, (xyz, st) in enumerate(sweeps[:max_sweeps]):
+        for t, q, a in (imu[k] if imu else []):
+            C.imu(t, q, a)
         t1 = time.perf_counter()
         C.push(xyz, st)
         lat.append(time.perf_counter() - t1)
@@ -202,7 +222,7 @@ def cpu_baseline(sweeps, budget_s=20.0, max_sweeps=80):
     busy = C.busy_seconds()
     C.close()
     return {"value": done / wall, "unit": "sweeps/s", "cores": 1, "kind": kind,
-            "sample": f"first {done} sweeps of the same HDL-64E sequence, sr->lo->lm->tm sequentially on one host thread",
+            "sample": f"first {done} sweeps of the same {label} sequence, sr->lo->lm->tm sequentially on one host thread",
             "p50_ms_per_sweep": 1e3 * statistics.median(lat),
             "node_busy_s": {"sr": busy[0], "lo": busy[1], "lm": busy[2], "tm": busy[3]},
             "pipelined_3proc_estimate_sweeps_per_s": done / max(busy[0], busy[1], busy[2], 1e-9),
@@ -212,13 +232,16 @@ def cpu_baseline(sweeps, budget_s=20.0, max_sweeps=80):
 def run_reference(args, rank, world):
     if rank != 0:
         return 0
+    if args.workload == "mapstress":
+        return run_mapstress(args, rank, world, 0, reference_only=True)
+    preset, seed0, workload = WORKLOADS[args.workload]
     n = min(args.steps + args.warmup, 80)
-    sweeps = gen_sweeps(2345, n)
-    cb = cpu_baseline(sweeps, budget_s=120.0, max_sweeps=n)
+    sweeps = gen_sweeps(seed0, n, preset)
+    cb = cpu_baseline(sweeps, budget_s=120.0, max_sweeps=n, preset=preset, imu=gen_imu(seed0, n, preset), label=args.workload)
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "sweeps/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / cb["value"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "note": "reference CPU nodes (oracle/_ref when built, else the oracle port), in-process, ROS stripped"},
+            "config": {"workload": workload, "note": "reference CPU nodes (oracle/_ref when built, else the oracle port), in-process, ROS stripped"},
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": "sweeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
@@ -233,6 +256,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--workload", default="hdl64", choices=sorted(WORKLOADS))
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -250,18 +274,29 @@ def main():
             os.environ["NCCL_DEBUG"] = "WARN"     # keep NCCL's version banner off stdout (one JSON line)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     pkg = importlib.import_module(PKG)
+    if args.workload == "mapstress":
+        return run_mapstress(args, rank, world, local_rank)
+    if args.workload == "seq64":
+        return run_seq64(args, rank, world, local_rank)
+    preset, seed0, workload = WORKLOADS[args.workload]
     W, K = max(args.warmup, 3), args.steps
     total = W + K
-    sweeps = gen_sweeps(2345 + rank, total)          # one independent sequence per rank
+    sweeps = gen_sweeps(seed0 + rank, total, preset)          # one independent sequence per rank
+    imu = gen_imu(seed0 + rank, total, preset)
+
+    def feed(G, k):
+        for t, q, a in imu[k % total]:
+            G.imu(t, q, a)
     npts = [x.shape[0] for x, _ in sweeps]
 
     # ---------------- value: inputs resident in HBM, no host sync inside the timed region ------
     dev = torch.device("cuda", local_rank)
     resident = [torch.from_numpy(x).to(dev) for x, _ in sweeps]
     aux = [first_last(x) for x, _ in sweeps]
-    P = pkg.make_params(PRESET, system_delay=0)
+    P = pkg.make_params(preset, system_delay=0)
     G = pkg.Pipeline(P, device=local_rank)
     for k in range(W):
+        feed(G, k)
         G.push_device(resident[k].data_ptr(), npts[k], aux[k][0], aux[k][1], sweeps[k][1])
     G.collect()
     torch.cuda.synchronize()
@@ -275,6 +310,7 @@ def main():
     t_wall0 = time.perf_counter()
     ev0.record(stream)
     for k in range(W, total):
+        feed(G, k)
         G.push_device(resident[k].data_ptr(), npts[k], aux[k][0], aux[k][1], sweeps[k][1])
     G.join()            # the pipeline stream waits for the registration / mapping streams: ev1 covers all work
     ev1.record(stream)
@@ -306,6 +342,7 @@ def main():
     pin_t = [torch.from_numpy(x).pin_memory() for x, _ in sweeps]
     pinned = [t.numpy() for t in pin_t]
     for k in range(W):
+        feed(G2, k)
         G2.push_async(pinned[k], sweeps[k][1])
     G2.collect()
     torch.cuda.synchronize()
@@ -314,6 +351,7 @@ def main():
     e2e_res = []
     t0 = time.perf_counter()
     for k in range(W, total):
+        feed(G2, k)
         G2.push_async(pinned[k], sweeps[k][1])
         if (k - W) % 128 == 127:
             e2e_res += G2.collect()
@@ -327,11 +365,13 @@ def main():
     # synchronous form: loam_pipeline_push() returns the sweep's poses; per-sweep latency
     G2 = pkg.Pipeline(P, device=local_rank)
     for k in range(W):
+        feed(G2, k)
         G2.push(pinned[k], sweeps[k][1])
     torch.cuda.synchronize()
     lat = []
     t1 = time.perf_counter()
     for k in range(W, total):
+        feed(G2, k)
         t2 = time.perf_counter()
         G2.push(pinned[k], sweeps[k][1])
         lat.append(time.perf_counter() - t2)
@@ -354,7 +394,8 @@ def main():
     if not args.no_profile:
         pkg.profile_enable(True)
         for k in range(min(total, 60)):
-            G2.push(pinned[k % total], sweeps[k % total][1] + 1000.0)  # continue the sequence state; timing only
+            if not imu[0]:   # (IMU-stamped sequences cannot be replayed at a later time: profile pass skipped below)
+                G2.push(pinned[k % total], sweeps[k % total][1] + 1000.0)  # continue the sequence state; timing only
         prof = pkg.profile_report()
         pkg.profile_enable(False)
         nsw = min(total, 60)
@@ -381,13 +422,13 @@ def main():
 
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cb = cpu_baseline(sweeps, budget_s=20.0, max_sweeps=80)
+        cb = cpu_baseline(sweeps, budget_s=20.0, max_sweeps=80, preset=preset, imu=imu, label=args.workload)
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "sweeps/s", "n_gpus": world, "steps": K, "warmup": W,
                 "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "sequences": world, "sweeps_per_sequence": K, "points_per_sweep": int(np.mean(npts)),
+                "config": {"workload": workload, "sequences": world, "sweeps_per_sequence": K, "points_per_sweep": int(np.mean(npts)),
                            "parallelism": f"seq{world}", "l2": "inputs larger than L2: %d distinct sweeps (%.0f MB) resident in HBM, each read once" % (total, sum(npts) * 12 / 1e6),
                            "timed_region": "K x (scanRegistration + laserOdometry + laserMapping every 2nd sweep + pose record); stages of consecutive sweeps overlap on 3 streams (+ copy stream) like the reference's nodes; CUDA events on the pipeline stream after a device-side join of all streams, no host sync inside"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),

@@ -135,6 +135,29 @@ void loam_lm_destroy(loam_lm* h);
 int loam_lm_imu(loam_lm* h, double stamp, const double quat[4]);
 /* consumes corner_last / surf_last / velodyne_cloud_3 / laser_odom_to_init of `odom` */
 int loam_lm_process(loam_lm* h, loam_lo* odom, double stamp);
+/* the same loop-body pass fed from HOST copies of the four topics (x,y,z,intensity per point;
+ * transform_sum = laserOdometry's transformSum before the message encoding) -- the form a caller
+ * that records / replays laserOdometry's output uses (BASELINE.json configs[2], mapping only) */
+int loam_lm_process_host(loam_lm* h, const float* corner_last, int n_corner, const float* surf_last, int n_surf,
+                         const float* full_res, int n_full, const float transform_sum[6], double stamp);
+/* asynchronous form with DEVICE-resident clouds (float4 x,y,z,intensity), enqueue only: nothing is
+ * copied but the odometry state; the arrays must stay unchanged until loam_lm_sync() (which also
+ * refreshes what loam_lm_state / loam_lm_download report).  loam_lm_stream() is the CUDA stream
+ * the node's passes are ordered on. */
+int loam_lm_process_device(loam_lm* h, const float* d_corner_last, int n_corner, const float* d_surf_last, int n_surf,
+                           const float* d_full_res, int n_full, const float transform_sum[6], double stamp);
+int loam_lm_sync(loam_lm* h);
+void* loam_lm_stream(loam_lm* h);
+/* map persistence (the reference cannot save its map): checkpoint / resume of
+ * the cube map laserCloudCornerArray / laserCloudSurfArray (laserMapping.cpp:74-81), the window
+ * centre (:64-66), transformSum..transformAftMapped (:96-100), frame counters (:404-405) and the
+ * IMU ring (:102-108) as one "LOAMMAP1" file (layout: csrc/lm_persist.cuh).  A run resumed from
+ * the file continues bit-identically. */
+int loam_lm_save_map(loam_lm* h, const char* path);
+int loam_lm_load_map(loam_lm* h, const char* path);
+/* a cloud of the node as binary PCD v0.7 (FIELDS x y z intensity): which = a loam_cloud selector
+ * accepted by loam_lm_download, or 20 / 21 = the whole corner / surf cube map */
+int loam_lm_export_pcd(loam_lm* h, int which, const char* path);
 int loam_lm_download(loam_lm* h, int which_cloud, float* xyzi, int cap_points, int* n);
 /* which = 100 / 101: the five neighbour indices per corner / surf query of the last LM iteration (-1 = rejected) */
 int loam_lm_download_ints(loam_lm* h, int which, int* out, int cap, int* n);

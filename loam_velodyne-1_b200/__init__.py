@@ -96,6 +96,14 @@ def lib():
     L.loam_lo_set_state.argtypes = [vp, vp, vp]
     L.loam_lm_imu.argtypes = [vp, cd, vp]
     L.loam_lm_process.argtypes = [vp, vp, cd]
+    L.loam_lm_process_host.argtypes = [vp, vp, ci, vp, ci, vp, ci, vp, cd]
+    L.loam_lm_process_device.argtypes = [vp, vp, ci, vp, ci, vp, ci, vp, cd]
+    L.loam_lm_sync.argtypes = [vp]
+    L.loam_lm_stream.restype = vp
+    L.loam_lm_stream.argtypes = [vp]
+    L.loam_lm_save_map.argtypes = [vp, ctypes.c_char_p]
+    L.loam_lm_load_map.argtypes = [vp, ctypes.c_char_p]
+    L.loam_lm_export_pcd.argtypes = [vp, ci, ctypes.c_char_p]
     L.loam_lm_download.argtypes = [vp, ci, vp, ci, ctypes.POINTER(ci)]
     L.loam_lm_download_ints.argtypes = [vp, ci, vp, ci, ctypes.POINTER(ci)]
     L.loam_lm_state.argtypes = [vp, vp, vp, vp, vp]
@@ -245,6 +253,36 @@ class LaserMapping(_Node):
 
     def process(self, lo, stamp):
         return _check(self.L.loam_lm_process(self.h, lo.h, float(stamp)))
+
+    def process_host(self, corner_last, surf_last, full_res, transform_sum, stamp):
+        """the same pass fed from host copies of laserOdometry's output (recorded / replayed)"""
+        c = np.ascontiguousarray(corner_last, dtype=np.float32).reshape(-1, 4)
+        f = np.ascontiguousarray(surf_last, dtype=np.float32).reshape(-1, 4)
+        a = np.ascontiguousarray(full_res, dtype=np.float32).reshape(-1, 4)
+        t = np.ascontiguousarray(transform_sum, dtype=np.float32)
+        return _check(self.L.loam_lm_process_host(self.h, c.ctypes.data, c.shape[0], f.ctypes.data, f.shape[0],
+                                                  a.ctypes.data, a.shape[0], t.ctypes.data, float(stamp)))
+
+    def process_device(self, d_corner, n_corner, d_surf, n_surf, d_full, n_full, transform_sum, stamp):
+        """enqueue only; device pointers to float4 clouds that stay unchanged until sync()"""
+        t = np.ascontiguousarray(transform_sum, dtype=np.float32)
+        return _check(self.L.loam_lm_process_device(self.h, ctypes.c_void_p(d_corner), n_corner, ctypes.c_void_p(d_surf), n_surf,
+                                                    ctypes.c_void_p(d_full), n_full, t.ctypes.data, float(stamp)))
+
+    def sync(self):
+        return _check(self.L.loam_lm_sync(self.h))
+
+    def stream(self):
+        return self.L.loam_lm_stream(self.h)
+
+    def save_map(self, path):
+        _check(self.L.loam_lm_save_map(self.h, os.fsencode(path)))
+
+    def load_map(self, path):
+        _check(self.L.loam_lm_load_map(self.h, os.fsencode(path)))
+
+    def export_pcd(self, which, path):
+        _check(self.L.loam_lm_export_pcd(self.h, which, os.fsencode(path)))
 
     def cloud(self, which, cap=None):
         return self._dl(self.L.loam_lm_download, which, np.float32, 4, cap=cap)

@@ -6,6 +6,7 @@
 #include "loam_sr.cuh"
 #include "loam_lo.cuh"
 #include "loam_lm.cuh"
+#include "lm_persist.cuh"
 #include "loam_pipeline.cuh"
 #include "debug_hooks.cuh"
 

@@ -104,6 +104,11 @@ def _load(kind):
     L.chk_get_floats.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int]
     L.chk_busy_seconds.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
     L.chk_lo_set_state.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    if hasattr(L, "chk_lm_push"):   # the CPU restatement only
+        L.chk_lm_push.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                                  ctypes.c_int, ctypes.c_void_p, ctypes.c_double, ctypes.POINTER(SweepResult)]
+        L.chk_lm_save_map.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
+        L.chk_lm_load_map.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
     _libs[kind] = L
     return L
 
@@ -168,3 +173,24 @@ class Checker:
         t = np.ascontiguousarray(transform, dtype=np.float32)
         s = np.ascontiguousarray(transform_sum, dtype=np.float32)
         self.L.chk_lo_set_state(self.h, t.ctypes.data, s.ctypes.data)
+
+    # ---- laserMapping alone (kind "port"): recorded laserOdometry output in, map files ----
+    def lm_push(self, corner, surf, full, transform_sum, stamp):
+        c = np.ascontiguousarray(corner, dtype=np.float32).reshape(-1, 4)
+        f = np.ascontiguousarray(surf, dtype=np.float32).reshape(-1, 4)
+        a = np.ascontiguousarray(full, dtype=np.float32).reshape(-1, 4)
+        t = np.ascontiguousarray(transform_sum, dtype=np.float32)
+        res = SweepResult()
+        self.L.chk_lm_push(self.h, c.ctypes.data, c.shape[0], f.ctypes.data, f.shape[0], a.ctypes.data, a.shape[0],
+                           t.ctypes.data, float(stamp), ctypes.byref(res))
+        return res
+
+    def lm_save_map(self, path):
+        rc = self.L.chk_lm_save_map(self.h, os.fsencode(path))
+        if rc != 0:
+            raise RuntimeError(f"chk_lm_save_map({path}) = {rc}")
+
+    def lm_load_map(self, path):
+        rc = self.L.chk_lm_load_map(self.h, os.fsencode(path))
+        if rc != 0:
+            raise RuntimeError(f"chk_lm_load_map({path}) = {rc}")

@@ -19,6 +19,11 @@ int chk_get_ints(void* h, int which, int* out, int cap);
 int chk_get_floats(void* h, int which, float* out, int cap);
 void chk_busy_seconds(void* h, double out[4]);
 void chk_lo_set_state(void* h, const float transform[6], const float transformSum[6]);
+/* port only: laserMapping alone on recorded laserOdometry output; "LOAMMAP1" map files */
+int chk_lm_push(void* h, const float* corner, int nc, const float* surf, int ns, const float* full, int nf,
+                const float transformSum[6], double stamp, loam_sweep_result* out);
+int chk_lm_save_map(void* h, const char* path);
+int chk_lm_load_map(void* h, const char* path);
 #ifdef __cplusplus
 }
 #endif

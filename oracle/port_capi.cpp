@@ -3,6 +3,7 @@
 // oracle/_ref (the reference's own sources compiled from /root/reference) exports the SAME
 // symbols, so either can serve as the checker.
 #include <chrono>
+#include <cstdio>
 #include "loam_port.hpp"
 #include "checker_api.h"
 
@@ -166,6 +167,124 @@ void chk_lo_set_state(void* hv, const float transform[6], const float transformS
   chk_handle* h = (chk_handle*)hv;
   memcpy(h->lo.transform, transform, sizeof(float) * 6);
   memcpy(h->lo.transformSum, transformSum, sizeof(float) * 6);
+}
+
+
+// ---- laserMapping alone, teacher-forced (BASELINE.json configs[2]) and its map file ----------
+// one loop-body pass of laserMapping.cpp:408-1096 fed with recorded copies of the four topics;
+// transformSum is laserOdometry's value BEFORE the message encoding (the round trip of :304-318 is applied here)
+int chk_lm_push(void* hv, const float* corner, int nc, const float* surf, int ns, const float* full, int nf,
+                const float transformSum[6], double stamp, loam_sweep_result* out) {
+  chk_handle* h = (chk_handle*)hv;
+  loam_sweep_result& r = h->res;
+  memset(&r, 0, sizeof(r));
+  r.sr_status = r.lo_status = r.lm_status = LOAM_NOT_READY;
+  LOOutput& o = h->odom;
+  auto fill = [](Cloud& c, const float* p, int n) {
+    c.points.resize(n);
+    for (int i = 0; i < n; i++) { c.points[i].x = p[4 * i]; c.points[i].y = p[4 * i + 1]; c.points[i].z = p[4 * i + 2]; c.points[i].intensity = p[4 * i + 3]; }
+    c.width = n; c.height = 1;
+  };
+  fill(o.cornerLast, corner, nc); fill(o.surfLast, surf, ns); fill(o.fullRes, full, nf);
+  memcpy(o.transformSum, transformSum, sizeof(float) * 6);
+  o.hasMappingInput = true;
+  o.stamp = stamp;
+  float sumMsg[6];
+  odometry_msg_roundtrip(o.transformSum, sumMsg);
+  double t0 = now_s();
+  bool mok = h->lm.process(o, sumMsg);
+  h->busy[2] += now_s() - t0;
+  memcpy(r.transform_sum, transformSum, sizeof(float) * 6);
+  if (mok) {
+    r.lm_status = LOAM_OK;
+    r.lm_iters = h->lm.lastIters; r.lm_rows = h->lm.lastRows; r.lm_degenerate = h->lm.isDegenerate;
+    r.n_map_corner = h->lm.lastCornerFromMapNum; r.n_map_surf = h->lm.lastSurfFromMapNum;
+    r.n_stack_corner = h->lm.lastCornerStackNum; r.n_stack_surf = h->lm.lastSurfStackNum;
+    memcpy(r.transform_aft_mapped, h->lm.transformAftMapped, sizeof(float) * 6);
+    memcpy(r.transform_bef_mapped, h->lm.transformBefMapped, sizeof(float) * 6);
+  }
+  if (out) *out = r;
+  return r.lm_status;
+}
+
+// "LOAMMAP1" (layout stated in loam_velodyne-1_b200/csrc/lm_persist.cuh; this is an independent
+// reader / writer over the oracle's own containers).  The oracle makes no claim about voxel order,
+// so it writes dirty = 1 for every non-empty cube and ignores the flag on load.
+namespace {
+struct MapHdr {
+  char magic[8]; int version; int dims[3]; int cen[3]; int frameCount, mapFrameCount; int isDegenerate;
+  float tf[5][6]; int imuPointerFront, imuPointerLast, hasImu, imuQueLength; long long total[2];
+};
+}
+int chk_lm_save_map(void* hv, const char* path) {
+  LaserMapping& m = ((chk_handle*)hv)->lm;
+  MapHdr H;
+  memset(&H, 0, sizeof(H));
+  memcpy(H.magic, "LOAMMAP1", 8);
+  H.version = 1;
+  H.dims[0] = LaserMapping::laserCloudWidth; H.dims[1] = LaserMapping::laserCloudHeight; H.dims[2] = LaserMapping::laserCloudDepth;
+  H.cen[0] = m.laserCloudCenWidth; H.cen[1] = m.laserCloudCenHeight; H.cen[2] = m.laserCloudCenDepth;
+  H.frameCount = m.frameCount; H.mapFrameCount = m.mapFrameCount; H.isDegenerate = m.isDegenerate ? 1 : 0;
+  const float* tfs[5] = {m.transformSum, m.transformIncre, m.transformTobeMapped, m.transformBefMapped, m.transformAftMapped};
+  for (int k = 0; k < 5; k++) memcpy(H.tf[k], tfs[k], sizeof(float) * 6);
+  H.imuPointerFront = m.imuPointerFront; H.imuPointerLast = m.imuPointerLast; H.hasImu = m.imuPointerLast >= 0; H.imuQueLength = LaserMapping::imuQueLength;
+  const std::vector<Cloud::Ptr>* arr[2] = {&m.laserCloudCornerArray, &m.laserCloudSurfArray};
+  for (int T = 0; T < 2; T++)
+    for (int c = 0; c < LaserMapping::laserCloudNum; c++) H.total[T] += (long long)(*arr[T])[c]->points.size();
+  FILE* f = fopen(path, "wb");
+  if (!f) return -1;
+  fwrite(&H, sizeof(H), 1, f);
+  fwrite(m.imuTime, sizeof(double), LaserMapping::imuQueLength, f);
+  fwrite(m.imuRoll, sizeof(float), LaserMapping::imuQueLength, f);
+  fwrite(m.imuPitch, sizeof(float), LaserMapping::imuQueLength, f);
+  for (int T = 0; T < 2; T++) {
+    std::vector<int> cnt(LaserMapping::laserCloudNum);
+    std::vector<unsigned char> dirty(LaserMapping::laserCloudNum);
+    for (int c = 0; c < LaserMapping::laserCloudNum; c++) { cnt[c] = (int)(*arr[T])[c]->points.size(); dirty[c] = cnt[c] > 0; }
+    fwrite(cnt.data(), sizeof(int), cnt.size(), f);
+    fwrite(dirty.data(), 1, dirty.size(), f);
+    for (int c = 0; c < LaserMapping::laserCloudNum; c++)
+      for (const PointType& p : (*arr[T])[c]->points) { float v[4] = {p.x, p.y, p.z, p.intensity}; fwrite(v, sizeof(float), 4, f); }
+  }
+  return fclose(f) == 0 ? 0 : -1;
+}
+int chk_lm_load_map(void* hv, const char* path) {
+  LaserMapping& m = ((chk_handle*)hv)->lm;
+  FILE* f = fopen(path, "rb");
+  if (!f) return -1;
+  MapHdr H;
+  if (fread(&H, sizeof(H), 1, f) != 1 || memcmp(H.magic, "LOAMMAP1", 8) != 0 || H.version != 1 || H.dims[0] != LaserMapping::laserCloudWidth ||
+      H.dims[1] != LaserMapping::laserCloudHeight || H.dims[2] != LaserMapping::laserCloudDepth || H.imuQueLength != LaserMapping::imuQueLength) {
+    fclose(f);
+    return -2;
+  }
+  bool ok = fread(m.imuTime, sizeof(double), LaserMapping::imuQueLength, f) == (size_t)LaserMapping::imuQueLength;
+  ok = ok && fread(m.imuRoll, sizeof(float), LaserMapping::imuQueLength, f) == (size_t)LaserMapping::imuQueLength;
+  ok = ok && fread(m.imuPitch, sizeof(float), LaserMapping::imuQueLength, f) == (size_t)LaserMapping::imuQueLength;
+  m.laserCloudCenWidth = H.cen[0]; m.laserCloudCenHeight = H.cen[1]; m.laserCloudCenDepth = H.cen[2];
+  m.frameCount = H.frameCount; m.mapFrameCount = H.mapFrameCount; m.isDegenerate = H.isDegenerate != 0;
+  float* tfs[5] = {m.transformSum, m.transformIncre, m.transformTobeMapped, m.transformBefMapped, m.transformAftMapped};
+  for (int k = 0; k < 5; k++) memcpy(tfs[k], H.tf[k], sizeof(float) * 6);
+  m.imuPointerFront = H.imuPointerFront; m.imuPointerLast = H.hasImu ? H.imuPointerLast : -1;
+  std::vector<Cloud::Ptr>* arr[2] = {&m.laserCloudCornerArray, &m.laserCloudSurfArray};
+  for (int T = 0; T < 2 && ok; T++) {
+    std::vector<int> cnt(LaserMapping::laserCloudNum);
+    std::vector<unsigned char> dirty(LaserMapping::laserCloudNum);
+    ok = ok && fread(cnt.data(), sizeof(int), cnt.size(), f) == cnt.size();
+    ok = ok && fread(dirty.data(), 1, dirty.size(), f) == dirty.size();
+    for (int c = 0; c < LaserMapping::laserCloudNum && ok; c++) {
+      Cloud& cl = *(*arr[T])[c];
+      cl.points.resize(cnt[c] > 0 ? cnt[c] : 0);
+      for (int i = 0; i < cnt[c] && ok; i++) {
+        float v[4];
+        ok = fread(v, sizeof(float), 4, f) == 4;
+        cl.points[i].x = v[0]; cl.points[i].y = v[1]; cl.points[i].z = v[2]; cl.points[i].intensity = v[3];
+      }
+      cl.width = (uint32_t)cl.points.size(); cl.height = 1;
+    }
+  }
+  fclose(f);
+  return ok ? 0 : -3;
 }
 
 }  // extern "C"

@@ -1,0 +1,142 @@
+"""GPU (-m gpu): laserMapping alone on recorded laserOdometry output (BASELINE.json configs[2],
+SURVEY.md §8d config 3), map checkpoint / resume through LOAMMAP1 files exchanged with the oracle
+in both directions, PCD export."""
+import numpy as np
+import pytest
+
+from conftest import biteq
+from lm_replay import read_map_file, record_lm_inputs_gpu, record_lm_inputs_oracle, shifted
+
+pytestmark = pytest.mark.gpu
+
+
+def _gpu_pass(M, r, dx=0.0, dstamp=0.0):
+    c, s, f, tsum, st = shifted(r, dx, dstamp)
+    assert M.process_host(c, s, f, tsum, st) == 0
+    return M.state()
+
+
+@pytest.mark.parametrize("preset,nsw", [(1, 40), (2, 14)])
+def test_lm_process_host_equals_oracle(pkg, checker, synth, preset, nsw):
+    rec = record_lm_inputs_oracle(checker, synth, preset, nsw)
+    assert len(rec) >= 6
+    C = checker.Checker(checker.make_params(preset), "port")
+    M = pkg.LaserMapping(pkg.make_params(preset, system_delay=0))
+    for i, r in enumerate(rec):
+        o = C.lm_push(r["corner"], r["surf"], r["full"], r["sum"], r["stamp"])
+        aft, bef, tobe, st = _gpu_pass(M, r)
+        assert biteq(aft, r["aft"]) and biteq(bef, r["bef"]), i       # equals the free-running oracle pipeline
+        assert biteq(aft, o.transform_aft_mapped[:]), i              # and the oracle's laserMapping alone
+        assert (st[0], st[3], st[4], st[5], st[6]) == (o.lm_iters, o.n_map_corner, o.n_map_surf, o.n_stack_corner, o.n_stack_surf), i
+        for which in (10, 11, 12, 13, 8):
+            assert np.array_equal(M.cloud(which, cap=1 << 20).view(np.uint32), C.cloud(which).view(np.uint32)), (i, which)
+        assert np.array_equal(M.ints(100), C.ints(100)) and np.array_equal(M.ints(101), C.ints(101)), i
+
+
+def test_lm_process_host_rejects_bad_arguments(pkg):
+    P = pkg.make_params(1, system_delay=0)
+    M = pkg.LaserMapping(P)
+    big = np.zeros((P.max_points + 1, 4), np.float32)
+    one = np.zeros((1, 4), np.float32)
+    with pytest.raises(pkg.LoamError):
+        M.process_host(big, one, one, np.zeros(6, np.float32), 0.0)
+    # empty clouds are legal: the reference runs the pass with nothing to match (:706 guards the LM loop)
+    e = np.zeros((0, 4), np.float32)
+    assert M.process_host(e, e, e, np.zeros(6, np.float32), 0.0) == 0
+    assert M.state()[3][0] == 0
+    with pytest.raises(pkg.LoamError):
+        M.load_map("/nonexistent/dir/x.loammap")
+
+
+def test_map_checkpoint_resume_gpu_and_oracle_both_directions(pkg, checker, synth, tmp_path):
+    rec = record_lm_inputs_oracle(checker, synth, 1, 48)
+    half = len(rec) // 2
+    P = pkg.make_params(1, system_delay=0)
+    A = pkg.LaserMapping(P)
+    C = checker.Checker(checker.make_params(1), "port")
+    for r in rec[:half]:
+        _gpu_pass(A, r)
+        C.lm_push(r["corner"], r["surf"], r["full"], r["sum"], r["stamp"])
+    g_path, o_path = str(tmp_path / "gpu.loammap"), str(tmp_path / "oracle.loammap")
+    A.save_map(g_path)
+    C.lm_save_map(o_path)
+    fg, fo = read_map_file(g_path), read_map_file(o_path)
+    for T in range(2):   # same cubes, same points, same order; only the dirty hints may differ
+        assert np.array_equal(fg["cnt"][T], fo["cnt"][T]) and np.array_equal(fg["pts"][T].view(np.uint32), fo["pts"][T].view(np.uint32))
+    for name in ("cen", "frameCount", "mapFrameCount", "tf", "total"):
+        assert np.array_equal(fg["header"][name], fo["header"][name]), name
+    B = pkg.LaserMapping(P)          # GPU resumes from its own file
+    B.load_map(g_path)
+    D = pkg.LaserMapping(P)          # GPU resumes from the oracle's file (every cube flagged dirty)
+    D.load_map(o_path)
+    C2 = checker.Checker(checker.make_params(1), "port")   # oracle resumes from the GPU's file
+    C2.lm_load_map(g_path)
+    for i, r in enumerate(rec[half:]):
+        a = _gpu_pass(A, r)
+        b = _gpu_pass(B, r)
+        d = _gpu_pass(D, r)
+        o = C2.lm_push(r["corner"], r["surf"], r["full"], r["sum"], r["stamp"])
+        for x in (b, d):
+            assert biteq(a[0], x[0]) and biteq(a[1], x[1]) and np.array_equal(a[3], x[3]), i
+        assert biteq(a[0], o.transform_aft_mapped[:]) and biteq(a[0], r["aft"]), i
+        assert np.array_equal(A.cloud(10).view(np.uint32), D.cloud(10).view(np.uint32))
+        assert np.array_equal(A.cloud(11).view(np.uint32), C2.cloud(11).view(np.uint32))
+    pa, pb = str(tmp_path / "a.loammap"), str(tmp_path / "d.loammap")
+    A.save_map(pa)
+    D.save_map(pb)
+    fa, fd = read_map_file(pa), read_map_file(pb)
+    for T in range(2):
+        assert np.array_equal(fa["cnt"][T], fd["cnt"][T]) and np.array_equal(fa["pts"][T].view(np.uint32), fd["pts"][T].view(np.uint32))
+
+
+def test_pcd_export(pkg, checker, synth, tmp_path):
+    rec = record_lm_inputs_oracle(checker, synth, 1, 24)
+    M = pkg.LaserMapping(pkg.make_params(1, system_delay=0))
+    for r in rec:
+        _gpu_pass(M, r)
+    for which in (10, 9, 8, 20, 21):
+        path = str(tmp_path / f"c{which}.pcd")
+        M.export_pcd(which, path)
+        raw = open(path, "rb").read()
+        head, _, body = raw.partition(b"DATA binary\n")
+        fields = dict(l.split(" ", 1) for l in head.decode().splitlines() if not l.startswith("#"))
+        assert fields["FIELDS"] == "x y z intensity" and fields["SIZE"] == "4 4 4 4" and fields["TYPE"] == "F F F F"
+        n = int(fields["POINTS"])
+        assert int(fields["WIDTH"]) == n and len(body) == 16 * n and n > 0
+        pts = np.frombuffer(body, "<f4").reshape(n, 4)
+        if which < 20:
+            assert np.array_equal(pts.view(np.uint32), M.cloud(which, cap=1 << 20).view(np.uint32))
+        else:
+            mp = str(tmp_path / "m.loammap")
+            M.save_map(mp)
+            assert np.array_equal(pts.view(np.uint32), read_map_file(mp)["pts"][which - 20].view(np.uint32))
+
+
+def test_mapping_only_stress_prepopulated_map_parity(pkg, checker, synth, tmp_path):
+    """config 3 at a size the oracle finishes in seconds: HDL-64 laserOdometry output replayed on
+    five parallel streets, the map handed to the oracle as a file, then the same passes on both"""
+    rec = record_lm_inputs_gpu(pkg, synth, 2, 42)
+    assert len(rec) >= 18
+    P = pkg.make_params(2, system_delay=0)
+    M = pkg.LaserMapping(P)
+    sizes = []
+    t = 0.0
+    for dx in (0.0, 18.0, -18.0, 36.0, -36.0):
+        for r in rec:
+            st = _gpu_pass(M, r, dx, t)[3]
+        t += 10.0
+        sizes.append(int(st[3] + st[4]))
+    assert sizes[-1] > 3 * sizes[0]
+    path = str(tmp_path / "stress.loammap")
+    M.save_map(path)
+    C = checker.Checker(checker.make_params(2), "port")
+    C.lm_load_map(path)
+    for i, r in enumerate(rec[8:12]):
+        c, s, f, tsum, stamp = shifted(r, 0.0, t)
+        o = C.lm_push(c, s, f, tsum, stamp)
+        aft, bef, tobe, st = _gpu_pass(M, r, 0.0, t)
+        assert o.lm_iters > 0
+        assert biteq(aft, o.transform_aft_mapped[:]) and biteq(bef, o.transform_bef_mapped[:]), i
+        assert (st[0], st[3], st[4]) == (o.lm_iters, o.n_map_corner, o.n_map_surf), i
+        assert np.array_equal(M.ints(100), C.ints(100)) and np.array_equal(M.ints(101), C.ints(101)), i
+        assert np.array_equal(M.cloud(10, cap=1 << 21).view(np.uint32), C.cloud(10, cap=1 << 21).view(np.uint32)), i
