@@ -55,6 +55,14 @@ inline void unpack(const std::vector<float>& xyzi, int n, Cloud* out) {
   }
   out->width = (uint32_t)n; out->height = 1; out->is_dense = true;
 }
+// pcl cloud (32-byte points) -> packed float4 x,y,z,intensity
+inline void pack(const Cloud& in, std::vector<float>* xyzi) {
+  xyzi->resize(4 * in.points.size() + 4);
+  for (size_t i = 0; i < in.points.size(); i++) {
+    const PointType& p = in.points[i];
+    (*xyzi)[4 * i] = p.x; (*xyzi)[4 * i + 1] = p.y; (*xyzi)[4 * i + 2] = p.z; (*xyzi)[4 * i + 3] = p.intensity;
+  }
+}
 template <typename H, typename F>
 inline void download(H* h, F fn, int which, Cloud* out) {
   int n = 0;
@@ -161,6 +169,26 @@ class LaserMapping {
     }
     return rc;
   }
+  // the same pass on laserOdometry output held by the caller (recorded / replayed / produced elsewhere):
+  // the three clouds of /laser_cloud_corner_last, /laser_cloud_surf_last, /velodyne_cloud_3 and transformSum
+  int process(const Cloud& corner_last, const Cloud& surf_last, const Cloud& full_res, const float transform_sum[6], double stamp, MapResult* out) {
+    std::vector<float> c, s, f;
+    detail::pack(corner_last, &c); detail::pack(surf_last, &s); detail::pack(full_res, &f);
+    int rc = check(loam_lm_process_host(h_, c.data(), (int)corner_last.points.size(), s.data(), (int)surf_last.points.size(),
+                                        f.data(), (int)full_res.points.size(), transform_sum, stamp));
+    if (rc == LOAM_OK && out) {
+      float tobe[6];
+      int st[8];
+      check(loam_lm_state(h_, out->transform_aft_mapped, out->transform_bef_mapped, tobe, st));
+      out->iterations = st[0]; out->rows = st[1]; out->degenerate = st[2];
+    }
+    return rc;
+  }
+  // map persistence: checkpoint / resume of the cube map, window and poses; PCD export of a cloud
+  // (which = LOAM_CLOUD_* of this node, or 20 / 21 = the whole corner / surf map)
+  void saveMap(const std::string& path) { check(loam_lm_save_map(h_, path.c_str())); }
+  void loadMap(const std::string& path) { check(loam_lm_load_map(h_, path.c_str())); }
+  void exportPCD(int which, const std::string& path) { check(loam_lm_export_pcd(h_, which, path.c_str())); }
   void cloud(int which, Cloud* out) { detail::download(h_, loam_lm_download, which, out); }
   loam_lm* handle() { return h_; }
  private:

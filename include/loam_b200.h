@@ -38,7 +38,9 @@ typedef struct loam_params {
   int lo_max_iter;      /* laserOdometry.cpp:470 (25)                                             */
   int lm_max_iter;      /* laserMapping.cpp:710 (10)                                              */
   int map_arena_points; /* product only: capacity of each cube-map arena, in points               */
-  int reserved[7];
+  int coop_ctas;        /* product only: CTAs of the persistent cooperative LM kernels (0 = one per SM); */
+                        /* smaller grids let several handles' kernels run side by side (configs[4])   */
+  int reserved[6];
 } loam_params;
 
 /* preset: 1 = VLP-16 (reference defaults), 2 = HDL-64E, 4 = 128-ring (BASELINE.json configs) */

@@ -8,6 +8,7 @@
 #include <string.h>
 #include <string>
 #include <map>
+#include <atomic>
 #include <vector>
 #include "loam_b200.h"
 #include "loam/detmath.h"
@@ -20,7 +21,7 @@ namespace loamgpu {
 namespace dm = loam::dm;
 
 void set_error(const char* fmt, ...);
-extern long long g_launches;
+extern std::atomic<long long> g_launches;
 extern int g_profile;   // 0 off, 1 per-kernel CUDA events (serialising), 2 timeline stamps around every launch (non-serialising), 3 stamps at node boundaries only
 
 struct ProfEntry { double ms = 0; long long calls = 0; };

@@ -12,7 +12,7 @@
 
 namespace loamgpu {
 
-long long g_launches = 0;
+std::atomic<long long> g_launches(0);
 int g_profile = 0;
 static thread_local char g_err[512] = "";
 static cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;
@@ -148,7 +148,7 @@ int loam_params_preset(loam_params* p, int preset) {
 }
 
 const char* loam_last_error(void) { return g_err; }
-long long loam_kernel_launch_count(void) { return g_launches; }
+long long loam_kernel_launch_count(void) { return g_launches.load(); }
 int loam_profile_enable(int on) {
   g_profile = on != 0 ? 1 : 0;
   prof_table().clear();

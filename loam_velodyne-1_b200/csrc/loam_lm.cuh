@@ -76,7 +76,8 @@ struct LMHandle {
     arena_cap = P.map_arena_points > 0 ? P.map_arena_points : (8 << 20);
     ecap = arena_cap / 4;
     if (ecap < 4 * cap) ecap = 4 * cap;
-    coop_blocks = prop.multiProcessorCount;
+    coop_blocks = prop.multiProcessorCount;   // one CTA per SM unless the caller asks for a smaller grid
+    if (P.coop_ctas > 0 && P.coop_ctas < coop_blocks) coop_blocks = P.coop_ctas;
     int per_sm = 0;
     CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lm_optimize, LM_THREADS, 0));
     if (per_sm < 1) { set_error("lm_optimize cannot be made resident"); return LOAM_ERR_CUDA; }

@@ -40,7 +40,8 @@ struct LOHandle {
     int per_sm = 0;
     CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lo_optimize, LO_THREADS, 0));
     if (per_sm < 1) { set_error("lo_optimize cannot be made resident"); return LOAM_ERR_CUDA; }
-    coop_blocks = prop.multiProcessorCount;  // one block per SM
+    coop_blocks = prop.multiProcessorCount;   // one CTA per SM unless the caller asks for a smaller grid
+    if (P.coop_ctas > 0 && P.coop_ctas < coop_blocks) coop_blocks = P.coop_ctas;
     int r = LOAM_OK;
     r |= d_state.alloc_zero(1, stream);
     r |= d_corner_last.alloc(cap); r |= d_surf_last.alloc(cap); r |= d_full_end.alloc(cap);

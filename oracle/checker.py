@@ -17,7 +17,7 @@ class LoamParams(ctypes.Structure):
                 ("ring_lower_deg", ctypes.c_float), ("ring_upper_deg", ctypes.c_float),
                 ("max_points", ctypes.c_int), ("system_delay", ctypes.c_int),
                 ("lo_max_iter", ctypes.c_int), ("lm_max_iter", ctypes.c_int),
-                ("map_arena_points", ctypes.c_int), ("reserved", ctypes.c_int * 7)]
+                ("map_arena_points", ctypes.c_int), ("coop_ctas", ctypes.c_int), ("reserved", ctypes.c_int * 6)]
 
 
 class SweepResult(ctypes.Structure):

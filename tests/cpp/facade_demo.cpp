@@ -2,7 +2,10 @@
 // node, on sweeps read from a binary file: for every sweep  sr.process -> lo.process ->
 // tm.onOdometry -> (lm.process -> tm.onMapping).  Prints one line of hex floats per sweep; the
 // Python test compares them bit for bit with the ctypes Pipeline.
-//   facade_demo <preset> <sweeps.bin>      sweeps.bin: int32 n_sweeps, then per sweep: int32 n, float64 stamp, n * 3 float32
+// With a third argument (a writable file name) a second LaserMapping is driven beside the first
+// from HOST copies of laserOdometry's clouds, check-pointed to that file half way and resumed in
+// a fresh object; its poses are printed as "lm2" and must equal "lm".
+//   facade_demo <preset> <sweeps.bin> [map file]     sweeps.bin: int32 n_sweeps, then per sweep: int32 n, float64 stamp, n * 3 float32
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -29,6 +32,8 @@ int main(int argc, char** argv) {
     loam::LaserOdometry lo(P);
     loam::LaserMapping lm(P);
     loam::TransformMaintenance tm;
+    const char* map_path = argc > 3 ? argv[3] : NULL;
+    loam::LaserMapping* lm2 = map_path ? new loam::LaserMapping(P) : NULL;
     for (int k = 0; k < nsw; k++) {
       int n = 0;
       double stamp = 0;
@@ -57,12 +62,27 @@ int main(int argc, char** argv) {
             hex6(mr.transform_aft_mapped);
             tm.onMapping(mr.transform_aft_mapped, mr.transform_bef_mapped);
           }
+          if (lm2) {
+            loam::Cloud corner, surf, full;
+            lo.cloud(LOAM_CLOUD_CORNER_LAST, &corner); lo.cloud(LOAM_CLOUD_SURF_LAST, &surf); lo.cloud(LOAM_CLOUD_FULL_END, &full);
+            loam::MapResult m2;
+            int rc2 = lm2->process(corner, surf, full, od.transform_sum, stamp, &m2);
+            printf(" lm2=%d", rc2);
+            if (rc2 == LOAM_OK) hex6(m2.transform_aft_mapped);
+            if (k == nsw / 2 || k == nsw / 2 + 1) {   // checkpoint, throw the node away, resume in a new one
+              lm2->saveMap(map_path);
+              delete lm2;
+              lm2 = new loam::LaserMapping(P);
+              lm2->loadMap(map_path);
+            }
+          }
         }
         printf(" tm");
         hex6(integrated.v);
       }
       printf("\n");
     }
+    delete lm2;
   } catch (const loam::Error& e) {
     fprintf(stderr, "error %d: %s\n", e.code, e.what());
     return 1;

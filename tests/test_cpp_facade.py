@@ -53,7 +53,7 @@ def test_facade_node_by_node_equals_pipeline(pkg, synth, tmp_path):
         for xyz, st in sweeps:
             f.write(struct.pack("<id", xyz.shape[0], st))
             f.write(np.ascontiguousarray(xyz, np.float32).tobytes())
-    r = subprocess.run([exe, str(preset), path], capture_output=True, text=True, timeout=300)
+    r = subprocess.run([exe, str(preset), path, os.path.join(tmp_path, "facade.loammap")], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr
     lines = r.stdout.strip().splitlines()
     assert len(lines) == nsw
@@ -74,4 +74,7 @@ def test_facade_node_by_node_equals_pipeline(pkg, synth, tmp_path):
             if g.lm_status == 0:
                 mapped += 1
                 assert f" lm=0 {hexes(g.transform_aft_mapped)}" in line, (k, line)
+                # the second LaserMapping: host clouds in, check-pointed to a file and resumed half way
+                assert f" lm2=0 {hexes(g.transform_aft_mapped)}" in line, (k, line)
     assert mapped >= 4
+    assert os.path.getsize(os.path.join(tmp_path, "facade.loammap")) > 4851 * 10

@@ -1,0 +1,68 @@
+"""GPU (-m gpu): the 64-sequence configuration (BASELINE.json configs[4]) -- several pipelines on one
+GPU, fed from host threads, with the cooperative LM kernels on a sub-grid so that they co-reside."""
+import threading
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+KEYS = ("transform", "transform_sum", "transform_aft_mapped", "transform_mapped")
+
+
+def _bits(r):
+    return b"".join(bytes(getattr(r, k)) for k in KEYS) + bytes([r.lo_iters, r.lm_iters])
+
+
+@pytest.mark.parametrize("ctas", [37, 16])
+def test_sub_grid_cooperative_kernels_keep_parity(pkg, checker, synth, ctas):
+    S = synth.Synth(1)
+    P = pkg.make_params(1, system_delay=0)
+    P.coop_ctas = ctas
+    G = pkg.Pipeline(P)
+    C = checker.Checker(checker.make_params(1), "port")
+    for k in range(30):
+        xyz, st = S.sweep(k)
+        g, r = G.push(xyz, st), C.push(xyz, st)
+        assert (g.lo_iters, g.lm_iters, g.lo_status, g.lm_status) == (r.lo_iters, r.lm_iters, r.lo_status, r.lm_status), k
+        for key in KEYS:
+            assert bytes(getattr(g, key)) == bytes(getattr(r, key)), (k, key)
+
+
+def test_concurrent_pipelines_from_host_threads_equal_sequential_runs(pkg, synth):
+    n_seq, nsw = 6, 24
+    P = pkg.make_params(1, system_delay=0)
+    P.map_arena_points = 1 << 20
+    P.coop_ctas = 37
+    data = {}
+    for s in range(n_seq):
+        S = synth.Synth(1, seed=1000 + s)
+        data[s] = [S.sweep(k) for k in range(nsw)]
+    ref = {}
+    for s in range(n_seq):
+        G = pkg.Pipeline(P)
+        ref[s] = [_bits(G.push(x, st)) for x, st in data[s]]
+        del G
+    pipes = {s: pkg.Pipeline(P) for s in range(n_seq)}
+    out = {s: [] for s in range(n_seq)}
+    errs = []
+
+    def worker(group):
+        try:
+            for k in range(nsw):
+                for s in group:
+                    pipes[s].push_async(data[s][k][0], data[s][k][1])
+            for s in group:
+                out[s] = [_bits(r) for r in pipes[s].collect()]
+        except Exception as e:  # surfaced below
+            errs.append(e)
+
+    ths = [threading.Thread(target=worker, args=([s for s in range(n_seq) if s % 3 == t],)) for t in range(3)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    assert not errs, errs
+    for s in range(n_seq):
+        assert out[s] == ref[s], s
+    assert len({tuple(v) for v in ref.values()}) == n_seq   # the sequences really differ
