@@ -581,8 +581,12 @@ def main():
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--workload", default="hdl64", choices=sorted(WORKLOADS))
     ap.add_argument("--host-threads", type=int, default=8, help="seq64: host threads feeding the pipelines of one GPU")
-    ap.add_argument("--coop-ctas", type=int, default=0, help="seq64: CTAs of the cooperative LM kernels per pipeline (0 = one per SM)")
+    ap.add_argument("--coop-ctas", type=int, default=37, help="seq64: CTAs of the cooperative LM kernels per pipeline (0 = one per SM)")
     args = ap.parse_args()
+    # a pipeline runs on 6 streams (copy, registration, odometry, mapping + side streams) and seq64 on
+    # hundreds: ask for the maximum number of hardware work queues so that independent streams are not
+    # serialised behind each other (must be set before CUDA starts; INTEGRATION.md recommends the same)
+    os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -717,16 +721,17 @@ def main():
     roofline = None
     kernels = None
     if not args.no_profile:
+        del G2
+        G2 = pkg.Pipeline(P, device=local_rank)     # the same sequence from its start, every launch bracketed by CUDA events
         pkg.profile_enable(True)
         for k in range(min(total, 60)):
-            if not imu[0]:   # (IMU-stamped sequences cannot be replayed at a later time: profile pass skipped below)
-                G2.push(pinned[k % total], sweeps[k % total][1] + 1000.0)  # continue the sequence state; timing only
+            feed(G2, k)
+            G2.push(pinned[k], sweeps[k][1])
         prof = pkg.profile_report()
         pkg.profile_enable(False)
         nsw = min(total, 60)
         tot_ms = sum(v[1] for v in prof.values())
         kernels = sorted(((name, v[0], v[1]) for name, v in prof.items()), key=lambda t: -t[2])
-        top = kernels[0]
         peak, peak_src = measured_peak()
         for name, calls, kms in kernels:   # dominant kernel for which an algorithmic byte count is defined
             ab = algorithmic_bytes(name, stats)

@@ -315,23 +315,41 @@ struct LMGatherArgs {
   float4* E[2];
   int ecap;
 };
+// Flat form: thread i copies local-map point i; its cube is found by a binary search over the
+// <= 126 segment starts staged in shared memory.  The work per CTA is the same whatever the cube
+// sizes are (a dense map keeps most of its points in a handful of cubes), and every load is
+// independent -- four in flight per thread.
 __global__ void __launch_bounds__(256) lm_gather_map(LMGatherArgs A) {
   const LMState* st = A.st;
-  const int v = blockIdx.x, T = blockIdx.y;
-  if (v >= st->validNum) return;
-  CubeDesc d = A.cubes[T][st->validInd[v]];
-  int dst = st->gatherOff[T][v];
-  if (dst + d.cnt > A.ecap) { if (threadIdx.x == 0 && blockIdx.z == 0) atomicOr(&A.st->error, 8); return; }
-  const float4* src = A.arena[T] + d.off;
-  // blockIdx.z splits a cube into slices; four independent loads per thread in flight
-  const int per = (d.cnt + (int)gridDim.z - 1) / (int)gridDim.z;
-  const int k0 = blockIdx.z * per, k1 = min(d.cnt, k0 + per);
-  for (int k = k0 + threadIdx.x; k < k1; k += 4 * 256) {
+  const int T = blockIdx.y;
+  __shared__ int s_off[128], s_src[128];
+  const int nv = st->validNum;
+  for (int v = threadIdx.x; v <= nv; v += 256) {
+    s_off[v] = st->gatherOff[T][v];
+    s_src[v] = v < nv ? A.cubes[T][st->validInd[v]].off : 0;
+  }
+  __syncthreads();
+  const int total = s_off[nv];
+  if (total > A.ecap) { if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(&A.st->error, 8); return; }
+  const float4* __restrict__ arena = A.arena[T];
+  float4* __restrict__ E = A.E[T];
+  for (int base = blockIdx.x * 1024; base < total; base += gridDim.x * 1024) {
     float4 p[4];
 #pragma unroll
-    for (int u = 0; u < 4; u++) p[u] = src[min(k + u * 256, k1 - 1)];
+    for (int u = 0; u < 4; u++) {
+      const int i = min(base + u * 256 + (int)threadIdx.x, total - 1);
+      int lo = 0, hi = nv;          // largest v with s_off[v] <= i (empty cubes share a start: take the last)
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (s_off[mid] <= i) lo = mid; else hi = mid;
+      }
+      p[u] = __ldg(&arena[s_src[lo] + (i - s_off[lo])]);
+    }
 #pragma unroll
-    for (int u = 0; u < 4; u++) if (k + u * 256 < k1) A.E[T][dst + k + u * 256] = p[u];
+    for (int u = 0; u < 4; u++) {
+      const int i = base + u * 256 + (int)threadIdx.x;
+      if (i < total) E[i] = p[u];
+    }
   }
 }
 

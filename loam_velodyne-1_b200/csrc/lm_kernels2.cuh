@@ -348,14 +348,36 @@ __global__ void __launch_bounds__(256) lm_surround_plan(LMSurroundArgs A) {
   __syncthreads();
   if (e < 250) st->surroundOff[e] = s_cnt[e];
 }
+// flat copy (see lm_gather_map): point i of the gathered cloud, its segment by binary search
 __global__ void __launch_bounds__(256) lm_surround_gather(LMSurroundArgs A) {
   const LMState* st = A.st;
-  const int e = blockIdx.x;
-  if (e >= 2 * st->surroundNum || st->surroundIn == 0) return;
-  const CubeDesc d = A.cubes[e & 1][st->surroundInd[e >> 1]];
-  const float4* src = A.arena[e & 1] + d.off;
-  float4* dst = A.S + st->surroundOff[e];
-  for (int k = threadIdx.x; k < d.cnt; k += 256) dst[k] = src[k];
+  __shared__ int s_off[256], s_src[256];
+  const int ne = min(2 * st->surroundNum, 250);
+  const int total = st->surroundIn;
+  if (ne == 0 || total == 0) return;
+  for (int e = threadIdx.x; e <= ne; e += 256) {
+    s_off[e] = e < ne ? st->surroundOff[e] : total;
+    s_src[e] = e < ne ? A.cubes[e & 1][st->surroundInd[e >> 1]].off : 0;
+  }
+  __syncthreads();
+  for (int base = blockIdx.x * 1024; base < total; base += gridDim.x * 1024) {
+    float4 p[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int i = min(base + u * 256 + (int)threadIdx.x, total - 1);
+      int lo = 0, hi = ne;
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (s_off[mid] <= i) lo = mid; else hi = mid;
+      }
+      p[u] = __ldg(&A.arena[lo & 1][s_src[lo] + (i - s_off[lo])]);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int i = base + u * 256 + (int)threadIdx.x;
+      if (i < total) A.S[i] = p[u];
+    }
+  }
 }
 
 // arena compaction: copy every live cube segment into the other arena (host-triggered)
@@ -399,15 +421,36 @@ __global__ void __launch_bounds__(1024) lm_compact_plan(LMCompactArgs A) {
   }
   if (threadIdx.x == 0) A.st->bump[T] = s_carry;
 }
+// flat copy: live point i of the new arena, its cube by binary search over the 4851 new offsets
+// (19 KB per type, cache resident); the descriptors are switched to the new offsets by
+// lm_compact_commit once every point has been copied
 __global__ void __launch_bounds__(256) lm_compact_copy(LMCompactArgs A) {
   const int T = blockIdx.y;
-  for (int c = blockIdx.x; c < CUBE_NUM; c += gridDim.x) {
-    CubeDesc d = A.cubes[T][c];
-    int no = A.new_off[T][c];
-    for (int k = threadIdx.x; k < d.cnt; k += 256) A.dst[T][no + k] = A.src[T][d.off + k];
-    __syncthreads();
-    if (threadIdx.x == 0) A.cubes[T][c].off = no;
+  const int total = A.st->bump[T];
+  const int* __restrict__ noff = A.new_off[T];
+  const CubeDesc* __restrict__ cubes = A.cubes[T];
+  for (int base = blockIdx.x * 1024; base < total; base += gridDim.x * 1024) {
+    float4 p[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int i = min(base + u * 256 + (int)threadIdx.x, total - 1);
+      int lo = 0, hi = CUBE_NUM;
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(&noff[mid]) <= i) lo = mid; else hi = mid;
+      }
+      p[u] = __ldg(&A.src[T][cubes[lo].off + (i - __ldg(&noff[lo]))]);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int i = base + u * 256 + (int)threadIdx.x;
+      if (i < total) A.dst[T][i] = p[u];
+    }
   }
+}
+__global__ void __launch_bounds__(256) lm_compact_commit(LMCompactArgs A) {
+  const int T = blockIdx.y;
+  for (int c = blockIdx.x * 256 + threadIdx.x; c < CUBE_NUM; c += gridDim.x * 256) A.cubes[T][c].off = A.new_off[T][c];
 }
 
 }  // namespace loamgpu

@@ -233,7 +233,7 @@ struct LMHandle {
     LMGatherArgs GA;
     GA.st = st; GA.ecap = ecap;
     for (int T = 0; T < 2; T++) { GA.cubes[T] = d_cubes[T].p; GA.arena[T] = arena[T]; GA.E[T] = d_E[T].p; }
-    LAUNCH("lm_gather_map", lm_gather_map, dim3(125, 2, 8), 256, 0, aux, GA);
+    LAUNCH("lm_gather_map", lm_gather_map, dim3(4 * nb, 2), 256, 0, aux, GA);
     // K5: kdtreeCornerFromMap / kdtreeSurfFromMap -> grid index, cell 1.02 m
     {
       GridPair gp;
@@ -313,7 +313,7 @@ struct LMHandle {
     SA.st = st; SA.S = d_S.p; SA.scap = ecap;
     for (int T = 0; T < 2; T++) { SA.cubes[T] = d_cubes[T].p; SA.arena[T] = d_arena[T][cur_arena].p; }
     LAUNCH("lm_surround_plan", lm_surround_plan, 1, 256, 0, stream, SA);
-    LAUNCH("lm_surround_gather", lm_surround_gather, 250, 256, 0, stream, SA);
+    LAUNCH("lm_surround_gather", lm_surround_gather, 4 * 148, 256, 0, stream, SA);
     CloudKeyPair cp;
     cp.njobs = 1;
     CloudKeyJob& cj = cp.j[0];
@@ -349,6 +349,7 @@ struct LMHandle {
     }
     LAUNCH("lm_compact_plan", lm_compact_plan, 2, 1024, 0, stream, CA);
     LAUNCH("lm_compact_copy", lm_compact_copy, dim3(296, 2), 256, 0, stream, CA);
+    LAUNCH("lm_compact_commit", lm_compact_commit, dim3(19, 2), 256, 0, stream, CA);
     CUDA_OK(cudaGetLastError());
     cur_arena ^= 1;
     sweeps_since_compact = 0;

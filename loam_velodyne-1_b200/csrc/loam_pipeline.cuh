@@ -112,10 +112,18 @@ struct PipelineHandle {
   // enqueue one sweep.  src_device: xyz is packed device memory and aux = {first xyz, last xyz}
   int push_async(const float* xyz, int n, int stride_bytes, double stamp, bool src_device, const float* aux, int first_idx) {
     if ((int)pending.size() >= RING) { set_error("result ring full: call collect"); return LOAM_ERR_CAPACITY; }
+    int rc = src_device ? sr.process_resident(xyz, n, aux, aux + 3, first_idx, stamp) : sr.process(xyz, n, stride_bytes, stamp);
+    return after_registration(rc, stamp);
+  }
+  // same for a sweep that arrives as raw Velodyne VLP-16 data packets (decoded on the device, pk_decode.cuh)
+  int push_packets_async(const unsigned char* packets, int n_packets, double stamp) {
+    if ((int)pending.size() >= RING) { set_error("result ring full: call collect"); return LOAM_ERR_CAPACITY; }
+    return after_registration(sr.process_packets(packets, n_packets, stamp), stamp);
+  }
+  int after_registration(int rc, double stamp) {
     Pending pd;
     pd.slot = next_slot;
     pd.sr_status = pd.lo_status = pd.lm_status = LOAM_NOT_READY;
-    int rc = src_device ? sr.process_resident(xyz, n, aux, aux + 3, first_idx, stamp) : sr.process(xyz, n, stride_bytes, stamp);
     if (rc < 0) return rc;
     if (g_profile == 3) prof_node("scanRegistration", sr_stream, false);
     if (rc == LOAM_OK) {
@@ -196,6 +204,15 @@ struct PipelineHandle {
     return LOAM_OK;
   }
 
+  int push_packets(const unsigned char* packets, int n_packets, double stamp, loam_sweep_result* out) {
+    int rc = push_packets_async(packets, n_packets, stamp);
+    if (rc < 0) return rc;
+    int got = 0;
+    int c = collect(nullptr, 0, &got);
+    if (c < 0) return c;
+    if (out) *out = res;
+    return res.sr_status;
+  }
   int push(const float* xyz, int n, int stride_bytes, double stamp, loam_sweep_result* out) {
     int rc = push_async(xyz, n, stride_bytes, stamp, false, nullptr, 0);
     if (rc < 0) return rc;

@@ -4,6 +4,7 @@
 #include <limits.h>
 #include "sr_kernels2.cuh"
 #include "pose_math.cuh"
+#include "pk_decode.cuh"
 
 namespace loamgpu {
 
@@ -24,6 +25,7 @@ struct SRHandle {
   // ev_free: compute -> copy, both also guard the reuse of the pinned staging buffer)
   static const int RAW_DEPTH = 4;
   DevBuf<float> d_raw2[RAW_DEPTH];
+  DevBuf<float> d_decoded;             // xyz of a sweep that arrived as raw packets (pk_decode.cuh)
   float* d_raw_cur = nullptr;
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_copied[RAW_DEPTH] = {nullptr, nullptr, nullptr, nullptr};
@@ -238,6 +240,49 @@ struct SRHandle {
     int rc = process_device(n, first, startOri, endOri, stamp);
     CUDA_OK(cudaEventRecord(ev_free[b], stream));
     return rc;
+  }
+
+  // raw-packet front end: `n_packets` VLP-16 data packets (1206 B each, HOST memory) holding one
+  // revolution.  The bytes go through the same staging ring / copy stream as an xyz sweep, are decoded
+  // by pk_decode_vlp16 on the node's stream, and the decoded points feed the unchanged node.
+  int process_packets(const unsigned char* packets, int n_packets, double stamp) {
+    processed = false;
+    if (!systemInited) {  // :213-219
+      systemInitCount++;
+      if (systemInitCount >= P.system_delay) systemInited = true;
+      return LOAM_NOT_READY;
+    }
+    if (n_packets <= 0 || !packets) { set_error("bad packet buffer"); return LOAM_ERR_ARG; }
+    const long long n_ll = (long long)n_packets * pk::POINTS_PER_PACKET;
+    if (n_ll > cap) { set_error("%d packets = %lld points exceed max_points=%d", n_packets, n_ll, cap); return LOAM_ERR_CAPACITY; }
+    const int n = (int)n_ll;
+    const size_t bytes = (size_t)n_packets * pk::PACKET_BYTES;
+    CUDA_OK(cudaSetDevice(device));
+    if (!d_decoded.p && d_decoded.alloc((size_t)cap * 3) != LOAM_OK) return LOAM_ERR_CUDA;
+    const int b = raw_sel;
+    raw_sel = (raw_sel + 1) % RAW_DEPTH;
+    CUDA_OK(cudaEventSynchronize(ev_copied[b]));
+    unsigned char* st = (unsigned char*)h_raw2[b].p;
+    memcpy(st, packets, bytes);
+    // first / last return of the revolution (scanRegistration.cpp:230-232 reads them on the host)
+    int first = -1, lastf = -1;
+    float p0[3], pl[3];
+    for (int i = 0; i < n && first < 0; i++)
+      if (pk::decode_point(st + (size_t)(i / pk::POINTS_PER_PACKET) * pk::PACKET_BYTES, i % pk::POINTS_PER_PACKET, p0)) first = i;
+    for (int i = n - 1; i >= 0 && lastf < 0; i--)
+      if (pk::decode_point(st + (size_t)(i / pk::POINTS_PER_PACKET) * pk::PACKET_BYTES, i % pk::POINTS_PER_PACKET, pl)) lastf = i;
+    if (first < 0) return LOAM_NOT_READY;
+    float startOri, endOri;
+    sweep_orientation(p0, pl, startOri, endOri);
+    unsigned char* d_pk = (unsigned char*)d_raw2[b].p;
+    CUDA_OK(cudaStreamWaitEvent(copy_stream, ev_free[b], 0));
+    CUDA_OK(cudaMemcpyAsync(d_pk, st, bytes, cudaMemcpyHostToDevice, copy_stream));
+    CUDA_OK(cudaEventRecord(ev_copied[b], copy_stream));
+    CUDA_OK(cudaStreamWaitEvent(stream, ev_copied[b], 0));
+    LAUNCH("pk_decode_vlp16", pk_decode_vlp16, n_packets < 1184 ? n_packets : 1184, 384, 0, stream, d_pk, n_packets, d_decoded.p);
+    CUDA_OK(cudaEventRecord(ev_free[b], stream));   // the packet bytes are consumed; d_decoded is ordered on `stream`
+    d_raw_cur = d_decoded.p;
+    return process_device(n, first, startOri, endOri, stamp);
   }
 
   // :230-238
