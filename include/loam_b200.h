@@ -110,6 +110,15 @@ int loam_sr_imu(loam_sr* h, double stamp, const double quat[4], const float acc[
 /* laserCloudHandler, :211-636.  xyz: n points, `stride_bytes` apart, 3 floats each, HOST memory,
  * sensor frame (x fwd, y left, z up), firing order.  NOT_READY while systemDelay swallows sweeps. */
 int loam_sr_process(loam_sr* h, const float* xyz, int n, int stride_bytes, double stamp);
+/* raw-packet front end: the same handler fed with the Velodyne VLP-16 data packets of
+ * one revolution (n_packets x 1206 bytes, HOST memory, single-return mode) instead of the decoded
+ * /velodyne_points cloud that scanRegistration.cpp:675 subscribes to.  The packets are decoded on
+ * the device (csrc/pk_decode.cuh states the arithmetic: the published packet format with an ideal
+ * calibration, azimuth interpolated inside a block pair as the velodyne_pointcloud driver does);
+ * no-return slots become NaN and are dropped by the node's NaN filter (:228). */
+#define LOAM_VLP16_PACKET_BYTES 1206
+#define LOAM_VLP16_POINTS_PER_PACKET 384
+int loam_sr_process_packets(loam_sr* h, const unsigned char* packets, int n_packets, double stamp);
 int loam_sr_download(loam_sr* h, int which_cloud, float* xyzi, int cap_points, int* n);
 int loam_sr_download_ints(loam_sr* h, int which, int* out, int cap, int* n);
 int loam_sr_download_floats(loam_sr* h, int which, float* out, int cap, int* n);
@@ -194,6 +203,10 @@ int loam_pipeline_push_async(loam_pipeline* h, const float* xyz, int n, int stri
 int loam_pipeline_push_device(loam_pipeline* h, const float* d_xyz, int n, const float first_last_xyz[6],
                               int first_index, double stamp);
 int loam_pipeline_collect(loam_pipeline* h, loam_sweep_result* out, int cap, int* n);
+/* the synchronous and the enqueue-only push for a sweep that arrives as raw VLP-16 packets */
+int loam_pipeline_push_packets(loam_pipeline* h, const unsigned char* packets, int n_packets, double stamp,
+                               loam_sweep_result* res);
+int loam_pipeline_push_packets_async(loam_pipeline* h, const unsigned char* packets, int n_packets, double stamp);
 /* The stages of consecutive sweeps overlap on internal streams (registration of sweep k+1 and
  * mapping of sweep k-1 beside the odometry of sweep k).  loam_pipeline_stream() is the odometry
  * stream; loam_pipeline_join() makes it wait (on the device, no host synchronisation) for all work
@@ -210,6 +223,8 @@ loam_lm* loam_pipeline_lm(loam_pipeline* h);
 int loam_debug_math(int fn, const float* x, const float* y, float* out, int n);
 /* op 0: QR solve (m x n, one rhs) 1: Jacobi eigen (values then row vectors) 2: LU inverse; `batch` systems */
 int loam_debug_linalg(int op, const float* A, const float* b, float* out, int m, int n, int batch);
+/* the device packet decoder alone: xyz receives n_packets * 384 points (3 floats each, NaN = no return) */
+int loam_debug_decode_packets(const unsigned char* packets, int n_packets, float* xyz);
 int loam_debug_sort_pairs(unsigned int* keys, unsigned int* vals, int n);
 int loam_debug_voxel_filter(const float* xyzi, int n, float leaf, float* out, int cap_out, int* n_out);
 /* same filter through the one-kernel cooperative path laserMapping uses for the incoming sweep */

@@ -85,6 +85,10 @@ def lib():
     L.loam_tm_destroy.argtypes = [vp]
     L.loam_sr_imu.argtypes = [vp, cd, vp, vp]
     L.loam_sr_process.argtypes = [vp, vp, ci, ci, cd]
+    L.loam_sr_process_packets.argtypes = [vp, vp, ci, cd]
+    L.loam_pipeline_push_packets.argtypes = [vp, vp, ci, cd, ctypes.POINTER(SweepResult)]
+    L.loam_pipeline_push_packets_async.argtypes = [vp, vp, ci, cd]
+    L.loam_debug_decode_packets.argtypes = [vp, ci, vp]
     L.loam_sr_download.argtypes = [vp, ci, vp, ci, ctypes.POINTER(ci)]
     L.loam_sr_download_ints.argtypes = [vp, ci, vp, ci, ctypes.POINTER(ci)]
     L.loam_sr_download_floats.argtypes = [vp, ci, vp, ci, ctypes.POINTER(ci)]
@@ -156,6 +160,21 @@ def profile_report():
     return out
 
 
+def _packets(packets):
+    pk = np.ascontiguousarray(packets, dtype=np.uint8)
+    if pk.ndim != 2 or pk.shape[1] != 1206:
+        raise ValueError("packets must be a (n_packets, 1206) uint8 array")
+    return pk
+
+
+def decode_packets(packets):
+    """test hook: the device VLP-16 decoder alone -> (n_packets * 384, 3) float32, NaN = no return"""
+    pk = _packets(packets)
+    out = np.empty((pk.shape[0] * 384, 3), np.float32)
+    _check(lib().loam_debug_decode_packets(pk.ctypes.data, pk.shape[0], out.ctypes.data))
+    return out
+
+
 class _Node:
     _prefix = None
 
@@ -199,6 +218,11 @@ class ScanRegistration(_Node):
     def process(self, xyz, stamp):
         xyz = np.ascontiguousarray(xyz, dtype=np.float32)
         return _check(self.L.loam_sr_process(self.h, xyz.ctypes.data, xyz.shape[0], xyz.strides[0], float(stamp)))
+
+    def process_packets(self, packets, stamp):
+        """packets: uint8 array (n_packets, 1206) of VLP-16 data packets of one revolution"""
+        pk = _packets(packets)
+        return _check(self.L.loam_sr_process_packets(self.h, pk.ctypes.data, pk.shape[0], float(stamp)))
 
     def cloud(self, which):
         return self._dl(self.L.loam_sr_download, which, np.float32, 4)
@@ -351,6 +375,16 @@ class Pipeline(_Node):
         _check(self.L.loam_pipeline_push(self.h, xyz.ctypes.data, xyz.shape[0], xyz.strides[0], float(stamp), ctypes.byref(res)))
         return res
 
+
+    def push_packets(self, packets, stamp):
+        pk = _packets(packets)
+        res = SweepResult()
+        _check(self.L.loam_pipeline_push_packets(self.h, pk.ctypes.data, pk.shape[0], float(stamp), ctypes.byref(res)))
+        return res
+
+    def push_packets_async(self, packets, stamp):
+        pk = _packets(packets)
+        return _check(self.L.loam_pipeline_push_packets_async(self.h, pk.ctypes.data, pk.shape[0], float(stamp)))
 
     def push_async(self, xyz, stamp):
         """pageable xyz is staged before this returns; CUDA-pinned packed xyz is read in place until collect()"""

@@ -208,6 +208,12 @@ int loam_sr_process(loam_sr* h, const float* xyz, int n, int stride_bytes, doubl
   if (r != LOAM_OK) return r;
   return h->h.sync_counts();
 }
+int loam_sr_process_packets(loam_sr* h, const unsigned char* packets, int n_packets, double stamp) {
+  if (!h) return LOAM_ERR_ARG;
+  int r = h->h.process_packets(packets, n_packets, stamp);
+  if (r != LOAM_OK) return r;
+  return h->h.sync_counts();
+}
 int loam_sr_download(loam_sr* hh, int which, float* xyzi, int cap, int* n) {
   if (!hh) return LOAM_ERR_ARG;
   SRHandle& h = hh->h;

@@ -82,3 +82,52 @@ class Synth:
         r = np.zeros(3)
         self.L.synth_gt_pose(self.h, float(t), p.ctypes.data, r.ctypes.data)
         return p, r
+
+
+# ---------------------------------------------------------------------------------------------
+# Velodyne VLP-16 data packets from a synthetic sweep (raw-packet front end)
+# ---------------------------------------------------------------------------------------------
+VLP16_PACKET_BYTES = 1206
+VLP16_LASER_DEG = np.array([-15, 1, -13, 3, -11, 5, -9, 7, -7, 9, -5, 11, -3, 13, -1, 15], np.float64)
+
+
+def vlp16_packets(xyz, stamp=0.0, drop=None):
+    """Encodes a preset-1 sweep (16 lasers x an even number of azimuth steps, every ray returned,
+    firing order as the generator emits it) as the sensor's own UDP payloads: (n_packets, 1206) uint8.
+    One generator azimuth step = one firing sequence; two per data block; 12 blocks per packet
+    (the last packet is padded with no-return blocks that continue the azimuth ramp).
+    drop: optional boolean mask (n,) of returns to encode as "no return" (distance 0)."""
+    xyz = np.asarray(xyz, np.float64)
+    n = xyz.shape[0]
+    assert n % 32 == 0, "needs an even number of 16-laser firing sequences"
+    steps = n // 16
+    d = np.sqrt((xyz ** 2).sum(axis=1))
+    raw = np.clip(np.rint(d / 0.002), 1, 65535).astype(np.uint16)
+    if drop is not None:
+        raw = np.where(np.asarray(drop, bool), np.uint16(0), raw)
+    first = xyz.reshape(steps, 16, 3)[:, 0, :]
+    az = np.degrees(np.arctan2(-first[:, 1], first[:, 0])) % 360.0          # clockwise from +x (forward)
+    az_blocks = np.rint(az[0::2] * 100.0).astype(np.int64) % 36000
+    nblk = steps // 2
+    npk = (nblk + 11) // 12
+    step_az = int((az_blocks[1] - az_blocks[0]) % 36000) if nblk > 1 else 40
+    pk = np.zeros((npk, VLP16_PACKET_BYTES), np.uint8)
+    raw_b = raw.reshape(nblk, 32)
+    for b in range(npk * 12):
+        p, k = divmod(b, 12)
+        o = 100 * k
+        pk[p, o], pk[p, o + 1] = 0xFF, 0xEE
+        a = int(az_blocks[b]) if b < nblk else int((az_blocks[-1] + step_az * (b - nblk + 1)) % 36000)
+        pk[p, o + 2], pk[p, o + 3] = a & 0xFF, a >> 8
+        if b < nblk:
+            body = np.zeros((32, 3), np.uint8)
+            body[:, 0] = raw_b[b] & 0xFF
+            body[:, 1] = raw_b[b] >> 8
+            body[:, 2] = (np.arange(32) * 7 + b) & 0xFF      # reflectivity: unused by LOAM
+            pk[p, o + 4:o + 100] = body.ravel()
+    t_us = int(stamp * 1e6)
+    for p in range(npk):
+        t = (t_us + int(p * 12 * 110.592)) & 0xFFFFFFFF
+        pk[p, 1200:1204] = [t & 0xFF, (t >> 8) & 0xFF, (t >> 16) & 0xFF, (t >> 24) & 0xFF]
+        pk[p, 1204], pk[p, 1205] = 0x37, 0x22                 # strongest return, VLP-16
+    return pk

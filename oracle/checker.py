@@ -109,8 +109,18 @@ def _load(kind):
                                   ctypes.c_int, ctypes.c_void_p, ctypes.c_double, ctypes.POINTER(SweepResult)]
         L.chk_lm_save_map.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
         L.chk_lm_load_map.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
+        L.chk_decode_packets.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
     _libs[kind] = L
     return L
+
+
+def decode_packets(packets, kind="port"):
+    """CPU restatement of the VLP-16 packet decoder (oracle/packet_port.hpp) -> (n_packets * 384, 3) float32"""
+    pk = np.ascontiguousarray(packets, dtype=np.uint8)
+    assert pk.ndim == 2 and pk.shape[1] == 1206
+    out = np.empty((pk.shape[0] * 384, 3), np.float32)
+    _load(kind).chk_decode_packets(pk.ctypes.data, pk.shape[0], out.ctypes.data)
+    return out
 
 
 class Checker:

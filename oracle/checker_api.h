@@ -24,6 +24,7 @@ int chk_lm_push(void* h, const float* corner, int nc, const float* surf, int ns,
                 const float transformSum[6], double stamp, loam_sweep_result* out);
 int chk_lm_save_map(void* h, const char* path);
 int chk_lm_load_map(void* h, const char* path);
+void chk_decode_packets(const unsigned char* packets, int n_packets, float* xyz);
 #ifdef __cplusplus
 }
 #endif

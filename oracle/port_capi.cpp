@@ -5,6 +5,7 @@
 #include <chrono>
 #include <cstdio>
 #include "loam_port.hpp"
+#include "packet_port.hpp"
 #include "checker_api.h"
 
 using namespace oracle;
@@ -285,6 +286,12 @@ int chk_lm_load_map(void* hv, const char* path) {
   }
   fclose(f);
   return ok ? 0 : -3;
+}
+
+
+// raw-packet front end: n_packets VLP-16 data packets -> n_packets * 384 points (NaN = no return)
+void chk_decode_packets(const unsigned char* packets, int n_packets, float* xyz) {
+  for (int p = 0; p < n_packets; p++) decode_vlp16_packet(packets + (size_t)1206 * p, xyz + (size_t)384 * 3 * p);
 }
 
 }  // extern "C"

@@ -1,0 +1,101 @@
+"""GPU (-m gpu): raw-packet front end -- the device VLP-16 decoder against the
+oracle's restatement, and the packet-fed pipeline against the oracle fed with the decoded cloud."""
+import numpy as np
+import pytest
+
+from conftest import biteq
+
+pytestmark = pytest.mark.gpu
+
+KEYS = ("transform", "transform_sum", "transform_aft_mapped", "transform_mapped")
+
+
+def _random_packets(rng, n_packets):
+    pk = rng.integers(0, 256, size=(n_packets, 1206), dtype=np.uint8)
+    az = int(rng.integers(0, 36000))
+    for p in range(n_packets):
+        for b in range(12):
+            o = 100 * b
+            pk[p, o], pk[p, o + 1] = 0xFF, 0xEE
+            pk[p, o + 2], pk[p, o + 3] = az & 0xFF, az >> 8
+            az = (az + int(rng.integers(1, 90))) % 36000
+            # a third of the returns missing
+            body = pk[p, o + 4:o + 100].reshape(32, 3)
+            miss = rng.random(32) < 0.33
+            body[miss, 0] = 0
+            body[miss, 1] = 0
+    pk[1, 300] = 0x12       # one corrupted block flag
+    return pk
+
+
+@pytest.mark.parametrize("n_packets", [1, 2, 75, 700])
+def test_device_packet_decoder_equals_oracle(pkg, checker, n_packets):
+    rng = np.random.default_rng(n_packets)
+    pk = _random_packets(rng, max(n_packets, 2))[:n_packets] if n_packets > 1 else _random_packets(rng, 2)[:1]
+    g = pkg.decode_packets(pk)
+    r = checker.decode_packets(pk)
+    assert g.shape == r.shape == (n_packets * 384, 3)
+    assert np.array_equal(np.isnan(g), np.isnan(r))
+    fin = np.isfinite(r)
+    assert 0.5 < fin.mean() < 0.8
+    assert np.array_equal(g[fin].view(np.uint32), r[fin].view(np.uint32))
+
+
+def test_packet_fed_pipeline_equals_oracle_on_decoded_cloud(pkg, checker, synth):
+    S = synth.Synth(1)
+    P = pkg.make_params(1, system_delay=0)
+    G = pkg.Pipeline(P)          # fed with the packets
+    X = pkg.Pipeline(P)          # fed with the decoded cloud
+    C = checker.Checker(checker.make_params(1), "port")
+    mapped = 0
+    for k in range(30):
+        xyz, st = S.sweep(k)
+        drop = np.zeros(xyz.shape[0], bool)
+        if k % 3 == 1:            # no-return holes, including the first and the last slots of the revolution
+            drop[:17] = True
+            drop[-40:] = True
+            drop[7000:7300] = True
+        pk = synth.vlp16_packets(xyz, st, drop=drop)
+        dec = checker.decode_packets(pk)
+        g = G.push_packets(pk, st)
+        x = X.push(dec, st)
+        r = C.push(dec, st)
+        for key in ("sr_status", "lo_status", "lm_status", "n_full", "n_sharp", "n_less_sharp", "n_flat", "n_less_flat", "lo_iters", "lm_iters"):
+            assert getattr(g, key) == getattr(r, key) == getattr(x, key), (k, key)
+        for key in KEYS:
+            assert bytes(getattr(g, key)) == bytes(getattr(r, key)) == bytes(getattr(x, key)), (k, key)
+        if g.sr_status == 0:
+            assert np.array_equal(G.sr.cloud(0).view(np.uint32), C.cloud(0).view(np.uint32)), k
+            assert np.array_equal(G.sr.cloud(4).view(np.uint32), C.cloud(4).view(np.uint32)), k
+        mapped += g.lm_status == 0
+    assert mapped >= 12
+
+
+def test_packet_entry_points_edge_cases(pkg, synth):
+    P = pkg.make_params(1, system_delay=0)
+    sr = pkg.ScanRegistration(P)
+    empty = np.zeros((3, 1206), np.uint8)       # flags missing: every slot is "no return"
+    assert sr.process_packets(empty, 0.0) == 1  # swallowed like the reference's first sweep / an empty cloud
+    assert sr.process_packets(empty, 0.1) == 1
+    too_many = np.zeros((P.max_points // 384 + 2, 1206), np.uint8)
+    with pytest.raises(pkg.LoamError):
+        sr.process_packets(too_many, 0.2)
+    with pytest.raises(ValueError):
+        sr.process_packets(np.zeros((2, 1000), np.uint8), 0.3)
+    S = synth.Synth(1)
+    xyz, st = S.sweep(0)
+    pk = synth.vlp16_packets(xyz, st)
+    assert sr.process_packets(pk, 0.4) == 0
+    assert sr.cloud(0).shape[0] == 28800
+    # async form: same results as the synchronous one
+    A, B = pkg.Pipeline(P), pkg.Pipeline(P)
+    res = []
+    for k in range(8):
+        xyz, st = S.sweep(k)
+        pk = synth.vlp16_packets(xyz, st)
+        A.push_packets_async(pk, st)
+        res.append(B.push_packets(pk, st))
+    got = A.collect()
+    assert len(got) == 8
+    for a, b in zip(got, res):
+        assert bytes(a.transform_mapped) == bytes(b.transform_mapped) and a.lm_status == b.lm_status

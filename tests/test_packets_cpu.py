@@ -1,0 +1,61 @@
+"""CPU: the oracle's VLP-16 packet decoder (oracle/packet_port.hpp) against hand-computed points of
+the published packet format, and the synthetic packetizer round trip."""
+import numpy as np
+
+from conftest import cloud_checksum
+
+
+def _one_block_packet(az_hundredths, raws, next_az=None):
+    pk = np.zeros((1, 1206), np.uint8)
+    for b in range(12):
+        o = 100 * b
+        pk[0, o], pk[0, o + 1] = 0xFF, 0xEE
+        a = (az_hundredths + 40 * b) % 36000 if next_az is None or b != 1 else next_az
+        pk[0, o + 2], pk[0, o + 3] = a & 0xFF, a >> 8
+    for k, r in enumerate(raws):
+        pk[0, 4 + 3 * k], pk[0, 5 + 3 * k] = r & 0xFF, r >> 8
+    return pk
+
+
+def test_decoder_known_answers(checker):
+    # block 0 at 90.00 deg, laser 0 (-15 deg) at 10 m, laser 1 (+1 deg) at 20 m, the rest no return
+    pts = checker.decode_packets(_one_block_packet(9000, [5000, 10000]))
+    assert pts.shape == (384, 3)
+    w = np.radians(-15.0)
+    # azimuth 90 deg clockwise from forward = pointing right: x ~ 0, y = -d cos(w)
+    assert np.allclose(pts[0], [0.0, -10.0 * np.cos(w), 10.0 * np.sin(w)], atol=2e-6 * 10)
+    # laser 1 fires 2.304 us later: 40 * 2.304 / 110.592 = 0.83 -> rounds to +1 hundredth of a degree
+    a = np.radians(90.01)
+    w = np.radians(1.0)
+    assert np.allclose(pts[1], [20 * np.cos(w) * np.cos(a), -20 * np.cos(w) * np.sin(a), 20 * np.sin(w)], atol=1e-5 * 20)
+    assert np.isnan(pts[2:32]).all()                      # distance 0 = no return
+    # second firing sequence of the block: +55.296 us -> half of the 0.40 deg block step
+    pts2 = checker.decode_packets(_one_block_packet(35990, [0] * 16 + [2500]))
+    a = np.radians((359.90 + 0.20) % 360.0)
+    w = np.radians(-15.0)
+    assert np.allclose(pts2[16], [5 * np.cos(w) * np.cos(a), -5 * np.cos(w) * np.sin(a), 5 * np.sin(w)], atol=1e-5 * 5)
+    # a block whose flag is not 0xFFEE is ignored
+    bad = _one_block_packet(9000, [5000])
+    bad[0, 0] = 0
+    assert np.isnan(checker.decode_packets(bad)[:32]).all()
+
+
+def test_packetizer_round_trip(checker, synth):
+    S = synth.Synth(1)
+    xyz, st = S.sweep(3)
+    pk = synth.vlp16_packets(xyz, st)
+    assert pk.shape == (75, 1206) and pk.dtype == np.uint8
+    dec = checker.decode_packets(pk)
+    assert dec.shape == (28800, 3) and np.isfinite(dec).all()
+    # 2 mm range quantisation + 0.01 deg azimuth quantisation + the intra-firing azimuth ramp the
+    # generator does not model (<= 0.125 deg + half a 0.2 deg step for the second firing of a block)
+    err = np.linalg.norm(dec - xyz, axis=1)
+    rng = np.linalg.norm(xyz, axis=1)
+    assert np.all(err < 0.004 + rng * np.radians(0.25))
+    assert abs(np.linalg.norm(dec, axis=1) - rng).max() < 0.0011
+    drop = np.zeros(28800, bool)
+    drop[:40] = True
+    drop[5000:5100] = True
+    dec2 = checker.decode_packets(synth.vlp16_packets(xyz, st, drop=drop))
+    assert np.isnan(dec2[drop]).all() and np.array_equal(dec2[~drop], dec[~drop])
+    assert int(cloud_checksum(pk)) == int(cloud_checksum(synth.vlp16_packets(xyz, st)))   # deterministic
