@@ -158,12 +158,13 @@ def algorithmic_bytes(kernel, s):
 
 def measured_traffic(kernel):
     """dram bytes per launch of `kernel` from the committed `ncu --set full` capture, if any"""
-    p = os.path.join(ROOT, "profiles", "r01_ncu_full_summary.json")
-    try:
-        d = json.load(open(p))
-        return float(d[kernel]["dram_bytes_per_launch"])
-    except Exception:
-        return None
+    for name in ("r01_ncu_full_summary_s8.json", "r01_ncu_full_summary.json"):   # newest capture first
+        try:
+            d = json.load(open(os.path.join(ROOT, "profiles", name)))
+            return float(d[kernel]["dram_bytes_per_launch"])
+        except Exception:
+            continue
+    return None
 
 
 def measured_peak():
@@ -716,6 +717,30 @@ def main():
            "poses_identical_to_resident_arm": bool(same),
            "sync": {"value": world * K / float(e2e_t[1].item()), "unit": "sweeps/s", "api": "loam_pipeline_push (returns the sweep's poses)",
                     "p50_ms_per_sweep": 1e3 * statistics.median(lat), "p99_ms_per_sweep": 1e3 * float(np.percentile(lat, 99))}}
+
+    if args.workload == "vlp16":
+        # raw-packet front end: the same stream as the sensor's own 1206-byte UDP payloads (3.1 B per point over PCIe)
+        synth = importlib.import_module(PKG + ".synth")
+        pks = [torch.from_numpy(synth.vlp16_packets(x, st)).pin_memory() for x, st in sweeps]
+        pkn = [t.numpy() for t in pks]
+        G3 = pkg.Pipeline(P, device=local_rank)
+        for k in range(W):
+            G3.push_packets_async(pkn[k], sweeps[k][1])
+        G3.collect()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        n_res = 0
+        for k in range(W, total):
+            G3.push_packets_async(pkn[k], sweeps[k][1])
+            if (k - W) % 128 == 127:
+                n_res += len(G3.collect())
+        n_res += len(G3.collect())
+        torch.cuda.synchronize()
+        pk_s = time.perf_counter() - t0
+        e2e["packets"] = {"value": world * K / pk_s, "unit": "sweeps/s", "h2d_bytes_per_step": int(pkn[0].size),
+                          "api": "loam_pipeline_push_packets_async per revolution (75 VLP-16 data packets, decoded on the device) + loam_pipeline_collect",
+                          "results": n_res}
+        del G3
 
     # ---------------- per-kernel device time (separate pass, CUDA events around every launch) ----
     roofline = None

@@ -100,6 +100,12 @@ class ScanRegistration {
     if (rc == LOAM_OK && out) features(out);
     return rc;
   }
+  // the same handler fed with the raw VLP-16 data packets of one revolution (n_packets x 1206 bytes)
+  int processPackets(const unsigned char* packets, int n_packets, double stamp, Features* out = nullptr) {
+    int rc = check(loam_sr_process_packets(h_, packets, n_packets, stamp));
+    if (rc == LOAM_OK && out) features(out);
+    return rc;
+  }
   void cloud(int which, Cloud* out) { detail::download(h_, loam_sr_download, which, out); }
   void features(Features* out) {
     cloud(LOAM_CLOUD_FULL, &out->full); cloud(LOAM_CLOUD_SHARP, &out->sharp); cloud(LOAM_CLOUD_LESS_SHARP, &out->less_sharp);
@@ -233,6 +239,12 @@ class Pipeline {
   int pushAsync(const pcl::PointCloud<PointT>& sweep, double stamp) {
     if (sweep.points.empty()) return LOAM_NOT_READY;
     return check(loam_pipeline_push_async(h_, &sweep.points[0].x, (int)sweep.points.size(), (int)sizeof(PointT), stamp));
+  }
+  int pushPackets(const unsigned char* packets, int n_packets, double stamp, SweepResult* res) {
+    return check(loam_pipeline_push_packets(h_, packets, n_packets, stamp, res));
+  }
+  int pushPacketsAsync(const unsigned char* packets, int n_packets, double stamp) {
+    return check(loam_pipeline_push_packets_async(h_, packets, n_packets, stamp));
   }
   std::vector<SweepResult> collect() {
     std::vector<SweepResult> out(1024);
