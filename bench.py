@@ -600,8 +600,7 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the sm_100a library has no CPU fallback")
     torch.cuda.set_device(local_rank)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"     # keep NCCL's version banner off stdout (one JSON line)
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL's banner / debug lines never reach stdout
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     pkg = importlib.import_module(PKG)
     if args.workload == "mapstress":
@@ -801,5 +800,31 @@ def ctypes_sizeof_record(pkg):
     return 32 + 48 + 48 + 12 + 48 + 16 + 24 + 8
 
 
+def _main_one_json_line():
+    """stdout carries exactly ONE JSON line: anything a library writes to fd 1 meanwhile (NCCL's version
+    banner, torchrun notices) is sent to stderr, and the line is written to the real stdout at the end"""
+    import io
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    buf = io.StringIO()
+    py_stdout, sys.stdout = sys.stdout, buf
+    try:
+        rc = main()
+    finally:
+        sys.stdout = py_stdout
+        sys.stdout.flush()
+        os.dup2(real, 1)
+        os.close(real)
+    lines = [l for l in buf.getvalue().splitlines() if l.strip()]
+    json_lines = [l for l in lines if l.lstrip().startswith("{")]
+    for l in lines:
+        if l not in json_lines:
+            print(l, file=sys.stderr)
+    if json_lines:
+        print(json_lines[-1], flush=True)
+    return rc
+
+
 if __name__ == "__main__":
-    sys.exit(main())
+    sys.exit(_main_one_json_line())

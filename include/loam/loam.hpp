@@ -144,6 +144,22 @@ class LaserOdometry {
     }
     return rc;
   }
+  // the same pass on features held by the caller (LaserOdometry::process(const Features&, OdomResult*))
+  int process(const Features& f, OdomResult* out) {
+    std::vector<float> c[5];
+    detail::pack(f.full, &c[0]); detail::pack(f.sharp, &c[1]); detail::pack(f.less_sharp, &c[2]); detail::pack(f.flat, &c[3]); detail::pack(f.less_flat, &c[4]);
+    int pub = 0;
+    int rc = check(loam_lo_process_host(h_, c[0].data(), (int)f.full.points.size(), c[1].data(), (int)f.sharp.points.size(),
+                                        c[2].data(), (int)f.less_sharp.points.size(), c[3].data(), (int)f.flat.points.size(),
+                                        c[4].data(), (int)f.less_flat.points.size(), f.imu_trans, &pub));
+    if (out) {
+      int st[4] = {0, 0, 0, 0};
+      check(loam_lo_state(h_, out->transform, out->transform_sum, st));
+      out->iterations = st[0]; out->rows = st[1]; out->degenerate = st[2];
+      out->has_mapping_input = pub != 0;
+    }
+    return rc;
+  }
   void cloud(int which, Cloud* out) { detail::download(h_, loam_lo_download, which, out); }
   loam_lo* handle() { return h_; }
  private:

@@ -132,6 +132,12 @@ void loam_lo_destroy(loam_lo* h);
  * sweep (:427-456).  *has_mapping_input = 1 on the sweeps whose clouds the reference publishes
  * to laserMapping (every (skipFrameNum+1)-th, :910-930). */
 int loam_lo_process(loam_lo* h, loam_sr* features, int* has_mapping_input);
+/* the same loop-body pass fed from HOST copies of the six topics (clouds as x,y,z,intensity per point,
+ * ring-major as scanRegistration emits them; imu_trans = the 12 floats of /imu_trans, NULL = zeros):
+ * the form for features that were computed, recorded or transported elsewhere */
+int loam_lo_process_host(loam_lo* h, const float* full, int n_full, const float* sharp, int n_sharp,
+                         const float* less_sharp, int n_less_sharp, const float* flat, int n_flat,
+                         const float* less_flat, int n_less_flat, const float imu_trans[12], int* has_mapping_input);
 int loam_lo_download(loam_lo* h, int which_cloud, float* xyzi, int cap_points, int* n);
 int loam_lo_download_ints(loam_lo* h, int which, int* out, int cap, int* n);
 int loam_lo_state(loam_lo* h, float transform[6], float transform_sum[6], int stats[4]);

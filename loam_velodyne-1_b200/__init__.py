@@ -94,6 +94,7 @@ def lib():
     L.loam_sr_download_floats.argtypes = [vp, ci, vp, ci, ctypes.POINTER(ci)]
     L.loam_sr_imu_trans.argtypes = [vp, vp]
     L.loam_lo_process.argtypes = [vp, vp, ctypes.POINTER(ci)]
+    L.loam_lo_process_host.argtypes = [vp, vp, ci, vp, ci, vp, ci, vp, ci, vp, ci, vp, ctypes.POINTER(ci)]
     L.loam_lo_download.argtypes = [vp, ci, vp, ci, ctypes.POINTER(ci)]
     L.loam_lo_download_ints.argtypes = [vp, ci, vp, ci, ctypes.POINTER(ci)]
     L.loam_lo_state.argtypes = [vp, vp, vp, vp]
@@ -246,6 +247,17 @@ class LaserOdometry(_Node):
     def process(self, sr):
         flag = ctypes.c_int()
         rc = _check(self.L.loam_lo_process(self.h, sr.h, ctypes.byref(flag)))
+        return rc, bool(flag.value)
+
+    def process_host(self, full, sharp, less_sharp, flat, less_flat, imu_trans=None):
+        """the same pass fed from host copies of scanRegistration's six topics"""
+        cl = [np.ascontiguousarray(c, dtype=np.float32).reshape(-1, 4) for c in (full, sharp, less_sharp, flat, less_flat)]
+        it = None if imu_trans is None else np.ascontiguousarray(imu_trans, dtype=np.float32)
+        flag = ctypes.c_int()
+        args = []
+        for c in cl:
+            args += [c.ctypes.data, c.shape[0]]
+        rc = _check(self.L.loam_lo_process_host(self.h, *args, None if it is None else it.ctypes.data, ctypes.byref(flag)))
         return rc, bool(flag.value)
 
     def cloud(self, which):

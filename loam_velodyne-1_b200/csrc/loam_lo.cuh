@@ -59,6 +59,7 @@ struct LOHandle {
   }
   ~LOHandle() {
     if (ev_dep) cudaEventDestroy(ev_dep);
+    if (carrier) { cudaStreamSynchronize(stream); delete carrier; }
     if (own_stream && stream) cudaStreamDestroy(stream);
   }
 
@@ -114,6 +115,24 @@ struct LOHandle {
     if (do_full) { frameCount = 0; *published = true; }  // :910-911
     last_published = *published;
     return LOAM_OK;
+  }
+
+  // the same pass fed from HOST copies of the six topics: a private scanRegistration handle on this
+  // node's stream serves as the feature carrier (SRHandle::set_features)
+  SRHandle* carrier = nullptr;
+  int process_host(const float* const clouds[5], const int counts[5], const float imu_trans[12], bool* published) {
+    *published = false;
+    if (!carrier) {
+      carrier = new SRHandle();
+      int r = carrier->init(&P, device, stream);
+      if (r != LOAM_OK) { delete carrier; carrier = nullptr; return r; }
+    }
+    int r = carrier->set_features(clouds, counts, imu_trans);
+    if (r != LOAM_OK) return r;
+    r = process(*carrier, published);
+    if (r < 0) return r;
+    int rr = carrier->release_bank(stream);
+    return rr < 0 ? rr : r;
   }
 
   int sync_state() {

@@ -2,6 +2,7 @@
 // ring buffer (sequential, host; scanRegistration.cpp:638-660,173-209) and enqueues the kernels.
 #pragma once
 #include <limits.h>
+#include <vector>
 #include "sr_kernels2.cuh"
 #include "pose_math.cuh"
 #include "pk_decode.cuh"
@@ -356,6 +357,55 @@ struct SRHandle {
   }
 
   const ImuState* imu_state_dev() const { return d_imu_state.p + imu_parity; }
+
+  // Feature carrier: fills the next output bank from HOST copies of the node's six topics (the five
+  // clouds, x,y,z,intensity per point, and the 12 floats of /imu_trans, :614-629), as if this node had
+  // produced them -- the form laserOdometry is fed in when the features were computed / recorded
+  // elsewhere.  The clouds must be ring-major as scanRegistration emits them (the reference's window
+  // scans, laserOdometry.cpp:484-525, rely on the same order).
+  int set_features(const float* const clouds[5], const int counts[5], const float imu_trans[12]) {
+    processed = false;
+    const int R = P.n_scans;
+    for (int c = 0; c < 5; c++) {
+      if (counts[c] < 0 || (counts[c] > 0 && !clouds[c])) { set_error("bad feature cloud %d", c); return LOAM_ERR_ARG; }
+      if (counts[c] > cap) { set_error("feature cloud %d of %d points exceeds max_points=%d", c, counts[c], cap); return LOAM_ERR_CAPACITY; }
+    }
+    std::vector<int> rc((size_t)R * 4, 0);
+    const int col_of[5] = {-1, 0, 1, 2, 3};   // full, sharp, less sharp, flat, less flat
+    for (int c = 1; c < 5; c++) {
+      int prev = 0;
+      for (int i = 0; i < counts[c]; i++) {
+        const int ring = (int)clouds[c][4 * (size_t)i + 3];
+        if (ring < prev || ring >= R) { set_error("feature cloud %d is not ring-major (point %d, ring %d)", c, i, ring); return LOAM_ERR_ARG; }
+        prev = ring;
+        rc[(size_t)ring * 4 + col_of[c]]++;
+      }
+    }
+    CUDA_OK(cudaSetDevice(device));
+    select_bank(cur_bank ^ 1);
+    CUDA_OK(cudaStreamWaitEvent(stream, bank[cur_bank].released, 0));
+    float4* dst[5] = {d_full.p, d_sharp.p, d_less_sharp.p, d_flat.p, d_less_flat.p};
+    for (int c = 0; c < 5; c++)
+      if (counts[c]) CUDA_OK(cudaMemcpyAsync(dst[c], clouds[c], sizeof(float4) * (size_t)counts[c], cudaMemcpyHostToDevice, stream));
+    SRCounts cn;
+    memset(&cn, 0, sizeof(cn));
+    cn.n_full = counts[0]; cn.n_sharp = counts[1]; cn.n_less_sharp = counts[2]; cn.n_flat = counts[3]; cn.n_less_flat = counts[4];
+    cn.h_min = INT_MAX; cn.last_valid = counts[0] - 1;
+    CUDA_OK(cudaMemcpyAsync(d_cnt.p, &cn, sizeof(cn), cudaMemcpyHostToDevice, stream));
+    CUDA_OK(cudaMemcpyAsync(d_ring_counts.p, rc.data(), sizeof(int) * rc.size(), cudaMemcpyHostToDevice, stream));
+    ImuState is;
+    memset(&is, 0, sizeof(is));
+    is.rpy_start[1] = imu_trans[0]; is.rpy_start[2] = imu_trans[1]; is.rpy_start[0] = imu_trans[2];
+    is.rpy_cur[1] = imu_trans[3]; is.rpy_cur[2] = imu_trans[4]; is.rpy_cur[0] = imu_trans[5];
+    for (int a = 0; a < 3; a++) { is.shift_from_start[a] = imu_trans[6 + a]; is.velo_from_start[a] = imu_trans[9 + a]; }
+    imu_parity ^= 1;
+    CUDA_OK(cudaMemcpyAsync(d_imu_state.p + imu_parity, &is, sizeof(is), cudaMemcpyHostToDevice, stream));
+    CUDA_OK(cudaStreamSynchronize(stream));   // the sources are pageable host memory of the caller
+    last_counts = cn;
+    *h_imu_state.p = is;
+    processed = true;
+    return LOAM_OK;
+  }
 
   // blocking: fetch the counters of the last sweep
   int sync_counts() {
