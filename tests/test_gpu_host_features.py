@@ -1,0 +1,54 @@
+"""GPU (-m gpu): laserOdometry fed from HOST copies of scanRegistration's six topics
+(loam_lo_process_host, SURVEY.md §8b `LaserOdometry::process(const Features&, OdomResult*)`)."""
+import numpy as np
+import pytest
+
+from conftest import biteq, feed_imu
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("preset,nsw", [(1, 30), (2, 8), (4, 6)])
+def test_lo_process_host_equals_oracle_and_device_path(pkg, checker, synth, preset, nsw):
+    S = synth.Synth(preset)
+    P = pkg.make_params(preset, system_delay=0)
+    C = checker.Checker(checker.make_params(preset), "port")
+    sr, lo_dev = pkg.ScanRegistration(P), pkg.LaserOdometry(P)
+    lo_host = pkg.LaserOdometry(P)
+    published = 0
+    for k in range(nsw):
+        xyz, st = S.sweep(k)
+        feed_imu(S, k, C, sr)
+        r = C.push(xyz, st)
+        g = sr.process(xyz, st)
+        assert g == r.sr_status
+        if r.sr_status != 0:
+            continue
+        feats = [C.cloud(w) for w in (0, 1, 2, 3, 4)]           # the oracle's features, held on the host
+        imu_trans = np.array(r.imu_trans[:], np.float32)
+        rc_h, pub_h = lo_host.process_host(*feats, imu_trans)
+        rc_d, pub_d = lo_dev.process(sr)
+        assert (rc_h, pub_h) == (rc_d, pub_d) == (r.lo_status, r.lm_status == 0), k
+        th, sh, ih = lo_host.state()
+        td, sd, idv = lo_dev.state()
+        assert biteq(th, td) and biteq(sh, sd) and np.array_equal(ih[:3], idv[:3]), k
+        assert biteq(th, r.transform[:]) and biteq(sh, r.transform_sum[:]), k
+        if rc_h == 0:
+            for which in (5, 6):
+                assert np.array_equal(lo_host.cloud(which).view(np.uint32), C.cloud(which).view(np.uint32)), (k, which)
+            if pub_h:
+                published += 1
+                assert np.array_equal(lo_host.cloud(7).view(np.uint32), C.cloud(7).view(np.uint32)), k
+    assert published >= 2
+
+
+def test_lo_process_host_rejects_unordered_features(pkg):
+    P = pkg.make_params(1, system_delay=0)
+    lo = pkg.LaserOdometry(P)
+    pts = np.zeros((4, 4), np.float32)
+    pts[:, 3] = [0.0, 2.0, 1.0, 3.0]          # rings out of order
+    with pytest.raises(pkg.LoamError):
+        lo.process_host(pts, pts[:1], pts, pts[:1], pts)
+    pts[:, 3] = [0.0, 1.0, 2.0, 99.0]         # ring outside the sensor
+    with pytest.raises(pkg.LoamError):
+        lo.process_host(pts, pts[:1], pts, pts[:1], pts)
