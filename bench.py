@@ -77,8 +77,12 @@ class ClockSampler:
         self.idx = gpu_index
 
     def start(self):
+        """started BEFORE the warm-up so that nvidia-smi is already emitting when the timed region begins
+        (a 60 ms region is shorter than its start-up); mark() is called at the start of the region and
+        stop() right after it: only the rows in between (plus one on either side) are used"""
+        self.begin = 0
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -89,10 +93,15 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append(line.strip())
 
+    def mark(self):
+        self.begin = max(len(self.rows) - 1, 0)
+
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.03)
+        end = len(self.rows) + 1
+        time.sleep(0.05)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
@@ -100,7 +109,8 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        rows = self.rows[self.begin:end] or self.rows[-2:]
+        for r in rows:
             f = [x.strip() for x in r.split(",")]
             if len(f) < 9:
                 continue
@@ -331,14 +341,15 @@ def run_mapstress(args, rank, world, local_rank, reference_only=False):
         c, f, a = d_in[i % span]
         Mx.process_device(c.data_ptr(), c.shape[0], f.data_ptr(), f.shape[0], a.data_ptr(), a.shape[0], seq[i]["sum"], stamps[i])
 
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     for i in range(W):
         enqueue(M1, i)
     M1.sync()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
+    sampler.mark()
     launches0 = pkg.kernel_launch_count()
     stream = torch.cuda.ExternalStream(M1.stream(), device=dev)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -483,8 +494,7 @@ def run_seq64(args, rank, world, local_rank):
     total = W + K
     P = pkg.make_params(preset, system_delay=0)
     P.map_arena_points = 1 << 20
-    if args.coop_ctas:
-        P.coop_ctas = args.coop_ctas
+    P.coop_ctas = 37 if args.coop_ctas is None else args.coop_ctas
     data = {s: gen_sweeps(seed0 + s, total, preset) for s in mine}
     n_threads = max(1, min(args.host_threads, len(mine)))
     groups = [mine[t::n_threads] for t in range(n_threads)]
@@ -582,7 +592,7 @@ def main():
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--workload", default="hdl64", choices=sorted(WORKLOADS))
     ap.add_argument("--host-threads", type=int, default=8, help="seq64: host threads feeding the pipelines of one GPU")
-    ap.add_argument("--coop-ctas", type=int, default=37, help="seq64: CTAs of the cooperative LM kernels per pipeline (0 = one per SM)")
+    ap.add_argument("--coop-ctas", type=int, default=None, help="CTAs of the cooperative LM kernels per pipeline (0 = one per SM; default 37 for seq64, else 0)")
     args = ap.parse_args()
     # a pipeline runs on 6 streams (copy, registration, odometry, mapping + side streams) and seq64 on
     # hundreds: ask for the maximum number of hardware work queues so that independent streams are not
@@ -623,7 +633,11 @@ def main():
     resident = [torch.from_numpy(x).to(dev) for x, _ in sweeps]
     aux = [first_last(x) for x, _ in sweeps]
     P = pkg.make_params(preset, system_delay=0)
+    if args.coop_ctas:
+        P.coop_ctas = args.coop_ctas
     G = pkg.Pipeline(P, device=local_rank)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     for k in range(W):
         feed(G, k)
         G.push_device(resident[k].data_ptr(), npts[k], aux[k][0], aux[k][1], sweeps[k][1])
@@ -631,8 +645,7 @@ def main():
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
+    sampler.mark()
     launches0 = pkg.kernel_launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     stream = torch.cuda.ExternalStream(G.stream(), device=dev)

@@ -260,6 +260,51 @@ __device__ __forceinline__ void grid_rows9(const GridView& g, const GridDesc& d,
     R.pre[k + 1] = R.pre[k] + (en - b);
   }
 }
+// Same block of cells, restricted to the cells that can hold a point with d2 <= r2 of the query
+// (qx,qy,qz).  r2 is an upper bound of the answer's largest distance that the caller KNOWS to be
+// attained by real points of this cloud (e.g. the previous LM iteration's neighbours measured from
+// the moved query), so dropping everything farther away cannot change an exact k-NN result.  Each
+// row lane tests its own row (distance of the query to the row's y-z square) and trims the x range
+// to the cells the ball reaches; a row is still ONE contiguous range, so nothing else changes.
+// Cell membership was decided in fp32 (floor((p - o) * inv_h)): every per-axis distance is reduced
+// by a margin far above that rounding before it is squared, which only makes the test keep more.
+template <int W>
+__device__ __forceinline__ void grid_rows9_bounded(const GridView& g, const GridDesc& d, int cx, int cy, int cz,
+                                                   float qx, float qy, float qz, float r2, GridRows9& R) {
+  static_assert(W >= 16, "one lane per row");
+  const int gl = lane_id() & (W - 1);
+  const unsigned int gmask = (W == 32) ? 0xffffffffu : (((1u << W) - 1u) << (lane_id() & ~(W - 1)));
+  int vb = 0, ve = 0;
+  if (gl < 9) {
+    const int oy = (gl % 3) - 1, oz = (gl / 3) - 1;
+    const int y = cy + oy, z = cz + oz;
+    if (y >= 0 && y < d.ny && z >= 0 && z < d.nz) {
+      const float margin = 4.0e-3f;
+      const float fx = qx - (d.ox + (float)cx * d.h), fy = qy - (d.oy + (float)cy * d.h), fz = qz - (d.oz + (float)cz * d.h);
+      const float dyv = fmaxf((oy < 0 ? fy : (oy > 0 ? d.h - fy : 0.f)) - margin, 0.f);
+      const float dzv = fmaxf((oz < 0 ? fz : (oz > 0 ? d.h - fz : 0.f)) - margin, 0.f);
+      const float base = dyv * dyv + dzv * dzv;
+      if (base <= r2) {
+        const float dxm = fmaxf(fx - margin, 0.f), dxp = fmaxf(d.h - fx - margin, 0.f);
+        const int x0 = max((base + dxm * dxm <= r2) ? cx - 1 : cx, 0);
+        const int x1 = min((base + dxp * dxp <= r2) ? cx + 1 : cx, d.nx - 1);
+        if (x0 <= x1) {
+          const int2* row = g.cell + (size_t)(z * d.ny + y) * d.nx;
+          int2 c0 = __ldg(&row[x0]);
+          int2 c1 = __ldg(&row[x1]);
+          vb = c0.x; ve = c1.x + c1.y;
+        }
+      }
+    }
+  }
+  R.pre[0] = 0;
+#pragma unroll
+  for (int k = 0; k < 9; k++) {
+    const int b = __shfl_sync(gmask, vb, k, W), en = __shfl_sync(gmask, ve, k, W);
+    R.beg[k] = b;
+    R.pre[k + 1] = R.pre[k] + (en - b);
+  }
+}
 // position in sorted_pts of flat candidate t (0 <= t < pre[9])
 __device__ __forceinline__ int grid_rows9_pos(const GridRows9& R, int t) {
   int pos = R.beg[0] + t;

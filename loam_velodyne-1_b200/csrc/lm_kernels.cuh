@@ -360,8 +360,12 @@ __global__ void __launch_bounds__(256) lm_gather_map(LMGatherArgs A) {
 // loads (grid_rows9), then every candidate load is independent: the dependent-load depth per
 // query is 2, not 3 x 27.  The 5-way merge uses the warp-reduce unit (redux.sync) on the distance
 // bits (non-negative floats order like unsigned ints), ties resolved by a second reduce on the index.
+// have_prev: out[0..4] still holds the five neighbours this query had in the PREVIOUS LM iteration
+// (same cloud, the query has moved by one small pose update).  Their largest distance from the new
+// position bounds the new fifth-neighbour distance from above, so only the cells that ball reaches
+// are scanned (grid_rows9_bounded): typically a third of the candidates, same exact answer.
 template <int W>
-__device__ __forceinline__ bool lm_knn5_group(const GridView& g, const GridDesc& d, float qx, float qy, float qz, float4* out) {
+__device__ __forceinline__ bool lm_knn5_group(const GridView& g, const GridDesc& d, float qx, float qy, float qz, float4* out, bool have_prev = false) {
   const int lane = lane_id();
   const int gl = lane & (W - 1);
   const unsigned int gmask = (W == 32) ? 0xffffffffu : (((1u << W) - 1u) << (lane & ~(W - 1)));
@@ -373,7 +377,21 @@ __device__ __forceinline__ bool lm_knn5_group(const GridView& g, const GridDesc&
     int cx = (int)floorf((qx - d.ox) * d.inv_h), cy = (int)floorf((qy - d.oy) * d.inv_h), cz = (int)floorf((qz - d.oz) * d.inv_h);
     // cell size >= 1.02 m: every point with d2 < 1 lies in the 3x3x3 block around the query cell
     GridRows9 R;
-    grid_rows9<W>(g, d, cx, cy, cz, R);
+    if (have_prev) {   // uniform inside the group
+      float r2 = 0.f;
+#pragma unroll
+      for (int k = 0; k < 5; k++) {
+        const float4 p = out[k];
+        float dx = qx - p.x, dy = qy - p.y, dz = qz - p.z;
+        float dd = 0.f;
+        dd += dx * dx; dd += dy * dy; dd += dz * dz;
+        r2 = fmaxf(r2, dd);
+      }
+      __syncwarp(gmask);   // every lane has read the old neighbours before any lane stores new ones
+      grid_rows9_bounded<W>(g, d, cx, cy, cz, qx, qy, qz, r2, R);
+    } else {
+      grid_rows9<W>(g, d, cx, cy, cz, R);
+    }
     total = R.pre[9];
     if (total >= 5) {
       // four independent candidate loads in flight per lane before the first one is consumed

@@ -216,7 +216,10 @@ __global__ void __launch_bounds__(LM_THREADS, 2) lm_optimize(LMOptArgs A) {
           const int T = q < Qc ? 0 : 1;
           const int k = T ? q - Qc : q;
           const float4 pointSel = lm_to_map(A.stack[T][k], g, s_T);
-          bool found = lm_knn5_group<LM_KW>(A.grid[T], T ? gd1 : gd0, pointSel.x, pointSel.y, pointSel.z, s_nb[act ? i : LM_CH + (lane / LM_KW)]);
+          // one chunk per CTA (always, at the configured sizes): s_nb[i] / s_found[i] still describe this
+          // query's previous iteration, which bounds the new search
+          const bool have_prev = act && iterCount > 0 && nmine <= LM_CH && s_found[i] != 0;
+          bool found = lm_knn5_group<LM_KW>(A.grid[T], T ? gd1 : gd0, pointSel.x, pointSel.y, pointSel.z, s_nb[act ? i : LM_CH + (lane / LM_KW)], have_prev);
           if (act && (lane & (LM_KW - 1)) == 0) s_found[i] = found ? 1 : 0;
         }
         __syncthreads();

@@ -38,10 +38,10 @@ def record_lm_inputs_gpu(pkg, synth, preset, nsw, seed=None):
     return rec
 
 
-def shifted(rec_item, dx, dstamp=0.0):
-    """the same laserOdometry output on a street `dx` metres to the left (LOAM x = left)"""
+def shifted(rec_item, dx, dstamp=0.0, axis=0):
+    """the same laserOdometry output on a street `dx` metres to the left (LOAM x = left; axis 1 = up, 2 = forward)"""
     s = rec_item["sum"].copy()
-    s[3] = np.float32(s[3] + np.float32(dx))
+    s[3 + axis] = np.float32(s[3 + axis] + np.float32(dx))
     return rec_item["corner"], rec_item["surf"], rec_item["full"], s, rec_item["stamp"] + dstamp
 
 

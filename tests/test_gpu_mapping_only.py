@@ -140,3 +140,35 @@ def test_mapping_only_stress_prepopulated_map_parity(pkg, checker, synth, tmp_pa
         assert (st[0], st[3], st[4]) == (o.lm_iters, o.n_map_corner, o.n_map_surf), i
         assert np.array_equal(M.ints(100), C.ints(100)) and np.array_equal(M.ints(101), C.ints(101)), i
         assert np.array_equal(M.cloud(10, cap=1 << 21).view(np.uint32), C.cloud(10, cap=1 << 21).view(np.uint32)), i
+
+
+def test_map_window_shifts_keep_parity(pkg, checker, synth, tmp_path):
+    """the 21x11x21 cube window follows the pose (laserMapping.cpp:454-614): odometry jumps of several
+    hundred metres along every axis, in both directions, shift the descriptor table by up to eight cubes
+    at once and clear the wrapped slabs; every pass must stay bit-equal to the oracle, and so must the map"""
+    rec = record_lm_inputs_oracle(checker, synth, 1, 26)
+    P = pkg.make_params(1, system_delay=0)
+    M = pkg.LaserMapping(P)
+    C = checker.Checker(checker.make_params(1), "port")
+    plan = [(0, 0.0), (0, 420.0), (0, -30.0), (2, 390.0), (1, 160.0), (1, -10.0), (2, -700.0), (0, -460.0), (0, 0.0)]
+    t = 0.0
+    cens = set()
+    for axis, off in plan:
+        for i, r in enumerate(rec[:8]):
+            c, s, f, tsum, st = shifted(r, off, t, axis)
+            o = C.lm_push(c, s, f, tsum, st)
+            assert M.process_host(c, s, f, tsum, st) == 0
+            aft, bef, tobe, stt = M.state()
+            assert biteq(aft, o.transform_aft_mapped[:]) and biteq(bef, o.transform_bef_mapped[:]), (axis, off, i)
+            assert (stt[0], stt[3], stt[4]) == (o.lm_iters, o.n_map_corner, o.n_map_surf), (axis, off, i)
+            assert np.array_equal(M.cloud(10, cap=1 << 20).view(np.uint32), C.cloud(10).view(np.uint32)), (axis, off, i)
+        t += 10.0
+        g_path, o_path = str(tmp_path / "g.loammap"), str(tmp_path / "o.loammap")
+        M.save_map(g_path)
+        C.lm_save_map(o_path)
+        fg, fo = read_map_file(g_path), read_map_file(o_path)
+        assert np.array_equal(fg["header"]["cen"], fo["header"]["cen"])
+        cens.add(tuple(int(v) for v in fg["header"]["cen"]))
+        for T in range(2):
+            assert np.array_equal(fg["cnt"][T], fo["cnt"][T]) and np.array_equal(fg["pts"][T].view(np.uint32), fo["pts"][T].view(np.uint32)), (axis, off, T)
+    assert len(cens) >= 5     # the window really moved
