@@ -65,6 +65,11 @@ struct LMState {
   int surroundOff[250];                 // start of every (cube, type) segment inside it
   int registeredN;                      // size of the registered full-resolution cloud
   int vxOverflow[4];
+  // snapshot taken by lm_insert_ids at the end of a pass: the map update, the registered cloud and the
+  // pose record of pass k run on the side stream while the front of pass k+1 (pose prediction, incoming
+  // filters) already overwrites stackN / transformTobeMapped on the main stream
+  int insN[2];
+  float insT[6];
 };
 
 struct LMTrig { float srx, crx, sry, cry, srz, crz; };
@@ -140,6 +145,7 @@ struct LMSetupArgs {
   LMState* st;
   const LOState* lo;        // transformSum of this sweep, cloud sizes
   CubeDesc* cubes[2];
+  int phase;                // 1: pose prediction only (nothing of the cube map is touched); 2: the rest; 0: both
 };
 
 // K1: one block.  /laser_odom_to_init hand-off (:304-318), transformAssociateToMap (:422),
@@ -150,7 +156,7 @@ __global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
   __shared__ int s_shift[3], s_center[3];
   __shared__ unsigned char s_fov[125], s_in[125];
   __shared__ int s_ind[125];
-  if (threadIdx.x == 0) {
+  if (threadIdx.x == 0 && A.phase != 2) {
     float sum[6];
     pm::odometry_msg_roundtrip(A.lo->transformSum, sum);
     for (int i = 0; i < 6; i++) st->transformSum[i] = sum[i];
@@ -161,6 +167,11 @@ __global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
     for (int i = 0; i < 6; i++) st->predT[i] = T[i];
     float4 py = lm_to_map(make_float4(0.0f, 10.0f, 0.0f, 0.f), g, T);
     st->pointOnYAxis[0] = py.x; st->pointOnYAxis[1] = py.y; st->pointOnYAxis[2] = py.z;
+    st->stackN2[0] = A.lo->n_corner_last; st->stackN2[1] = A.lo->n_surf_last;
+  }
+  if (A.phase == 1) return;
+  if (threadIdx.x == 0) {
+    const float* T = st->transformTobeMapped;
     int cI = lm_cube_coord(T[3], st->cenW), cJ = lm_cube_coord(T[4], st->cenH), cK = lm_cube_coord(T[5], st->cenD);
     // net shifts per axis: +1 per `while (center < 3)`, -1 per `while (center >= dim - 3)`
     int dims[3] = {CUBE_W, CUBE_H, CUBE_D};
@@ -173,7 +184,6 @@ __global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
       s_center[a] = c[a];
     }
     st->cenW += s_shift[0]; st->cenH += s_shift[1]; st->cenD += s_shift[2];
-    st->stackN2[0] = A.lo->n_corner_last; st->stackN2[1] = A.lo->n_surf_last;
   }
   __syncthreads();
   // apply the shifts to the descriptor tables, one (line, type) per thread

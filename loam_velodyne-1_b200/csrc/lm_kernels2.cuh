@@ -300,7 +300,7 @@ __global__ void __launch_bounds__(256) lm_registered(LMState* st, const float4* 
   __shared__ LMTrig s_g;
   __shared__ float s_T[6];
   if (threadIdx.x == 0) {
-    for (int i = 0; i < 6; i++) s_T[i] = st->transformTobeMapped[i];
+    for (int i = 0; i < 6; i++) s_T[i] = st->insT[i];   // the refined pose of this pass (snapshot of lm_insert_ids)
     s_g = lm_trig(s_T);
   }
   __syncthreads();

@@ -64,6 +64,10 @@ __global__ void __launch_bounds__(256) lm_insert_ids(LMInsertArgs A) {
   __syncthreads();
   const LMTrig g = s_g;
   const int n0 = st->stackN[0], n1 = st->stackN[1];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {   // what the side-stream kernels of this pass read (LMState::insN / insT)
+    st->insN[0] = n0; st->insN[1] = n1;
+    for (int i = 0; i < 6; i++) st->insT[i] = s_T[i];
+  }
   const int cenW = st->cenW, cenH = st->cenH, cenD = st->cenD;
   for (int i = blockIdx.x * 256 + threadIdx.x; i < n0 + n1; i += gridDim.x * 256) {
     int T = i < n0 ? 0 : 1;
@@ -167,7 +171,7 @@ __global__ void __launch_bounds__(1024, 1) lm_sort_new(LMSortNewArgs A) {
   __shared__ CtaRadixSmem S;
   LMState* st = A.st;
   const int T = blockIdx.x;
-  const int n = st->stackN[T];
+  const int n = st->insN[T];
   DBG_STAMP(0);
   for (int k = threadIdx.x; k < n; k += blockDim.x) {
     int cube = A.ins_cube[T][k];
@@ -205,7 +209,7 @@ __global__ void __launch_bounds__(BN_THREADS, 1) lm_bucket_new(LMSortNewArgs A) 
   __shared__ int s_ws[BN_THREADS / 32];
   LMState* st = A.st;
   const int T = blockIdx.y;
-  const int n = st->stackN[T];
+  const int n = st->insN[T];
   const int np = st->nproc[T];
   if (blockIdx.x == 0 && threadIdx.x == 0) st->newSel[T] = 0;
   const int per = (n + BN_THREADS - 1) / BN_THREADS;          // contiguous chunk per thread: stable

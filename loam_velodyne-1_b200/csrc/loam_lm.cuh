@@ -199,7 +199,7 @@ struct LMHandle {
     }
     if (g_profile == 3) prof_node("laserMapping", stream, true);
     int rc = run(in, stamp);
-    if (bank >= 0) CUDA_OK(cudaEventRecord(ev_in_done[bank], stream));
+    if (bank >= 0) CUDA_OK(cudaEventRecord(ev_in_done[bank], aux));   // the side stream holds the pass's last reader of the bank
     return rc;
   }
 
@@ -207,12 +207,20 @@ struct LMHandle {
     LMState* st = d_state.p;
     const int nb = 148;
     float4* arena[2] = {d_arena[0][cur_arena].p, d_arena[1][cur_arena].p};
-    // K1
+    // Stream plan of one pass (`stream` = main, `aux` = side; the side stream still holds the map update
+    // of the PREVIOUS pass, which therefore runs beside this pass's pose prediction and incoming filters):
+    //   main: K1a pose prediction -> K2 stack transform -> K3 incoming filters -> [wait side] K6 LM loop -> K7a insert ids
+    //   side: [map update of pass k-1] -> [wait K1a] K1b window shift + cube selection -> K4 gather -> K5 index
+    //         ... [wait K7a] K8 registered cloud, K7b-d map update, compaction, surround, pose record
+    // K1a
     LMSetupArgs SA;
-    SA.st = st; SA.lo = in.lo; SA.cubes[0] = d_cubes[0].p; SA.cubes[1] = d_cubes[1].p;
+    SA.st = st; SA.lo = in.lo; SA.cubes[0] = d_cubes[0].p; SA.cubes[1] = d_cubes[1].p; SA.phase = 1;
     LAUNCH("lm_setup", lm_setup, 1, 256, 0, stream, SA);
     CUDA_OK(cudaEventRecord(ev_fork, stream));
     CUDA_OK(cudaStreamWaitEvent(aux, ev_fork, 0));
+    // K1b on the side stream, behind the previous pass's map update (both work on the cube descriptors)
+    SA.phase = 2;
+    LAUNCH("lm_setup_cubes", lm_setup, 1, 256, 0, aux, SA);
     // K2
     LMStackArgs KA;
     KA.st = st; KA.in[0] = in.corner_last; KA.in[1] = in.surf_last; KA.out[0] = d_stack2[0].p; KA.out[1] = d_stack2[1].p;
@@ -258,28 +266,28 @@ struct LMHandle {
       g_launches++;
       if (g_profile) prof_end("lm_optimize", stream);
     }
-    // K8 on the side stream: needs only the refined pose
-    CUDA_OK(cudaEventRecord(ev_fork, stream));
-    CUDA_OK(cudaStreamWaitEvent(aux, ev_fork, 0));
-    LAUNCH("lm_registered", lm_registered, 2 * nb, 256, 0, aux, st, in.full_end, &in.lo->n_full_end, d_registered.p);
-    CUDA_OK(cudaEventRecord(ev_aux, aux));
-    // K7: insert + per-cube refilter (lm_refilter.cuh)
+    // K7: insert + per-cube refilter (lm_refilter.cuh).  K7a stays on the main stream (it reads the stack
+    // and the refined pose, and snapshots both for the side stream); everything after it is the side stream's.
     {
       LMInsertArgs IA;
       IA.st = st;
       for (int T = 0; T < 2; T++) { IA.stack[T] = d_stack[T].p; IA.ins_pts[T] = d_ins_pts[T].p; IA.ins_cube[T] = d_ins_cube[T].p; IA.ins_key[T] = d_ins_key[T].p; IA.touch_cnt[T] = d_touch[T].p; }
       LAUNCH("lm_insert_ids", lm_insert_ids, nb, 256, 0, stream, IA);
+      CUDA_OK(cudaEventRecord(ev_fork, stream));
+      CUDA_OK(cudaStreamWaitEvent(aux, ev_fork, 0));
+      // K8: registered cloud
+      LAUNCH("lm_registered", lm_registered, 2 * nb, 256, 0, aux, st, in.full_end, &in.lo->n_full_end, d_registered.p);
       LMPlanArgs PA;
       PA.st = st;
       for (int T = 0; T < 2; T++) { PA.cubes[T] = d_cubes[T].p; PA.touch_cnt[T] = d_touch[T].p; PA.cube_rank[T] = d_rank[T].p; }
-      LAUNCH("lm_refilter_plan", lm_refilter_plan, 2, 1024, 0, stream, PA);
+      LAUNCH("lm_refilter_plan", lm_refilter_plan, 2, 1024, 0, aux, PA);
       LMSortNewArgs NA;
       NA.st = st;
       for (int T = 0; T < 2; T++) {
         NA.ins_cube[T] = d_ins_cube[T].p; NA.ins_key[T] = d_ins_key[T].p; NA.cube_rank[T] = d_rank[T].p;
         for (int k = 0; k < 2; k++) { NA.nk[T][k] = d_nk[T][k].p; NA.nv[T][k] = d_nv[T][k].p; }
       }
-      LAUNCH("lm_bucket_new", lm_bucket_new, dim3(BN_GRID, 2), BN_THREADS, BN_SMEM, stream, NA);
+      LAUNCH("lm_bucket_new", lm_bucket_new, dim3(BN_GRID, 2), BN_THREADS, BN_SMEM, aux, NA);
       LMCubeArgs CA;
       CA.st = st; CA.scap = ecap;
       for (int T = 0; T < 2; T++) {
@@ -287,7 +295,7 @@ struct LMHandle {
         CA.touch_cnt[T] = d_touch[T].p; CA.cube_rank[T] = d_rank[T].p;
         for (int k = 0; k < 2; k++) { CA.nk[T][k] = d_nk[T][k].p; CA.nv[T][k] = d_nv[T][k].p; CA.sk[T][k] = d_sk[T][k].p; CA.sv[T][k] = d_sv[T][k].p; }
       }
-      LAUNCH("lm_refilter_cube", lm_refilter_cube, dim3(RF_GRID, 2), RF_THREADS, RF_SMEM, stream, CA);
+      LAUNCH("lm_refilter_cube", lm_refilter_cube, dim3(RF_GRID, 2), RF_THREADS, RF_SMEM, aux, CA);
     }
     if (++sweeps_since_compact >= 8) {  // bounded garbage in the log-structured arena
       int cr = compact();
@@ -301,7 +309,8 @@ struct LMHandle {
       int sr_ = surround();
       if (sr_ != LOAM_OK) return sr_;
     }
-    CUDA_OK(cudaStreamWaitEvent(stream, ev_aux, 0));   // join the side stream: the pass is complete on `stream`
+    // no join here: the side stream's work is ordered before the next pass's K1b, and everything that
+    // needs the pass to be complete (sync_state, the pipeline's collect / join, the destructor) waits for `aux`
     CUDA_OK(cudaGetLastError());
     return LOAM_OK;
   }
@@ -312,24 +321,24 @@ struct LMHandle {
     LMSurroundArgs SA;
     SA.st = st; SA.S = d_S.p; SA.scap = ecap;
     for (int T = 0; T < 2; T++) { SA.cubes[T] = d_cubes[T].p; SA.arena[T] = d_arena[T][cur_arena].p; }
-    LAUNCH("lm_surround_plan", lm_surround_plan, 1, 256, 0, stream, SA);
-    LAUNCH("lm_surround_gather", lm_surround_gather, 4 * 148, 256, 0, stream, SA);
+    LAUNCH("lm_surround_plan", lm_surround_plan, 1, 256, 0, aux, SA);
+    LAUNCH("lm_surround_gather", lm_surround_gather, 4 * 148, 256, 0, aux, SA);
     CloudKeyPair cp;
     cp.njobs = 1;
     CloudKeyJob& cj = cp.j[0];
     cj.pts = d_S.p; cj.n_ptr = &st->surroundIn; cj.bbox = d_ubbox.p; cj.keys = d_ukeys[0].p; cj.vals = d_uvals[0].p;
     cj.overflow = &st->vxOverflow[2]; cj.leaf = 0.2f;
     cp.j[1] = cj;
-    LAUNCH("vx_bbox", vx_bbox, dim3(296, 1), 256, 0, stream, cp);
-    LAUNCH("vx_cloud_keys", vx_cloud_keys, dim3(296, 1), 256, 0, stream, cp);
-    LAUNCH("vx_rearm_bbox", vx_rearm_bbox, 1, 32, 0, stream, cp);
+    LAUNCH("vx_bbox", vx_bbox, dim3(296, 1), 256, 0, aux, cp);
+    LAUNCH("vx_cloud_keys", vx_cloud_keys, dim3(296, 1), 256, 0, aux, cp);
+    LAUNCH("vx_rearm_bbox", vx_rearm_bbox, 1, 32, 0, aux, cp);
     SortPair sp;
     sp.njobs = 1;
     SortJob& sj = sp.j[0];
     sj.keys[0] = d_ukeys[0].p; sj.keys[1] = d_ukeys[1].p; sj.vals[0] = d_uvals[0].p; sj.vals[1] = d_uvals[1].p;
     sj.hist = d_uhist.p; sj.digit_total = d_udig.p; sj.n_ptr = &st->surroundIn; sj.nblk_cap = (ecap + RS_TILE - 1) / RS_TILE + 1;
     sp.j[1] = sj;
-    int r = radix_sort_pairs(sp, ecap, stream);
+    int r = radix_sort_pairs(sp, ecap, aux);
     if (r != LOAM_OK) return r;
     VoxelPair vp;
     vp.njobs = 1;
@@ -338,7 +347,7 @@ struct LMHandle {
     vj.block_heads = d_uheads.p; vj.out = d_surround.p; vj.out_base_ptr = nullptr; vj.out_count = &st->surroundN;
     vj.seg_count = nullptr; vj.seg_shift = 0; vj.nblk_cap = (ecap + VX_TILE - 1) / VX_TILE + 1;
     vp.j[1] = vj;
-    return voxel_reduce_sorted(vp, ecap, stream);
+    return voxel_reduce_sorted(vp, ecap, aux);
   }
 
   int compact() {
@@ -347,9 +356,9 @@ struct LMHandle {
     for (int T = 0; T < 2; T++) {
       CA.cubes[T] = d_cubes[T].p; CA.src[T] = d_arena[T][cur_arena].p; CA.dst[T] = d_arena[T][cur_arena ^ 1].p; CA.new_off[T] = d_newoff[T].p;
     }
-    LAUNCH("lm_compact_plan", lm_compact_plan, 2, 1024, 0, stream, CA);
-    LAUNCH("lm_compact_copy", lm_compact_copy, dim3(296, 2), 256, 0, stream, CA);
-    LAUNCH("lm_compact_commit", lm_compact_commit, dim3(19, 2), 256, 0, stream, CA);
+    LAUNCH("lm_compact_plan", lm_compact_plan, 2, 1024, 0, aux, CA);
+    LAUNCH("lm_compact_copy", lm_compact_copy, dim3(296, 2), 256, 0, aux, CA);
+    LAUNCH("lm_compact_commit", lm_compact_commit, dim3(19, 2), 256, 0, aux, CA);
     CUDA_OK(cudaGetLastError());
     cur_arena ^= 1;
     sweeps_since_compact = 0;
@@ -357,6 +366,7 @@ struct LMHandle {
   }
 
   int sync_state() {
+    CUDA_OK(cudaStreamSynchronize(aux));   // map update, registered cloud, surround map of the last pass
     CUDA_OK(cudaMemcpyAsync(h_state.p, d_state.p, sizeof(LMState), cudaMemcpyDeviceToHost, stream));
     CUDA_OK(cudaStreamSynchronize(stream));
     last_state = *h_state.p;

@@ -43,7 +43,7 @@ __global__ void pipe_record_lm(PipeRecord* out, const LMState* lm) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   for (int i = 0; i < 6; i++) { out->aft[i] = lm->transformAftMapped[i]; out->bef[i] = lm->transformBefMapped[i]; }
   out->lm_iters = lm->iters; out->lm_rows = lm->rows; out->lm_deg = lm->isDegenerate; out->lm_error = lm->error;
-  for (int T = 0; T < 2; T++) { out->mapN[T] = lm->mapN[T]; out->stackN[T] = lm->stackN[T]; out->bump[T] = lm->bump[T]; }
+  for (int T = 0; T < 2; T++) { out->mapN[T] = lm->mapN[T]; out->stackN[T] = lm->insN[T]; out->bump[T] = lm->bump[T]; }
   out->surroundN = lm->surroundN;
 }
 
@@ -89,6 +89,7 @@ struct PipelineHandle {
   ~PipelineHandle() {
     if (sr.copy_stream) cudaStreamSynchronize(sr.copy_stream);
     if (sr_stream) { cudaStreamSynchronize(sr_stream); cudaStreamDestroy(sr_stream); }
+    if (lm.aux) cudaStreamSynchronize(lm.aux);
     if (lm_stream) { cudaStreamSynchronize(lm_stream); cudaStreamDestroy(lm_stream); }
     if (stream) { cudaStreamSynchronize(stream); cudaStreamDestroy(stream); }
     for (int i = 0; i < 2; i++) if (ev_join[i]) cudaEventDestroy(ev_join[i]);
@@ -99,6 +100,8 @@ struct PipelineHandle {
     CUDA_OK(cudaEventRecord(ev_join[0], sr_stream));
     CUDA_OK(cudaEventRecord(ev_join[1], lm_stream));
     CUDA_OK(cudaStreamWaitEvent(stream, ev_join[0], 0));
+    CUDA_OK(cudaStreamWaitEvent(stream, ev_join[1], 0));
+    CUDA_OK(cudaEventRecord(ev_join[1], lm.aux));          // the map update of the last mapped sweep
     CUDA_OK(cudaStreamWaitEvent(stream, ev_join[1], 0));
     return LOAM_OK;
   }
@@ -145,7 +148,7 @@ struct PipelineHandle {
         pd.lm_status = mrc;
       }
       if (pd.lm_status == LOAM_OK) {
-        LAUNCH("pipe_record_lm", pipe_record_lm, 1, 32, 0, lm_stream, h_ring.p + pd.slot, lm.d_state.p);
+        LAUNCH("pipe_record_lm", pipe_record_lm, 1, 32, 0, lm.aux, h_ring.p + pd.slot, lm.d_state.p);   // behind the pass's map update
       }
     }
     next_slot = (next_slot + 1) % RING;
@@ -157,6 +160,7 @@ struct PipelineHandle {
   int collect(loam_sweep_result* out, int cap, int* n) {
     CUDA_OK(cudaStreamSynchronize(stream));
     CUDA_OK(cudaStreamSynchronize(lm_stream));
+    CUDA_OK(cudaStreamSynchronize(lm.aux));
     int k = 0;
     while (!pending.empty()) {
       Pending pd = pending.front();
