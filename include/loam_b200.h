@@ -157,6 +157,11 @@ int loam_lm_process(loam_lm* h, loam_lo* odom, double stamp);
  * that records / replays laserOdometry's output uses (BASELINE.json configs[2], mapping only) */
 int loam_lm_process_host(loam_lm* h, const float* corner_last, int n_corner, const float* surf_last, int n_surf,
                          const float* full_res, int n_full, const float transform_sum[6], double stamp);
+/* the form a ROS node uses (adapters/ros/): transform_sum_decoded is what laserOdometryHandler
+ * (laserMapping.cpp:304-321) obtained from the /laser_odom_to_init message with tf getRPY, so the
+ * library must not apply the message round trip again */
+int loam_lm_process_msg(loam_lm* h, const float* corner_last, int n_corner, const float* surf_last, int n_surf,
+                        const float* full_res, int n_full, const float transform_sum_decoded[6], double stamp);
 /* asynchronous form with DEVICE-resident clouds (float4 x,y,z,intensity), enqueue only: nothing is
  * copied but the odometry state; the arrays must stay unchanged until loam_lm_sync() (which also
  * refreshes what loam_lm_state / loam_lm_download report).  loam_lm_stream() is the CUDA stream
@@ -188,6 +193,11 @@ void loam_tm_destroy(loam_tm* h);
 int loam_tm_on_mapping(loam_tm* h, const float aft_mapped[6], const float bef_mapped[6]);
 /* laserOdometryHandler :147-180; writes /integrated_to_init */
 int loam_tm_on_odometry(loam_tm* h, const float transform_sum[6], float integrated[6]);
+
+/* the same two handlers for poses that were already decoded from their nav_msgs/Odometry messages
+ * (transformMaintenance.cpp:151-161 / :186-196 in a ROS node) */
+int loam_tm_on_mapping_msg(loam_tm* h, const float aft_mapped_decoded[6], const float bef_mapped[6]);
+int loam_tm_on_odometry_msg(loam_tm* h, const float transform_sum_decoded[6], float integrated[6]);
 
 /* ---- whole pipeline: sr -> lo -> (lm when lo publishes) -> tm, one stream, one device ---- */
 typedef struct loam_pipeline loam_pipeline;

@@ -158,7 +158,8 @@ __global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
   __shared__ int s_ind[125];
   if (threadIdx.x == 0 && A.phase != 2) {
     float sum[6];
-    pm::odometry_msg_roundtrip(A.lo->transformSum, sum);
+    if (A.lo->sum_decoded) { for (int i = 0; i < 6; i++) sum[i] = A.lo->transformSum[i]; }
+    else pm::odometry_msg_roundtrip(A.lo->transformSum, sum);
     for (int i = 0; i < 6; i++) st->transformSum[i] = sum[i];
     pm::transformAssociateToMap(st->transformSum, st->transformBefMapped, st->transformAftMapped, st->transformIncre, st->transformTobeMapped);
     const float* T = st->transformTobeMapped;

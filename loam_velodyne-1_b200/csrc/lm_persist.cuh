@@ -35,7 +35,7 @@ struct MapFileHeader {
 // is copied but the 100-byte odometry state).  Enqueue only: the caller synchronises through
 // LMHandle::sync_state().
 inline int lm_process_clouds(LMHandle& h, const float* corner, int nc, const float* surf, int ns, const float* full, int nf,
-                             const float transform_sum[6], double stamp, bool on_device) {
+                             const float transform_sum[6], double stamp, bool on_device, bool sum_decoded = false) {
   if (nc < 0 || ns < 0 || nf < 0 || (nc && !corner) || (ns && !surf) || (nf && !full) || !transform_sum) return LOAM_ERR_ARG;
   if (nc > h.cap || ns > h.cap || nf > h.cap) { set_error("laserMapping input cloud exceeds max_points (%d)", h.cap); return LOAM_ERR_CAPACITY; }
   h.frameCount++;
@@ -49,6 +49,7 @@ inline int lm_process_clouds(LMHandle& h, const float* corner, int nc, const flo
   for (int i = 0; i < 6; i++) ls.transformSum[i] = transform_sum[i];
   ls.n_corner_last = nc; ls.n_surf_last = ns; ls.n_full_end = nf;
   ls.cornerLastNum = nc; ls.surfLastNum = ns;
+  ls.sum_decoded = sum_decoded ? 1 : 0;
   LMHandle::Input in;
   in.lo = h.d_in_state[bank].p;
   if (on_device) {

@@ -30,6 +30,8 @@ struct LOState {
   int iters, rows;         // stats of the last sweep
   int index_enable;        // cornerLastNum > 10 && surfLastNum > 100 (:903)
   int n_corner_last, n_surf_last, n_full_end;  // sizes of the device clouds
+  int sum_decoded;         // laserMapping input only: transformSum was already decoded from the /laser_odom_to_init
+                           // message by the caller (a ROS node's laserOdometryHandler, laserMapping.cpp:304-321)
 };
 
 struct LOArgs {

@@ -386,14 +386,17 @@ struct TMHost {
     for (int i = 0; i < 6; i++) transformSum[i] = transformIncre[i] = transformMapped[i] = transformBefMapped[i] = transformAftMapped[i] = 0;
   }
   // odomAftMappedHandler :182-203: pose arrives as a quaternion (decoded here), bef as twist floats
-  void on_mapping(const float aft[6], const float bef[6]) {
+  // decoded = the caller (a ROS node) already took getRPY of the message's quaternion
+  void on_mapping(const float aft[6], const float bef[6], bool decoded = false) {
     float a[6];
-    pm::odometry_msg_roundtrip(aft, a);
+    if (decoded) { for (int i = 0; i < 6; i++) a[i] = aft[i]; }
+    else pm::odometry_msg_roundtrip(aft, a);
     for (int i = 0; i < 6; i++) { transformAftMapped[i] = a[i]; transformBefMapped[i] = bef[i]; }
   }
   // laserOdometryHandler :147-180
-  void on_odometry(const float sum[6], float integrated[6]) {
-    pm::odometry_msg_roundtrip(sum, transformSum);
+  void on_odometry(const float sum[6], float integrated[6], bool decoded = false) {
+    if (decoded) { for (int i = 0; i < 6; i++) transformSum[i] = sum[i]; }
+    else pm::odometry_msg_roundtrip(sum, transformSum);
     pm::transformAssociateToMap(transformSum, transformBefMapped, transformAftMapped, transformIncre, transformMapped);
     for (int i = 0; i < 6; i++) integrated[i] = transformMapped[i];
   }

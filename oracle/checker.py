@@ -70,6 +70,8 @@ def build(verbose=False):
 
 
 def lib_path(kind):
+    if kind.endswith(".so"):   # a library with the checker API built elsewhere (tests/adapter: the ROS adapter nodes)
+        return kind
     return {"port": os.path.join(_HERE, "liboracle_port.so"),
             "port-libm": os.path.join(_HERE, "liboracle_port_libm.so"),
             "reference": os.path.join(_HERE, "_ref", "libloam_ref.so")}[kind]
@@ -91,6 +93,8 @@ def _load(kind):
             build()
         if not os.path.exists(path):
             raise FileNotFoundError(path)
+    if kind.endswith(".so") and not os.path.exists(path):
+        raise FileNotFoundError(path)
     L = ctypes.CDLL(path)
     L.chk_kind.restype = ctypes.c_char_p
     L.chk_create.restype = ctypes.c_void_p

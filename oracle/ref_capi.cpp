@@ -4,6 +4,7 @@
 // SURVEY.md §3.0 does.  Each handle loads private copies of the node libraries (the nodes keep
 // their state in file-scope globals), so several handles can coexist in one process.
 #include <dlfcn.h>
+#include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -54,13 +55,17 @@ bool load_node(Node& n, const std::string& name) {
 #endif
   // private copy => private globals
   char tmpl[256];
-  snprintf(tmpl, sizeof(tmpl), "/tmp/loamref_%d_%d_%s.so", (int)getpid(), g_serial.fetch_add(1), name.c_str());
+  // unique per process, per driver library (two builds of this driver can live in one process: the
+  // reference's nodes and tests/adapter's) and per load
+  snprintf(tmpl, sizeof(tmpl), "/tmp/loamref_%d_%lx_%d_%s.so", (int)getpid(), (unsigned long)(uintptr_t)&g_serial, g_serial.fetch_add(1), name.c_str());
   std::string cmd = "cp '" + src + "' '" + tmpl + "'";
   if (system(cmd.c_str()) != 0) { fprintf(stderr, "ref_capi: cannot copy %s\n", src.c_str()); return false; }
   n.tmp = tmpl;
   n.dl = dlopen(tmpl, RTLD_NOW | RTLD_LOCAL);
-  if (!n.dl) { fprintf(stderr, "ref_capi: dlopen failed: %s\n", dlerror()); return false; }
-  unlink(tmpl);
+  if (!n.dl) { fprintf(stderr, "ref_capi: dlopen failed: %s\n", dlerror()); unlink(tmpl); return false; }
+  // the copy stays on disk until the node is unloaded: glibc identifies loaded objects by (device,
+  // inode), and an unlinked copy's inode can be handed to the next copy, which dlopen would then
+  // take for the library that is already loaded
   n.start = (void (*)())n.sym("node_start");
   n.stop = (void (*)())n.sym("node_stop");
   n.post_cloud = (void (*)(const char*, const float*, int, int, double))n.sym("node_post_cloud");
@@ -138,6 +143,7 @@ void chk_destroy(void* hv) {
     if (n->dl) {
       if (n->stop) n->stop();
       dlclose(n->dl);
+      if (!n->tmp.empty()) unlink(n->tmp.c_str());
     }
   }
   delete h;

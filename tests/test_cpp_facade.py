@@ -78,3 +78,14 @@ def test_facade_node_by_node_equals_pipeline(pkg, synth, tmp_path):
                 assert f" lm2=0 {hexes(g.transform_aft_mapped)}" in line, (k, line)
     assert mapped >= 4
     assert os.path.getsize(os.path.join(tmp_path, "facade.loammap")) > 4851 * 10
+
+
+def test_ros_adapter_nodes_compile_against_the_ros_stand_ins(pkg):
+    """adapters/ros/*.cpp build (and link against libloam_b200.so) with the oracle's ROS / tf / pcl_conversions
+    stand-ins; running them needs a GPU (tests/test_gpu_ros_adapter.py)"""
+    if not os.path.exists(pkg.LIB_PATH):
+        importlib.import_module(PKG + ".build").build_cuda()
+    r = subprocess.run(["bash", os.path.join(ROOT, "tests", "adapter", "build_adapter.sh")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    for name in ("libref_sr_1.so", "libref_lo.so", "libref_lm.so", "libref_tm.so", "libloam_ref.so"):
+        assert os.path.exists(os.path.join(ROOT, "tests", "adapter", "_build", name))
