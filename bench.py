@@ -161,6 +161,18 @@ def algorithmic_bytes(kernel, s):
         return N * (4.0 + 4.0 + 2.0 + 2.0) + (Ns + Nls + Nf) * 4.0
     if kernel == "lm_gather_map":
         return M * 32.0
+    if kernel == "lm_registered":
+        return N * 32.0
+    if kernel == "lm_stack_transform":
+        return (Nls + Nlf) * 32.0
+    if kernel == "lm_handoff":
+        return (Nls + Nlf + N) * 32.0
+    if kernel == "lm_insert_ids":      # stack point in, map-frame point + cube id + voxel key out
+        return Q * (16.0 + 16.0 + 8.0)
+    if kernel == "sr_compact":
+        return (Ns + Nls + Nf + Nlf) * 32.0
+    if kernel == "sr_ring_scan":       # per-block ring histograms
+        return (N / 256.0) * 64 * 4.0 * 2
     if kernel in ("grid_count", "grid_scatter", "grid_bbox"):
         return (Nls + Nlf + M) / 2.0 * 24.0
     return None
@@ -781,7 +793,15 @@ def main():
                             "share_of_device_time": kms / tot_ms,
                             "note": "working set of one HDL-64 sweep (~10 MB) is L2-resident and the LM kernels are latency-bound; see DESIGN.md §5"}
                 break
-        kernels = [{"kernel": n, "calls": c, "ms": round(m, 4), "share": round(m / tot_ms, 4)} for n, c, m in kernels[:16]]
+        rows = []
+        for n, c, m in kernels[:20]:   # per kernel: algorithmic bytes / live launch time against the measured HBM peak
+            e = {"kernel": n, "calls": c, "ms": round(m, 4), "share": round(m / tot_ms, 4), "avg_launch_us": round(1e3 * m / c, 2)}
+            ab = algorithmic_bytes(n, stats)
+            if ab is not None:
+                e["algorithmic_GBps"] = round(ab / (m * 1e-3 / c) / 1e9, 1)
+                e["frac_of_hbm_peak"] = round(e["algorithmic_GBps"] / peak, 4)
+            rows.append(e)
+        kernels = rows
     del G2
 
     # ---------------- the one collective of the multi-sequence configuration ---------------------
