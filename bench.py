@@ -244,7 +244,16 @@ def cpu_baseline(sweeps, budget_s=20.0, max_sweeps=80, preset=None, imu=None, la
     wall = time.perf_counter() - t0
     busy = C.busy_seconds()
     C.close()
-    return {"value": done / wall, "unit": "sweeps/s", "cores": 1, "kind": kind,
+    piped = None
+    if not imu or not any(imu):
+        # the way the reference is deployed: one process per node, topic queues of depth 2 between them
+        # (three host threads here, the CPU restatement's node objects; IMU-free sequences only)
+        Cp = checker.Checker(checker.make_params(PRESET if preset is None else preset), "port")
+        tp, _ = Cp.run_pipelined(sweeps[:done])
+        Cp.close()
+        piped = {"value": done / tp, "unit": "sweeps/s", "cores": 3, "kind": "port",
+                 "sample": f"the same {done} sweeps, scanRegistration / laserOdometry / laserMapping on one thread each, depth-2 queues"}
+    return {"value": done / wall, "unit": "sweeps/s", "cores": 1, "kind": kind, "pipelined_3threads": piped,
             "sample": f"first {done} sweeps of the same {label} sequence, sr->lo->lm->tm sequentially on one host thread",
             "p50_ms_per_sweep": 1e3 * statistics.median(lat),
             "node_busy_s": {"sr": busy[0], "lo": busy[1], "lm": busy[2], "tm": busy[3]},

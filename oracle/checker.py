@@ -113,6 +113,8 @@ def _load(kind):
                                   ctypes.c_int, ctypes.c_void_p, ctypes.c_double, ctypes.POINTER(SweepResult)]
         L.chk_lm_save_map.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
         L.chk_lm_load_map.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
+        L.chk_run_pipelined.restype = ctypes.c_double
+        L.chk_run_pipelined.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
         L.chk_decode_packets.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
     _libs[kind] = L
     return L
@@ -208,3 +210,13 @@ class Checker:
         rc = self.L.chk_lm_load_map(self.h, os.fsencode(path))
         if rc != 0:
             raise RuntimeError(f"chk_lm_load_map({path}) = {rc}")
+
+    def run_pipelined(self, sweeps):
+        """kind "port": sr / lo / lm on three threads joined by depth-2 queues (the reference's process
+        pipeline); sweeps = [(xyz, stamp), ...]; returns (wall seconds, /integrated_to_init poses [n, 6])"""
+        xyz = np.ascontiguousarray(np.concatenate([np.asarray(x, np.float32).reshape(-1, 3) for x, _ in sweeps]), np.float32)
+        counts = np.array([np.asarray(x).shape[0] for x, _ in sweeps], np.int32)
+        stamps = np.array([st for _, st in sweeps], np.float64)
+        poses = np.zeros((len(sweeps), 6), np.float32)
+        t = self.L.chk_run_pipelined(self.h, xyz.ctypes.data, counts.ctypes.data, stamps.ctypes.data, len(sweeps), poses.ctypes.data)
+        return float(t), poses

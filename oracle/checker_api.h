@@ -24,6 +24,8 @@ int chk_lm_push(void* h, const float* corner, int nc, const float* surf, int ns,
                 const float transformSum[6], double stamp, loam_sweep_result* out);
 int chk_lm_save_map(void* h, const char* path);
 int chk_lm_load_map(void* h, const char* path);
+/* port only: the three nodes on three threads with depth-2 queues, as the reference's processes run */
+double chk_run_pipelined(void* h, const float* xyz, const int* counts, const double* stamps, int n_sweeps, float* poses);
 void chk_decode_packets(const unsigned char* packets, int n_packets, float* xyz);
 #ifdef __cplusplus
 }

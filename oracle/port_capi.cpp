@@ -289,6 +289,75 @@ int chk_lm_load_map(void* hv, const char* path) {
 }
 
 
+// The reference runs its nodes as separate processes joined by topic queues: sweep k+1 is registered
+// while sweep k is in the odometry and an earlier one in the mapping.  Same structure with one thread
+// per node and queues of depth 2 (the reference's subscriber queue size) between them; a full queue
+// blocks the producer instead of dropping the message, so every sweep is processed.  IMU-free
+// sequences only.  xyz: n_sweeps arrays back to back, counts[k] points each.  poses: n_sweeps x 6
+// (/integrated_to_init).  Returns the wall-clock seconds of the run.
+}  // extern "C"
+#include <condition_variable>
+#include <deque>
+#include <mutex>
+#include <thread>
+namespace {
+template <class T> struct BoundedQueue {
+  std::deque<T> q; std::mutex m; std::condition_variable cv; size_t cap = 2; bool closed = false;
+  void push(T&& v) { std::unique_lock<std::mutex> l(m); cv.wait(l, [&] { return q.size() < cap; }); q.push_back(std::move(v)); cv.notify_all(); }
+  bool pop(T& v) { std::unique_lock<std::mutex> l(m); cv.wait(l, [&] { return !q.empty() || closed; }); if (q.empty()) return false; v = std::move(q.front()); q.pop_front(); cv.notify_all(); return true; }
+  void close() { std::unique_lock<std::mutex> l(m); closed = true; cv.notify_all(); }
+};
+struct FeatMsg { int k; bool ok; SRFeatures f; };
+struct OdomMsg { int k; bool ok; LOOutput o; };
+}
+extern "C" {
+double chk_run_pipelined(void* hv, const float* xyz, const int* counts, const double* stamps, int n_sweeps, float* poses) {
+  chk_handle* h = (chk_handle*)hv;
+  BoundedQueue<FeatMsg> q1;
+  BoundedQueue<OdomMsg> q2;
+  std::mutex tm_mu;   // transformMaintenance receives from both nodes (its two callbacks never overlap in the reference either)
+  auto t0 = std::chrono::steady_clock::now();
+  std::thread t_sr([&] {
+    size_t off = 0;
+    for (int k = 0; k < n_sweeps; k++) {
+      FeatMsg m; m.k = k;
+      m.ok = h->sr.process(xyz + off * 3, counts[k], 3, stamps[k], m.f);
+      off += (size_t)counts[k];
+      q1.push(std::move(m));
+    }
+    q1.close();
+  });
+  std::thread t_lo([&] {
+    FeatMsg m;
+    while (q1.pop(m)) {
+      if (!m.ok) continue;
+      OdomMsg o; o.k = m.k;
+      o.ok = h->lo.process(m.f, o.o);
+      if (!o.ok) continue;
+      float sumMsg[6];
+      odometry_msg_roundtrip(o.o.transformSum, sumMsg);
+      { std::lock_guard<std::mutex> l(tm_mu); h->tm.onOdometry(sumMsg, poses + 6 * (size_t)m.k); }
+      if (o.o.hasMappingInput) q2.push(std::move(o));
+    }
+    q2.close();
+  });
+  std::thread t_lm([&] {
+    OdomMsg o;
+    while (q2.pop(o)) {
+      float sumMsg[6];
+      odometry_msg_roundtrip(o.o.transformSum, sumMsg);
+      if (h->lm.process(o.o, sumMsg)) {
+        float aftMsg[6];
+        aft_mapped_msg_roundtrip(h->lm.transformAftMapped, aftMsg);
+        std::lock_guard<std::mutex> l(tm_mu);
+        h->tm.onMapping(aftMsg, h->lm.transformBefMapped);
+      }
+    }
+  });
+  t_sr.join(); t_lo.join(); t_lm.join();
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
 // raw-packet front end: n_packets VLP-16 data packets -> n_packets * 384 points (NaN = no return)
 void chk_decode_packets(const unsigned char* packets, int n_packets, float* xyz) {
   for (int p = 0; p < n_packets; p++) decode_vlp16_packet(packets + (size_t)1206 * p, xyz + (size_t)384 * 3 * p);

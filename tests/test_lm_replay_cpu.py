@@ -59,3 +59,20 @@ def test_oracle_lateral_replicas_grow_the_local_map(checker, synth):
         sizes.append(o.n_map_corner + o.n_map_surf)
     assert sizes[1] > 1.5 * sizes[0] and sizes[2] > 2.2 * sizes[0]
     assert np.isfinite(np.array(o.transform_aft_mapped[:])).all()
+
+
+def test_oracle_three_thread_pipeline_builds_the_same_map(checker, synth):
+    """the measured 'reference deployment' baseline of bench.py (one thread per node, depth-2 queues):
+    odometry and mapping do not depend on timing, so the map it builds equals the sequential run's
+    (only /integrated_to_init depends on when the mapping correction arrives, as in the reference)"""
+    S = synth.Synth(1)
+    sw = [S.sweep(k) for k in range(24)]
+    A = checker.Checker(checker.make_params(1), "port")
+    for x, st in sw:
+        A.push(x, st)
+    B = checker.Checker(checker.make_params(1), "port")
+    wall, poses = B.run_pipelined(sw)
+    assert wall > 0 and poses.shape == (24, 6) and np.isfinite(poses).all()
+    for which in (10, 11, 5, 6):
+        assert np.array_equal(A.cloud(which).view(np.uint32), B.cloud(which).view(np.uint32)), which
+    assert np.abs(poses[-1] - np.array(A.push(*S.sweep(24)).transform_mapped[:])).max() < 0.5
