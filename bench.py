@@ -299,8 +299,8 @@ def run_mapstress(args, rank, world, local_rank, reference_only=False):
     import torch.distributed as dist
     pkg = importlib.import_module(PKG)
     synth = importlib.import_module(PKG + ".synth")
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    from lm_replay import record_lm_inputs_gpu, shifted
+    replay = importlib.import_module(PKG + ".replay")
+    record_lm_inputs_gpu, shifted = replay.record_lm_inputs_gpu, replay.shifted
     preset, seed0, workload = WORKLOADS["mapstress"]
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)

@@ -2,10 +2,10 @@
 import importlib, os, sys, time
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, ROOT)
 pkg = importlib.import_module("loam_velodyne-1_b200")
 synth = importlib.import_module("loam_velodyne-1_b200.synth")
-from lm_replay import record_lm_inputs_gpu, shifted
+_r = importlib.import_module("loam_velodyne-1_b200.replay"); record_lm_inputs_gpu, shifted = _r.record_lm_inputs_gpu, _r.shifted
 nsw = int(sys.argv[1]) if len(sys.argv) > 1 else 260
 spacing = float(sys.argv[2]) if len(sys.argv) > 2 else 18.0
 t0 = time.time()
