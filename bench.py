@@ -671,10 +671,15 @@ def main():
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     stream = torch.cuda.ExternalStream(G.stream(), device=dev)
     t_wall0 = time.perf_counter()
+    wait0 = pkg.host_wait_ns()
+    node0 = pkg.host_node_ns()
     ev0.record(stream)
     for k in range(W, total):
         feed(G, k)
         G.push_device(resident[k].data_ptr(), npts[k], aux[k][0], aux[k][1], sweeps[k][1])
+    t_wait = (pkg.host_wait_ns() - wait0) * 1e-9   # of which blocked on the library's back-pressure events
+    t_node = [(a - b) * 1e-6 for a, b in zip(pkg.host_node_ns(), node0)]
+    t_enq = time.perf_counter() - t_wall0      # host time to enqueue the K sweeps (launch-bound if ~= the device time)
     G.join()            # the pipeline stream waits for the registration / mapping streams: ev1 covers all work
     ev1.record(stream)
     results = G.collect()
@@ -828,7 +833,7 @@ def main():
                            "parallelism": f"seq{world}", "l2": "inputs larger than L2: %d distinct sweeps (%.0f MB) resident in HBM, each read once" % (total, sum(npts) * 12 / 1e6),
                            "timed_region": "K x (scanRegistration + laserOdometry + laserMapping every 2nd sweep + pose record); stages of consecutive sweeps overlap on 3 streams (+ copy stream) like the reference's nodes; CUDA events on the pipeline stream after a device-side join of all streams, no host sync inside"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
-                "wall_ms_incl_launch": float(ms_t[1].item()),
+                "wall_ms_incl_launch": float(ms_t[1].item()), "host_enqueue_ms": t_enq * 1e3, "host_backpressure_wait_ms": t_wait * 1e3, "host_enqueue_ms_by_node": {"sr": t_node[0], "lo": t_node[1], "lm": t_node[2]},
                 "mean_counts": stats, "roofline": roofline, "top_kernels": kernels, "cpu_baseline": cb,
                 "poses_gathered": [int(table.shape[0]), int(table.shape[1])]}
         print(json.dumps(line))

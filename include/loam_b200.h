@@ -264,6 +264,11 @@ int loam_debug_trace_dump(const char* path);
 
 /* number of kernel launches issued by this library on the calling process so far */
 long long loam_kernel_launch_count(void);
+/* nanoseconds the calling host threads spent blocked on the library's back-pressure events (staging
+ * buffers, parameter slots) since the library was loaded: enqueue time minus this = launch cost */
+long long loam_debug_host_wait_ns(void);
+/* host nanoseconds the pipeline entry points spent enqueueing each node (sr, lo + record, lm) */
+void loam_debug_host_node_ns(long long out[3]);
 /* per-kernel device time accumulated since the last reset (CUDA events; 0 when profiling is off) */
 int loam_profile_enable(int on);
 int loam_profile_report(char* buf, int cap);

@@ -75,6 +75,7 @@ def lib():
     vp, ci, cd = ctypes.c_void_p, ctypes.c_int, ctypes.c_double
     L.loam_last_error.restype = ctypes.c_char_p
     L.loam_kernel_launch_count.restype = ctypes.c_longlong
+    L.loam_debug_host_wait_ns.restype = ctypes.c_longlong
     L.loam_params_preset.argtypes = [ctypes.POINTER(LoamParams), ci]
     L.loam_profile_enable.argtypes = [ci]
     L.loam_profile_report.argtypes = [ctypes.c_char_p, ci]
@@ -145,6 +146,16 @@ def make_params(preset, system_delay=0):
 
 def kernel_launch_count():
     return int(lib().loam_kernel_launch_count())
+
+
+def host_wait_ns():
+    return int(lib().loam_debug_host_wait_ns())
+
+
+def host_node_ns():
+    out = (ctypes.c_longlong * 3)()
+    lib().loam_debug_host_node_ns(out)
+    return [int(x) for x in out]
 
 
 def profile_enable(on=True):

@@ -22,6 +22,11 @@ namespace dm = loam::dm;
 
 void set_error(const char* fmt, ...);
 extern std::atomic<long long> g_launches;
+extern std::atomic<long long> g_host_wait_ns;   // host time spent blocked on back-pressure events (staging / parameter slots)
+long long now_ns();
+extern std::atomic<long long> g_host_node_ns[3];  // host time the pipeline spent enqueueing scanRegistration / laserOdometry / laserMapping
+struct HostNode { int i; long long t0; HostNode(int i_) : i(i_), t0(now_ns()) {} ~HostNode() { g_host_node_ns[i] += now_ns() - t0; } };
+struct HostWait { long long t0; HostWait() : t0(now_ns()) {} ~HostWait() { g_host_wait_ns += now_ns() - t0; } };
 extern int g_profile;   // 0 off, 1 per-kernel CUDA events (serialising), 2 timeline stamps around every launch (non-serialising), 3 stamps at node boundaries only
 
 struct ProfEntry { double ms = 0; long long calls = 0; };
@@ -113,7 +118,7 @@ struct PinnedRing {
   int upload(T* dst, const T& v, cudaStream_t s) {
     int i = next;
     next = (next + 1) % N;
-    if (cudaEventSynchronize(ev[i]) != cudaSuccess) return LOAM_ERR_CUDA;
+    { HostWait hw; if (cudaEventSynchronize(ev[i]) != cudaSuccess) return LOAM_ERR_CUDA; }
     *p[i] = v;
     // a kernel reads the pinned slot instead of a copy-engine transfer: the copy engines execute
     // their queue in order, so a small H2D that has to wait for its stream (e.g. the mapping

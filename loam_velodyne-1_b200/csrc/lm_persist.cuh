@@ -76,6 +76,7 @@ inline int lm_save_map(LMHandle& h, const char* path) {
   if (r == LOAM_OK && h.cur_arena != arena_before) r = h.sync_state();   // a compaction was due: read the state it left
   if (r != LOAM_OK) return r;
   CUDA_OK(cudaStreamSynchronize(h.aux));
+  CUDA_OK(cudaStreamSynchronize(h.aux2));
   const LMState& s = h.last_state;
   MapFileHeader H;
   memset(&H, 0, sizeof(H));
@@ -176,6 +177,7 @@ inline int lm_load_map(LMHandle& h, const char* path) {
   if (!ok) { set_error("%s is truncated or inconsistent", path); return LOAM_ERR_ARG; }
   CUDA_OK(cudaStreamSynchronize(h.stream));
   CUDA_OK(cudaStreamSynchronize(h.aux));
+  CUDA_OK(cudaStreamSynchronize(h.aux2));
   h.cur_arena = 0;
   h.sweeps_since_compact = 0;
   LMState s;
@@ -215,6 +217,7 @@ inline int lm_export_pcd(LMHandle& h, int which, const char* path) {
   if (r == LOAM_OK && h.cur_arena != arena_before) r = h.sync_state();
   if (r != LOAM_OK) return r;
   CUDA_OK(cudaStreamSynchronize(h.aux));
+  CUDA_OK(cudaStreamSynchronize(h.aux2));
   const LMState& s = h.last_state;
   std::vector<float4> pts;
   const float4* src = nullptr;

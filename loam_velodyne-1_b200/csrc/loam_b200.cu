@@ -13,6 +13,9 @@
 namespace loamgpu {
 
 std::atomic<long long> g_launches(0);
+std::atomic<long long> g_host_wait_ns(0);
+std::atomic<long long> g_host_node_ns[3];
+long long now_ns() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return (long long)ts.tv_sec * 1000000000ll + ts.tv_nsec; }
 int g_profile = 0;
 static thread_local char g_err[512] = "";
 static cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;
@@ -149,6 +152,8 @@ int loam_params_preset(loam_params* p, int preset) {
 
 const char* loam_last_error(void) { return g_err; }
 long long loam_kernel_launch_count(void) { return g_launches.load(); }
+long long loam_debug_host_wait_ns(void) { return g_host_wait_ns.load(); }
+void loam_debug_host_node_ns(long long out[3]) { for (int i = 0; i < 3; i++) out[i] = g_host_node_ns[i].load(); }
 int loam_profile_enable(int on) {
   g_profile = on != 0 ? 1 : 0;
   prof_table().clear();

@@ -18,6 +18,12 @@ struct LMHandle {
   // beside the map update (K7)
   cudaStream_t aux = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_aux = nullptr;
+  // second side stream (low priority) for the products of a pass that nothing on the device waits for:
+  // the registered cloud and the voxel filter of the surround map.  They would otherwise sit on `aux`
+  // between the map update of pass k and the window shift of pass k+1, i.e. on the cycle
+  // LM loop -> map update -> window shift -> gather -> index -> LM loop that sets the mapping rate.
+  cudaStream_t aux2 = nullptr;
+  cudaEvent_t ev_reg = nullptr, ev_sur_in = nullptr, ev_sur_done = nullptr;
   int cap = 0, ecap = 0, arena_cap = 0, coop_blocks = 0;
   int cur_arena = 0;
   int sweeps_since_compact = 0;
@@ -71,6 +77,12 @@ struct LMHandle {
       CUDA_OK(cudaStreamCreateWithPriority(&aux, cudaStreamNonBlocking, pri));
       CUDA_OK(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
       CUDA_OK(cudaEventCreateWithFlags(&ev_aux, cudaEventDisableTiming));
+      int lo_pri = 0, hi_pri = 0;
+      CUDA_OK(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
+      CUDA_OK(cudaStreamCreateWithPriority(&aux2, cudaStreamNonBlocking, lo_pri));
+      CUDA_OK(cudaEventCreateWithFlags(&ev_reg, cudaEventDisableTiming));
+      CUDA_OK(cudaEventCreateWithFlags(&ev_sur_in, cudaEventDisableTiming));
+      CUDA_OK(cudaEventCreateWithFlags(&ev_sur_done, cudaEventDisableTiming));
     }
     cap = P.max_points;
     arena_cap = P.map_arena_points > 0 ? P.map_arena_points : (8 << 20);
@@ -142,8 +154,12 @@ struct LMHandle {
   ~LMHandle() {
     if (ev_dep) cudaEventDestroy(ev_dep);
     if (aux) { cudaStreamSynchronize(aux); cudaStreamDestroy(aux); }
+    if (aux2) { cudaStreamSynchronize(aux2); cudaStreamDestroy(aux2); }
     if (ev_fork) cudaEventDestroy(ev_fork);
     if (ev_aux) cudaEventDestroy(ev_aux);
+    if (ev_reg) cudaEventDestroy(ev_reg);
+    if (ev_sur_in) cudaEventDestroy(ev_sur_in);
+    if (ev_sur_done) cudaEventDestroy(ev_sur_done);
     for (int b = 0; b < 2; b++) {
       if (ev_in_ready[b]) cudaEventDestroy(ev_in_ready[b]);
       if (ev_in_done[b]) cudaEventDestroy(ev_in_done[b]);
@@ -275,8 +291,10 @@ struct LMHandle {
       LAUNCH("lm_insert_ids", lm_insert_ids, nb, 256, 0, stream, IA);
       CUDA_OK(cudaEventRecord(ev_fork, stream));
       CUDA_OK(cudaStreamWaitEvent(aux, ev_fork, 0));
-      // K8: registered cloud
-      LAUNCH("lm_registered", lm_registered, 2 * nb, 256, 0, aux, st, in.full_end, &in.lo->n_full_end, d_registered.p);
+      CUDA_OK(cudaStreamWaitEvent(aux2, ev_fork, 0));
+      // K8: registered cloud (second side stream: beside the map update)
+      LAUNCH("lm_registered", lm_registered, 2 * nb, 256, 0, aux2, st, in.full_end, &in.lo->n_full_end, d_registered.p);
+      CUDA_OK(cudaEventRecord(ev_reg, aux2));
       LMPlanArgs PA;
       PA.st = st;
       for (int T = 0; T < 2; T++) { PA.cubes[T] = d_cubes[T].p; PA.touch_cnt[T] = d_touch[T].p; PA.cube_rank[T] = d_rank[T].p; }
@@ -309,8 +327,12 @@ struct LMHandle {
       int sr_ = surround();
       if (sr_ != LOAM_OK) return sr_;
     }
+    // the registered cloud was the pass's last reader of the input bank: `aux` (on which the caller
+    // releases the bank) picks it up here, long after the 5 us kernel has finished
+    CUDA_OK(cudaStreamWaitEvent(aux, ev_reg, 0));
     // no join here: the side stream's work is ordered before the next pass's K1b, and everything that
-    // needs the pass to be complete (sync_state, the pipeline's collect / join, the destructor) waits for `aux`
+    // needs the pass to be complete (sync_state, the pipeline's collect / join, the destructor) waits for
+    // `aux` and `aux2` (sync_side / join_side)
     CUDA_OK(cudaGetLastError());
     return LOAM_OK;
   }
@@ -321,8 +343,14 @@ struct LMHandle {
     LMSurroundArgs SA;
     SA.st = st; SA.S = d_S.p; SA.scap = ecap;
     for (int T = 0; T < 2; T++) { SA.cubes[T] = d_cubes[T].p; SA.arena[T] = d_arena[T][cur_arena].p; }
+    // the gather copies the cubes out of the arena on `aux` (ordered with the map updates); the voxel
+    // filter of the copy runs on `aux2`, beside the next passes
+    CUDA_OK(cudaStreamWaitEvent(aux, ev_sur_done, 0));   // the previous surround filter still reads d_S / surroundIn
     LAUNCH("lm_surround_plan", lm_surround_plan, 1, 256, 0, aux, SA);
     LAUNCH("lm_surround_gather", lm_surround_gather, 4 * 148, 256, 0, aux, SA);
+    CUDA_OK(cudaEventRecord(ev_sur_in, aux));
+    CUDA_OK(cudaStreamWaitEvent(aux2, ev_sur_in, 0));
+    cudaStream_t aux = this->aux2;   // everything below: second side stream
     CloudKeyPair cp;
     cp.njobs = 1;
     CloudKeyJob& cj = cp.j[0];
@@ -347,7 +375,25 @@ struct LMHandle {
     vj.block_heads = d_uheads.p; vj.out = d_surround.p; vj.out_base_ptr = nullptr; vj.out_count = &st->surroundN;
     vj.seg_count = nullptr; vj.seg_shift = 0; vj.nblk_cap = (ecap + VX_TILE - 1) / VX_TILE + 1;
     vp.j[1] = vj;
-    return voxel_reduce_sorted(vp, ecap, aux);
+    r = voxel_reduce_sorted(vp, ecap, aux);
+    if (r != LOAM_OK) return r;
+    CUDA_OK(cudaEventRecord(ev_sur_done, aux));
+    return LOAM_OK;
+  }
+
+  // host waits for both side streams
+  int sync_side() {
+    CUDA_OK(cudaStreamSynchronize(aux));
+    CUDA_OK(cudaStreamSynchronize(aux2));
+    return LOAM_OK;
+  }
+  // stream `s` waits for both side streams (no host sync); `ev` is a scratch event of the caller
+  int join_side(cudaStream_t s, cudaEvent_t ev) {
+    CUDA_OK(cudaEventRecord(ev, aux));
+    CUDA_OK(cudaStreamWaitEvent(s, ev, 0));
+    CUDA_OK(cudaEventRecord(ev, aux2));
+    CUDA_OK(cudaStreamWaitEvent(s, ev, 0));
+    return LOAM_OK;
   }
 
   int compact() {
@@ -366,7 +412,7 @@ struct LMHandle {
   }
 
   int sync_state() {
-    CUDA_OK(cudaStreamSynchronize(aux));   // map update, registered cloud, surround map of the last pass
+    { int sr_ = sync_side(); if (sr_ != LOAM_OK) return sr_; }   // map update, registered cloud, surround map of the last pass
     CUDA_OK(cudaMemcpyAsync(h_state.p, d_state.p, sizeof(LMState), cudaMemcpyDeviceToHost, stream));
     CUDA_OK(cudaStreamSynchronize(stream));
     last_state = *h_state.p;

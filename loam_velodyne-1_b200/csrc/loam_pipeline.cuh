@@ -35,7 +35,7 @@ __global__ void pipe_record(PipeRecord* out, const SRCounts* cnt, const ImuState
   for (int i = 0; i < 6; i++) { r.aft[i] = 0.f; r.bef[i] = 0.f; }
   r.lm_iters = 0; r.lm_rows = 0; r.lm_deg = 0; r.lm_error = 0;
   for (int T = 0; T < 2; T++) { r.mapN[T] = 0; r.stackN[T] = 0; r.bump[T] = 0; }
-  r.surroundN = 0; r.pad = 0;
+  r.surroundN = -1; r.pad = 0;   // -1: no surround map on this sweep (pipe_record_surround fills it in)
   *out = r;
 }
 // ... and its mapping part, appended on the mapping stream when the sweep was mapped
@@ -44,6 +44,10 @@ __global__ void pipe_record_lm(PipeRecord* out, const LMState* lm) {
   for (int i = 0; i < 6; i++) { out->aft[i] = lm->transformAftMapped[i]; out->bef[i] = lm->transformBefMapped[i]; }
   out->lm_iters = lm->iters; out->lm_rows = lm->rows; out->lm_deg = lm->isDegenerate; out->lm_error = lm->error;
   for (int T = 0; T < 2; T++) { out->mapN[T] = lm->mapN[T]; out->stackN[T] = lm->insN[T]; out->bump[T] = lm->bump[T]; }
+}
+// ... and the size of the surround map, on the stream that filters it
+__global__ void pipe_record_surround(PipeRecord* out, const LMState* lm) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
   out->surroundN = lm->surroundN;
 }
 
@@ -90,6 +94,7 @@ struct PipelineHandle {
     if (sr.copy_stream) cudaStreamSynchronize(sr.copy_stream);
     if (sr_stream) { cudaStreamSynchronize(sr_stream); cudaStreamDestroy(sr_stream); }
     if (lm.aux) cudaStreamSynchronize(lm.aux);
+    if (lm.aux2) cudaStreamSynchronize(lm.aux2);
     if (lm_stream) { cudaStreamSynchronize(lm_stream); cudaStreamDestroy(lm_stream); }
     if (stream) { cudaStreamSynchronize(stream); cudaStreamDestroy(stream); }
     for (int i = 0; i < 2; i++) if (ev_join[i]) cudaEventDestroy(ev_join[i]);
@@ -101,9 +106,7 @@ struct PipelineHandle {
     CUDA_OK(cudaEventRecord(ev_join[1], lm_stream));
     CUDA_OK(cudaStreamWaitEvent(stream, ev_join[0], 0));
     CUDA_OK(cudaStreamWaitEvent(stream, ev_join[1], 0));
-    CUDA_OK(cudaEventRecord(ev_join[1], lm.aux));          // the map update of the last mapped sweep
-    CUDA_OK(cudaStreamWaitEvent(stream, ev_join[1], 0));
-    return LOAM_OK;
+    return lm.join_side(stream, ev_join[1]);                 // the map update / surround map of the last mapped sweeps
   }
 
   int imu(double stamp, const double quat[4], const float acc[3]) {
@@ -115,7 +118,8 @@ struct PipelineHandle {
   // enqueue one sweep.  src_device: xyz is packed device memory and aux = {first xyz, last xyz}
   int push_async(const float* xyz, int n, int stride_bytes, double stamp, bool src_device, const float* aux, int first_idx) {
     if ((int)pending.size() >= RING) { set_error("result ring full: call collect"); return LOAM_ERR_CAPACITY; }
-    int rc = src_device ? sr.process_resident(xyz, n, aux, aux + 3, first_idx, stamp) : sr.process(xyz, n, stride_bytes, stamp);
+    int rc;
+    { HostNode hn(0); rc = src_device ? sr.process_resident(xyz, n, aux, aux + 3, first_idx, stamp) : sr.process(xyz, n, stride_bytes, stamp); }
     return after_registration(rc, stamp);
   }
   // same for a sweep that arrives as raw Velodyne VLP-16 data packets (decoded on the device, pk_decode.cuh)
@@ -132,6 +136,7 @@ struct PipelineHandle {
     if (rc == LOAM_OK) {
       pd.sr_status = LOAM_OK;
       bool pub = false;
+      long long t_lo = now_ns();
       int lrc = lo.process(sr, &pub);
       if (lrc < 0) return lrc;
       if (g_profile == 3) prof_node("laserOdometry", stream, false);
@@ -141,6 +146,8 @@ struct PipelineHandle {
       LAUNCH("pipe_record", pipe_record, 1, 32, 0, stream, h_ring.p + pd.slot, sr.d_cnt.p, sr.imu_state_dev(), lo.d_state.p);
       int rr = sr.release_bank(stream);
       if (rr < 0) return rr;
+      g_host_node_ns[1] += now_ns() - t_lo;
+      HostNode hn(2);
       if (lrc == LOAM_OK && pub) {
         int mrc = lm.process(lo, stamp);
         if (mrc < 0) return mrc;
@@ -149,6 +156,7 @@ struct PipelineHandle {
       }
       if (pd.lm_status == LOAM_OK) {
         LAUNCH("pipe_record_lm", pipe_record_lm, 1, 32, 0, lm.aux, h_ring.p + pd.slot, lm.d_state.p);   // behind the pass's map update
+        if (lm.last_surround) LAUNCH("pipe_record_surround", pipe_record_surround, 1, 32, 0, lm.aux2, h_ring.p + pd.slot, lm.d_state.p);
       }
     }
     next_slot = (next_slot + 1) % RING;
@@ -160,7 +168,7 @@ struct PipelineHandle {
   int collect(loam_sweep_result* out, int cap, int* n) {
     CUDA_OK(cudaStreamSynchronize(stream));
     CUDA_OK(cudaStreamSynchronize(lm_stream));
-    CUDA_OK(cudaStreamSynchronize(lm.aux));
+    { int sr_ = lm.sync_side(); if (sr_ != LOAM_OK) return sr_; }
     int k = 0;
     while (!pending.empty()) {
       Pending pd = pending.front();
@@ -196,7 +204,8 @@ struct PipelineHandle {
             memcpy(m.transformBefMapped, q.bef, sizeof(float) * 6);
             m.iters = q.lm_iters; m.rows = q.lm_rows; m.isDegenerate = q.lm_deg;
             m.mapN[0] = q.mapN[0]; m.mapN[1] = q.mapN[1]; m.stackN[0] = q.stackN[0]; m.stackN[1] = q.stackN[1];
-            m.bump[0] = q.bump[0]; m.bump[1] = q.bump[1]; m.registeredN = q.cnt.n_full; m.surroundN = q.surroundN;
+            m.bump[0] = q.bump[0]; m.bump[1] = q.bump[1]; m.registeredN = q.cnt.n_full;
+            if (q.surroundN >= 0) m.surroundN = q.surroundN;
             tm.on_mapping(q.aft, q.bef);
           }
         }

@@ -211,7 +211,7 @@ struct SRHandle {
       else cudaGetLastError();
     }
     if (!hr) {
-      CUDA_OK(cudaEventSynchronize(ev_copied[b]));   // previous transfer out of this staging buffer is done
+      { HostWait hw; CUDA_OK(cudaEventSynchronize(ev_copied[b])); }   // previous transfer out of this staging buffer is done
       float* st = h_raw2[b].p;
       if (sf == 3) memcpy(st, xyz, sizeof(float) * 3 * (size_t)n);
       else
