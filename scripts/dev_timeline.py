@@ -46,7 +46,7 @@ for s in streams:
     print(f"stream {s}: busy {busy:.0f} us ({100 * busy / span:.0f}%)  " + "  ".join(f"{k}={v / nsw:.1f}" for k, v in top))
 # one steady-state period (two sweeps) as text: kernels in start order with stream tag
 mid = t0 + (t1 - t0) // 2
-tag = {s: "ABCD"[i] for i, s in enumerate(streams)}
+tag = {s: "ABCDEFGH"[i] for i, s in enumerate(streams)}
 sel = sorted([e for e in ev if mid <= e[2] < mid + (3_000_000 if mode == 3 else 1_000_000) and e[3] - e[2] >= 4000], key=lambda e: e[2])
 for e in sel:
-    print(f"  {(e[2] - mid) / 1e3:8.1f} -> {(e[3] - mid) / 1e3:8.1f}  ({(e[3] - e[2]) / 1e3:6.1f} us)  " + "                    " * "ABCD".index(tag[e[1]]) + e[0])
+    print(f"  {(e[2] - mid) / 1e3:8.1f} -> {(e[3] - mid) / 1e3:8.1f}  ({(e[3] - e[2]) / 1e3:6.1f} us)  " + "                    " * "ABCDEFGH".index(tag[e[1]]) + e[0])
