@@ -520,6 +520,8 @@ def run_seq64(args, rank, world, local_rank):
     n_threads = max(1, min(args.host_threads, len(mine)))
     groups = [mine[t::n_threads] for t in range(n_threads)]
 
+    host_wait = [0.0]
+
     def run_arm(resident):
         pipes = {s: pkg.Pipeline(P, device=local_rank) for s in mine}
         if resident:
@@ -563,6 +565,7 @@ def run_seq64(args, rank, world, local_rank):
         if world > 1:
             dist.barrier()
         l0 = pkg.kernel_launch_count()
+        w0 = pkg.host_wait_ns()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         ev0.record()
@@ -572,11 +575,14 @@ def run_seq64(args, rank, world, local_rank):
         torch.cuda.synchronize()
         wall = time.perf_counter() - t0
         launches = pkg.kernel_launch_count() - l0
+        # share of the feeding threads' time spent blocked on the library's back-pressure events
+        host_wait[0] = (pkg.host_wait_ns() - w0) * 1e-9 / (n_threads * wall)
         return ev0.elapsed_time(ev1), wall, launches, results
 
     sampler = ClockSampler(local_rank)
     sampler.start()
     ms, wall, launches, res_r = run_arm(True)
+    wait_frac = host_wait[0]
     clocks = sampler.stop()
     ms_e, wall_e, _, res_e = run_arm(False)
     same = all(len(res_r[s]) == len(res_e[s]) == K and all(bytes(a.transform_mapped) == bytes(b.transform_mapped) for a, b in zip(res_r[s], res_e[s])) for s in mine)
@@ -593,7 +599,7 @@ def run_seq64(args, rank, world, local_rank):
                            "coop_ctas": int(P.coop_ctas), "parallelism": f"seq{n_seq}/gpu{world}",
                            "l2": "inputs larger than L2: %d distinct sweeps (%.0f MB) per GPU, each read once" % (len(mine) * total, len(mine) * total * 28800 * 12 / 1e6),
                            "timed_region": "one step = one sweep of every sequence through sr -> lo -> (lm every 2nd) -> tm; device-wide synchronise on both sides"},
-                "clocks": clocks, "gpu_launches": int(launches),
+                "clocks": clocks, "gpu_launches": int(launches), "host_backpressure_wait_frac": wait_frac,
                 "e2e": {"value": n_seq * K / (e2e_ms * 1e-3), "unit": "sweeps/s", "h2d_bytes_per_step": n_seq * 28800 * 12, "d2h_bytes_per_step": n_seq * ctypes_sizeof_record(pkg),
                         "api": "loam_pipeline_push_async per sweep per sequence from pinned host memory + loam_pipeline_collect", "poses_identical_to_resident_arm": bool(same)},
                 "poses_gathered": [int(table.shape[0]), int(table.shape[1])], "roofline": None, "cpu_baseline": None}
