@@ -180,7 +180,7 @@ def algorithmic_bytes(kernel, s):
 
 def measured_traffic(kernel):
     """dram bytes per launch of `kernel` from the committed `ncu --set full` capture, if any"""
-    for name in ("r01_ncu_full_summary_s8.json", "r01_ncu_full_summary.json"):   # newest capture first
+    for name in ("r01_ncu_full_summary_s10.json", "r01_ncu_full_summary_s8.json", "r01_ncu_full_summary.json"):   # newest capture first
         try:
             d = json.load(open(os.path.join(ROOT, "profiles", name)))
             return float(d[kernel]["dram_bytes_per_launch"])

@@ -149,14 +149,123 @@ __global__ void __launch_bounds__(512) sr_sort_sectors(const float* __restrict__
 
 // K-G: one CTA per ring.  Greedy selection :476-566 with the suppression flags shared by the six
 // sectors of the ring (they spill up to 5 positions across sector boundaries, App. A.1 §14).
-// The picks of a ring are strictly sequential, so the whole working set of the ring is staged in
+// The picks of a sector are strictly sequential, so the whole working set of the ring is staged in
 // shared memory first (sorted (curvature, index) pairs, picked flags, a running count of the
-// "gap" flags) and warp 0 then runs the greedy scans without touching global memory:
+// "gap" flags) and the greedy scans run without touching global memory:
 //   position j is suppressed by a pick p  <=>  |j - p| <= 5 and no gap flag lies between them
 //                                         <=>  |j - p| <= 5 and seg[j] == seg[p]   (seg = prefix count of gap flags)
 // which every lane evaluates locally for its own candidate after the pick is broadcast.
+//
+// The six sectors of a ring depend on each other only through the flags a sector raises in the first
+// five positions of the NEXT one (its "forward spill"; the backward spill lands in a sector that is
+// already finished and only shows in the final flags).  So six warps run the six sectors at once, each
+// as if nothing spilled into it, keeping their out-of-sector marks aside; warp 0 then walks the
+// sectors in order: a sector's speculative result is exactly the sequential one unless one of ITS
+// picks sits on a position the previous sector's final spill newly flags (a flagged position is only
+// ever skipped, and a position examined while unflagged is either picked or ends the scan), in which
+// case that sector alone is redone with the right flags.  Rings with a sector shorter than 11 points
+// (a spill could reach the sector after next) take the plain sequential path.
 constexpr int SEL_THREADS = 256;
 constexpr int SEL_CAP = SR_RING_CAP + 32;   // ring window: [scanStart - 5, scanEnd + 5)
+struct SelShared {
+  unsigned char picked[SEL_CAP];
+  unsigned char picked0[SEL_CAP];   // flags as staged (before any pick of this ring)
+  unsigned short seg[SEL_CAP];
+  int ind[SEL_CAP];      // sorted order, window-relative
+  float curv[SEL_CAP];   // curvature in sorted order
+  short cpick[6][20], fpick[6][4];   // picks of every sector in emission order (window-relative)
+  int nc[6], nf[6];
+  unsigned int fwd[6], bwd[6];       // out-of-sector marks: bit b of fwd = position ep+1+b, of bwd = position sp-1-b
+};
+
+// one warp: the two greedy scans of sector [sp, ep] (window-relative positions = index - w0).
+// direct: marks go straight into the flags wherever they land (sequential path); otherwise marks
+// outside [sp, ep] are collected in fwd / bwd.
+__device__ __forceinline__ void sel_sector(SelShared& S, int j, int sp, int ep, int w0, int wn, bool direct) {
+  const int lane = threadIdx.x & 31;
+  int nc = 0, nf = 0;
+  if (lane == 0) { S.fwd[j] = 0u; S.bwd[j] = 0u; }
+  __syncwarp();
+  // ---- corners: k = ep .. sp ----
+  int largest = 0;
+  bool done = false;
+  for (int base = ep; base >= sp && !done; base -= 32) {
+    const int k = base - lane;
+    const bool valid = k >= sp;
+    const int ind = valid ? S.ind[k - w0] : 0;
+    const float c = valid ? S.curv[k - w0] : 0.f;
+    const int seg = S.seg[ind];
+    bool ok = valid && (c > 0.1) && S.picked[ind] == 0;
+    const unsigned int stop = __ballot_sync(0xffffffffu, valid && !(c > 0.1));
+    while (true) {
+      const unsigned int mk = __ballot_sync(0xffffffffu, ok);
+      if (mk == 0) break;
+      const int L = __ffs(mk) - 1;
+      const int pind = __shfl_sync(0xffffffffu, ind, L);
+      const int pseg = __shfl_sync(0xffffffffu, seg, L);
+      largest++;
+      if (largest <= 20) {          // :484-493: the first two are sharp (label 2), the rest less sharp (label 1)
+        if (lane == 0) S.cpick[j][nc] = (short)pind;
+        nc++;
+      } else {
+        done = true;
+        break;
+      }
+      if (lane < 11) {   // :495-520, positions pind-5 .. pind+5
+        const int q = pind - 5 + lane;
+        if (q >= 0 && q < wn && S.seg[q] == pseg) {
+          const int qa = q + w0;
+          if (direct || (qa >= sp && qa <= ep)) S.picked[q] = 1;
+          else if (qa > ep) atomicOr(&S.fwd[j], 1u << (qa - ep - 1));
+          else atomicOr(&S.bwd[j], 1u << (sp - 1 - qa));
+        }
+      }
+      if (abs(ind - pind) <= 5 && seg == pseg) ok = false;
+      if (lane <= L) ok = false;
+    }
+    __syncwarp();
+    if (stop) done = true;  // ascending sort: everything further down has c <= 0.1
+  }
+  // ---- flat: k = sp .. ep ----
+  int smallest = 0;
+  done = false;
+  for (int base = sp; base <= ep && !done; base += 32) {
+    const int k = base + lane;
+    const bool valid = k <= ep;
+    const int ind = valid ? S.ind[k - w0] : 0;
+    const float c = valid ? S.curv[k - w0] : 0.f;
+    const int seg = S.seg[ind];
+    bool ok = valid && (c < 0.1) && S.picked[ind] == 0;
+    const unsigned int stop = __ballot_sync(0xffffffffu, valid && !(c < 0.1));
+    while (true) {
+      const unsigned int mk = __ballot_sync(0xffffffffu, ok);
+      if (mk == 0) break;
+      const int L = __ffs(mk) - 1;
+      const int pind = __shfl_sync(0xffffffffu, ind, L);
+      const int pseg = __shfl_sync(0xffffffffu, seg, L);
+      if (lane == 0) S.fpick[j][nf] = (short)pind;
+      nf++;
+      smallest++;
+      if (smallest >= 4) { done = true; break; }  // :534-536 breaks BEFORE marking
+      if (lane < 11) {
+        const int q = pind - 5 + lane;
+        if (q >= 0 && q < wn && S.seg[q] == pseg) {
+          const int qa = q + w0;
+          if (direct || (qa >= sp && qa <= ep)) S.picked[q] = 1;
+          else if (qa > ep) atomicOr(&S.fwd[j], 1u << (qa - ep - 1));
+          else atomicOr(&S.bwd[j], 1u << (sp - 1 - qa));
+        }
+      }
+      if (abs(ind - pind) <= 5 && seg == pseg) ok = false;
+      if (lane <= L) ok = false;
+    }
+    __syncwarp();
+    if (stop) done = true;
+  }
+  if (lane == 0) { S.nc[j] = nc; S.nf[j] = nf; }
+  __syncwarp();
+}
+
 __global__ void __launch_bounds__(SEL_THREADS) sr_select(const float* __restrict__ curvature, const int* __restrict__ sort_ind,
                                                          const int* __restrict__ scan_start, const int* __restrict__ scan_end,
                                                          const int* __restrict__ ring_start, const unsigned char* __restrict__ gapflag,
@@ -164,22 +273,20 @@ __global__ void __launch_bounds__(SEL_THREADS) sr_select(const float* __restrict
                                                          int* __restrict__ sharp_idx, int* __restrict__ less_sharp_idx,
                                                          int* __restrict__ flat_idx, int* __restrict__ ring_counts,
                                                          SRCounts* __restrict__ cnt) {
-  __shared__ unsigned char s_picked[SEL_CAP];
-  __shared__ unsigned short s_seg[SEL_CAP];
-  __shared__ int s_ind[SEL_CAP];      // sorted order, window-relative
-  __shared__ float s_curv[SEL_CAP];   // curvature in sorted order
+  extern __shared__ unsigned char sel_smem[];
+  SelShared& S = *reinterpret_cast<SelShared*>(sel_smem);
   __shared__ int s_wsum[SEL_THREADS / 32];
-  __shared__ int s_carry;
+  __shared__ int s_carry, s_parallel;
   const int ring = blockIdx.x;
-  const int lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nfull = cnt->n_full;
-  const int S = scan_start[ring], E = scan_end[ring];
+  const int Sx = scan_start[ring], E = scan_end[ring];
   int* my_sharp = sharp_idx + ring * SR_SHARP_PER_RING;
   int* my_less = less_sharp_idx + ring * SR_LESS_SHARP_PER_RING;
   int* my_flat = flat_idx + ring * SR_FLAT_PER_RING;
-  const int w0 = max(S - 5, 0), w1 = min(E + 5, nfull);   // window of positions this ring can touch
+  const int w0 = max(Sx - 5, 0), w1 = min(E + 5, nfull);   // window of positions this ring can touch
   const int wn = w1 - w0;
-  if (E <= S || wn <= 0 || S < 0) {   // no sector holds a point (:463-464 give ep < sp)
+  if (E <= Sx || wn <= 0 || Sx < 0) {   // no sector holds a point (:463-464 give ep < sp)
     if (threadIdx.x == 0) { ring_counts[ring * 4 + 0] = 0; ring_counts[ring * 4 + 1] = 0; ring_counts[ring * 4 + 2] = 0; }
     return;
   }
@@ -194,7 +301,9 @@ __global__ void __launch_bounds__(SEL_THREADS) sr_select(const float* __restrict
     const int k = base + threadIdx.x;
     int gf = 0;
     if (k < wn) {
-      s_picked[k] = picked[w0 + k];
+      const unsigned char f = picked[w0 + k];
+      S.picked[k] = f;
+      S.picked0[k] = f;
       gf = (k > 0 && gapflag[w0 + k]) ? 1 : 0;   // gap between w0+k-1 and w0+k
     }
     int x = gf;
@@ -206,93 +315,102 @@ __global__ void __launch_bounds__(SEL_THREADS) sr_select(const float* __restrict
     __syncthreads();
     int off = s_carry;
     for (int w = 0; w < (int)(threadIdx.x >> 5); w++) off += s_wsum[w];
-    if (k < wn) s_seg[k] = (unsigned short)(off + x);
+    if (k < wn) S.seg[k] = (unsigned short)(off + x);
     __syncthreads();
     if (threadIdx.x == SEL_THREADS - 1) s_carry = off + x;
     __syncthreads();
   }
-  for (int k = S + threadIdx.x; k < min(E, nfull); k += SEL_THREADS) {   // sectors tile [S, E-1]
+  for (int k = Sx + threadIdx.x; k < min(E, nfull); k += SEL_THREADS) {   // sectors tile [S, E-1]
     const int ind = sort_ind[k];
-    s_ind[k - w0] = ind - w0;
-    s_curv[k - w0] = curvature[ind];
+    S.ind[k - w0] = ind - w0;
+    S.curv[k - w0] = curvature[ind];
+  }
+  if (threadIdx.x == 0) {
+    int par = 1;
+    for (int j = 0; j < 6; j++) {
+      int sp, ep;
+      sector_bounds(scan_start, scan_end, ring, j, sp, ep);
+      if (sp < 0 || ep >= nfull || ep - sp + 1 < 11) par = 0;
+      S.nc[j] = 0; S.nf[j] = 0; S.fwd[j] = 0u; S.bwd[j] = 0u;
+    }
+    s_parallel = par;
   }
   __syncthreads();
-  // ---- greedy scans, warp 0 ----
-  if (threadIdx.x < 32) {
-    int n_sharp = 0, n_less = 0, n_flat = 0;
+  const bool parallel = s_parallel != 0;
+  if (parallel) {
+    // ---- six sectors at once, each blind to its neighbours' marks ----
+    if (warp < 6) {
+      int sp, ep;
+      sector_bounds(scan_start, scan_end, ring, warp, sp, ep);
+      sel_sector(S, warp, sp, ep, w0, wn, false);
+    }
+    __syncthreads();
+    // ---- warp 0: accept or redo the sectors in order ----
+    if (warp == 0) {
+      for (int j = 1; j < 6; j++) {
+        int sp, ep;
+        sector_bounds(scan_start, scan_end, ring, j, sp, ep);
+        const unsigned int in = S.fwd[j - 1];          // final forward spill of the previous sector
+        if (in == 0u) continue;
+        // positions it newly flags, and whether this sector picked one of them
+        unsigned int fresh = 0u;
+        for (int b = 0; b < 5; b++)
+          if ((in >> b & 1u) && S.picked0[sp + b - w0] == 0) fresh |= 1u << b;
+        bool hit = false;
+        if (fresh) {
+          const int nc = S.nc[j], nf = S.nf[j];
+          int pos = -1;
+          if (lane < nc) pos = S.cpick[j][lane];
+          else if (lane - 20 >= 0 && lane - 20 < nf) pos = S.fpick[j][lane - 20];
+          const int b = pos < 0 ? -1 : pos + w0 - sp;
+          hit = __any_sync(0xffffffffu, b >= 0 && b < 5 && (fresh >> b & 1u));
+        }
+        if (!hit) {
+          if (lane < 5 && (in >> lane & 1u)) S.picked[sp + lane - w0] = 1;
+          __syncwarp();
+          continue;
+        }
+        for (int q = sp - w0 + lane; q <= ep - w0; q += 32) S.picked[q] = S.picked0[q];
+        __syncwarp();
+        if (lane < 5 && (in >> lane & 1u)) S.picked[sp + lane - w0] = 1;
+        __syncwarp();
+        sel_sector(S, j, sp, ep, w0, wn, false);
+      }
+      // out-of-sector marks that no later scan needed: backward spills, and the last sector's forward one
+      if (lane < 30) {
+        const int j = lane / 5, b = lane % 5;
+        int sp, ep;
+        sector_bounds(scan_start, scan_end, ring, j, sp, ep);
+        if (S.bwd[j] >> b & 1u) { const int q = sp - 1 - b - w0; if (q >= 0 && q < wn) S.picked[q] = 1; }
+        if (j == 5 && (S.fwd[5] >> b & 1u)) { const int q = ep + 1 + b - w0; if (q >= 0 && q < wn) S.picked[q] = 1; }
+      }
+    }
+  } else if (warp == 0) {
     for (int j = 0; j < 6; j++) {
       int sp, ep;
       sector_bounds(scan_start, scan_end, ring, j, sp, ep);
       if (sp < 0 || ep >= nfull || ep < sp) continue;
-      // ---- corners: k = ep .. sp ----
-      int largest = 0;
-      bool done = false;
-      for (int base = ep; base >= sp && !done; base -= 32) {
-        const int k = base - lane;
-        const bool valid = k >= sp;
-        const int ind = valid ? s_ind[k - w0] : 0;
-        const float c = valid ? s_curv[k - w0] : 0.f;
-        const int seg = s_seg[ind];
-        bool ok = valid && (c > 0.1) && s_picked[ind] == 0;
-        const unsigned int stop = __ballot_sync(0xffffffffu, valid && !(c > 0.1));
-        while (true) {
-          const unsigned int mk = __ballot_sync(0xffffffffu, ok);
-          if (mk == 0) break;
-          const int L = __ffs(mk) - 1;
-          const int pind = __shfl_sync(0xffffffffu, ind, L);
-          const int pseg = __shfl_sync(0xffffffffu, seg, L);
-          largest++;
-          if (largest <= 2) {
-            if (lane == 0) { label[w0 + pind] = 2; my_sharp[n_sharp] = w0 + pind; my_less[n_less] = w0 + pind; }
-            n_sharp++; n_less++;
-          } else if (largest <= 20) {
-            if (lane == 0) { label[w0 + pind] = 1; my_less[n_less] = w0 + pind; }
-            n_less++;
-          } else {
-            done = true;
-            break;
-          }
-          if (lane < 11) {   // :495-520, positions pind-5 .. pind+5
-            const int q = pind - 5 + lane;
-            if (q >= 0 && q < wn && s_seg[q] == pseg) s_picked[q] = 1;
-          }
-          if (abs(ind - pind) <= 5 && seg == pseg) ok = false;
-          if (lane <= L) ok = false;
-        }
-        __syncwarp();
-        if (stop) done = true;  // ascending sort: everything further down has c <= 0.1
+      sel_sector(S, j, sp, ep, w0, wn, true);
+    }
+  }
+  __syncthreads();
+  // ---- emission in the reference's order: sector by sector, corners then flats ----
+  if (warp == 0) {
+    int n_sharp = 0, n_less = 0, n_flat = 0;
+    for (int j = 0; j < 6; j++) {
+      const int nc = S.nc[j], nf = S.nf[j];
+      if (lane < nc) {
+        const int g = w0 + S.cpick[j][lane];
+        label[g] = lane < 2 ? 2 : 1;
+        if (lane < 2) my_sharp[n_sharp + lane] = g;
+        my_less[n_less + lane] = g;
       }
-      // ---- flat: k = sp .. ep ----
-      int smallest = 0;
-      done = false;
-      for (int base = sp; base <= ep && !done; base += 32) {
-        const int k = base + lane;
-        const bool valid = k <= ep;
-        const int ind = valid ? s_ind[k - w0] : 0;
-        const float c = valid ? s_curv[k - w0] : 0.f;
-        const int seg = s_seg[ind];
-        bool ok = valid && (c < 0.1) && s_picked[ind] == 0;
-        const unsigned int stop = __ballot_sync(0xffffffffu, valid && !(c < 0.1));
-        while (true) {
-          const unsigned int mk = __ballot_sync(0xffffffffu, ok);
-          if (mk == 0) break;
-          const int L = __ffs(mk) - 1;
-          const int pind = __shfl_sync(0xffffffffu, ind, L);
-          const int pseg = __shfl_sync(0xffffffffu, seg, L);
-          if (lane == 0) { label[w0 + pind] = -1; my_flat[n_flat] = w0 + pind; }
-          n_flat++;
-          smallest++;
-          if (smallest >= 4) { done = true; break; }  // :534-536 breaks BEFORE marking
-          if (lane < 11) {
-            const int q = pind - 5 + lane;
-            if (q >= 0 && q < wn && s_seg[q] == pseg) s_picked[q] = 1;
-          }
-          if (abs(ind - pind) <= 5 && seg == pseg) ok = false;
-          if (lane <= L) ok = false;
-        }
-        __syncwarp();
-        if (stop) done = true;
+      if (lane < nf) {
+        const int g = w0 + S.fpick[j][lane];
+        label[g] = -1;
+        my_flat[n_flat + lane] = g;
       }
+      n_sharp += min(nc, 2); n_less += nc; n_flat += nf;
     }
     if (lane == 0) {
       ring_counts[ring * 4 + 0] = n_sharp;
@@ -300,9 +418,8 @@ __global__ void __launch_bounds__(SEL_THREADS) sr_select(const float* __restrict
       ring_counts[ring * 4 + 2] = n_flat;
     }
   }
-  __syncthreads();
   // cloudNeighborPicked after selection (only ever raised; windows of different rings are disjoint)
-  for (int k = threadIdx.x; k < wn; k += SEL_THREADS) if (s_picked[k]) picked[w0 + k] = 1;
+  for (int k = threadIdx.x; k < wn; k += SEL_THREADS) if (S.picked[k]) picked[w0 + k] = 1;
 }
 
 // K-H: one block per ring.  surfPointsLessFlatScan = positions k in [scanStart, scanEnd-1] with
