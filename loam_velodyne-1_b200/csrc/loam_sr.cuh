@@ -34,7 +34,8 @@ struct SRHandle {
   int raw_sel = 0;
   DevBuf<short> d_ring;
   DevBuf<float> d_ori, d_reltime, d_curv;
-  DevBuf<int> d_hist, d_ring_start, d_scan_start, d_scan_end, d_pos, d_sort_ind;
+  DevBuf<int> d_hist, d_ring_start, d_scan_start, d_scan_end, d_pos, d_sort_ind, d_ring_tot;
+  DevBuf<unsigned int> d_scan_ticket;
   DevBuf<unsigned char> d_picked, d_gap, d_steps;
   DevBuf<signed char> d_label;
   DevBuf<int> d_sharp_ring, d_less_sharp_ring, d_flat_ring, d_blockmax;
@@ -101,7 +102,7 @@ struct SRHandle {
     for (int b = 0; b < RAW_DEPTH; b++) { r |= d_raw2[b].alloc((size_t)cap * 3); r |= h_raw2[b].alloc((size_t)cap * 3); }
     r |= d_ring.alloc(cap); r |= d_ori.alloc(cap); r |= d_reltime.alloc(cap);
     r |= d_curv.alloc_zero(cap, stream); r |= d_hist.alloc((size_t)R * nblk_cap); r |= d_ring_start.alloc(R + 1);
-    r |= d_scan_start.alloc(R); r |= d_scan_end.alloc(R); r |= d_pos.alloc(cap); r |= d_sort_ind.alloc_zero(cap, stream);
+    r |= d_scan_start.alloc(R); r |= d_scan_end.alloc(R); r |= d_ring_tot.alloc_zero(SR_MAX_RINGS, stream); r |= d_scan_ticket.alloc_zero(1, stream); r |= d_pos.alloc(cap); r |= d_sort_ind.alloc_zero(cap, stream);
     r |= d_picked.alloc_zero(cap + 16, stream); r |= d_gap.alloc_zero(cap + 16, stream); r |= d_steps.alloc(cap);
     r |= d_label.alloc_zero(cap, stream);
     r |= d_sharp_ring.alloc((size_t)R * SR_SHARP_PER_RING); r |= d_less_sharp_ring.alloc((size_t)R * SR_LESS_SHARP_PER_RING);
@@ -328,7 +329,8 @@ struct SRHandle {
     init.last_valid = -1;
     if (h_cnt_init.upload(d_cnt.p, init, stream) != LOAM_OK) { set_error("counter upload failed"); return LOAM_ERR_CUDA; }
     LAUNCH("sr_ring_ori", sr_ring_ori, nblk, SR_BLK, 0, stream, d_raw_cur, n, 3, Pd, startOri, d_ring.p, d_ori.p, d_hist.p, nblk, d_cnt.p);
-    LAUNCH("sr_ring_scan", sr_ring_scan, 1, 1024, 0, stream, d_hist.p, nblk, R, d_ring_start.p, d_scan_start.p, d_scan_end.p, d_cnt.p, cap);
+    LAUNCH("sr_ring_scan", sr_ring_scan, R, RSC_THREADS, 0, stream, d_hist.p, nblk, R, d_ring_start.p, d_scan_start.p, d_scan_end.p, d_cnt.p, cap,
+           d_ring_tot.p, d_scan_ticket.p);
     LAUNCH("sr_scatter", sr_scatter, nblk, SR_BLK, 0, stream, d_raw_cur, n, 3, Pd, startOri, endOri, d_ring.p, d_ori.p, d_hist.p, d_ring_start.p, nblk,
            d_cnt.p, d_full.p, d_pos.p, d_reltime.p);
     if (has_imu && imu.pointer_last >= 0) {  // :286

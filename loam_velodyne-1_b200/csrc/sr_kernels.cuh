@@ -137,36 +137,52 @@ __global__ void __launch_bounds__(SR_BLK) sr_ring_ori(const float* __restrict__ 
 // per-block counts (exclusive, relative to the ring), the ring totals give ring_start[] and
 // cloudSize; scanStartInd/scanEndInd exactly as the loop :359-393 derives them from ring changes
 // inside [5, cloudSize-6].  sr_scatter adds ring_start[ring] to the relative offsets.
-__global__ void __launch_bounds__(1024) sr_ring_scan(int* __restrict__ hist, int nblk, int n_scans,
-                                                     int* __restrict__ ring_start, int* __restrict__ scan_start,
-                                                     int* __restrict__ scan_end, SRCounts* cnt, int max_points) {
+// One CTA per ring scans that ring's row of block counts; the last CTA to finish (ticket counter)
+// turns the ring totals into ring_start / scanStartInd / scanEndInd.
+constexpr int RSC_THREADS = 256;
+__global__ void __launch_bounds__(RSC_THREADS) sr_ring_scan(int* __restrict__ hist, int nblk, int n_scans,
+                                                            int* __restrict__ ring_start, int* __restrict__ scan_start,
+                                                            int* __restrict__ scan_end, SRCounts* cnt, int max_points,
+                                                            int* ring_tot, unsigned int* ticket) {
+  __shared__ int s_w[RSC_THREADS / 32];
+  __shared__ int s_run, s_last;
   __shared__ int s_tot[SR_MAX_RINGS];
   __shared__ int s_start[SR_MAX_RINGS + 1];
   const int lane = lane_id(), warp = threadIdx.x >> 5;
-  for (int r = warp; r < n_scans; r += 32) {
+  {
+    const int r = blockIdx.x;
     int* row = hist + (size_t)r * nblk;
-    int run = 0;
-    for (int b0 = 0; b0 < nblk; b0 += 128) {   // four independent loads per lane in flight
-      int v[4], x[4];
-#pragma unroll
-      for (int u = 0; u < 4; u++) { int i = b0 + u * 32 + lane; v[u] = i < nblk ? row[i] : 0; }
-#pragma unroll
-      for (int u = 0; u < 4; u++) {
-        x[u] = v[u];
-        for (int o = 1; o < 32; o <<= 1) {
-          int y = __shfl_up_sync(0xffffffffu, x[u], o);
-          if (lane >= o) x[u] += y;
-        }
+    if (threadIdx.x == 0) s_run = 0;
+    __syncthreads();
+    for (int b0 = 0; b0 < nblk; b0 += RSC_THREADS) {
+      const int i = b0 + threadIdx.x;
+      const int v = i < nblk ? row[i] : 0;
+      int x = v;
+      for (int o = 1; o < 32; o <<= 1) {
+        int y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
       }
-#pragma unroll
-      for (int u = 0; u < 4; u++) {
-        int i = b0 + u * 32 + lane;
-        if (i < nblk) row[i] = run + x[u] - v[u];
-        run += __shfl_sync(0xffffffffu, x[u], 31);
-      }
+      if (lane == 31) s_w[warp] = x;
+      __syncthreads();
+      int off = s_run;
+      for (int w = 0; w < warp; w++) off += s_w[w];
+      if (i < nblk) row[i] = off + x - v;
+      __syncthreads();
+      if (threadIdx.x == RSC_THREADS - 1) s_run = off + x;
+      __syncthreads();
     }
-    if (lane == 0) s_tot[r] = run;
+    if (threadIdx.x == 0) {
+      ring_tot[r] = s_run;
+      __threadfence();
+      const unsigned int t = atomicAdd(ticket, 1u);
+      s_last = (t == (unsigned int)n_scans - 1u) ? 1 : 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    if (threadIdx.x == 0) *ticket = 0u;   // re-arm for the next sweep (stream order)
+    __threadfence();
   }
+  for (int r = threadIdx.x; r < n_scans; r += RSC_THREADS) s_tot[r] = *((volatile int*)&ring_tot[r]);
   __syncthreads();
   if (warp == 0) {
     int run = 0;
@@ -185,11 +201,11 @@ __global__ void __launch_bounds__(1024) sr_ring_scan(int* __restrict__ hist, int
   }
   __syncthreads();
   const int cloudSize = s_start[n_scans];
-  for (int r = threadIdx.x; r < n_scans; r += 1024) { scan_start[r] = 0; scan_end[r] = 0; }
+  for (int r = threadIdx.x; r < n_scans; r += RSC_THREADS) { scan_start[r] = 0; scan_end[r] = 0; }
   __syncthreads();
   // every ring r > 0 that owns a position inside [5, cloudSize-6] starts a scan (:383-390) and
   // closes the scan of ring r-1 (the ring id the reference tracks is simply "previous ring + 1")
-  for (int r = threadIdx.x; r < n_scans; r += 1024) {
+  for (int r = threadIdx.x; r < n_scans; r += RSC_THREADS) {
     int f = s_start[r], c = s_start[r + 1] - f;
     if (c <= 0 || r == 0) continue;
     int lo = f > 5 ? f : 5;
