@@ -133,8 +133,7 @@ struct SRHandle {
     memset(&last_counts, 0, sizeof(last_counts));
     memset(h_imu_state.p, 0, sizeof(ImuState));
     CUDA_OK(cudaFuncSetAttribute(sr_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SelShared)));
-    CUDA_OK(cudaFuncSetAttribute(sr_lessflat, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)((sizeof(unsigned long long) + sizeof(float4)) * SR_RING_CAP)));
+    CUDA_OK(cudaFuncSetAttribute(sr_lessflat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LessFlatSmem)));
     CUDA_OK(cudaStreamSynchronize(stream));
     return LOAM_OK;
   }
@@ -348,7 +347,7 @@ struct SRHandle {
     LAUNCH("sr_sort_sectors", sr_sort_sectors, dim3(6, R), 512, 0, stream, d_curv.p, d_sort_ind.p, d_scan_start.p, d_scan_end.p, d_cnt.p);
     LAUNCH("sr_select", sr_select, R, SEL_THREADS, sizeof(SelShared), stream, d_curv.p, d_sort_ind.p, d_scan_start.p, d_scan_end.p, d_ring_start.p, d_gap.p,
            d_picked.p, d_label.p, d_sharp_ring.p, d_less_sharp_ring.p, d_flat_ring.p, d_ring_counts.p, d_cnt.p);
-    size_t smem = (sizeof(unsigned long long) + sizeof(float4)) * SR_RING_CAP;
+    size_t smem = sizeof(LessFlatSmem);
     LAUNCH("sr_lessflat", sr_lessflat, R, 1024, smem, stream, d_full.p, d_label.p, d_scan_start.p, d_scan_end.p, d_lessflat_tmp.p, d_ring_counts.p, d_cnt.p);
     LAUNCH("sr_compact", sr_compact, R, 128, 0, stream, d_full.p, d_ring_counts.p, R, d_sharp_ring.p, d_less_sharp_ring.p, d_flat_ring.p,
            d_lessflat_tmp.p, d_sharp.p, d_less_sharp.p, d_flat.p, d_less_flat.p, d_sharp_idx.p, d_less_sharp_idx.p, d_flat_idx.p, d_cnt.p, cap);

@@ -2,6 +2,7 @@
 // selection / less-flat voxel filter / compaction (scanRegistration.cpp:359-582).
 #pragma once
 #include "sr_kernels.cuh"
+#include "cta_radix.cuh"
 
 namespace loamgpu {
 
@@ -426,13 +427,18 @@ __global__ void __launch_bounds__(SEL_THREADS) sr_select(const float* __restrict
 // cloudLabel[k] <= 0 in index order (:568-572), then pcl::VoxelGrid(0.2) (:575-581, App. B.1):
 // cell = (int)(floor(p*5) - (float)min_b), idx = i + j*dx + k*dx*dy, output ascending idx,
 // centroid of all four fields = running fp32 sum in input order / (float)count.
-__global__ void __launch_bounds__(1024) sr_lessflat(const float4* __restrict__ full, const signed char* __restrict__ label,
+struct LessFlatSmem {
+  float4 pts[SR_RING_CAP];
+  unsigned int k[2][SR_RING_CAP], v[2][SR_RING_CAP];
+  CtaRadixSmem R;
+};
+__global__ void __launch_bounds__(1024, 2) sr_lessflat(const float4* __restrict__ full, const signed char* __restrict__ label,
                                                     const int* __restrict__ scan_start, const int* __restrict__ scan_end,
                                                     float4* __restrict__ out_tmp, int* __restrict__ ring_counts,
                                                     SRCounts* cnt) {
   extern __shared__ unsigned char smem_raw[];
-  unsigned long long* keys = (unsigned long long*)smem_raw;                 // SR_RING_CAP
-  float4* pts = (float4*)(smem_raw + sizeof(unsigned long long) * SR_RING_CAP);  // SR_RING_CAP
+  LessFlatSmem& LS = *reinterpret_cast<LessFlatSmem*>(smem_raw);
+  float4* pts = LS.pts;
   __shared__ int s_scan[32];
   __shared__ int s_carry, s_m, s_out;
   __shared__ unsigned int s_mn[3], s_mx[3];
@@ -444,6 +450,7 @@ __global__ void __launch_bounds__(1024) sr_lessflat(const float4* __restrict__ f
   __syncthreads();
   if (lo < 0) lo = 0;
   if (hi >= nfull) hi = nfull - 1;
+  DBG_STAMP(20);
   // ordered compaction of candidates into pts[]
   for (int base = lo; base <= hi; base += 1024) {
     int k = base + threadIdx.x;
@@ -481,6 +488,7 @@ __global__ void __launch_bounds__(1024) sr_lessflat(const float4* __restrict__ f
     __syncthreads();
   }
   int m = s_carry;
+  DBG_STAMP(21);
   if (m > SR_RING_CAP) { if (threadIdx.x == 0) atomicOr(&cnt->error, 2); m = SR_RING_CAP; }
   if (m == 0) { if (threadIdx.x == 0) ring_counts[ring * 4 + 3] = 0; return; }
   const float inv = 1.0f / 0.2f;  // inverse_leaf_size = 1/leaf in fp32
@@ -491,40 +499,35 @@ __global__ void __launch_bounds__(1024) sr_lessflat(const float4* __restrict__ f
     int maxb = (int)floorf(mx * inv);
     divb[a] = maxb - minb[a] + 1;
   }
-  int np2 = 2;
-  while (np2 < m) np2 <<= 1;
-  for (int k = threadIdx.x; k < np2; k += 1024) {
-    unsigned long long key = ~0ull;
-    if (k < m) {
-      float4 p = pts[k];
-      int i0 = (int)(floorf(p.x * inv) - (float)minb[0]);
-      int i1 = (int)(floorf(p.y * inv) - (float)minb[1]);
-      int i2 = (int)(floorf(p.z * inv) - (float)minb[2]);
-      unsigned int idx = (unsigned int)(i0 + i1 * divb[0] + i2 * divb[0] * divb[1]);
-      key = ((unsigned long long)idx << 32) | (unsigned int)k;
-    }
-    keys[k] = key;
+  for (int k = threadIdx.x; k < m; k += 1024) {
+    float4 p = pts[k];
+    int i0 = (int)(floorf(p.x * inv) - (float)minb[0]);
+    int i1 = (int)(floorf(p.y * inv) - (float)minb[1]);
+    int i2 = (int)(floorf(p.z * inv) - (float)minb[2]);
+    LS.k[0][k] = (unsigned int)(i0 + i1 * divb[0] + i2 * divb[0] * divb[1]);
+    LS.v[0][k] = (unsigned int)k;
   }
   __syncthreads();
-  for (int size = 2; size <= np2; size <<= 1) {
-    for (int stride = size >> 1; stride > 0; stride >>= 1) {
-      for (int t = threadIdx.x; t < (np2 >> 1); t += 1024) {
-        int a_ = 2 * t - (t & (stride - 1));
-        int b_ = a_ + stride;
-        bool up = ((a_ & size) == 0);
-        unsigned long long a = keys[a_], b = keys[b_];
-        if ((a > b) == up) { keys[a_] = b; keys[b_] = a; }
-      }
-      __syncthreads();
-    }
+  DBG_STAMP(22);
+  // ascending (voxel index, position): stable LSD radix sort over the bytes the largest index needs
+  // (a 66-step bitonic network on 2048 keys took 17 of this kernel's 25 us)
+  const unsigned int max_idx = (unsigned int)divb[0] * (unsigned int)divb[1] * (unsigned int)divb[2] - 1u;
+  const int passes = max_idx < (1u << 8) ? 1 : (max_idx < (1u << 16) ? 2 : (max_idx < (1u << 24) ? 3 : 4));
+  int cur = 0;
+  for (int ps = 0; ps < passes; ps++) {
+    cta_radix_pass_reg<SR_RING_CAP / 1024>(LS.k[cur], LS.v[cur], LS.k[cur ^ 1], LS.v[cur ^ 1], m, 8 * ps, LS.R);
+    cur ^= 1;
   }
+  const unsigned int* kk = LS.k[cur];
+  const unsigned int* vv = LS.v[cur];
+  DBG_STAMP(23);
   // segment heads -> ordered output slots
   if (threadIdx.x == 0) s_carry = 0;
   __syncthreads();
   for (int base = 0; base < m; base += 1024) {
     int k = base + threadIdx.x;
     int head = 0;
-    if (k < m) head = (k == 0) || ((keys[k] >> 32) != (keys[k - 1] >> 32));
+    if (k < m) head = (k == 0) || (kk[k] != kk[k - 1]);
     int x = head;
     for (int o = 1; o < 32; o <<= 1) {
       int y = __shfl_up_sync(0xffffffffu, x, o);
@@ -543,11 +546,11 @@ __global__ void __launch_bounds__(1024) sr_lessflat(const float4* __restrict__ f
     __syncthreads();
     int slot = s_carry + s_scan[threadIdx.x >> 5] + x - head;
     if (head) {
-      unsigned long long hk = keys[k] >> 32;
+      const unsigned int hk = kk[k];
       float c0 = 0.f, c1 = 0.f, c2 = 0.f, c3 = 0.f;
       int q = k;
-      while (q < m && (keys[q] >> 32) == hk) {
-        float4 p = pts[(int)(keys[q] & 0xffffffffu)];
+      while (q < m && kk[q] == hk) {
+        float4 p = pts[(int)vv[q]];
         c0 += p.x; c1 += p.y; c2 += p.z; c3 += p.w;
         q++;
       }
@@ -560,6 +563,7 @@ __global__ void __launch_bounds__(1024) sr_lessflat(const float4* __restrict__ f
     __syncthreads();
   }
   if (threadIdx.x == 0) ring_counts[ring * 4 + 3] = s_carry;
+  DBG_STAMP(24);
 }
 
 // K-I: one block per ring: offsets = exclusive scan over rings of the four per-ring counts, then
