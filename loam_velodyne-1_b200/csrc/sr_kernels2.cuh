@@ -277,7 +277,7 @@ __global__ void __launch_bounds__(SEL_THREADS) sr_select(const float* __restrict
   extern __shared__ unsigned char sel_smem[];
   SelShared& S = *reinterpret_cast<SelShared*>(sel_smem);
   __shared__ int s_wsum[SEL_THREADS / 32];
-  __shared__ int s_carry, s_parallel;
+  __shared__ int s_parallel;
   const int ring = blockIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nfull = cnt->n_full;
@@ -295,31 +295,32 @@ __global__ void __launch_bounds__(SEL_THREADS) sr_select(const float* __restrict
     if (threadIdx.x == 0) { atomicOr(&cnt->error, 2); ring_counts[ring * 4 + 0] = 0; ring_counts[ring * 4 + 1] = 0; ring_counts[ring * 4 + 2] = 0; }
     return;
   }
+  DBG_STAMP(25);
   // ---- stage: picked flags, prefix count of gap flags, sorted (index, curvature) ----
-  if (threadIdx.x == 0) s_carry = 0;
-  __syncthreads();
-  for (int base = 0; base < wn; base += SEL_THREADS) {
-    const int k = base + threadIdx.x;
-    int gf = 0;
-    if (k < wn) {
+  // every thread owns a contiguous chunk of the window: serial count of its gap flags, ONE block-wide
+  // scan of the 256 chunk totals, then the running count inside the chunk
+  {
+    const int C = (wn + SEL_THREADS - 1) / SEL_THREADS;   // <= 17
+    const int k0 = threadIdx.x * C, k1 = min(k0 + C, wn);
+    int tot = 0;
+    for (int k = k0; k < k1; k++) {
       const unsigned char f = picked[w0 + k];
       S.picked[k] = f;
       S.picked0[k] = f;
-      gf = (k > 0 && gapflag[w0 + k]) ? 1 : 0;   // gap between w0+k-1 and w0+k
+      const int gf = (k > 0 && gapflag[w0 + k]) ? 1 : 0;   // gap between w0+k-1 and w0+k
+      tot += gf;
+      S.seg[k] = (unsigned short)gf;
     }
-    int x = gf;
+    int x = tot;
     for (int o = 1; o < 32; o <<= 1) {
       int y = __shfl_up_sync(0xffffffffu, x, o);
       if (lane >= o) x += y;
     }
-    if (lane == 31) s_wsum[threadIdx.x >> 5] = x;
+    if (lane == 31) s_wsum[warp] = x;
     __syncthreads();
-    int off = s_carry;
-    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) off += s_wsum[w];
-    if (k < wn) S.seg[k] = (unsigned short)(off + x);
-    __syncthreads();
-    if (threadIdx.x == SEL_THREADS - 1) s_carry = off + x;
-    __syncthreads();
+    int run = x - tot;
+    for (int w = 0; w < warp; w++) run += s_wsum[w];
+    for (int k = k0; k < k1; k++) { run += S.seg[k]; S.seg[k] = (unsigned short)run; }
   }
   for (int k = Sx + threadIdx.x; k < min(E, nfull); k += SEL_THREADS) {   // sectors tile [S, E-1]
     const int ind = sort_ind[k];
@@ -338,6 +339,7 @@ __global__ void __launch_bounds__(SEL_THREADS) sr_select(const float* __restrict
   }
   __syncthreads();
   const bool parallel = s_parallel != 0;
+  DBG_STAMP(26);
   if (parallel) {
     // ---- six sectors at once, each blind to its neighbours' marks ----
     if (warp < 6) {
@@ -346,6 +348,7 @@ __global__ void __launch_bounds__(SEL_THREADS) sr_select(const float* __restrict
       sel_sector(S, warp, sp, ep, w0, wn, false);
     }
     __syncthreads();
+    DBG_STAMP(27);
     // ---- warp 0: accept or redo the sectors in order ----
     if (warp == 0) {
       for (int j = 1; j < 6; j++) {
@@ -395,6 +398,7 @@ __global__ void __launch_bounds__(SEL_THREADS) sr_select(const float* __restrict
     }
   }
   __syncthreads();
+  DBG_STAMP(28);
   // ---- emission in the reference's order: sector by sector, corners then flats ----
   if (warp == 0) {
     int n_sharp = 0, n_less = 0, n_flat = 0;
@@ -421,6 +425,7 @@ __global__ void __launch_bounds__(SEL_THREADS) sr_select(const float* __restrict
   }
   // cloudNeighborPicked after selection (only ever raised; windows of different rings are disjoint)
   for (int k = threadIdx.x; k < wn; k += SEL_THREADS) if (S.picked[k]) picked[w0 + k] = 1;
+  DBG_STAMP(29);
 }
 
 // K-H: one block per ring.  surfPointsLessFlatScan = positions k in [scanStart, scanEnd-1] with

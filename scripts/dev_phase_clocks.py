@@ -48,6 +48,7 @@ for k in range(nsw):
     for b in (0, 20, 60, 80, 100, 120, 130, 140):
         t0_, t1_, t2_, t3_ = dc[256 + b], dc[832 + b], dc[448 + b], dc[640 + b]
         print(f"   LO last-search CTA{b} warp0: transform={(t1_-t0_)/1.965e3:.1f} nn1={(t2_-t1_)/1.965e3:.1f} window+residual={(t3_-t2_)/1.965e3:.1f} us")
+    print(f"   sr_select ring0: stage={(dc[26]-dc[25])/1.965e3:.1f} six sectors={(dc[27]-dc[26])/1.965e3:.1f} accept/redo={(dc[28]-dc[27])/1.965e3:.1f} emit={(dc[29]-dc[28])/1.965e3:.1f} us")
     print(f"   sr_lessflat ring0: compact={(dc[21]-dc[20])/1.965e3:.1f} keys={(dc[22]-dc[21])/1.965e3:.1f} sort={(dc[23]-dc[22])/1.965e3:.1f} centroids={(dc[24]-dc[23])/1.965e3:.1f} us")
     print("   LO it0 per-CTA feature phase us: " + " ".join(f"{v:.0f}" for v in ft))
     for which, tag in ((0, "LO"), (1, "LM")):
