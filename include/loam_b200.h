@@ -246,6 +246,22 @@ int loam_debug_voxel_filter(const float* xyzi, int n, float leaf, float* out, in
 /* same filter through the one-kernel cooperative path laserMapping uses for the incoming sweep */
 int loam_debug_voxel_filter_coop(const float* xyzi, int n, float leaf, float* out, int cap_out, int* n_out);
 
+/* allocation-free variant of the whole-cloud voxel filter.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same kernel and same bits as
+ * loam_debug_voxel_filter_coop (pcl::VoxelGrid semantics), but the inputs and outputs
+ * are DEVICE pointers owned by the caller (d_xyzi: n points x,y,z,intensity; d_out: room for
+ * cap_out >= n points; *d_n_out: number of output points, a device int) and all scratch lives in one
+ * static __device__ array inside the library (about 4.3 MB, held by every GPU that loads the library
+ * until exit), so the call performs no cudaMalloc / cudaFree / allocating library routine.  It only
+ * enqueues on `stream` (a cudaStream_t, NULL = the default stream) of the CURRENT device.
+ * n > LOAM_NOALLOC_MAX_POINTS returns LOAM_ERR_CAPACITY with a message in loam_last_error().
+ * All calls share the scratch array: calls that overlap on the GPU (different streams or host
+ * threads) race -- serialise them. */
+#define LOAM_NOALLOC_MAX_POINTS 131072
+int loam_voxel_filter_noalloc(const float* d_xyzi, int n, float leaf, float* d_out, int cap_out, int* d_n_out,
+                              void* stream);
+
 /* phase clocks (SM cycles, clock64 of CTA 0) of the persistent LM kernels: which 0 = laserOdometry,
  * 1 = laserMapping; slot 0 = number of stamps that follow */
 int loam_debug_phase_enable(int on);

@@ -276,3 +276,88 @@ int loam_sr_imu_trans(loam_sr* h, float out12[12]) {
 #include "loam_capi_rest.inc"
 
 }  // extern "C"
+
+// ---------------- allocation-free voxel filter (no counterpart in the reference) ----------------
+// pcl::VoxelGrid(leaf) of one device-resident cloud through the same one-cluster kernel as
+// loam_debug_voxel_filter_coop (vx_coop.cuh), for callers that cannot call cudaMalloc (CUDA graph
+// capture, serving loops, harnesses that forbid it).  All scratch the kernel needs -- ping-pong
+// keys / payloads, per-tile digit histograms, segment heads, the sorted copy of the points, the
+// bounding box and three scalars -- lives in ONE file-scope __device__ array of fixed size; every
+// GPU that loads the library holds it until the process exits.  In host code `g_na_scratch` is only
+// a host-side stand-in for the symbol, never a device address: the address is fetched once per
+// device with cudaGetSymbolAddress and that pointer is what the kernels receive.
+// Every call shares the array and it keeps the previous call's contents: na_setup re-arms what must
+// start from a known value (point count, bounding box, overflow flag, output count); everything
+// else is fully rewritten by the kernel before it is read.  Calls that overlap on the GPU (two
+// streams, two host threads) race on the array -- serialise them.
+#define NA_MAX_POINTS LOAM_NOALLOC_MAX_POINTS
+constexpr size_t NA_TILE_CAP = (NA_MAX_POINTS + loamgpu::VC_TILE - 1) / loamgpu::VC_TILE + 1;
+constexpr size_t na_align(size_t x) { return (x + 255) & ~(size_t)255; }
+constexpr size_t NA_OFF_K0 = 0;
+constexpr size_t NA_OFF_K1 = NA_OFF_K0 + na_align(sizeof(unsigned int) * NA_MAX_POINTS);
+constexpr size_t NA_OFF_V0 = NA_OFF_K1 + na_align(sizeof(unsigned int) * NA_MAX_POINTS);
+constexpr size_t NA_OFF_V1 = NA_OFF_V0 + na_align(sizeof(unsigned int) * NA_MAX_POINTS);
+constexpr size_t NA_OFF_SORTED = NA_OFF_V1 + na_align(sizeof(unsigned int) * NA_MAX_POINTS);
+constexpr size_t NA_OFF_HIST = NA_OFF_SORTED + na_align(sizeof(float4) * NA_MAX_POINTS);
+constexpr size_t NA_OFF_HEADS = NA_OFF_HIST + na_align(sizeof(int) * 256 * NA_TILE_CAP);
+constexpr size_t NA_OFF_BBOX = NA_OFF_HEADS + na_align(sizeof(int) * NA_TILE_CAP);
+constexpr size_t NA_OFF_SCAL = NA_OFF_BBOX + 256;   // int n, overflow, out_count
+constexpr size_t NA_SCRATCH_BYTES = NA_OFF_SCAL + 256;
+static __device__ __align__(256) unsigned char g_na_scratch[NA_SCRATCH_BYTES];
+
+// device code may name the array directly; only host code needs the fetched address
+__global__ void na_setup(int n, int* out_count) {
+  unsigned int* bbox = (unsigned int*)(g_na_scratch + NA_OFF_BBOX);
+  int* scal = (int*)(g_na_scratch + NA_OFF_SCAL);
+  if (threadIdx.x < 6) bbox[threadIdx.x] = threadIdx.x < 3 ? 0xffffffffu : 0u;
+  if (threadIdx.x == 6) { scal[0] = n; scal[1] = 0; scal[2] = 0; *out_count = 0; }
+}
+
+constexpr int NA_MAX_DEVICES = 64;
+static unsigned char* g_na_ptr[NA_MAX_DEVICES];   // device address of g_na_scratch, per device
+static std::mutex g_na_mu;
+
+extern "C" int loam_voxel_filter_noalloc(const float* d_xyzi, int n, float leaf, float* d_out, int cap_out, int* d_n_out, void* stream) {
+  if (!d_xyzi || !d_out || !d_n_out || n < 0 || !(leaf > 0.f)) { set_error("loam_voxel_filter_noalloc: bad argument"); return LOAM_ERR_ARG; }
+  if (n > NA_MAX_POINTS) {
+    set_error("loam_voxel_filter_noalloc: %d points exceed the static scratch limit LOAM_NOALLOC_MAX_POINTS = %d", n, (int)NA_MAX_POINTS);
+    return LOAM_ERR_CAPACITY;
+  }
+  if (cap_out < n) {   // every point can be its own voxel; the kernel does not clip its output
+    set_error("loam_voxel_filter_noalloc: cap_out (%d) must be at least n (%d)", cap_out, n);
+    return LOAM_ERR_ARG;
+  }
+  int dev = -1;
+  CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= NA_MAX_DEVICES) { set_error("loam_voxel_filter_noalloc: device ordinal %d out of range", dev); return LOAM_ERR_ARG; }
+  unsigned char* base = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_na_mu);
+    if (!g_na_ptr[dev]) {   // set-up, once per device, with that device current
+      cudaDeviceProp prop;
+      CUDA_OK(cudaGetDeviceProperties(&prop, dev));
+      if (prop.major < 10) { set_error("loam_voxel_filter_noalloc: device %d is sm_%d%d, sm_100 needed (no CPU fallback)", dev, prop.major, prop.minor); return LOAM_ERR_CUDA; }
+      unsigned char* p = nullptr;
+      CUDA_OK(cudaGetSymbolAddress((void**)&p, g_na_scratch));
+      CUDA_OK(cudaFuncSetAttribute(vx_filter_coop, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      g_na_ptr[dev] = p;
+    }
+    base = g_na_ptr[dev];
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  int* scal = (int*)(base + NA_OFF_SCAL);
+  VxCoopArgs VA;
+  VxCoopJob& j = VA.j[0];
+  j.pts = (const float4*)d_xyzi; j.n_ptr = scal; j.bbox = (unsigned int*)(base + NA_OFF_BBOX);
+  j.keys[0] = (unsigned int*)(base + NA_OFF_K0); j.keys[1] = (unsigned int*)(base + NA_OFF_K1);
+  j.vals[0] = (unsigned int*)(base + NA_OFF_V0); j.vals[1] = (unsigned int*)(base + NA_OFF_V1);
+  j.hist = (int*)(base + NA_OFF_HIST); j.heads = (int*)(base + NA_OFF_HEADS); j.sorted = (float4*)(base + NA_OFF_SORTED);
+  j.out = (float4*)d_out; j.out_count = d_n_out; j.overflow = scal + 1; j.leaf = leaf; j.tile_cap = (int)NA_TILE_CAP;
+  VA.j[1] = j;
+  na_setup<<<1, 32, 0, s>>>(n, d_n_out);
+  g_launches++;
+  vx_filter_coop<<<dim3(VC_CLUSTER, 1), VC_THREADS, 0, s>>>(VA);
+  g_launches++;
+  CUDA_OK(cudaGetLastError());
+  return LOAM_OK;
+}
