@@ -234,18 +234,7 @@ loam_sr* loam_pipeline_sr(loam_pipeline* h);
 loam_lo* loam_pipeline_lo(loam_pipeline* h);
 loam_lm* loam_pipeline_lm(loam_pipeline* h);
 
-/* ---- test hooks: device versions of the building blocks, host pointers in and out ---- */
-/* fn: 0 sin 1 cos 2 atan 3 atan2(y,x) 4 asin 5 sqrt 6 x/y 7 x*y+x (unfused) -- loam/detmath.h on the device */
-int loam_debug_math(int fn, const float* x, const float* y, float* out, int n);
-/* op 0: QR solve (m x n, one rhs) 1: Jacobi eigen (values then row vectors) 2: LU inverse; `batch` systems */
-int loam_debug_linalg(int op, const float* A, const float* b, float* out, int m, int n, int batch);
-/* the device packet decoder alone: xyz receives n_packets * 384 points (3 floats each, NaN = no return) */
-int loam_debug_decode_packets(const unsigned char* packets, int n_packets, float* xyz);
-int loam_debug_sort_pairs(unsigned int* keys, unsigned int* vals, int n);
-int loam_debug_voxel_filter(const float* xyzi, int n, float leaf, float* out, int cap_out, int* n_out);
-/* same filter through the one-kernel cooperative path laserMapping uses for the incoming sweep */
-int loam_debug_voxel_filter_coop(const float* xyzi, int n, float leaf, float* out, int cap_out, int* n_out);
-
+/* ---- allocation-free entry point ---- */
 /* allocation-free variant of the whole-cloud voxel filter.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code under CUDA graph
  * capture, tight serving loops, harnesses that forbid it).  Same kernel and same bits as
@@ -262,29 +251,10 @@ int loam_debug_voxel_filter_coop(const float* xyzi, int n, float leaf, float* ou
 int loam_voxel_filter_noalloc(const float* d_xyzi, int n, float leaf, float* d_out, int cap_out, int* d_n_out,
                               void* stream);
 
-/* phase clocks (SM cycles, clock64 of CTA 0) of the persistent LM kernels: which 0 = laserOdometry,
- * 1 = laserMapping; slot 0 = number of stamps that follow */
-int loam_debug_phase_enable(int on);
-int loam_debug_phase_clocks(int which, long long* out, int n);
-
-/* map-update statistics of the last mapped sweep, 2 x 8 ints (corner, surf): merge cubes, general-path
- * cubes, append-only cubes, max old points, max new points, points written, -, cubes gone dirty */
-int loam_debug_lm_counters(loam_lm* h, int* out, int n);
-
-/* timeline of the pipeline's streams: while enabled, every launch is bracketed by one-thread
- * kernels that write %globaltimer on the launch's stream (nothing is synchronised);
- * on = 3 stamps only the begin and end of every node pass (light enough not to disturb the
- * overlap).  loam_debug_trace_dump writes "kernel,stream,start_ns,end_ns" rows and returns their number */
-int loam_debug_trace_enable(int on);
-int loam_debug_trace_dump(const char* path);
+/* test / development hooks (loam_debug_*): include/loam_b200_debug.h */
 
 /* number of kernel launches issued by this library on the calling process so far */
 long long loam_kernel_launch_count(void);
-/* nanoseconds the calling host threads spent blocked on the library's back-pressure events (staging
- * buffers, parameter slots) since the library was loaded: enqueue time minus this = launch cost */
-long long loam_debug_host_wait_ns(void);
-/* host nanoseconds the pipeline entry points spent enqueueing each node (sr, lo + record, lm) */
-void loam_debug_host_node_ns(long long out[3]);
 /* per-kernel device time accumulated since the last reset (CUDA events; 0 when profiling is off) */
 int loam_profile_enable(int on);
 int loam_profile_report(char* buf, int cap);

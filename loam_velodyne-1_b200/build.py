@@ -18,7 +18,7 @@ def _newer(target, sources):
 def build_cuda(force=False, verbose=False):
     csrc = os.path.join(HERE, "csrc")
     srcs = [os.path.join(csrc, f) for f in os.listdir(csrc)] + [
-        os.path.join(ROOT, "include", "loam_b200.h"), os.path.join(ROOT, "include", "loam", "detmath.h")]
+        os.path.join(ROOT, "include", "loam_b200.h"), os.path.join(ROOT, "include", "loam_b200_debug.h"), os.path.join(ROOT, "include", "loam", "detmath.h")]
     if not force and not _newer(LIB, srcs):
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
@@ -27,6 +27,8 @@ def build_cuda(force=False, verbose=False):
            "-Xcompiler", "-fPIC,-ffp-contract=off,-O2", "-shared",
            "-I", os.path.join(ROOT, "include"), "-I", csrc,
            os.path.join(csrc, "loam_b200.cu"), "-o", LIB, "-lcudart_static", "-lpthread", "-ldl", "-lrt"]
+    if os.environ.get("LOAM_PHASE_CLOCKS"):   # dev builds only: clock64 stamps inside the persistent LM kernels
+        cmd.insert(1, "-DLOAM_PHASE_CLOCKS")
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")

@@ -11,6 +11,7 @@
 #include <atomic>
 #include <vector>
 #include "loam_b200.h"
+#include "loam_b200_debug.h"
 #include "loam/detmath.h"
 
 #ifndef M_PI
@@ -162,12 +163,20 @@ __device__ __forceinline__ unsigned int warp_match8(int d, bool in) {
 
 // phase clocks of the two persistent kernels (test hook, loam_debug_phase_clocks): when enabled,
 // thread 0 of CTA 0 stamps clock64() at the phase boundaries of every LM iteration
+// Compiled in only with -DLOAM_PHASE_CLOCKS (LOAM_PHASE_CLOCKS=1 python loam_velodyne-1_b200/build.py --force,
+// scripts/dev_phase_clocks.py): in the default build PHASE_ON is the constant 0 and every stamp, the flag load
+// in the per-feature loops included, is removed by the compiler.
 constexpr int PHASE_CLK_N = 512;
+#ifdef LOAM_PHASE_CLOCKS
 __device__ int g_phase_on = 0;
+#define PHASE_ON (g_phase_on)
+#else
+#define PHASE_ON 0
+#endif
 __device__ long long g_phase_clk[2][PHASE_CLK_N];
 __device__ long long g_rf_clk[2 * 250 * 8];   // lm_refilter_cube: 8 stamps per (type, rank)
 __device__ long long g_dbg_clk[1024];           // ad-hoc stamps of single-CTA kernels (dev only)
-#define DBG_STAMP(slot) do { if (g_phase_on && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_dbg_clk[slot] = clock64(); } while (0)
+#define DBG_STAMP(slot) do { if (PHASE_ON && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_dbg_clk[slot] = clock64(); } while (0)
 __device__ __forceinline__ void phase_stamp(int which, int& slot) {
   if (slot >= 0 && slot < PHASE_CLK_N) g_phase_clk[which][slot++] = clock64();
 }

@@ -3,6 +3,7 @@
 #pragma once
 #include "sort_voxel.cuh"
 #include "linalg.cuh"
+#include "lo_kernels2.cuh"
 
 namespace loamgpu {
 
@@ -55,6 +56,27 @@ __global__ void dbg_linalg_kernel(int op, const float* A, const float* b, float*
     for (int i = 0; i < n; i++) o[i] = w[i];
     for (int i = 0; i < n * n; i++) o[n + i] = v[i];
   }
+}
+
+// lm_solve_step (lo_kernels2.cuh) on `batch` given normal equations, one thread each.  mode 0 = as the
+// LM kernels run it (fp64 LDL^T pre-test that may skip the Jacobi eigen-decomposition), mode 1 = the
+// eigen-decomposition always (the reference's unconditional cv::eigen, laserOdometry.cpp:770-791)
+__global__ void dbg_solve_step_kernel(const float* AtA, const float* AtB, int batch, float thr, int mode, int* deg, float* matP, float* X) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= batch) return;
+  double tot[28];
+  int k = 0;
+  for (int i = 0; i < 6; i++)
+    for (int j = i; j < 6; j++) tot[k++] = (double)AtA[(size_t)t * 36 + i * 6 + j];
+  for (int i = 0; i < 6; i++) tot[21 + i] = (double)AtB[(size_t)t * 6 + i];
+  tot[27] = 0.0;
+  int d = 0;
+  float P[36], x[6];
+  if (mode == 0) lm_solve_step<false>(tot, true, thr, &d, P, x);
+  else lm_solve_step<true>(tot, true, thr, &d, P, x);
+  deg[t] = d;
+  for (int i = 0; i < 36; i++) matP[(size_t)t * 36 + i] = P[i];
+  for (int i = 0; i < 6; i++) X[(size_t)t * 6 + i] = x[i];
 }
 
 }  // namespace loamgpu

@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(LM_THREADS, 2) lm_optimize(LMOptArgs A) {
   __shared__ unsigned char s_found[LM_CH];
   const int lane = lane_id(), warp = threadIdx.x >> 5;
   LMState* st = A.st;
-  int clk = (blockIdx.x == 0 && threadIdx.x == 0 && g_phase_on) ? 1 : -1;
+  int clk = (blockIdx.x == 0 && threadIdx.x == 0 && PHASE_ON) ? 1 : -1;
 #define PS() do { if (clk >= 0) phase_stamp(1, clk); } while (0)
   PS();
   if (threadIdx.x == 0) {

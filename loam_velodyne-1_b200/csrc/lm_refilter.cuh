@@ -410,7 +410,7 @@ __device__ __forceinline__ void rf_cube(const LMCubeArgs& A, const int T, const 
   const int cenW = st->cenW, cenH = st->cenH, cenD = st->cenD;
   if (threadIdx.x == 0) s_dirty = 0;
   __syncthreads();
-  long long* clk = (threadIdx.x == 0 && srank == 0 && g_phase_on) ? g_rf_clk + ((size_t)T * PROC_MAX + r) * 8 : nullptr;
+  long long* clk = (threadIdx.x == 0 && srank == 0 && PHASE_ON) ? g_rf_clk + ((size_t)T * PROC_MAX + r) * 8 : nullptr;
 #define RS(k) do { if (clk) clk[k] = clock64(); } while (0)
   if (clk) { for (int k = 0; k < 8; k++) clk[k] = 0; clk[7] = ((long long)n_old << 32) | (unsigned int)n_new; }
   RS(0);

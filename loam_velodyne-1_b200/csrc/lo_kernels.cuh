@@ -179,7 +179,7 @@ __device__ void lo_corner_search(const LOArgs& A, const int* roff, int R, const 
   const int lane = lane_id();
   int bi; float bd;
   grid_nn1_warp(A.corner_grid, sel.x, sel.y, sel.z, 25.f, bi, bd);
-  if (g_phase_on && threadIdx.x == 0) g_dbg_clk[448 + blockIdx.x] = clock64();
+  if (PHASE_ON && threadIdx.x == 0) g_dbg_clk[448 + blockIdx.x] = clock64();
   int closestPointInd = -1, minPointInd2 = -1;
   if (bi >= 0 && bd < 25) {
     closestPointInd = bi;
@@ -232,7 +232,7 @@ __device__ void lo_surf_search(const LOArgs& A, const int* roff, int R, const fl
   const int lane = lane_id();
   int bi; float bd;
   grid_nn1_warp(A.surf_grid, sel.x, sel.y, sel.z, 25.f, bi, bd);
-  if (g_phase_on && threadIdx.x == 0) g_dbg_clk[448 + blockIdx.x] = clock64();
+  if (PHASE_ON && threadIdx.x == 0) g_dbg_clk[448 + blockIdx.x] = clock64();
   int closestPointInd = -1, minPointInd2 = -1, minPointInd3 = -1;
   if (bi >= 0 && bd < 25) {
     closestPointInd = bi;

@@ -7,6 +7,7 @@ namespace loamgpu {
 // Solve step shared by odometry and mapping: normal equations from the reduced sums, QR solve,
 // (iteration 0) eigen-degeneracy analysis, projection.  laserOdometry.cpp:765-797 /
 // laserMapping.cpp:922-954.  tot[0..20] upper triangle of AtA, tot[21..26] AtB.
+template <bool ALWAYS_EIGEN = false>
 __device__ __forceinline__ void lm_solve_step(const double* tot, bool first_iter, float eig_thresh, int* isDegenerate, float* matP, float* X) {
   float AtA[36], A2[36], b2[6];
   {
@@ -35,7 +36,7 @@ __device__ __forceinline__ void lm_solve_step(const double* tot, bool first_iter
     double trace = 0.0;
 #pragma unroll
     for (int i = 0; i < 6; i++) trace += (double)AtA[i * 6 + i];
-    if (la::spd6_above(AtA, (double)eig_thresh + 1.0e-4 * trace)) {
+    if (!ALWAYS_EIGEN && la::spd6_above(AtA, (double)eig_thresh + 1.0e-4 * trace)) {
       *isDegenerate = 0;
       for (int i = 0; i < 36; i++) matP[i] = (i % 7 == 0) ? 1.f : 0.f;
     } else {
@@ -194,7 +195,7 @@ __global__ void __launch_bounds__(LO_THREADS, 2) lo_optimize(LOArgs A) {
   __shared__ int s_triok[LO_WARPS];
   const int lane = lane_id(), warp = threadIdx.x >> 5;
   LOState* st = A.st;
-  int clk = (blockIdx.x == 0 && threadIdx.x == 0 && g_phase_on) ? 1 : -1;
+  int clk = (blockIdx.x == 0 && threadIdx.x == 0 && PHASE_ON) ? 1 : -1;
 #define PS() do { if (clk >= 0) phase_stamp(0, clk); } while (0)
   PS();
   const int R = A.n_scans;
@@ -216,6 +217,10 @@ __global__ void __launch_bounds__(LO_THREADS, 2) lo_optimize(LOArgs A) {
   __syncthreads();
   const int n_sharp = A.cnt->n_sharp, n_flat = A.cnt->n_flat;
   const int F = n_sharp + n_flat;
+  if (F > A.fcap) {   // cannot happen through the C ABI (set_features / sr_select bound the clouds); never index past the row slabs
+    if (blockIdx.x == 0 && threadIdx.x == 0) { st->iters = 0; st->rows = 0; }
+    return;
+  }
   const int n_corner_last = st->n_corner_last, n_surf_last = st->n_surf_last;
   // every CTA owns a contiguous slice of the features (the critical path is the single most
   // expensive feature, so spreading features over CTAs does not help)
@@ -234,7 +239,7 @@ __global__ void __launch_bounds__(LO_THREADS, 2) lo_optimize(LOArgs A) {
       __syncthreads();
       double acc = 0.0;
       long long dbg_t0 = 0;
-      if (iterCount == 0 && g_phase_on && threadIdx.x == 0) dbg_t0 = clock64();
+      if (iterCount == 0 && PHASE_ON && threadIdx.x == 0) dbg_t0 = clock64();
       for (int j0 = 0; j0 < nmine; j0 += LO_WARPS) {
         const int f = f_lo + j0 + warp;
         const bool first_pass = (j0 == 0);
@@ -243,9 +248,9 @@ __global__ void __launch_bounds__(LO_THREADS, 2) lo_optimize(LOArgs A) {
           // ---- transform, (search), residual -> row slab of this iteration ----
           const bool is_corner = f < n_sharp;
           const float4 pt = is_corner ? A.sharp[f] : A.flat[f - n_sharp];
-          if (refresh && g_phase_on && threadIdx.x == 0) g_dbg_clk[256 + blockIdx.x] = clock64();
+          if (refresh && PHASE_ON && threadIdx.x == 0) g_dbg_clk[256 + blockIdx.x] = clock64();
           const float4 sel = lo_transform_to_start(pt, s_tr);
-          if (refresh && g_phase_on && threadIdx.x == 0) g_dbg_clk[832 + blockIdx.x] = clock64();
+          if (refresh && PHASE_ON && threadIdx.x == 0) g_dbg_clk[832 + blockIdx.x] = clock64();
           bool valid = false;
           float4 coeff = make_float4(0, 0, 0, 0);
           if (is_corner) {
@@ -289,7 +294,7 @@ __global__ void __launch_bounds__(LO_THREADS, 2) lo_optimize(LOArgs A) {
               if (ok) valid = lo_surf_residual(sel, t1, t2, t3, iterCount, coeff);
             }
           }
-          if (refresh && g_phase_on && threadIdx.x == 0) g_dbg_clk[640 + blockIdx.x] = clock64();
+          if (refresh && PHASE_ON && threadIdx.x == 0) g_dbg_clk[640 + blockIdx.x] = clock64();
           if (lane == 0) {
             A.coeff[(size_t)iterCount * A.fcap + f] = coeff;
             A.row_valid[(size_t)iterCount * A.fcap + f] = valid ? 1 : 0;
@@ -312,7 +317,7 @@ __global__ void __launch_bounds__(LO_THREADS, 2) lo_optimize(LOArgs A) {
         }
         __syncthreads();
         if (first_pass) PS();  // 0: features + rows of the first pass done
-        if (first_pass && iterCount == 0 && g_phase_on && threadIdx.x == 0) g_dbg_clk[64 + blockIdx.x] = clock64() - dbg_t0;
+        if (first_pass && iterCount == 0 && PHASE_ON && threadIdx.x == 0) g_dbg_clk[64 + blockIdx.x] = clock64() - dbg_t0;
         red_rows_warped(s_row, LO_WARPS, iterCount + 1, acc);
         __syncthreads();
       }

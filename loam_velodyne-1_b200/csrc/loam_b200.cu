@@ -104,8 +104,14 @@ using namespace loamgpu;
 
 // test hook: phase clocks of lo_optimize (which = 0) / lm_optimize (1); see common.cuh
 extern "C" int loam_debug_phase_enable(int on) {
+#ifdef LOAM_PHASE_CLOCKS
   CUDA_OK(cudaMemcpyToSymbol(g_phase_on, &on, sizeof(int)));
   return LOAM_OK;
+#else
+  (void)on;
+  set_error("phase clocks are compiled out of this build (rebuild with -DLOAM_PHASE_CLOCKS)");
+  return LOAM_ERR_ARG;
+#endif
 }
 extern "C" int loam_debug_phase_clocks(int which, long long* out, int n) {
   if (which == 3) {

@@ -372,6 +372,15 @@ struct SRHandle {
       if (counts[c] < 0 || (counts[c] > 0 && !clouds[c])) { set_error("bad feature cloud %d", c); return LOAM_ERR_ARG; }
       if (counts[c] > cap) { set_error("feature cloud %d of %d points exceeds max_points=%d", c, counts[c], cap); return LOAM_ERR_CAPACITY; }
     }
+    {  // the sharp / less-sharp / flat banks hold what scanRegistration can emit: 12 / 120 / 24 points per ring
+      const int lim[5] = {cap, R * SR_SHARP_PER_RING, R * SR_LESS_SHARP_PER_RING, R * SR_FLAT_PER_RING, cap};
+      const char* nm[5] = {"full", "sharp", "less-sharp", "flat", "less-flat"};
+      for (int c = 1; c < 4; c++)
+        if (counts[c] > lim[c]) {
+          set_error("%s feature cloud of %d points exceeds the bank of %d points (%d rings x %d per ring)", nm[c], counts[c], lim[c], R, lim[c] / R);
+          return LOAM_ERR_CAPACITY;
+        }
+    }
     std::vector<int> rc((size_t)R * 4, 0);
     const int col_of[5] = {-1, 0, 1, 2, 3};   // full, sharp, less sharp, flat, less flat
     for (int c = 1; c < 5; c++) {

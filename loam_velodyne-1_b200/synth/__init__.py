@@ -47,11 +47,14 @@ def _load():
 
 
 class Synth:
-    def __init__(self, preset, seed=None, threads=None):
+    def __init__(self, preset, seed=None, threads=None, scene=0):
+        """scene 0 = the BASELINE.json scene of the preset; preset 1 also has the branch-coverage scenes
+        1 "tunnel", 2 "plain", 3 "sparse" (synth.cpp build())"""
         self.L = _load()
         self.preset = preset
+        self.scene = scene
         self.seed = DEFAULT_SEED[preset] if seed is None else seed
-        self.h = self.L.synth_create(preset, self.seed)
+        self.h = self.L.synth_create(preset + 16 * scene, self.seed)
         self.rings = self.L.synth_rings(self.h)
         self.az = self.L.synth_azimuth_steps(self.h)
         self.has_imu = bool(self.L.synth_has_imu(self.h))

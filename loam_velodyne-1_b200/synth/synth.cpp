@@ -58,7 +58,8 @@ struct Sensor {
 };
 
 struct Config {
-  int preset;
+  int preset;   // sensor + trajectory: 1 VLP-16, 2 HDL-64E, 4 128 rings + IMU
+  int scene_id = 0;  // 0 = the BASELINE.json scene of the preset; 1.. = branch-coverage scenes (VLP-16 only), see build()
   uint64_t seed;
   Sensor sensor;
   Scene scene;
@@ -173,7 +174,49 @@ void add_box(Scene& s, double x0, double x1, double y0, double y1, double z0, do
 void build(Config& c) {
   Sensor& s = c.sensor;
   Scene& sc = c.scene;
-  if (c.preset == 1) {  // VLP-16 in a closed corridor (BASELINE config 1)
+  if (c.preset == 1 && c.scene_id != 0) {
+    // Scenes that drive the reference into its guard branches (laserOdometry.cpp:697-700, :770-811,
+    // laserMapping.cpp:886-889, :927-954), which the BASELINE scenes never take:
+    //  1 "tunnel": smooth open-ended tube, nothing along the axis within range -> translation along x
+    //     is unobservable -> isDegenerate in laserOdometry and laserMapping
+    //  2 "ribbed tunnel": the tube with longitudinal ribs -> large corner clouds, x still unobservable
+    //  3 "sparse": ground plane seen by the three lowest rings only + groups of thin poles -> a handful of
+    //     features: fewer than 10 / 50 selected rows, corner clouds of <= 10 points
+    s.rings = 16; s.az = 1800; s.noise_sigma = 0.01;
+    const double e[16] = {-15, 1, -13, 3, -11, 5, -9, 7, -7, 9, -5, 11, -3, 13, -1, 15};
+    s.elev_deg.assign(e, e + 16);
+    if (c.scene_id == 1) {
+      sc.has_room = true;
+      sc.room.lo[0] = -5000; sc.room.hi[0] = 5000; sc.room.lo[1] = -2; sc.room.hi[1] = 2;
+      sc.room.lo[2] = -1.2; sc.room.hi[2] = 1.8;
+      sc.max_range = 60.0;
+    } else if (c.scene_id == 2) {
+      // the same tube with longitudinal ribs (hand rail, cable tray, kerb, ceiling rail): plenty of true
+      // edges, every one parallel to the axis, so x stays unobservable while the corner clouds are large
+      sc.has_room = true;
+      sc.room.lo[0] = -5000; sc.room.hi[0] = 5000; sc.room.lo[1] = -2; sc.room.hi[1] = 2;
+      sc.room.lo[2] = -1.2; sc.room.hi[2] = 1.8;
+      sc.max_range = 60.0;
+      sc.binw = 500.0;
+      add_box(sc, -5000, 5000, 1.8, 2.0, 0.2, 0.4);
+      add_box(sc, -5000, 5000, -2.0, -1.75, -0.6, -0.35);
+      add_box(sc, -5000, 5000, -0.3, 0.3, 1.6, 1.8);
+      add_box(sc, -5000, 5000, 1.2, 1.5, -1.2, -1.0);
+      s.noise_sigma = 0.005;
+    } else {
+      sc.has_ground = true; sc.ground_z = -1.2; sc.max_range = 7.5;   // -15 deg ring at 4.6 m, -13 deg at 5.3 m, -11 deg at 6.3 m
+      // groups of seven thin poles: each crossing ring picks up 4+ corner points inside one 60-degree
+      // sector, of which only two become "sharp" -- so the less-sharp cloud stays well above the next
+      // sweep's sharp count (the reference reads laserCloudCornerLast[j] for j < cornerPointsSharpNum,
+      // laserOdometry.cpp:486: past the end of the cloud otherwise, which no test may rely on)
+      for (int k = 0; k < 40; k++) {
+        const double cx = 3.0 + 6.0 * k, cy = (k % 2) ? -2.5 : 2.0;
+        for (int q = 0; q < 7; q++) {
+          Cyl p; p.cx = cx + 0.35 * q; p.cy = cy; p.r = 0.06; p.z0 = -1.2; p.z1 = 3.0; sc.cyls.push_back(p);
+        }
+      }
+    }
+  } else if (c.preset == 1) {  // VLP-16 in a closed corridor (BASELINE config 1)
     s.rings = 16; s.az = 1800; s.noise_sigma = 0.01;
     const double e[16] = {-15, 1, -13, 3, -11, 5, -9, 7, -7, 9, -5, 11, -3, 13, -1, 15};
     s.elev_deg.assign(e, e + 16);
@@ -233,7 +276,8 @@ extern "C" {
 
 void* synth_create(int preset, uint64_t seed) {
   Handle* h = new Handle();
-  h->cfg.preset = preset;
+  h->cfg.preset = preset % 16;     // preset + 16 * scene
+  h->cfg.scene_id = preset / 16;
   h->cfg.seed = seed;
   build(h->cfg);
   return h;

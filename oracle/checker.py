@@ -1,8 +1,9 @@
 """ORACLE (test infrastructure): ctypes wrapper over the checker API (oracle/checker_api.h).
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import
-this.  kind = "port" (CPU restatement), "port-libm" (same with glibc trig) or "reference"
-(oracle/_ref/libloam_ref.so: the reference's own sources compiled from /root/reference).
+this.  kind = "port" (CPU restatement), "port-libm" (same with glibc trig), "reference"
+(oracle/_ref/libloam_ref.so: the reference's own sources compiled from /root/reference) or
+"reference-libm" (the same sources with glibc's trig instead of loam/detmath.h).
 """
 import ctypes
 import os
@@ -74,7 +75,8 @@ def lib_path(kind):
         return kind
     return {"port": os.path.join(_HERE, "liboracle_port.so"),
             "port-libm": os.path.join(_HERE, "liboracle_port_libm.so"),
-            "reference": os.path.join(_HERE, "_ref", "libloam_ref.so")}[kind]
+            "reference": os.path.join(_HERE, "_ref", "libloam_ref.so"),
+            "reference-libm": os.path.join(_HERE, "_ref", "libloam_ref_libm.so")}[kind]
 
 
 def available(kind):
@@ -89,7 +91,7 @@ def _load(kind):
         return _libs[kind]
     path = lib_path(kind)
     if not os.path.exists(path):
-        if kind != "reference":
+        if not kind.startswith("reference"):
             build()
         if not os.path.exists(path):
             raise FileNotFoundError(path)
@@ -108,6 +110,8 @@ def _load(kind):
     L.chk_get_floats.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int]
     L.chk_busy_seconds.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
     L.chk_lo_set_state.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    if hasattr(L, "chk_lo_push"):   # not in the ROS-adapter driver (tests/adapter)
+        L.chk_lo_push.argtypes = [ctypes.c_void_p] + [ctypes.c_void_p, ctypes.c_int] * 5 + [ctypes.c_void_p, ctypes.c_double, ctypes.POINTER(SweepResult)]
     if hasattr(L, "chk_lm_push"):   # the CPU restatement only
         L.chk_lm_push.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
                                   ctypes.c_int, ctypes.c_void_p, ctypes.c_double, ctypes.POINTER(SweepResult)]
@@ -116,6 +120,7 @@ def _load(kind):
         L.chk_run_pipelined.restype = ctypes.c_double
         L.chk_run_pipelined.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
         L.chk_decode_packets.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+        L.chk_solve_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     _libs[kind] = L
     return L
 
@@ -189,6 +194,17 @@ class Checker:
         t = np.ascontiguousarray(transform, dtype=np.float32)
         s = np.ascontiguousarray(transform_sum, dtype=np.float32)
         self.L.chk_lo_set_state(self.h, t.ctypes.data, s.ctypes.data)
+
+    def lo_push(self, full, sharp, less_sharp, flat, less_flat, imu_trans=None, stamp=0.0):
+        """laserOdometry (and what follows it) fed with host copies of scanRegistration's six topics"""
+        cl = [np.ascontiguousarray(c, dtype=np.float32).reshape(-1, 4) for c in (full, sharp, less_sharp, flat, less_flat)]
+        it = None if imu_trans is None else np.ascontiguousarray(imu_trans, dtype=np.float32)
+        res = SweepResult()
+        args = []
+        for c in cl:
+            args += [c.ctypes.data, c.shape[0]]
+        self.L.chk_lo_push(self.h, *args, None if it is None else it.ctypes.data, float(stamp), ctypes.byref(res))
+        return res
 
     # ---- laserMapping alone (kind "port"): recorded laserOdometry output in, map files ----
     def lm_push(self, corner, surf, full, transform_sum, stamp):

@@ -19,11 +19,19 @@ int chk_get_ints(void* h, int which, int* out, int cap);
 int chk_get_floats(void* h, int which, float* out, int cap);
 void chk_busy_seconds(void* h, double out[4]);
 void chk_lo_set_state(void* h, const float transform[6], const float transformSum[6]);
+/* the chain laserOdometry -> transformMaintenance -> laserMapping fed with HOST copies of scanRegistration's
+ * six topics (x,y,z,intensity per point; imu_trans = the 12 floats of /imu_trans, NULL = zeros) */
+int chk_lo_push(void* h, const float* full, int n_full, const float* sharp, int n_sharp, const float* less_sharp, int n_less_sharp,
+                const float* flat, int n_flat, const float* less_flat, int n_less_flat, const float imu_trans[12], double stamp,
+                loam_sweep_result* out);
 /* port only: laserMapping alone on recorded laserOdometry output; "LOAMMAP1" map files */
 int chk_lm_push(void* h, const float* corner, int nc, const float* surf, int ns, const float* full, int nf,
                 const float transformSum[6], double stamp, loam_sweep_result* out);
 int chk_lm_save_map(void* h, const char* path);
 int chk_lm_load_map(void* h, const char* path);
+/* port only: the solve step of one LM iteration (cv::solve, cv::eigen threshold scan, matP, projection) on
+ * `batch` given normal equations, laserOdometry.cpp:765-797 (thr 10) / laserMapping.cpp:922-954 (thr 100) */
+void chk_solve_step(const float* AtA, const float* AtB, int batch, float thr, int* isDegenerate, float* matP36, float* X6);
 /* port only: the three nodes on three threads with depth-2 queues, as the reference's processes run */
 double chk_run_pipelined(void* h, const float* xyz, const int* counts, const double* stamps, int n_sweeps, float* poses);
 void chk_decode_packets(const unsigned char* packets, int n_packets, float* xyz);

@@ -56,15 +56,10 @@ int chk_imu(void* hv, double stamp, const double quat[4], const float acc[3]) {
   return 0;
 }
 
-int chk_push_sweep(void* hv, const float* xyz, int n, double stamp, loam_sweep_result* out) {
-  chk_handle* h = (chk_handle*)hv;
+// laserOdometry -> transformMaintenance -> (laserMapping -> transformMaintenance) on h->feat
+static void run_from_features(chk_handle* h, double t1) {
   loam_sweep_result& r = h->res;
-  r.sr_status = r.lo_status = r.lm_status = LOAM_NOT_READY;
-  double t0 = now_s();
-  bool ok = h->sr.process(xyz, n, 3, stamp, h->feat);
-  double t1 = now_s();
-  h->busy[0] += t1 - t0;
-  if (ok) {
+  {
     r.sr_status = LOAM_OK;
     r.n_full = (int)h->feat.full.size(); r.n_sharp = (int)h->feat.sharp.size(); r.n_less_sharp = (int)h->feat.lessSharp.size();
     r.n_flat = (int)h->feat.flat.size(); r.n_less_flat = (int)h->feat.lessFlat.size();
@@ -100,9 +95,45 @@ int chk_push_sweep(void* hv, const float* xyz, int n, double stamp, loam_sweep_r
       }
     }
   }
+}
+
+int chk_push_sweep(void* hv, const float* xyz, int n, double stamp, loam_sweep_result* out) {
+  chk_handle* h = (chk_handle*)hv;
+  loam_sweep_result& r = h->res;
+  r.sr_status = r.lo_status = r.lm_status = LOAM_NOT_READY;
+  double t0 = now_s();
+  bool ok = h->sr.process(xyz, n, 3, stamp, h->feat);
+  double t1 = now_s();
+  h->busy[0] += t1 - t0;
+  if (ok) run_from_features(h, t1);
   if (out) *out = r;
   return r.sr_status;
 }
+
+// the same chain fed with HOST copies of scanRegistration's six topics (x,y,z,intensity per point;
+// imu_trans = the 12 floats of /imu_trans, NULL = zeros): what laserOdometry.cpp:281-381 receives
+int chk_lo_push(void* hv, const float* full, int n_full, const float* sharp, int n_sharp, const float* less_sharp, int n_less_sharp,
+                const float* flat, int n_flat, const float* less_flat, int n_less_flat, const float imu_trans[12], double stamp,
+                loam_sweep_result* out) {
+  chk_handle* h = (chk_handle*)hv;
+  loam_sweep_result& r = h->res;
+  r.sr_status = r.lo_status = r.lm_status = LOAM_NOT_READY;
+  auto fill = [](Cloud& c, const float* p, int n) {
+    c.points.resize(n);
+    for (int i = 0; i < n; i++) { c.points[i].x = p[4 * i]; c.points[i].y = p[4 * i + 1]; c.points[i].z = p[4 * i + 2]; c.points[i].intensity = p[4 * i + 3]; }
+    c.width = n; c.height = 1;
+  };
+  SRFeatures& f = h->feat;
+  fill(f.full, full, n_full); fill(f.sharp, sharp, n_sharp); fill(f.lessSharp, less_sharp, n_less_sharp);
+  fill(f.flat, flat, n_flat); fill(f.lessFlat, less_flat, n_less_flat);
+  for (int i = 0; i < 12; i++) f.imuTrans[i] = imu_trans ? imu_trans[i] : 0.f;
+  f.sharpIdx.clear(); f.lessSharpIdx.clear(); f.flatIdx.clear();
+  f.stamp = stamp;
+  run_from_features(h, now_s());
+  if (out) *out = r;
+  return r.sr_status;
+}
+
 
 int chk_get_cloud(void* hv, int which, float* out, int cap) {
   chk_handle* h = (chk_handle*)hv;
@@ -157,6 +188,11 @@ int chk_get_floats(void* hv, int which, float* out, int cap) {
     for (int i = 0; i < n && i < cap; i++) out[i] = h->sr.cloudCurvature[i];
     return n;
   }
+  if (which == 1 || which == 2) {  // matP of laserOdometry (:405) / laserMapping (:386)
+    const cv::Mat& P = which == 1 ? h->lo.matP : h->lm.matP;
+    for (int i = 0; i < 36 && i < cap; i++) out[i] = P.at<float>(i / 6, i % 6);
+    return 36;
+  }
   return -1;
 }
 
@@ -170,6 +206,47 @@ void chk_lo_set_state(void* hv, const float transform[6], const float transformS
   memcpy(h->lo.transformSum, transformSum, sizeof(float) * 6);
 }
 
+
+// the solve step of one LM iteration on given normal equations: cv::solve(QR), and -- as at
+// iterCount == 0 -- cv::eigen, the threshold scan and matP = matV.inv() * matV2, then the projection
+// (laserOdometry.cpp:765-797 with thr 10, laserMapping.cpp:922-954 with thr 100).  `batch` systems:
+// AtA [batch][36], AtB [batch][6] -> isDegenerate [batch], matP [batch][36], X [batch][6]
+void chk_solve_step(const float* AtA, const float* AtB, int batch, float thr, int* isDegenerate, float* matP36, float* X6) {
+  for (int t = 0; t < batch; t++) {
+    cv::Mat matAtA(6, 6, CV_32F, cv::Scalar::all(0)), matAtB(6, 1, CV_32F, cv::Scalar::all(0)), matX(6, 1, CV_32F, cv::Scalar::all(0));
+    cv::Mat matP(6, 6, CV_32F, cv::Scalar::all(0));
+    for (int i = 0; i < 6; i++) {
+      for (int j = 0; j < 6; j++) matAtA.at<float>(i, j) = AtA[t * 36 + i * 6 + j];
+      matAtB.at<float>(i, 0) = AtB[t * 6 + i];
+    }
+    cv::solve(matAtA, matAtB, matX, cv::DECOMP_QR);
+    cv::Mat matE(1, 6, CV_32F, cv::Scalar::all(0));
+    cv::Mat matV(6, 6, CV_32F, cv::Scalar::all(0));
+    cv::Mat matV2(6, 6, CV_32F, cv::Scalar::all(0));
+    cv::eigen(matAtA, matE, matV);
+    matV.copyTo(matV2);
+    bool deg = false;
+    for (int i = 5; i >= 0; i--) {
+      if (matE.at<float>(0, i) < thr) {
+        for (int j = 0; j < 6; j++) matV2.at<float>(i, j) = 0;
+        deg = true;
+      } else {
+        break;
+      }
+    }
+    matP = matV.inv() * matV2;
+    if (deg) {
+      cv::Mat matX2(6, 1, CV_32F, cv::Scalar::all(0));
+      matX.copyTo(matX2);
+      matX = matP * matX2;
+    }
+    isDegenerate[t] = deg ? 1 : 0;
+    for (int i = 0; i < 6; i++) {
+      for (int j = 0; j < 6; j++) matP36[t * 36 + i * 6 + j] = matP.at<float>(i, j);
+      X6[t * 6 + i] = matX.at<float>(i, 0);
+    }
+  }
+}
 
 // ---- laserMapping alone, teacher-forced (BASELINE.json configs[2]) and its map file ----------
 // one loop-body pass of laserMapping.cpp:408-1096 fed with recorded copies of the four topics;

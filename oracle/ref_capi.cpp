@@ -37,6 +37,14 @@ struct Node {
 
 std::atomic<int> g_serial(0);
 
+std::vector<std::string>& doomed() { static std::vector<std::string> v; return v; }
+void remove_doomed() { for (const std::string& p : doomed()) unlink(p.c_str()); }
+void remove_at_exit(const std::string& path) {
+  static bool armed = false;
+  if (!armed) { atexit(remove_doomed); armed = true; }
+  doomed().push_back(path);
+}
+
 std::string self_dir() {
   Dl_info info;
   if (dladdr((void*)&self_dir, &info) && info.dli_fname) {
@@ -143,7 +151,9 @@ void chk_destroy(void* hv) {
     if (n->dl) {
       if (n->stop) n->stop();
       dlclose(n->dl);
-      if (!n->tmp.empty()) unlink(n->tmp.c_str());
+      // dlclose may leave the object mapped (libstdc++ unique symbols make it NODELETE); its file is
+      // therefore only removed when the process exits, so that its inode cannot be handed to a later copy
+      if (!n->tmp.empty()) remove_at_exit(n->tmp);
     }
   }
   delete h;
@@ -159,24 +169,13 @@ int chk_imu(void* hv, double stamp, const double quat[4], const float acc[3]) {
   return 0;
 }
 
-int chk_push_sweep(void* hv, const float* xyz, int n, double stamp, loam_sweep_result* out) {
-  Handle* h = (Handle*)hv;
+// the six scanRegistration topics held in h->full / c_sharp / ... / res.imu_trans -> laserOdometry ->
+// transformMaintenance -> laserMapping, routed as the topic graph does
+static void run_from_features(Handle* h, double stamp) {
   loam_sweep_result& r = h->res;
-  r.sr_status = r.lo_status = r.lm_status = LOAM_NOT_READY;
-  Node &sr = h->sr, &lo = h->lo, &lm = h->lm, &tm = h->tm;
-  sr.out_clear();
-  sr.post_cloud("/velodyne_points", xyz, n, 3, stamp);
-  sr.cycle();
-  if (sr.out_count("/velodyne_cloud_2") > 0) {
+  Node &lo = h->lo, &lm = h->lm, &tm = h->tm;
+  {
     r.sr_status = LOAM_OK;
-    r.n_full = h->n_full = fetch(sr, "/velodyne_cloud_2", h->full, h->buf);
-    r.n_sharp = fetch(sr, "/laser_cloud_sharp", h->c_sharp, h->buf);
-    r.n_less_sharp = fetch(sr, "/laser_cloud_less_sharp", h->c_less_sharp, h->buf);
-    r.n_flat = fetch(sr, "/laser_cloud_flat", h->c_flat, h->buf);
-    r.n_less_flat = fetch(sr, "/laser_cloud_less_flat", h->c_less_flat, h->buf);
-    std::vector<float> it;
-    int ni = fetch(sr, "/imu_trans", it, h->buf);
-    for (int i = 0; i < 4 && i < ni; i++) { r.imu_trans[3 * i] = it[4 * i]; r.imu_trans[3 * i + 1] = it[4 * i + 1]; r.imu_trans[3 * i + 2] = it[4 * i + 2]; }
     // -> laserOdometry (six topics, same stamp)
     lo.out_clear();
     lo.post_cloud("/laser_cloud_sharp", h->c_sharp.data(), r.n_sharp, 4, stamp);
@@ -238,9 +237,50 @@ int chk_push_sweep(void* hv, const float* xyz, int n, double stamp, loam_sweep_r
       }
     }
   }
+}
+
+int chk_push_sweep(void* hv, const float* xyz, int n, double stamp, loam_sweep_result* out) {
+  Handle* h = (Handle*)hv;
+  loam_sweep_result& r = h->res;
+  r.sr_status = r.lo_status = r.lm_status = LOAM_NOT_READY;
+  Node& sr = h->sr;
+  sr.out_clear();
+  sr.post_cloud("/velodyne_points", xyz, n, 3, stamp);
+  sr.cycle();
+  if (sr.out_count("/velodyne_cloud_2") > 0) {
+    r.n_full = h->n_full = fetch(sr, "/velodyne_cloud_2", h->full, h->buf);
+    r.n_sharp = fetch(sr, "/laser_cloud_sharp", h->c_sharp, h->buf);
+    r.n_less_sharp = fetch(sr, "/laser_cloud_less_sharp", h->c_less_sharp, h->buf);
+    r.n_flat = fetch(sr, "/laser_cloud_flat", h->c_flat, h->buf);
+    r.n_less_flat = fetch(sr, "/laser_cloud_less_flat", h->c_less_flat, h->buf);
+    std::vector<float> it;
+    int ni = fetch(sr, "/imu_trans", it, h->buf);
+    for (int i = 0; i < 4 && i < ni; i++) { r.imu_trans[3 * i] = it[4 * i]; r.imu_trans[3 * i + 1] = it[4 * i + 1]; r.imu_trans[3 * i + 2] = it[4 * i + 2]; }
+    run_from_features(h, stamp);
+  }
   if (out) *out = r;
   return r.sr_status;
 }
+
+// the same chain fed with HOST copies of scanRegistration's six topics (checker_api.h)
+int chk_lo_push(void* hv, const float* full, int n_full, const float* sharp, int n_sharp, const float* less_sharp, int n_less_sharp,
+                const float* flat, int n_flat, const float* less_flat, int n_less_flat, const float imu_trans[12], double stamp,
+                loam_sweep_result* out) {
+  Handle* h = (Handle*)hv;
+  loam_sweep_result& r = h->res;
+  r.sr_status = r.lo_status = r.lm_status = LOAM_NOT_READY;
+  h->full.assign(full, full + (size_t)4 * n_full);
+  h->c_sharp.assign(sharp, sharp + (size_t)4 * n_sharp);
+  h->c_less_sharp.assign(less_sharp, less_sharp + (size_t)4 * n_less_sharp);
+  h->c_flat.assign(flat, flat + (size_t)4 * n_flat);
+  h->c_less_flat.assign(less_flat, less_flat + (size_t)4 * n_less_flat);
+  r.n_full = h->n_full = n_full; r.n_sharp = n_sharp; r.n_less_sharp = n_less_sharp; r.n_flat = n_flat; r.n_less_flat = n_less_flat;
+  for (int i = 0; i < 12; i++) r.imu_trans[i] = imu_trans ? imu_trans[i] : 0.f;
+  run_from_features(h, stamp);
+  if (out) *out = r;
+  return r.sr_status;
+}
+
 
 int chk_get_cloud(void* hv, int which, float* out, int cap) {
   Handle* h = (Handle*)hv;

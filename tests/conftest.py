@@ -54,3 +54,13 @@ def feed_imu(S, k, *sinks):
             t, q, a = S.imu(j)
             for s in sinks:
                 s.imu(t, q, a)
+
+
+def inside_reference_domain(prev, r):
+    """laserOdometry.cpp:486 / :592 bound the forward scans over the LAST corner / surf cloud by THIS sweep's
+    sharp / flat count; when that exceeds the last cloud's size the reference reads past the end of the
+    cloud (undefined behaviour, nothing to be equal to).  True when sweep `r` (after `prev`) stays clear of
+    that: every guard-branch scene is checked for it, so parity is only claimed where the reference defines it."""
+    if prev is None or prev.sr_status != 0 or r.lo_iters == 0:
+        return True
+    return r.n_sharp <= prev.n_less_sharp and r.n_flat <= prev.n_less_flat

@@ -52,3 +52,22 @@ def test_lo_process_host_rejects_unordered_features(pkg):
     pts[:, 3] = [0.0, 1.0, 2.0, 99.0]         # ring outside the sensor
     with pytest.raises(pkg.LoamError):
         lo.process_host(pts, pts[:1], pts, pts[:1], pts)
+
+
+def test_lo_process_host_rejects_feature_clouds_beyond_the_banks(pkg):
+    """sharp / less-sharp / flat clouds larger than what scanRegistration can emit (12 / 120 / 24 points per
+    ring) but below max_points must be refused, not copied past the device banks"""
+    P = pkg.make_params(1, system_delay=0)
+    lo = pkg.LaserOdometry(P)
+    def cloud(n):
+        c = np.zeros((n, 4), np.float32)
+        c[:, 3] = np.minimum(np.arange(n) * 16 // max(n, 1), 15)
+        return c
+    ok = cloud(100)
+    for which, n in ((1, 16 * 12 + 1), (2, 16 * 120 + 1), (3, 16 * 24 + 1)):
+        args = [cloud(2000), ok[:10], ok, ok[:10], cloud(2000)]
+        args[which] = cloud(n)
+        with pytest.raises(pkg.LoamError, match="exceeds the bank"):
+            lo.process_host(*args)
+    rc, _ = lo.process_host(cloud(2000), cloud(16 * 12), cloud(16 * 120), cloud(16 * 24), cloud(2000))   # exactly full banks are fine
+    assert rc in (0, 1)

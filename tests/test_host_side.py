@@ -33,11 +33,14 @@ def test_generator_is_bit_reproducible(synth):
 
 
 def test_capi_exports_every_declared_symbol(pkg):
-    """include/loam_b200.h is the contract: the built library must export exactly those entry points"""
+    """include/*.h is the contract (loam_b200.h = the drop-in boundary, loam_b200_debug.h = the test hooks):
+    the built library must export every entry point they declare"""
     if not os.path.exists(pkg.LIB_PATH):
         import importlib
         importlib.import_module(PKG + ".build").build_cuda()
-    hdr = open(os.path.join(ROOT, "include", "loam_b200.h")).read()
+    hdr = open(os.path.join(ROOT, "include", "loam_b200.h")).read() + open(os.path.join(ROOT, "include", "loam_b200_debug.h")).read()
+    boundary = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "loam_b200.h")).read(), flags=re.S)
+    assert "loam_debug_" not in boundary   # the hooks stay out of the boundary header
     hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
     names = sorted(set(re.findall(r"\b(loam_[a-z0-9_]+)\s*\(", hdr)))
     assert len(names) > 35
