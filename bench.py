@@ -50,12 +50,13 @@ def shard_sequences(n_seq, rank, world):
     return [s for s in range(n_seq) if s % world == rank]
 
 
-def gather_poses(local, n_seq, n_sweeps, rank, world, device="cuda"):
-    """one collective: every rank contributes a dense [n_seq, n_sweeps, 6] table that is zero outside
-    its own sequences; the sum over ranks is the full table (NCCL all_reduce over NVLink, gloo on CPU)"""
+def gather_poses(local, n_seq, n_sweeps, rank, world, device="cuda", width=6):
+    """one collective: every rank contributes a dense [n_seq, n_sweeps, width] table that is zero outside
+    its own sequences; the sum over ranks is the full table (NCCL all_reduce over NVLink, gloo on CPU).
+    width 6 = the /integrated_to_init pose; POSE_STATS_WIDTH = pose + the per-sweep stats of STAT_KEYS"""
     import torch
     import torch.distributed as dist
-    t = torch.zeros((n_seq, n_sweeps, 6), dtype=torch.float32)
+    t = torch.zeros((n_seq, n_sweeps, width), dtype=torch.float32)
     for s, p in local.items():
         t[s] = torch.from_numpy(np.asarray(p, np.float32))
     if world > 1:
@@ -65,64 +66,120 @@ def gather_poses(local, n_seq, n_sweeps, rank, world, device="cuda"):
     return t.numpy()
 
 
+STAT_KEYS = ("lo_iters", "lo_rows", "lo_degenerate", "lm_iters", "lm_rows", "lm_degenerate", "n_sharp", "n_less_sharp", "n_flat", "n_less_flat",
+             "n_map_corner", "n_map_surf", "n_stack_corner", "n_stack_surf")
+POSE_STATS_WIDTH = 6 + len(STAT_KEYS)
+
+
+def pose_stats_rows(results):
+    """per sweep: the 6 floats of /integrated_to_init followed by the sweep's statistics (north_star: the one
+    collective gathers "poses and stats"); counters are small integers, exact in fp32"""
+    return np.array([list(r.transform_mapped[:]) + [float(getattr(r, k)) for k in STAT_KEYS] for r in results], np.float32).reshape(-1, POSE_STATS_WIDTH)
+
+
 # ---------------------------------------------------------------------------------------------
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region"""
+    """SM clock and throttle reasons sampled DURING the timed region, in-process through NVML (one
+    sampling thread on rank 0 only: N ranks x one `nvidia-smi -lms 20` child each used to compete with
+    the feeding threads for the host cores).  Falls back to nvidia-smi if pynvml cannot be used."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    BITS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
 
-    def __init__(self, gpu_index):
-        self.rows = []
-        self.proc = None
+    def __init__(self, gpu_index, enabled=True):
+        self.rows = []      # (sm_mhz, max_mhz, reasons bitmask)
         self.idx = gpu_index
+        self.enabled = enabled
+        self.begin = 0
+        self.stop_flag = False
+        self.th = None
+        self.how = None
+
+    def _nvml_loop(self, nv, h):
+        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                try:
+                    why = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    why = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.rows.append((float(sm), float(mx), int(why)))
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def _smi_loop(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.proc.stdout:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                why = sum(self.BITS[n] for n, v in zip(names, f[5:9]) if v.lower().startswith("active"))
+                self.rows.append((float(f[1]), float(f[2]), why))
+            except ValueError:
+                continue
 
     def start(self):
-        """started BEFORE the warm-up so that nvidia-smi is already emitting when the timed region begins
-        (a 60 ms region is shorter than its start-up); mark() is called at the start of the region and
-        stop() right after it: only the rows in between (plus one on either side) are used"""
-        self.begin = 0
+        """started BEFORE the warm-up; mark() is called at the start of the timed region and stop() right
+        after it: only the samples in between (plus one on either side) are used"""
+        if not self.enabled:
+            return
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            # NVML enumerates all GPUs of the box; under CUDA_VISIBLE_DEVICES the CUDA ordinal is remapped
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = self.idx
+            if vis:
+                try:
+                    phys = int(vis.split(",")[self.idx])
+                except Exception:
+                    phys = self.idx
+            h = nv.nvmlDeviceGetHandleByIndex(phys)
+            self.how = "nvml"
+            self.th = threading.Thread(target=self._nvml_loop, args=(nv, h), daemon=True)
+            self.th.start()
+            return
+        except Exception:
+            pass
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.th = threading.Thread(target=self._read, daemon=True)
+            self.how = "nvidia-smi"
+            self.th = threading.Thread(target=self._smi_loop, daemon=True)
             self.th.start()
         except Exception:
-            self.proc = None
-
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append(line.strip())
+            self.how = None
 
     def mark(self):
         self.begin = max(len(self.rows) - 1, 0)
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        if not self.enabled:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "note": "sampled on rank 0 only"}
+        if not self.how:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no clock source available"]}
         time.sleep(0.03)
         end = len(self.rows) + 1
-        time.sleep(0.05)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        rows = self.rows[self.begin:end] or self.rows[-2:]
-        for r in rows:
-            f = [x.strip() for x in r.split(",")]
-            if len(f) < 9:
-                continue
+        self.stop_flag = True
+        if self.how == "nvidia-smi":
+            time.sleep(0.05)
+            self.proc.terminate()
             try:
-                sm.append(float(f[1])); mx.append(float(f[2]))
-            except ValueError:
-                continue
-            for name, v in zip(names, f[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        rows = self.rows[self.begin:end] or self.rows[-2:]
+        sm = [r[0] for r in rows]
+        mx = [r[1] for r in rows]
+        why = 0
+        for r in rows:
+            why |= r[2]
+        reasons = sorted(n for n, bit in self.BITS.items() if why & bit)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "reasons": reasons, "source": self.how}
 
 
 def algorithmic_bytes(kernel, s):
@@ -248,17 +305,31 @@ def cpu_baseline(sweeps, budget_s=20.0, max_sweeps=80, preset=None, imu=None, la
     if not imu or not any(imu):
         # the way the reference is deployed: one process per node, topic queues of depth 2 between them
         # (three host threads here, the CPU restatement's node objects; IMU-free sequences only)
-        Cp = checker.Checker(checker.make_params(PRESET if preset is None else preset), "port")
+        Cp = checker.Checker(checker.make_params(PRESET if preset is None else preset), kind)
         tp, _ = Cp.run_pipelined(sweeps[:done])
         Cp.close()
-        piped = {"value": done / tp, "unit": "sweeps/s", "cores": 3, "kind": "port",
-                 "sample": f"the same {done} sweeps, scanRegistration / laserOdometry / laserMapping on one thread each, depth-2 queues"}
+        piped = {"value": done / tp, "unit": "sweeps/s", "cores": 3, "kind": kind,
+                 "sample": f"the same {done} sweeps, scanRegistration / laserOdometry / laserMapping on one host thread each, topic queues of depth 2 (the reference's deployed form: one process per node)"}
     return {"value": done / wall, "unit": "sweeps/s", "cores": 1, "kind": kind, "pipelined_3threads": piped,
             "sample": f"first {done} sweeps of the same {label} sequence, sr->lo->lm->tm sequentially on one host thread",
             "p50_ms_per_sweep": 1e3 * statistics.median(lat),
             "node_busy_s": {"sr": busy[0], "lo": busy[1], "lm": busy[2], "tm": busy[3]},
             "pipelined_3proc_estimate_sweeps_per_s": done / max(busy[0], busy[1], busy[2], 1e-9),
             "host": {"nproc": os.cpu_count()}}
+
+
+NOMINAL_POINTS = {1: 16 * 1800, 2: 64 * 2000, 4: 128 * 2048}
+
+
+def stream_config(workload_key, world, W, K):
+    """the `config` object of the single-stream workloads; built from the command line only, so that both
+    arms (this repo's and --impl reference) print the identical dict"""
+    preset, _, workload = WORKLOADS[workload_key]
+    total = W + K
+    return {"workload": workload, "sequences": world, "sweeps_per_sequence": K, "points_per_sweep": NOMINAL_POINTS[preset],
+            "parallelism": f"seq{world}",
+            "l2": "inputs larger than L2: %d distinct sweeps (%.0f MB) per sequence, each read once" % (total, total * NOMINAL_POINTS[preset] * 12 / 1e6),
+            "timed_region": "K x (scanRegistration + laserOdometry + laserMapping every 2nd sweep + pose record); one step = one sweep through the whole pipeline"}
 
 
 def run_reference(args, rank, world):
@@ -269,15 +340,28 @@ def run_reference(args, rank, world):
     if args.workload == "seq64":
         return run_seq64_reference(args)
     preset, seed0, workload = WORKLOADS[args.workload]
-    n = min(args.steps + args.warmup, 80)
+    W = max(args.warmup, 3)
+    n = min(args.steps + W, 80)
     sweeps = gen_sweeps(seed0, n, preset)
     cb = cpu_baseline(sweeps, budget_s=120.0, max_sweeps=n, preset=preset, imu=gen_imu(seed0, n, preset), label=args.workload)
-    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "sweeps/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / cb["value"], "higher_is_better": True,
+    # headline of this arm = the reference as it is deployed (one thread per node, "the program consumes two
+    # cores", README.md:46) when the sequence has no IMU; the single-thread sequential figure is kept beside it
+    seq = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "p50_ms_per_sweep", "node_busy_s")}
+    piped = cb.get("pipelined_3threads")
+    if piped:
+        head = dict(piped)
+        head["sequential_1thread"] = seq
+    else:
+        head = dict(seq)
+        head["note"] = "IMU sequence: the three-thread runner feeds no IMU, so the sequential figure is the headline"
+    head["host"] = cb["host"]
+    line = {"impl": "reference", "metric": METRIC, "value": head["value"], "unit": "sweeps/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": W, "ms_per_step": 1e3 / head["value"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload, "note": "reference CPU nodes (oracle/_ref when built, else the oracle port), in-process, ROS stripped"},
-            "cpu_baseline": cb,
-            "e2e": {"value": cb["value"], "unit": "sweeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+            "config": stream_config(args.workload, args.gpus, W, args.steps),
+            "note": "reference CPU nodes (oracle/_ref = the reference's own sources when built, else the oracle port), in-process, ROS stripped; ONE sequence on the host cores whatever --gpus says",
+            "cpu_baseline": head,
+            "e2e": {"value": head["value"], "unit": "sweeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
     return 0
 
@@ -639,6 +723,14 @@ def main():
     if world > 1:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL's banner / debug lines never reach stdout
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # communicator bring-up (connections, proxy threads) happens at the FIRST collective: do it here, let it
+        # settle, and only then start the arms -- the timed regions themselves contain no collective
+        warm = torch.ones(1 << 20, device=torch.device("cuda", local_rank))
+        for _ in range(3):
+            dist.all_reduce(warm)
+        torch.cuda.synchronize()
+        dist.barrier()
+        time.sleep(0.2)
     pkg = importlib.import_module(PKG)
     if args.workload == "mapstress":
         return run_mapstress(args, rank, world, local_rank)
@@ -663,7 +755,7 @@ def main():
     if args.coop_ctas:
         P.coop_ctas = args.coop_ctas
     G = pkg.Pipeline(P, device=local_rank)
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(local_rank, enabled=(rank == 0))
     sampler.start()
     for k in range(W):
         feed(G, k)
@@ -672,6 +764,7 @@ def main():
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
+        torch.cuda.synchronize()
     sampler.mark()
     launches0 = pkg.kernel_launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -697,7 +790,11 @@ def main():
     launches = pkg.kernel_launch_count() - launches0
     ms = ev0.elapsed_time(ev1)
     ms_t = torch.tensor([ms, t_wall * 1e3], dtype=torch.float64, device=dev)
+    per_rank_ms = [ms]
     if world > 1:
+        allms = [torch.zeros_like(ms_t) for _ in range(world)]
+        dist.all_gather(allms, ms_t)
+        per_rank_ms = [float(x[0].item()) for x in allms]     # skew between the ranks, reported beside the MAX
         dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
     ms_max = float(ms_t[0].item())
     value = world * K / (ms_max * 1e-3)
@@ -705,7 +802,7 @@ def main():
     for key in ("n_full", "n_sharp", "n_less_sharp", "n_flat", "n_less_flat", "lo_iters", "lm_iters", "n_map_corner", "n_map_surf", "n_stack_corner", "n_stack_surf"):
         vals = [getattr(r, key) for r in results if r.sr_status == 0 and (not key.startswith(("lm_", "n_map", "n_stack")) or r.lm_status == 0)]
         stats[key] = float(np.mean(vals)) if vals else 0.0
-    poses_local = {rank: np.array([r.transform_mapped[:] for r in results], np.float32)}
+    poses_local = {rank: pose_stats_rows(results)}
     del G
 
     # ---------------- e2e: public C-ABI calls, HOST buffers, H2D + D2H inside every step ---------
@@ -751,14 +848,18 @@ def main():
         lat.append(time.perf_counter() - t2)
     sync_s = time.perf_counter() - t1
     e2e_t = torch.tensor([e2e_s, sync_s], dtype=torch.float64, device=dev)
+    per_rank_e2e_ms = [e2e_s * 1e3]
     if world > 1:
         dist.barrier()
+        alle = [torch.zeros_like(e2e_t) for _ in range(world)]
+        dist.all_gather(alle, e2e_t)
+        per_rank_e2e_ms = [float(x[0].item()) * 1e3 for x in alle]
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
     e2e_value = world * K / float(e2e_t[0].item())
     d2h = ctypes_sizeof_record(pkg)
     e2e = {"value": e2e_value, "unit": "sweeps/s", "h2d_bytes_per_step": int(np.mean(npts[W:]) * 12), "d2h_bytes_per_step": d2h,
            "api": "loam_pipeline_push_async per sweep from pinned host memory + loam_pipeline_collect every 128 sweeps",
-           "poses_identical_to_resident_arm": bool(same),
+           "poses_identical_to_resident_arm": bool(same), "per_rank_ms": [round(x, 3) for x in per_rank_e2e_ms],
            "sync": {"value": world * K / float(e2e_t[1].item()), "unit": "sweeps/s", "api": "loam_pipeline_push (returns the sweep's poses)",
                     "p50_ms_per_sweep": 1e3 * statistics.median(lat), "p99_ms_per_sweep": 1e3 * float(np.percentile(lat, 99))}}
 
@@ -822,10 +923,15 @@ def main():
                 e["frac_of_hbm_peak"] = round(e["algorithmic_GBps"] / peak, 4)
             rows.append(e)
         kernels = rows
+        if roofline is not None:
+            # every kernel SURVEY §8(d) counts as HBM-streaming, with its own fraction of the measured peak
+            # (algorithmic bytes per launch / live CUDA-event time); the persistent LM kernels are latency chains
+            roofline["kernels"] = [{"kernel": e["kernel"], "achieved": e["algorithmic_GBps"], "frac": e["frac_of_hbm_peak"],
+                                    "avg_launch_us": e["avg_launch_us"], "share": e["share"]} for e in rows if "frac_of_hbm_peak" in e]
     del G2
 
     # ---------------- the one collective of the multi-sequence configuration ---------------------
-    table = gather_poses(poses_local, world, K, rank, world, device=dev)
+    table = gather_poses(poses_local, world, K, rank, world, device=dev, width=POSE_STATS_WIDTH)
 
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -835,13 +941,14 @@ def main():
         line = {"metric": METRIC, "value": value, "unit": "sweeps/s", "n_gpus": world, "steps": K, "warmup": W,
                 "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
-                "config": {"workload": workload, "sequences": world, "sweeps_per_sequence": K, "points_per_sweep": int(np.mean(npts)),
-                           "parallelism": f"seq{world}", "l2": "inputs larger than L2: %d distinct sweeps (%.0f MB) resident in HBM, each read once" % (total, sum(npts) * 12 / 1e6),
-                           "timed_region": "K x (scanRegistration + laserOdometry + laserMapping every 2nd sweep + pose record); stages of consecutive sweeps overlap on 3 streams (+ copy stream) like the reference's nodes; CUDA events on the pipeline stream after a device-side join of all streams, no host sync inside"},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+                "config": stream_config(args.workload, world, W, K),
+                "timing": "stages of consecutive sweeps overlap on 3 streams (+ copy stream) like the reference's nodes; CUDA events on the pipeline stream after a device-side join of all streams, no host sync inside; MAX over ranks",
+                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "per_rank_ms": [round(x, 3) for x in per_rank_ms],
                 "wall_ms_incl_launch": float(ms_t[1].item()), "host_enqueue_ms": t_enq * 1e3, "host_backpressure_wait_ms": t_wait * 1e3, "host_enqueue_ms_by_node": {"sr": t_node[0], "lo": t_node[1], "lm": t_node[2]},
                 "mean_counts": stats, "roofline": roofline, "top_kernels": kernels, "cpu_baseline": cb,
-                "poses_gathered": [int(table.shape[0]), int(table.shape[1])]}
+                "poses_gathered": [int(table.shape[0]), int(table.shape[1])],
+                "gathered": {"shape": [int(x) for x in table.shape], "columns": ["integrated_to_init[6]"] + list(STAT_KEYS),
+                             "collective": "one all_reduce(SUM) of a zero-padded table after the timed region (NCCL; gloo in the CPU tests)"}}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -112,6 +112,9 @@ def _load(kind):
     L.chk_lo_set_state.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     if hasattr(L, "chk_lo_push"):   # not in the ROS-adapter driver (tests/adapter)
         L.chk_lo_push.argtypes = [ctypes.c_void_p] + [ctypes.c_void_p, ctypes.c_int] * 5 + [ctypes.c_void_p, ctypes.c_double, ctypes.POINTER(SweepResult)]
+    if hasattr(L, "chk_run_pipelined"):   # port and reference builds: the nodes on three threads
+        L.chk_run_pipelined.restype = ctypes.c_double
+        L.chk_run_pipelined.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
     if hasattr(L, "chk_lm_push"):   # the CPU restatement only
         L.chk_lm_push.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
                                   ctypes.c_int, ctypes.c_void_p, ctypes.c_double, ctypes.POINTER(SweepResult)]
@@ -228,7 +231,7 @@ class Checker:
             raise RuntimeError(f"chk_lm_load_map({path}) = {rc}")
 
     def run_pipelined(self, sweeps):
-        """kind "port": sr / lo / lm on three threads joined by depth-2 queues (the reference's process
+        """kind "port" or "reference": sr / lo / lm on three threads joined by depth-2 queues (the reference's process
         pipeline); sweeps = [(xyz, stamp), ...]; returns (wall seconds, /integrated_to_init poses [n, 6])"""
         xyz = np.ascontiguousarray(np.concatenate([np.asarray(x, np.float32).reshape(-1, 3) for x, _ in sweeps]), np.float32)
         counts = np.array([np.asarray(x).shape[0] for x, _ in sweeps], np.int32)

@@ -32,7 +32,7 @@ int chk_lm_load_map(void* h, const char* path);
 /* port only: the solve step of one LM iteration (cv::solve, cv::eigen threshold scan, matP, projection) on
  * `batch` given normal equations, laserOdometry.cpp:765-797 (thr 10) / laserMapping.cpp:922-954 (thr 100) */
 void chk_solve_step(const float* AtA, const float* AtB, int batch, float thr, int* isDegenerate, float* matP36, float* X6);
-/* port only: the three nodes on three threads with depth-2 queues, as the reference's processes run */
+/* port and reference: the three nodes on three threads with depth-2 queues, as the reference's processes run */
 double chk_run_pipelined(void* h, const float* xyz, const int* counts, const double* stamps, int n_sweeps, float* poses);
 void chk_decode_packets(const unsigned char* packets, int n_packets, float* xyz);
 #ifdef __cplusplus

@@ -344,3 +344,106 @@ void chk_lo_set_state(void* hv, const float transform[6], const float transformS
 }
 
 }  // extern "C"
+
+// ---- the reference as it is deployed: one thread per node, topic queues of depth 2 between them ----------
+// (scanRegistration / laserOdometry / laserMapping are separate processes in the reference, "the program
+// consumes two cores", README.md:46; transformMaintenance's two callbacks run under one lock)
+#include <condition_variable>
+#include <chrono>
+#include <deque>
+#include <mutex>
+#include <thread>
+namespace {
+template <class T> struct Mailbox {
+  std::deque<T> q; std::mutex m; std::condition_variable cv; size_t cap = 2; bool closed = false;
+  void push(T&& v) { std::unique_lock<std::mutex> l(m); cv.wait(l, [&] { return q.size() < cap; }); q.push_back(std::move(v)); cv.notify_all(); }
+  bool pop(T& v) { std::unique_lock<std::mutex> l(m); cv.wait(l, [&] { return !q.empty() || closed; }); if (q.empty()) return false; v = std::move(q.front()); q.pop_front(); cv.notify_all(); return true; }
+  void close() { std::unique_lock<std::mutex> l(m); closed = true; cv.notify_all(); }
+};
+struct SixTopics { int k; double stamp; std::vector<float> full, sharp, less_sharp, flat, less_flat, imu_trans; };
+struct OdomTopics { int k; double stamp; double odom[14]; bool have_odom, clouds, full3; std::vector<float> corner_last, surf_last, full_end; };
+}  // namespace
+
+extern "C" double chk_run_pipelined(void* hv, const float* xyz, const int* counts, const double* stamps, int n_sweeps, float* poses) {
+  Handle* h = (Handle*)hv;
+  Node &sr = h->sr, &lo = h->lo, &lm = h->lm, &tm = h->tm;
+  Mailbox<SixTopics> q1;
+  Mailbox<OdomTopics> q2;
+  std::mutex tm_mu;
+  auto t0 = std::chrono::steady_clock::now();
+  std::thread t_sr([&] {
+    std::vector<float> scratch((size_t)4 * 400000);
+    size_t off = 0;
+    for (int k = 0; k < n_sweeps; k++) {
+      sr.out_clear();
+      sr.post_cloud("/velodyne_points", xyz + off * 3, counts[k], 3, stamps[k]);
+      off += (size_t)counts[k];
+      sr.cycle();
+      if (sr.out_count("/velodyne_cloud_2") <= 0) continue;
+      SixTopics m; m.k = k; m.stamp = stamps[k];
+      fetch(sr, "/velodyne_cloud_2", m.full, scratch); fetch(sr, "/laser_cloud_sharp", m.sharp, scratch);
+      fetch(sr, "/laser_cloud_less_sharp", m.less_sharp, scratch); fetch(sr, "/laser_cloud_flat", m.flat, scratch);
+      fetch(sr, "/laser_cloud_less_flat", m.less_flat, scratch);
+      std::vector<float> it;
+      int ni = fetch(sr, "/imu_trans", it, scratch);
+      m.imu_trans.assign(12, 0.f);
+      for (int i = 0; i < 4 && i < ni; i++) { m.imu_trans[3 * i] = it[4 * i]; m.imu_trans[3 * i + 1] = it[4 * i + 1]; m.imu_trans[3 * i + 2] = it[4 * i + 2]; }
+      q1.push(std::move(m));
+    }
+    q1.close();
+  });
+  std::thread t_lo([&] {
+    std::vector<float> scratch((size_t)4 * 400000);
+    SixTopics m;
+    while (q1.pop(m)) {
+      lo.out_clear();
+      lo.post_cloud("/laser_cloud_sharp", m.sharp.data(), (int)m.sharp.size() / 4, 4, m.stamp);
+      lo.post_cloud("/laser_cloud_less_sharp", m.less_sharp.data(), (int)m.less_sharp.size() / 4, 4, m.stamp);
+      lo.post_cloud("/laser_cloud_flat", m.flat.data(), (int)m.flat.size() / 4, 4, m.stamp);
+      lo.post_cloud("/laser_cloud_less_flat", m.less_flat.data(), (int)m.less_flat.size() / 4, 4, m.stamp);
+      lo.post_cloud("/velodyne_cloud_2", m.full.data(), (int)m.full.size() / 4, 4, m.stamp);
+      lo.post_cloud("/imu_trans", m.imu_trans.data(), 4, 3, m.stamp);
+      lo.cycle();
+      OdomTopics o; o.k = m.k; o.stamp = m.stamp;
+      o.have_odom = lo.out_count("/laser_odom_to_init") > 0;
+      o.clouds = lo.out_count("/laser_cloud_corner_last") > 0;
+      o.full3 = lo.out_count("/velodyne_cloud_3") > 0;
+      if (!o.have_odom && !o.clouds) continue;
+      if (o.have_odom) {
+        lo.get_odom("/laser_odom_to_init", o.odom);
+        std::lock_guard<std::mutex> l(tm_mu);
+        tm.out_clear();
+        tm.post_odom("/laser_odom_to_init", o.odom);
+        tm.cycle();
+        if (tm.get_floats) tm.get_floats(0, poses + 6 * (size_t)m.k, 6);
+      }
+      if (o.clouds) { fetch(lo, "/laser_cloud_corner_last", o.corner_last, scratch); fetch(lo, "/laser_cloud_surf_last", o.surf_last, scratch); }
+      if (o.full3) fetch(lo, "/velodyne_cloud_3", o.full_end, scratch);
+      // an odometry-only sweep (clouds not published) still reaches laserMapping, as on the topic graph
+      q2.push(std::move(o));
+    }
+    q2.close();
+  });
+  std::thread t_lm([&] {
+    OdomTopics o;
+    while (q2.pop(o)) {
+      lm.out_clear();
+      if (o.have_odom) lm.post_odom("/laser_odom_to_init", o.odom);
+      if (o.clouds) {
+        lm.post_cloud("/laser_cloud_corner_last", o.corner_last.data(), (int)o.corner_last.size() / 4, 4, o.stamp);
+        lm.post_cloud("/laser_cloud_surf_last", o.surf_last.data(), (int)o.surf_last.size() / 4, 4, o.stamp);
+      }
+      if (o.full3) lm.post_cloud("/velodyne_cloud_3", o.full_end.data(), (int)o.full_end.size() / 4, 4, o.stamp);
+      lm.cycle();
+      if (lm.out_count("/aft_mapped_to_init") > 0) {
+        double am[14];
+        lm.get_odom("/aft_mapped_to_init", am);
+        std::lock_guard<std::mutex> l(tm_mu);
+        tm.post_odom("/aft_mapped_to_init", am);
+        tm.cycle();
+      }
+    }
+  });
+  t_sr.join(); t_lo.join(); t_lm.join();
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
