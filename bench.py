@@ -703,6 +703,7 @@ def main():
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--workload", default="hdl64", choices=sorted(WORKLOADS))
     ap.add_argument("--host-threads", type=int, default=8, help="seq64: host threads feeding the pipelines of one GPU")
+    ap.add_argument("--dev-flags", type=int, default=0, help="development A/B switches passed through loam_params.reserved[0] (0 = the shipped configuration)")
     ap.add_argument("--coop-ctas", type=int, default=None, help="CTAs of the cooperative LM kernels per pipeline (0 = one per SM; default 37 for seq64, else 0)")
     args = ap.parse_args()
     # a pipeline runs on 6 streams (copy, registration, odometry, mapping + side streams) and seq64 on
@@ -754,6 +755,7 @@ def main():
     P = pkg.make_params(preset, system_delay=0)
     if args.coop_ctas:
         P.coop_ctas = args.coop_ctas
+    P.reserved[0] = args.dev_flags
     G = pkg.Pipeline(P, device=local_rank)
     sampler = ClockSampler(local_rank, enabled=(rank == 0))
     sampler.start()

@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libloam_b200.so")
+LIB_PATH = os.environ.get("LOAM_B200_LIB") or os.path.join(_HERE, "libloam_b200.so")   # LOAM_B200_LIB: a development build (e.g. with -DLOAM_PHASE_CLOCKS)
 
 LOAM_OK, LOAM_NOT_READY = 0, 1
 

@@ -27,6 +27,11 @@ def build_cuda(force=False, verbose=False):
            "-Xcompiler", "-fPIC,-ffp-contract=off,-O2", "-shared",
            "-I", os.path.join(ROOT, "include"), "-I", csrc,
            os.path.join(csrc, "loam_b200.cu"), "-o", LIB, "-lcudart_static", "-lpthread", "-ldl", "-lrt"]
+    for var in ("LOAM_LO_MAXREG", "LOAM_LM_MAXREG"):   # dev builds: register caps of the two persistent kernels
+        if os.environ.get(var):
+            cmd.insert(1, "-D%s=%s" % (var, os.environ[var]))
+    if os.environ.get("LOAM_LIB_OUT"):
+        cmd[cmd.index("-o") + 1] = os.environ["LOAM_LIB_OUT"]
     if os.environ.get("LOAM_PHASE_CLOCKS"):   # dev builds only: clock64 stamps inside the persistent LM kernels
         cmd.insert(1, "-DLOAM_PHASE_CLOCKS")
     if verbose:

@@ -117,9 +117,9 @@ __global__ void __launch_bounds__(256) grid_bbox(GridPair gp) {
   }
 }
 
-__device__ __forceinline__ GridDesc grid_make_desc(const GridBuf& g) {
+__device__ __forceinline__ GridDesc grid_make_desc(const GridBuf& g, int n_given = -1) {
   GridDesc d;
-  int n = min(*g.n_ptr, g.cap);
+  int n = min(n_given >= 0 ? n_given : *g.n_ptr, g.cap);
   d.n_points = n;
   d.valid = n > 0 ? 1 : 0;
   float mn[3], mx[3];
@@ -198,6 +198,93 @@ __global__ void __launch_bounds__(256) grid_scatter(GridPair gp) {
   for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
     int dst = g.cell[g.pt_cell[i]].x + g.pt_rank[i];
     float4 p = g.pts[i];
+    p.w = __int_as_float(i);
+    g.sorted_pts[dst] = p;
+  }
+}
+
+// ---- the same five phases as device functions, for kernels that build an index in their own tail
+// (lo_optimize's epilogue, lm_front): `tid` / `nthr` = index and number of the threads taking part (all
+// threads of all participating CTAs), the caller separates the phases with its own grid / cluster barrier.
+// Phase 1: the caller folds the points' bounding box into g.bbox (flipped-float atomics, armed on entry).
+__device__ __forceinline__ void bbox_block_commit(unsigned int* bbox, const float* mn, const float* mx, float (*s_mn)[3], float (*s_mx)[3], int nwarps) {
+  float lo[3], hi[3];
+  for (int a = 0; a < 3; a++) {
+    lo[a] = mn[a]; hi[a] = mx[a];
+    for (int o = 16; o > 0; o >>= 1) {
+      lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+      hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+    }
+  }
+  const int warp = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane_id() == 0) for (int a = 0; a < 3; a++) { s_mn[warp][a] = lo[a]; s_mx[warp][a] = hi[a]; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    const int a = threadIdx.x;
+    float l = s_mn[0][a], h = s_mx[0][a];
+    for (int w = 1; w < nwarps; w++) { l = fminf(l, s_mn[w][a]); h = fmaxf(h, s_mx[w][a]); }
+    if (l <= h) {
+      atomicMin(&bbox[a], float_flip(l));
+      atomicMax(&bbox[3 + a], float_flip(h));
+    }
+  }
+}
+// Phase 2: descriptor from the bounding box (every thread computes the same one) + zeroed cell table
+__device__ __forceinline__ GridDesc gridp_setup(const GridBuf& g, int n, int tid, int nthr) {
+  GridBuf gl = g;
+  unsigned int bb[6];
+  for (int a = 0; a < 6; a++) bb[a] = __ldcg(&g.bbox[a]);
+  gl.bbox = bb;
+  GridDesc d = grid_make_desc(gl, n);
+  int4* c4 = (int4*)g.cell;   // two cells per 16-byte store (the table is cudaMalloc-aligned)
+  const int n4 = (d.ncells + 1) / 2;
+  for (int c = tid; c < n4; c += nthr) c4[c] = make_int4(0, 0, 0, 0);
+  if (tid == 0) { *g.desc = d; *g.cursor = 0; }
+  return d;
+}
+// Phase 3: cell of every point and its rank inside the cell; re-arms the bounding box for the next build
+__device__ __forceinline__ void gridp_count(const GridBuf& g, const GridDesc& d, int tid, int nthr) {
+  if (tid < 6) g.bbox[tid] = tid < 3 ? 0xffffffffu : 0u;
+  for (int i = tid; i < d.n_points; i += nthr) {
+    float4 p = __ldcg(&g.pts[i]);
+    int cx = grid_cell_coord(p.x, d.ox, d.inv_h, d.nx), cy = grid_cell_coord(p.y, d.oy, d.inv_h, d.ny), cz = grid_cell_coord(p.z, d.oz, d.inv_h, d.nz);
+    int c = (cz * d.ny + cy) * d.nx + cx;
+    g.pt_cell[i] = c;
+    g.pt_rank[i] = atomicAdd(&g.cell[c].y, 1);
+  }
+}
+// Phase 4: one warp per x-row, as grid_alloc
+__device__ __forceinline__ void gridp_alloc(const GridBuf& g, const GridDesc& d, int wid, int nwarps) {
+  const int lane = lane_id();
+  const int nrows = d.ny * d.nz;
+  for (int row = wid; row < nrows; row += nwarps) {
+    int2* cells = g.cell + (size_t)row * d.nx;
+    int tot = 0;
+    for (int x = lane; x < d.nx; x += 32) tot += __ldcg(&cells[x].y);
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+    if (tot == 0) continue;
+    int base = 0;
+    if (lane == 0) base = atomicAdd(g.cursor, tot);
+    int run = __shfl_sync(0xffffffffu, base, 0);
+    for (int x0 = 0; x0 < d.nx; x0 += 32) {
+      int x = x0 + lane;
+      int c = x < d.nx ? __ldcg(&cells[x].y) : 0;
+      int incl = c;
+      for (int o = 1; o < 32; o <<= 1) {
+        int y = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += y;
+      }
+      if (x < d.nx) cells[x].x = run + incl - c;
+      run += __shfl_sync(0xffffffffu, incl, 31);
+    }
+  }
+}
+// Phase 5: counting-sort scatter
+__device__ __forceinline__ void gridp_scatter(const GridBuf& g, const GridDesc& d, int tid, int nthr) {
+  for (int i = tid; i < d.n_points; i += nthr) {
+    int dst = __ldcg(&g.cell[g.pt_cell[i]].x) + g.pt_rank[i];
+    float4 p = __ldcg(&g.pts[i]);
     p.w = __int_as_float(i);
     g.sorted_pts[dst] = p;
   }

@@ -156,19 +156,38 @@ __global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
   __shared__ int s_shift[3], s_center[3];
   __shared__ unsigned char s_fov[125], s_in[125];
   __shared__ int s_ind[125];
-  if (threadIdx.x == 0 && A.phase != 2) {
-    float sum[6];
-    if (A.lo->sum_decoded) { for (int i = 0; i < 6; i++) sum[i] = A.lo->transformSum[i]; }
-    else pm::odometry_msg_roundtrip(A.lo->transformSum, sum);
-    for (int i = 0; i < 6; i++) st->transformSum[i] = sum[i];
-    pm::transformAssociateToMap(st->transformSum, st->transformBefMapped, st->transformAftMapped, st->transformIncre, st->transformTobeMapped);
-    const float* T = st->transformTobeMapped;
-    LMTrig g = lm_trig(T);
-    st->predTrig[0] = g.srx; st->predTrig[1] = g.crx; st->predTrig[2] = g.sry; st->predTrig[3] = g.cry; st->predTrig[4] = g.srz; st->predTrig[5] = g.crz;
-    for (int i = 0; i < 6; i++) st->predT[i] = T[i];
-    float4 py = lm_to_map(make_float4(0.0f, 10.0f, 0.0f, 0.f), g, T);
-    st->pointOnYAxis[0] = py.x; st->pointOnYAxis[1] = py.y; st->pointOnYAxis[2] = py.z;
-    st->stackN2[0] = A.lo->n_corner_last; st->stackN2[1] = A.lo->n_surf_last;
+  if (threadIdx.x < 32 && A.phase != 2) {
+    // pose prediction on one warp: the sines / cosines of the nine input angles of transformAssociateToMap are
+    // evaluated by 18 lanes at once, lane 0 runs the closed forms against the table (pm::transformAssociateToMapV:
+    // same expression trees, same bits)
+    __shared__ float s_ang[16], s_sn[16], s_cs[16];
+    const int lane = threadIdx.x;
+    if (lane == 0) {
+      float sum[6];
+      if (A.lo->sum_decoded) { for (int i = 0; i < 6; i++) sum[i] = A.lo->transformSum[i]; }
+      else pm::odometry_msg_roundtrip(A.lo->transformSum, sum);
+      for (int i = 0; i < 6; i++) st->transformSum[i] = sum[i];
+      for (int i = 0; i < 3; i++) { s_ang[i] = sum[i]; s_ang[3 + i] = st->transformBefMapped[i]; s_ang[6 + i] = st->transformAftMapped[i]; }
+    }
+    __syncwarp();
+    {
+      const int j = lane & 15;
+      if (j < 9) {
+        const float a = s_ang[j];
+        if (lane < 16) s_sn[j] = dm::sin(a); else s_cs[j] = dm::cos(a);
+      }
+      __syncwarp();
+    }
+    if (lane == 0) {
+      pm::transformAssociateToMapV(s_sn, s_cs, st->transformSum, st->transformBefMapped, st->transformAftMapped, st->transformIncre, st->transformTobeMapped);
+      const float* T = st->transformTobeMapped;
+      LMTrig g = lm_trig(T);
+      st->predTrig[0] = g.srx; st->predTrig[1] = g.crx; st->predTrig[2] = g.sry; st->predTrig[3] = g.cry; st->predTrig[4] = g.srz; st->predTrig[5] = g.crz;
+      for (int i = 0; i < 6; i++) st->predT[i] = T[i];
+      float4 py = lm_to_map(make_float4(0.0f, 10.0f, 0.0f, 0.f), g, T);
+      st->pointOnYAxis[0] = py.x; st->pointOnYAxis[1] = py.y; st->pointOnYAxis[2] = py.z;
+      st->stackN2[0] = A.lo->n_corner_last; st->stackN2[1] = A.lo->n_surf_last;
+    }
   }
   if (A.phase == 1) return;
   if (threadIdx.x == 0) {

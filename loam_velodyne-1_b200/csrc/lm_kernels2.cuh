@@ -165,7 +165,10 @@ __device__ __forceinline__ void lm_transform_update(LMState* st, float* T, const
 // finishes the sum (ascending CTA order) and the 6x6 solve, so no broadcast is needed.
 constexpr int LM_CH = 256;   // queries per CTA per pass
 constexpr int LM_KW = 16;    // lanes cooperating on one 5-NN query (8 was measured slower: 22.5 vs 20 us per iteration)
-__global__ void __launch_bounds__(LM_THREADS, 2) lm_optimize(LMOptArgs A) {
+#ifndef LOAM_LM_MAXREG
+#define LOAM_LM_MAXREG 128
+#endif
+__global__ void __maxnreg__(LOAM_LM_MAXREG) lm_optimize(LMOptArgs A) {
   cg::grid_group grid = cg::this_grid();
   __shared__ float s_T[6];
   __shared__ LMTrig s_trig;

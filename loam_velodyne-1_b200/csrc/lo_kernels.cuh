@@ -53,6 +53,17 @@ struct LOArgs {
   int n_scans;
   int fcap;
   int max_iter;
+  int contiguous;               // 1 = contiguous feature slices per CTA (the round-1 assignment), 0 = strided
+  // epilogue of the same kernel: TransformToEnd + swap (:875-899), bookkeeping (:901-903) and the rebuild of
+  // the two indices (:905-906) -- the grid is resident anyway, so the node's tail costs four more grid
+  // barriers instead of seven launches
+  const float4* less_sharp; const float4* less_flat; const float4* full;
+  float4* corner_last_out; float4* surf_last_out; float4* full_end;
+  int do_full;
+  int epilogue;                 // 0 = stop after the pose integration (the tail then runs as separate launches; A/B switch)
+  GridBuf gb[2];
+  const int* ring_counts;       // [n_scans][4] per-ring sizes of the four feature clouds of this sweep
+  int* corner_roff_out; int* surf_roff_out;
 };
 
 // TransformToStart :101-124
@@ -132,6 +143,92 @@ __device__ __forceinline__ float4 lo_transform_to_end(const float4 pi, const flo
   float4 po;
   po.x = dm::cos(imuRollLast) * x11 + dm::sin(imuRollLast) * y11;
   po.y = -dm::sin(imuRollLast) * x11 + dm::cos(imuRollLast) * y11;
+  po.z = z11;
+  po.w = int(pi.w);
+  return po;
+}
+
+struct ToEndConsts { float srx, crx, sry, cry, srz, crz; float s[6], c[6]; };
+// angle j of lo_to_end_consts: 0..2 = transform rx, ry, rz; 3..8 = imuRollStart, imuPitchStart, imuYawStart, imuYawLast, imuPitchLast, imuRollLast
+__device__ __forceinline__ float lo_to_end_angle(int j, const float* transform, const float* imu) {
+  switch (j) {
+    case 0: return transform[0];
+    case 1: return transform[1];
+    case 2: return transform[2];
+    case 3: return imu[2];
+    case 4: return imu[0];
+    case 5: return imu[1];
+    case 6: return imu[4];
+    case 7: return imu[3];
+    default: return imu[5];
+  }
+}
+// 18 threads t = 0..17 of a CTA fill the shared ToEndConsts: t < 9 the sine of angle t, else the cosine of angle t - 9
+__device__ __forceinline__ void lo_to_end_consts(ToEndConsts* k, int t, const float* transform, const float* imu) {
+  if (t >= 18) return;
+  const int j = t % 9;
+  const float a = lo_to_end_angle(j, transform, imu);
+  const float v = t < 9 ? dm::sin(a) : dm::cos(a);
+  float* sv[9] = {&k->srx, &k->sry, &k->srz, &k->s[0], &k->s[1], &k->s[2], &k->s[3], &k->s[4], &k->s[5]};
+  float* cv[9] = {&k->crx, &k->cry, &k->crz, &k->c[0], &k->c[1], &k->c[2], &k->c[3], &k->c[4], &k->c[5]};
+  *(t < 9 ? sv[j] : cv[j]) = v;
+}
+// Same expression tree; the sines / cosines of the nine angles that do not depend on the point (the whole-sweep
+// transform and the six IMU angles) are taken from `k` (lo_to_end_consts), where they were computed by the
+// same functions on the same arguments -- identical bits, 18 fdlibm evaluations per point fewer.
+__device__ __forceinline__ float4 lo_transform_to_end_pre(const float4 pi, const float* transform, const float* imu /*12*/, const ToEndConsts& k) {
+  float s = 10 * (pi.w - int(pi.w));
+  float rx = s * transform[0];
+  float ry = s * transform[1];
+  float rz = s * transform[2];
+  float tx = s * transform[3];
+  float ty = s * transform[4];
+  float tz = s * transform[5];
+  float x1 = dm::cos(rz) * (pi.x - tx) + dm::sin(rz) * (pi.y - ty);
+  float y1 = -dm::sin(rz) * (pi.x - tx) + dm::cos(rz) * (pi.y - ty);
+  float z1 = (pi.z - tz);
+  float x2 = x1;
+  float y2 = dm::cos(rx) * y1 + dm::sin(rx) * z1;
+  float z2 = -dm::sin(rx) * y1 + dm::cos(rx) * z1;
+  float x3 = dm::cos(ry) * x2 - dm::sin(ry) * z2;
+  float y3 = y2;
+  float z3 = dm::sin(ry) * x2 + dm::cos(ry) * z2;
+  rx = transform[0];
+  ry = transform[1];
+  rz = transform[2];
+  tx = transform[3];
+  ty = transform[4];
+  tz = transform[5];
+  float x4 = k.cry * x3 + k.sry * z3;
+  float y4 = y3;
+  float z4 = -k.sry * x3 + k.cry * z3;
+  float x5 = x4;
+  float y5 = k.crx * y4 - k.srx * z4;
+  float z5 = k.srx * y4 + k.crx * z4;
+  float x6 = k.crz * x5 - k.srz * y5 + tx;
+  float y6 = k.srz * x5 + k.crz * y5 + ty;
+  float z6 = z5 + tz;
+  const float imuPitchStart = imu[0], imuYawStart = imu[1], imuRollStart = imu[2];
+  const float imuPitchLast = imu[3], imuYawLast = imu[4], imuRollLast = imu[5];
+  const float imuShiftFromStartX = imu[6], imuShiftFromStartY = imu[7], imuShiftFromStartZ = imu[8];
+  float x7 = k.c[0] * (x6 - imuShiftFromStartX) - k.s[0] * (y6 - imuShiftFromStartY);
+  float y7 = k.s[0] * (x6 - imuShiftFromStartX) + k.c[0] * (y6 - imuShiftFromStartY);
+  float z7 = z6 - imuShiftFromStartZ;
+  float x8 = x7;
+  float y8 = k.c[1] * y7 - k.s[1] * z7;
+  float z8 = k.s[1] * y7 + k.c[1] * z7;
+  float x9 = k.c[2] * x8 + k.s[2] * z8;
+  float y9 = y8;
+  float z9 = -k.s[2] * x8 + k.c[2] * z8;
+  float x10 = k.c[3] * x9 - k.s[3] * z9;
+  float y10 = y9;
+  float z10 = k.s[3] * x9 + k.c[3] * z9;
+  float x11 = x10;
+  float y11 = k.c[4] * y10 + k.s[4] * z10;
+  float z11 = -k.s[4] * y10 + k.c[4] * z10;
+  float4 po;
+  po.x = k.c[5] * x11 + k.s[5] * y11;
+  po.y = -k.s[5] * x11 + k.c[5] * y11;
   po.z = z11;
   po.w = int(pi.w);
   return po;

@@ -98,6 +98,69 @@ __device__ __forceinline__ void lo_integrate(LOState* st, const float* transform
   transformSum[3] = tx; transformSum[4] = ty; transformSum[5] = tz;
 }
 
+// sines and cosines of up to 16 angles, one evaluation per lane: lane l < 16 writes sn[l] = sin(angles[l]),
+// lane 16 + l writes cs[l] = cos(angles[l])
+__device__ __forceinline__ void trig_table_warp(const float* angles, int count, float* sn, float* cs) {
+  const int lane = lane_id(), j = lane & 15;
+  if (j < count) {
+    const float a = angles[j];
+    if (lane < 16) sn[j] = dm::sin(a); else cs[j] = dm::cos(a);
+  }
+  __syncwarp();
+}
+
+// lo_integrate (:830-856) on one warp: the sines / cosines of the input angles of AccumulateRotation and
+// PluginIMURotation are evaluated by the lanes at once (a single thread needs ~0.5 us per fp64 fdlibm call and
+// there are ~45 of them), lane 0 then runs the closed forms against the tables -- same expression trees, and
+// every table entry is what the same function returns for the same argument
+struct LOIntegrateSmem { float ang[16], sn[16], cs[16]; };
+__device__ __forceinline__ void lo_integrate_warp(LOState* st, const float* transform, const float* imu, LOIntegrateSmem* W) {
+  const int lane = lane_id();
+  float* transformSum = st->transformSum;
+  // table 1: cx cy cz lx ly lz of AccumulateRotation, then the six IMU angles (bl*, al* of PluginIMURotation)
+  if (lane == 0) {
+    W->ang[0] = transformSum[0]; W->ang[1] = transformSum[1]; W->ang[2] = transformSum[2];
+    W->ang[3] = -transform[0]; W->ang[4] = -transform[1] * 1.05; W->ang[5] = -transform[2];
+    for (int i = 0; i < 6; i++) W->ang[6 + i] = imu[i];
+  }
+  __syncwarp();
+  trig_table_warp(W->ang, 12, W->sn, W->cs);
+  if (lane == 0) {
+    float rx, ry, rz;
+    pm::AccumulateRotationV(W->sn, W->cs, transformSum[0], transformSum[1], transformSum[2],
+                            -transform[0], -transform[1] * 1.05, -transform[2], rx, ry, rz);
+    W->ang[12] = rx; W->ang[13] = ry; W->ang[14] = rz;
+  }
+  __syncwarp();
+  trig_table_warp(W->ang + 12, 3, W->sn + 12, W->cs + 12);
+  if (lane == 0) {
+    const float imuPitchStart = imu[0], imuYawStart = imu[1], imuRollStart = imu[2];
+    const float imuPitchLast = imu[3], imuYawLast = imu[4], imuRollLast = imu[5];
+    const float imuShiftFromStartX = imu[6], imuShiftFromStartY = imu[7], imuShiftFromStartZ = imu[8];
+    float rx = W->ang[12], ry = W->ang[13], rz = W->ang[14], tx, ty, tz;
+    const float srx = W->sn[12], sry = W->sn[13], srz = W->sn[14], crx = W->cs[12], cry = W->cs[13], crz = W->cs[14];
+    float x1 = crz * (transform[3] - imuShiftFromStartX) - srz * (transform[4] - imuShiftFromStartY);
+    float y1 = srz * (transform[3] - imuShiftFromStartX) + crz * (transform[4] - imuShiftFromStartY);
+    float z1 = transform[5] * 1.05 - imuShiftFromStartZ;
+    float x2 = x1;
+    float y2 = crx * y1 - srx * z1;
+    float z2 = srx * y1 + crx * z1;
+    tx = transformSum[3] - (cry * x2 + sry * z2);
+    ty = transformSum[4] - y2;
+    tz = transformSum[5] - (-sry * x2 + cry * z2);
+    // PluginIMURotation(bc = rx ry rz, bl = imu start angles, al = imu last angles): its table is
+    // [bcx bcy bcz blx bly blz alx aly alz] = table entries 12..14 followed by 6..11
+    float sn9[9], cs9[9];
+    for (int i = 0; i < 3; i++) { sn9[i] = W->sn[12 + i]; cs9[i] = W->cs[12 + i]; }
+    for (int i = 0; i < 6; i++) { sn9[3 + i] = W->sn[6 + i]; cs9[3 + i] = W->cs[6 + i]; }
+    pm::PluginIMURotationV(sn9, cs9, rx, ry, rz, imuPitchStart, imuYawStart, imuRollStart,
+                           imuPitchLast, imuYawLast, imuRollLast, rx, ry, rz);
+    transformSum[0] = rx; transformSum[1] = ry; transformSum[2] = rz;
+    transformSum[3] = tx; transformSum[4] = ty; transformSum[5] = tz;
+  }
+  __syncwarp();
+}
+
 // ---- deterministic reductions shared by lo_optimize and lm_optimize ---------------------------
 // rows: [n][8] floats = a[0..5], b, valid.  28 sums (21 upper AtA, 6 AtB, row count) in fp64.
 constexpr int RED_GROUPS = 8;
@@ -179,7 +242,10 @@ __device__ __forceinline__ void red_finish(cg::grid_group& grid, double acc, dou
 
 // The whole per-sweep LM loop :458-856 as one cooperative kernel.  Every CTA owns a contiguous
 // slice of the features, one warp per feature.
-__global__ void __launch_bounds__(LO_THREADS, 2) lo_optimize(LOArgs A) {
+#ifndef LOAM_LO_MAXREG
+#define LOAM_LO_MAXREG 128
+#endif
+__global__ void __maxnreg__(LOAM_LO_MAXREG) lo_optimize(LOArgs A) {
   cg::grid_group grid = cg::this_grid();
   __shared__ float s_tr[6];
   __shared__ float s_trig[6];
@@ -222,12 +288,18 @@ __global__ void __launch_bounds__(LO_THREADS, 2) lo_optimize(LOArgs A) {
     return;
   }
   const int n_corner_last = st->n_corner_last, n_surf_last = st->n_surf_last;
-  // every CTA owns a contiguous slice of the features (the critical path is the single most
-  // expensive feature, so spreading features over CTAs does not help)
-  const int per = (F + (int)gridDim.x - 1) / (int)gridDim.x;
-  const int f_lo = min((int)blockIdx.x * per, F), nmine = min(f_lo + per, F) - f_lo;
+  // CTA b owns features b, b + G, b + 2G, ...: the corner features (the first n_sharp ones; their two ring
+  // scans make them the expensive ones) are spread evenly over the CTAs instead of filling the first few,
+  // which is what the slowest CTA at the iteration's grid barrier was waiting for.  A.contiguous = contiguous
+  // slices.
+  const int G = (int)gridDim.x;
+  const int per = (F + G - 1) / G;
+  const int f_lo = A.contiguous ? min((int)blockIdx.x * per, F) : (int)blockIdx.x;
+  const int f_step = A.contiguous ? 1 : G;
+  const int nmine = A.contiguous ? min(f_lo + per, F) - f_lo : ((F > (int)blockIdx.x) ? (F - (int)blockIdx.x + G - 1) / G : 0);
   int iters_done = 0;
-  if (st->cornerLastNum > 10 && st->surfLastNum > 100) {  // :465
+  const bool gate = st->cornerLastNum > 10 && st->surfLastNum > 100;  // :465
+  if (gate) {
     for (int iterCount = 0; iterCount < A.max_iter; iterCount++) {
       iters_done = iterCount + 1;
       const bool refresh = (iterCount % 5 == 0);
@@ -241,7 +313,7 @@ __global__ void __launch_bounds__(LO_THREADS, 2) lo_optimize(LOArgs A) {
       long long dbg_t0 = 0;
       if (iterCount == 0 && PHASE_ON && threadIdx.x == 0) dbg_t0 = clock64();
       for (int j0 = 0; j0 < nmine; j0 += LO_WARPS) {
-        const int f = f_lo + j0 + warp;
+        const int f = f_lo + (j0 + warp) * f_step;
         const bool first_pass = (j0 == 0);
         s_row[warp * 32 + lane][7] = 0.f;
         if (j0 + warp < nmine) {
@@ -343,13 +415,110 @@ __global__ void __launch_bounds__(LO_THREADS, 2) lo_optimize(LOArgs A) {
       if (s_stop) break;
     }
   }
+  // without an iteration no grid barrier has been passed yet: the state written below (and by the epilogue)
+  // is still being read by CTAs that are only now starting
+  if (!gate) grid.sync();
+  if (blockIdx.x == 0 && warp == 0) {
+    __shared__ LOIntegrateSmem s_int;
+    lo_integrate_warp(st, s_tr, s_imu, &s_int);
+  }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
-    lo_integrate(st, s_tr, s_imu);
     for (int i = 0; i < 6; i++) st->transform[i] = s_tr[i];
     for (int i = 0; i < 36; i++) st->matP[i] = s_matP[i];
     st->isDegenerate = s_deg;
     st->iters = iters_done;
     st->rows = s_rows;
+  }
+  PS();
+  if (!A.epilogue) {
+    if (clk >= 0) g_phase_clk[0][0] = clk - 1;
+    return;
+  }
+  // ---- epilogue: the node's tail on the grid that is resident anyway.  Every CTA left the loop behind the
+  // same grid barrier, so nobody reads corner_last / surf_last / the two indices any more. ----
+  {
+    __shared__ float s_mn[LO_WARPS][3], s_mx[LO_WARPS][3];
+    __shared__ ToEndConsts s_k;
+    lo_to_end_consts(&s_k, threadIdx.x, s_tr, s_imu);
+    __syncthreads();
+    const ToEndConsts kc = s_k;
+    const int tid = blockIdx.x * LO_THREADS + threadIdx.x, nthr = gridDim.x * LO_THREADS;
+    const int n0 = A.cnt->n_less_sharp, n1 = A.cnt->n_less_flat, n2 = A.do_full ? A.cnt->n_full : 0;
+    // TransformToEnd + swap (:875-899); the bounding boxes of the two new "last" clouds come for free
+    {
+      float mn[3] = {3.0e38f, 3.0e38f, 3.0e38f}, mx[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+      for (int i = tid; i < n0; i += nthr) {
+        const float4 p = lo_transform_to_end_pre(A.less_sharp[i], s_tr, s_imu, kc);
+        A.corner_last_out[i] = p;
+        mn[0] = fminf(mn[0], p.x); mx[0] = fmaxf(mx[0], p.x);
+        mn[1] = fminf(mn[1], p.y); mx[1] = fmaxf(mx[1], p.y);
+        mn[2] = fminf(mn[2], p.z); mx[2] = fmaxf(mx[2], p.z);
+      }
+      bbox_block_commit(A.gb[0].bbox, mn, mx, s_mn, s_mx, LO_WARPS);
+    }
+    {
+      float mn[3] = {3.0e38f, 3.0e38f, 3.0e38f}, mx[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+      for (int i = tid; i < n1; i += nthr) {
+        const float4 p = lo_transform_to_end_pre(A.less_flat[i], s_tr, s_imu, kc);
+        A.surf_last_out[i] = p;
+        mn[0] = fminf(mn[0], p.x); mx[0] = fmaxf(mx[0], p.x);
+        mn[1] = fminf(mn[1], p.y); mx[1] = fmaxf(mx[1], p.y);
+        mn[2] = fminf(mn[2], p.z); mx[2] = fmaxf(mx[2], p.z);
+      }
+      bbox_block_commit(A.gb[1].bbox, mn, mx, s_mn, s_mx, LO_WARPS);
+    }
+    for (int i = tid; i < n2; i += nthr) A.full_end[i] = lo_transform_to_end_pre(A.full[i], s_tr, s_imu, kc);
+    // bookkeeping (:901-903) and the ring offset tables of the clouds that just became the "last" ones
+    if (blockIdx.x == 0 && warp == 0) {
+      for (int T = 0; T < 2; T++) {
+        int* roff = T ? A.surf_roff_out : A.corner_roff_out;
+        const int col = T ? 3 : 1;
+        int run = 0;
+        for (int r0 = 0; r0 < R; r0 += 32) {
+          const int r = r0 + lane;
+          const int c = r < R ? A.ring_counts[r * 4 + col] : 0;
+          int x = c;
+          for (int o = 1; o < 32; o <<= 1) {
+            int y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+          }
+          if (r < R) roff[r] = run + x - c;
+          run += __shfl_sync(0xffffffffu, x, 31);
+        }
+        if (lane == 0) roff[R] = run;
+      }
+      if (lane == 0) {
+        st->n_corner_last = n0; st->n_surf_last = n1;
+        st->cornerLastNum = n0; st->surfLastNum = n1;
+        st->index_enable = (n0 > 10 && n1 > 100) ? 1 : 0;
+        if (A.do_full) st->n_full_end = n2;
+      }
+    }
+    PS();
+    // index rebuild (:905-906: kdtree*Last->setInputCloud), skipped as in the reference's gate at :903
+    if (n0 > 10 && n1 > 100) {
+      __threadfence();
+      grid.sync();
+      const GridDesc d0 = gridp_setup(A.gb[0], n0, tid, nthr);
+      const GridDesc d1 = gridp_setup(A.gb[1], n1, tid, nthr);
+      __threadfence();
+      grid.sync();
+      gridp_count(A.gb[0], d0, tid, nthr);
+      gridp_count(A.gb[1], d1, tid, nthr);
+      __threadfence();
+      grid.sync();
+      const int wid = blockIdx.x * LO_WARPS + warp, nw = gridDim.x * LO_WARPS;
+      gridp_alloc(A.gb[0], d0, wid, nw);
+      gridp_alloc(A.gb[1], d1, wid, nw);
+      __threadfence();
+      grid.sync();
+      gridp_scatter(A.gb[0], d0, tid, nthr);
+      gridp_scatter(A.gb[1], d1, tid, nthr);
+    } else if (blockIdx.x == 0 && threadIdx.x < 12) {
+      // nothing was built: re-arm the two boxes for the next sweep
+      A.gb[threadIdx.x / 6].bbox[threadIdx.x % 6] = (threadIdx.x % 6) < 3 ? 0xffffffffu : 0u;
+    }
+    PS();
   }
   if (clk >= 0) g_phase_clk[0][0] = clk - 1;
 #undef PS

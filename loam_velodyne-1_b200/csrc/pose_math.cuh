@@ -205,5 +205,136 @@ LOAM_HD void transformAssociateToMap(const float transformSum[6], const float tr
   transformTobeMapped[5] = transformAftMapped[5] - (-sin(transformTobeMapped[1]) * x2 + cos(transformTobeMapped[1]) * z2);
 }
 
+
+
+// ---- the same three functions with the sines / cosines of their INPUT angles supplied by the caller --------
+// (identical expression trees, generated from the text above: sin(a) -> sn[i], cos(a) -> cs[i], i = position of
+// the angle in the argument list).  On the device the table is filled by the lanes of a warp at once; each entry
+// is what the same detmath function returns for the same argument, so the results are bit-identical.  Angles
+// that are computed inside (asin / atan2 results) are still evaluated in place.
+LOAM_HD void AccumulateRotationV(const float* sn, const float* cs, float cx, float cy, float cz, float lx, float ly, float lz,
+                                 float& ox, float& oy, float& oz) {
+    float srx = cs[3]*cs[0]*sn[4]*sn[2] - cs[0]*cs[2]*sn[3] - cs[3]*cs[4]*sn[0];
+    ox = -asin(srx);
+    float srycrx = sn[3]*(cs[1]*sn[2] - cs[2]*sn[0]*sn[1]) + cs[3]*sn[4]*(cs[1]*cs[2]
+                 + sn[0]*sn[1]*sn[2]) + cs[3]*cs[4]*cs[0]*sn[1];
+    float crycrx = cs[3]*cs[4]*cs[0]*cs[1] - cs[3]*sn[4]*(cs[2]*sn[1]
+                 - cs[1]*sn[0]*sn[2]) - sn[3]*(sn[1]*sn[2] + cs[1]*cs[2]*sn[0]);
+    oy = atan2(srycrx / cos(ox), crycrx / cos(ox));
+    float srzcrx = sn[0]*(cs[5]*sn[4] - cs[4]*sn[3]*sn[5]) + cs[0]*sn[2]*(cs[4]*cs[5]
+                 + sn[3]*sn[4]*sn[5]) + cs[3]*cs[0]*cs[2]*sn[5];
+    float crzcrx = cs[3]*cs[5]*cs[0]*cs[2] - cs[0]*sn[2]*(cs[4]*sn[5]
+                 - cs[5]*sn[3]*sn[4]) - sn[0]*(sn[4]*sn[5] + cs[4]*cs[5]*sn[3]);
+    oz = atan2(srzcrx / cos(ox), crzcrx / cos(ox));
+  }
+
+LOAM_HD void PluginIMURotationV(const float* sn, const float* cs, float bcx, float bcy, float bcz, float blx, float bly, float blz,
+                                float alx, float aly, float alz, float& acx, float& acy, float& acz) {
+    float sbcx = sn[0]; float cbcx = cs[0]; float sbcy = sn[1]; float cbcy = cs[1];
+    float sbcz = sn[2]; float cbcz = cs[2];
+    float sblx = sn[3]; float cblx = cs[3]; float sbly = sn[4]; float cbly = cs[4];
+    float sblz = sn[5]; float cblz = cs[5];
+    float salx = sn[6]; float calx = cs[6]; float saly = sn[7]; float caly = cs[7];
+    float salz = sn[8]; float calz = cs[8];
+    float srx = -sbcx*(salx*sblx + calx*caly*cblx*cbly + calx*cblx*saly*sbly)
+              - cbcx*cbcz*(calx*saly*(cbly*sblz - cblz*sblx*sbly)
+              - calx*caly*(sbly*sblz + cbly*cblz*sblx) + cblx*cblz*salx)
+              - cbcx*sbcz*(calx*caly*(cblz*sbly - cbly*sblx*sblz)
+              - calx*saly*(cbly*cblz + sblx*sbly*sblz) + cblx*salx*sblz);
+    acx = -asin(srx);
+    float srycrx = (cbcy*sbcz - cbcz*sbcx*sbcy)*(calx*saly*(cbly*sblz - cblz*sblx*sbly)
+                 - calx*caly*(sbly*sblz + cbly*cblz*sblx) + cblx*cblz*salx)
+                 - (cbcy*cbcz + sbcx*sbcy*sbcz)*(calx*caly*(cblz*sbly - cbly*sblx*sblz)
+                 - calx*saly*(cbly*cblz + sblx*sbly*sblz) + cblx*salx*sblz)
+                 + cbcx*sbcy*(salx*sblx + calx*caly*cblx*cbly + calx*cblx*saly*sbly);
+    float crycrx = (cbcz*sbcy - cbcy*sbcx*sbcz)*(calx*caly*(cblz*sbly - cbly*sblx*sblz)
+                 - calx*saly*(cbly*cblz + sblx*sbly*sblz) + cblx*salx*sblz)
+                 - (sbcy*sbcz + cbcy*cbcz*sbcx)*(calx*saly*(cbly*sblz - cblz*sblx*sbly)
+                 - calx*caly*(sbly*sblz + cbly*cblz*sblx) + cblx*cblz*salx)
+                 + cbcx*cbcy*(salx*sblx + calx*caly*cblx*cbly + calx*cblx*saly*sbly);
+    acy = atan2(srycrx / cos(acx), crycrx / cos(acx));
+    float srzcrx = sbcx*(cblx*cbly*(calz*saly - caly*salx*salz)
+                 - cblx*sbly*(caly*calz + salx*saly*salz) + calx*salz*sblx)
+                 - cbcx*cbcz*((caly*calz + salx*saly*salz)*(cbly*sblz - cblz*sblx*sbly)
+                 + (calz*saly - caly*salx*salz)*(sbly*sblz + cbly*cblz*sblx)
+                 - calx*cblx*cblz*salz) + cbcx*sbcz*((caly*calz + salx*saly*salz)*(cbly*cblz
+                 + sblx*sbly*sblz) + (calz*saly - caly*salx*salz)*(cblz*sbly - cbly*sblx*sblz)
+                 + calx*cblx*salz*sblz);
+    float crzcrx = sbcx*(cblx*sbly*(caly*salz - calz*salx*saly)
+                 - cblx*cbly*(saly*salz + caly*calz*salx) + calx*calz*sblx)
+                 + cbcx*cbcz*((saly*salz + caly*calz*salx)*(sbly*sblz + cbly*cblz*sblx)
+                 + (caly*salz - calz*salx*saly)*(cbly*sblz - cblz*sblx*sbly)
+                 + calx*calz*cblx*cblz) - cbcx*sbcz*((saly*salz + caly*calz*salx)*(cblz*sbly
+                 - cbly*sblx*sblz) + (caly*salz - calz*salx*saly)*(cbly*cblz + sblx*sbly*sblz)
+                 - calx*calz*cblx*sblz);
+    acz = atan2(srzcrx / cos(acx), crzcrx / cos(acx));
+  }
+
+LOAM_HD void transformAssociateToMapV(const float* sn, const float* cs, const float transformSum[6], const float transformBefMapped[6],
+                                    const float transformAftMapped[6], float transformIncre[6],
+                                    float transformTobeMapped[6]) {
+  float x1 = cs[1] * (transformBefMapped[3] - transformSum[3])
+           - sn[1] * (transformBefMapped[5] - transformSum[5]);
+  float y1 = transformBefMapped[4] - transformSum[4];
+  float z1 = sn[1] * (transformBefMapped[3] - transformSum[3])
+           + cs[1] * (transformBefMapped[5] - transformSum[5]);
+  float x2 = x1;
+  float y2 = cs[0] * y1 + sn[0] * z1;
+  float z2 = -sn[0] * y1 + cs[0] * z1;
+  transformIncre[3] = cs[2] * x2 + sn[2] * y2;
+  transformIncre[4] = -sn[2] * x2 + cs[2] * y2;
+  transformIncre[5] = z2;
+  float sbcx = sn[0]; float cbcx = cs[0];
+  float sbcy = sn[1]; float cbcy = cs[1];
+  float sbcz = sn[2]; float cbcz = cs[2];
+  float sblx = sn[3]; float cblx = cs[3];
+  float sbly = sn[4]; float cbly = cs[4];
+  float sblz = sn[5]; float cblz = cs[5];
+  float salx = sn[6]; float calx = cs[6];
+  float saly = sn[7]; float caly = cs[7];
+  float salz = sn[8]; float calz = cs[8];
+  float srx = -sbcx*(salx*sblx + calx*caly*cblx*cbly + calx*cblx*saly*sbly)
+            - cbcx*cbcz*(calx*saly*(cbly*sblz - cblz*sblx*sbly)
+            - calx*caly*(sbly*sblz + cbly*cblz*sblx) + cblx*cblz*salx)
+            - cbcx*sbcz*(calx*caly*(cblz*sbly - cbly*sblx*sblz)
+            - calx*saly*(cbly*cblz + sblx*sbly*sblz) + cblx*salx*sblz);
+  transformTobeMapped[0] = -asin(srx);
+  float srycrx = (cbcy*sbcz - cbcz*sbcx*sbcy)*(calx*saly*(cbly*sblz - cblz*sblx*sbly)
+               - calx*caly*(sbly*sblz + cbly*cblz*sblx) + cblx*cblz*salx)
+               - (cbcy*cbcz + sbcx*sbcy*sbcz)*(calx*caly*(cblz*sbly - cbly*sblx*sblz)
+               - calx*saly*(cbly*cblz + sblx*sbly*sblz) + cblx*salx*sblz)
+               + cbcx*sbcy*(salx*sblx + calx*caly*cblx*cbly + calx*cblx*saly*sbly);
+  float crycrx = (cbcz*sbcy - cbcy*sbcx*sbcz)*(calx*caly*(cblz*sbly - cbly*sblx*sblz)
+               - calx*saly*(cbly*cblz + sblx*sbly*sblz) + cblx*salx*sblz)
+               - (sbcy*sbcz + cbcy*cbcz*sbcx)*(calx*saly*(cbly*sblz - cblz*sblx*sbly)
+               - calx*caly*(sbly*sblz + cbly*cblz*sblx) + cblx*cblz*salx)
+               + cbcx*cbcy*(salx*sblx + calx*caly*cblx*cbly + calx*cblx*saly*sbly);
+  transformTobeMapped[1] = atan2(srycrx / cos(transformTobeMapped[0]), crycrx / cos(transformTobeMapped[0]));
+  float srzcrx = sbcx*(cblx*cbly*(calz*saly - caly*salx*salz)
+               - cblx*sbly*(caly*calz + salx*saly*salz) + calx*salz*sblx)
+               - cbcx*cbcz*((caly*calz + salx*saly*salz)*(cbly*sblz - cblz*sblx*sbly)
+               + (calz*saly - caly*salx*salz)*(sbly*sblz + cbly*cblz*sblx)
+               - calx*cblx*cblz*salz) + cbcx*sbcz*((caly*calz + salx*saly*salz)*(cbly*cblz
+               + sblx*sbly*sblz) + (calz*saly - caly*salx*salz)*(cblz*sbly - cbly*sblx*sblz)
+               + calx*cblx*salz*sblz);
+  float crzcrx = sbcx*(cblx*sbly*(caly*salz - calz*salx*saly)
+               - cblx*cbly*(saly*salz + caly*calz*salx) + calx*calz*sblx)
+               + cbcx*cbcz*((saly*salz + caly*calz*salx)*(sbly*sblz + cbly*cblz*sblx)
+               + (caly*salz - calz*salx*saly)*(cbly*sblz - cblz*sblx*sbly)
+               + calx*calz*cblx*cblz) - cbcx*sbcz*((saly*salz + caly*calz*salx)*(cblz*sbly
+               - cbly*sblx*sblz) + (caly*salz - calz*salx*saly)*(cbly*cblz + sblx*sbly*sblz)
+               - calx*calz*cblx*sblz);
+  transformTobeMapped[2] = atan2(srzcrx / cos(transformTobeMapped[0]), crzcrx / cos(transformTobeMapped[0]));
+  x1 = cos(transformTobeMapped[2]) * transformIncre[3] - sin(transformTobeMapped[2]) * transformIncre[4];
+  y1 = sin(transformTobeMapped[2]) * transformIncre[3] + cos(transformTobeMapped[2]) * transformIncre[4];
+  z1 = transformIncre[5];
+  x2 = x1;
+  y2 = cos(transformTobeMapped[0]) * y1 - sin(transformTobeMapped[0]) * z1;
+  z2 = sin(transformTobeMapped[0]) * y1 + cos(transformTobeMapped[0]) * z1;
+  transformTobeMapped[3] = transformAftMapped[3] - (cos(transformTobeMapped[1]) * x2 + sin(transformTobeMapped[1]) * z2);
+  transformTobeMapped[4] = transformAftMapped[4] - y2;
+  transformTobeMapped[5] = transformAftMapped[5] - (-sin(transformTobeMapped[1]) * x2 + cos(transformTobeMapped[1]) * z2);
+}
+
 }  // namespace pm
 }  // namespace loamgpu

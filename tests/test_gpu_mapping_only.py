@@ -142,6 +142,50 @@ def test_mapping_only_stress_prepopulated_map_parity(pkg, checker, synth, tmp_pa
         assert np.array_equal(M.cloud(10, cap=1 << 21).view(np.uint32), C.cloud(10, cap=1 << 21).view(np.uint32)), i
 
 
+def test_mapping_only_at_the_benchmarked_map_size(pkg, checker, synth, tmp_path):
+    """BASELINE.json configs[2] at the size bench.py --workload mapstress times: 260 HDL-64 sweeps of recorded
+    laserOdometry output replayed on eight parallel streets (~1.4 M local-map points), the map handed to the
+    oracle as a file, then six further passes on both sides: poses, iteration / row counts, the 5-NN index
+    lists of the last iteration, the gathered local map and the stack clouds bit-equal; at the end the two
+    map files agree cube by cube.  (The 8-CTA-cluster refilter, the arena compaction and the bounded 5-NN
+    re-search are the parts most likely to diverge late -- this is where they would.)"""
+    rec = record_lm_inputs_gpu(pkg, synth, 2, 260)
+    P = pkg.make_params(2, system_delay=0)
+    M = pkg.LaserMapping(P)
+    t = 0.0
+    offsets = [((j + 1) // 2) * 18.0 * (1.0 if j % 2 else -1.0) for j in range(8)]     # bench._lateral_offsets(8)
+    for dx in offsets:
+        for r in rec:
+            c, s, f, tsum, st = shifted(r, dx, t)
+            assert M.process_host(c, s, f, tsum, st) == 0
+        t += 100.0
+    path = str(tmp_path / "prepopulated.loammap")
+    M.save_map(path)
+    C = checker.Checker(checker.make_params(2), "port")
+    C.lm_load_map(path)
+    n_map = 0
+    for i, r in enumerate(rec[30:36]):
+        c, s, f, tsum, stamp = shifted(r, 0.0, t + 0.2 * i)
+        o = C.lm_push(c, s, f, tsum, stamp)
+        assert M.process_host(c, s, f, tsum, stamp) == 0
+        aft, bef, tobe, st = M.state()
+        assert o.lm_iters > 0
+        assert biteq(aft, o.transform_aft_mapped[:]) and biteq(bef, o.transform_bef_mapped[:]), i
+        assert (st[0], st[1], st[3], st[4], st[5], st[6]) == (o.lm_iters, o.lm_rows, o.n_map_corner, o.n_map_surf, o.n_stack_corner, o.n_stack_surf), i
+        n_map = o.n_map_corner + o.n_map_surf
+        assert np.array_equal(M.ints(100), C.ints(100)) and np.array_equal(M.ints(101), C.ints(101)), i
+        for w in (10, 11, 12, 13):
+            assert np.array_equal(M.cloud(w, cap=1 << 21).view(np.uint32), C.cloud(w, cap=1 << 21).view(np.uint32)), (i, w)
+    assert n_map > 1_000_000, n_map
+    g_path, o_path = str(tmp_path / "g.loammap"), str(tmp_path / "o.loammap")
+    M.save_map(g_path)
+    C.lm_save_map(o_path)
+    fg, fo = read_map_file(g_path), read_map_file(o_path)
+    for T in range(2):
+        assert np.array_equal(fg["cnt"][T], fo["cnt"][T]), T
+        assert np.array_equal(fg["pts"][T].view(np.uint32), fo["pts"][T].view(np.uint32)), T
+
+
 def test_map_window_shifts_keep_parity(pkg, checker, synth, tmp_path):
     """the 21x11x21 cube window follows the pose (laserMapping.cpp:454-614): odometry jumps of several
     hundred metres along every axis, in both directions, shift the descriptor table by up to eight cubes

@@ -66,3 +66,51 @@ def test_concurrent_pipelines_from_host_threads_equal_sequential_runs(pkg, synth
     for s in range(n_seq):
         assert out[s] == ref[s], s
     assert len({tuple(v) for v in ref.values()}) == n_seq   # the sequences really differ
+
+
+def test_all_64_sequences_on_sub_grids_equal_the_oracle(pkg, checker, synth):
+    """BASELINE.json configs[4] as bench.py --workload seq64 runs it: the 64 seeds (1000..1063), 20 sweeps
+    each, one pipeline per sequence on ONE GPU with the cooperative LM kernels on 37-CTA sub-grids, fed by 8
+    host threads -- every pose and iteration count of every sequence against the oracle (run on host threads
+    beside it; ctypes releases the GIL)"""
+    n_seq, nsw, n_threads = 64, 20, 8
+    P = pkg.make_params(1, system_delay=0)
+    P.map_arena_points = 1 << 20
+    P.coop_ctas = 37
+    data = {}
+    for s in range(n_seq):
+        S = synth.Synth(1, seed=1000 + s, threads=2)
+        data[s] = [S.sweep(k) for k in range(nsw)]
+    pipes = {s: pkg.Pipeline(P) for s in range(n_seq)}
+    got = {s: [] for s in range(n_seq)}
+    want = {s: [] for s in range(n_seq)}
+    errs = []
+
+    def gpu_worker(group):
+        try:
+            for k in range(nsw):
+                for s in group:
+                    pipes[s].push_async(data[s][k][0], data[s][k][1])
+            for s in group:
+                got[s] = [_bits(r) for r in pipes[s].collect()]
+        except Exception as e:
+            errs.append(e)
+
+    def cpu_worker(group):
+        try:
+            for s in group:
+                C = checker.Checker(checker.make_params(1), "port")
+                want[s] = [_bits(C.push(x, st)) for x, st in data[s]]
+                C.close()
+        except Exception as e:
+            errs.append(e)
+
+    ths = [threading.Thread(target=gpu_worker, args=([s for s in range(n_seq) if s % n_threads == t],)) for t in range(n_threads)]
+    ths += [threading.Thread(target=cpu_worker, args=([s for s in range(n_seq) if s % n_threads == t],)) for t in range(n_threads)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    assert not errs, errs
+    for s in range(n_seq):
+        assert len(got[s]) == nsw and got[s] == want[s], s
