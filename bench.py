@@ -703,7 +703,7 @@ def main():
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--workload", default="hdl64", choices=sorted(WORKLOADS))
     ap.add_argument("--host-threads", type=int, default=8, help="seq64: host threads feeding the pipelines of one GPU")
-    ap.add_argument("--dev-flags", type=int, default=0, help="development A/B switches passed through loam_params.reserved[0] (0 = the shipped configuration)")
+    ap.add_argument("--dev-flags", type=int, default=0, help="development A/B switches passed through loam_params.dev_flags (0 = the shipped configuration)")
     ap.add_argument("--coop-ctas", type=int, default=None, help="CTAs of the cooperative LM kernels per pipeline (0 = one per SM; default 37 for seq64, else 0)")
     args = ap.parse_args()
     # a pipeline runs on 6 streams (copy, registration, odometry, mapping + side streams) and seq64 on
@@ -755,7 +755,7 @@ def main():
     P = pkg.make_params(preset, system_delay=0)
     if args.coop_ctas:
         P.coop_ctas = args.coop_ctas
-    P.reserved[0] = args.dev_flags
+    P.dev_flags = args.dev_flags
     G = pkg.Pipeline(P, device=local_rank)
     sampler = ClockSampler(local_rank, enabled=(rank == 0))
     sampler.start()
@@ -865,29 +865,40 @@ def main():
            "sync": {"value": world * K / float(e2e_t[1].item()), "unit": "sweeps/s", "api": "loam_pipeline_push (returns the sweep's poses)",
                     "p50_ms_per_sweep": 1e3 * statistics.median(lat), "p99_ms_per_sweep": 1e3 * float(np.percentile(lat, 99))}}
 
-    if args.workload == "vlp16":
-        # raw-packet front end: the same stream as the sensor's own 1206-byte UDP payloads (3.1 B per point over PCIe)
+    if args.workload in ("vlp16", "hdl64"):
+        # raw-packet front end: the same stream as the sensor's own 1206-byte UDP payloads
+        # (3.1 B per point over PCIe instead of 12), decoded on the device; packet_metadata = 1 takes ring id and
+        # relTime from the packet fields (no atan / atan2 / halfPassed), 0 runs the reference's SR-1 on the decoded cloud
         synth = importlib.import_module(PKG + ".synth")
-        pks = [torch.from_numpy(synth.vlp16_packets(x, st)).pin_memory() for x, st in sweeps]
+        if args.workload == "vlp16":
+            pks = [torch.from_numpy(synth.vlp16_packets(x, st)).pin_memory() for x, st in sweeps]
+        else:
+            Sg = synth.Synth(preset, seed=seed0 + rank)
+            pks = [torch.from_numpy(synth.hdl64_packets(*Sg.sweep_grid(k))).pin_memory() for k in range(total)]
         pkn = [t.numpy() for t in pks]
-        G3 = pkg.Pipeline(P, device=local_rank)
-        for k in range(W):
-            G3.push_packets_async(pkn[k], sweeps[k][1])
-        G3.collect()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        n_res = 0
-        for k in range(W, total):
-            G3.push_packets_async(pkn[k], sweeps[k][1])
-            if (k - W) % 128 == 127:
-                n_res += len(G3.collect())
-        n_res += len(G3.collect())
-        torch.cuda.synchronize()
-        pk_s = time.perf_counter() - t0
-        e2e["packets"] = {"value": world * K / pk_s, "unit": "sweeps/s", "h2d_bytes_per_step": int(pkn[0].size),
-                          "api": "loam_pipeline_push_packets_async per revolution (75 VLP-16 data packets, decoded on the device) + loam_pipeline_collect",
-                          "results": n_res}
-        del G3
+        e2e["packets"] = {}
+        for meta in (1, 0):
+            Pp = pkg.make_params(preset, system_delay=0)
+            Pp.packet_metadata = meta
+            Pp.dev_flags = args.dev_flags
+            G3 = pkg.Pipeline(Pp, device=local_rank)
+            for k in range(W):
+                G3.push_packets_async(pkn[k], sweeps[k][1])
+            G3.collect()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            n_res = 0
+            for k in range(W, total):
+                G3.push_packets_async(pkn[k], sweeps[k][1])
+                if (k - W) % 128 == 127:
+                    n_res += len(G3.collect())
+            n_res += len(G3.collect())
+            torch.cuda.synchronize()
+            pk_s = time.perf_counter() - t0
+            e2e["packets"]["packet_metadata=%d" % meta] = {"value": K / pk_s, "unit": "sweeps/s (this rank)", "h2d_bytes_per_step": int(pkn[0].size), "results": n_res}
+            del G3
+        e2e["packets"]["api"] = "loam_pipeline_push_packets_async per revolution (%d %s data packets, decoded on the device) + loam_pipeline_collect" % (
+            pkn[0].shape[0], "VLP-16" if args.workload == "vlp16" else "HDL-64E")
 
     # ---------------- per-kernel device time (separate pass, CUDA events around every launch) ----
     roofline = None

@@ -40,7 +40,14 @@ typedef struct loam_params {
   int map_arena_points; /* product only: capacity of each cube-map arena, in points               */
   int coop_ctas;        /* product only: CTAs of the persistent cooperative LM kernels (0 = one per SM); */
                         /* smaller grids let several handles' kernels run side by side (configs[4])   */
-  int reserved[6];
+  int dev_flags;        /* product only: development A/B switches (0 = the shipped configuration)            */
+  int packet_metadata;  /* raw-packet front end (loam_*_packets): 0 = decode the packets to xyz and run the     */
+                        /* reference's SR-1 unchanged (ring from atan, relTime from atan2 + halfPassed,          */
+                        /* scanRegistration.cpp:248-284); 1 = ring id from the laser id and relTime from the     */
+                        /* packet's azimuth field, fused with the decoder: no atan / atan2 per point, no        */
+                        /* halfPassed scan (csrc/pk_decode.cuh states the arithmetic and   */
+                        /* its difference to the reference)                                                     */
+  int reserved[4];
 } loam_params;
 
 /* preset: 1 = VLP-16 (reference defaults), 2 = HDL-64E, 4 = 128-ring (BASELINE.json configs) */
@@ -116,6 +123,8 @@ int loam_sr_process(loam_sr* h, const float* xyz, int n, int stride_bytes, doubl
  * the device (csrc/pk_decode.cuh states the arithmetic: the published packet format with an ideal
  * calibration, azimuth interpolated inside a block pair as the velodyne_pointcloud driver does);
  * no-return slots become NaN and are dropped by the node's NaN filter (:228). */
+#define LOAM_PACKET_BYTES 1206             /* VLP-16 and HDL-64E data packets alike */
+#define LOAM_POINTS_PER_PACKET 384
 #define LOAM_VLP16_PACKET_BYTES 1206
 #define LOAM_VLP16_POINTS_PER_PACKET 384
 int loam_sr_process_packets(loam_sr* h, const unsigned char* packets, int n_packets, double stamp);

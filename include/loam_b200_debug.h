@@ -28,6 +28,11 @@ int loam_debug_solve_step(const float* AtA, const float* AtB, int batch, float t
 int loam_debug_matp(void* node, int which, float out36[36]);
 /* the device packet decoder alone: xyz receives n_packets * 384 points (3 floats each, NaN = no return) */
 int loam_debug_decode_packets(const unsigned char* packets, int n_packets, float* xyz);
+/* the packet front end of the sensor `p` describes (16 rings / ring_model 0 = VLP-16, 64 rings / ring_model 1 =
+ * HDL-64E): decoded xyz per slot and, when ring and reltime are given, ring id and relTime as
+ * loam_params.packet_metadata = 1 derives them from the packet fields (ring -1 = no return) */
+int loam_debug_packet_front_end(const loam_params* p, const unsigned char* packets, int n_packets, float* xyz, int* ring,
+                                float* reltime);
 int loam_debug_sort_pairs(unsigned int* keys, unsigned int* vals, int n);
 int loam_debug_voxel_filter(const float* xyzi, int n, float leaf, float* out, int cap_out, int* n_out);
 /* same filter through the one-kernel cooperative path laserMapping uses for the incoming sweep */

@@ -29,7 +29,8 @@ class LoamParams(ctypes.Structure):
                 ("ring_lower_deg", ctypes.c_float), ("ring_upper_deg", ctypes.c_float),
                 ("max_points", ctypes.c_int), ("system_delay", ctypes.c_int),
                 ("lo_max_iter", ctypes.c_int), ("lm_max_iter", ctypes.c_int),
-                ("map_arena_points", ctypes.c_int), ("coop_ctas", ctypes.c_int), ("reserved", ctypes.c_int * 6)]
+                ("map_arena_points", ctypes.c_int), ("coop_ctas", ctypes.c_int),
+                ("dev_flags", ctypes.c_int), ("packet_metadata", ctypes.c_int), ("reserved", ctypes.c_int * 4)]
 
 
 class SweepResult(ctypes.Structure):
@@ -90,6 +91,7 @@ def lib():
     L.loam_pipeline_push_packets.argtypes = [vp, vp, ci, cd, ctypes.POINTER(SweepResult)]
     L.loam_pipeline_push_packets_async.argtypes = [vp, vp, ci, cd]
     L.loam_debug_decode_packets.argtypes = [vp, ci, vp]
+    L.loam_debug_packet_front_end.argtypes = [ctypes.POINTER(LoamParams), vp, ci, vp, vp, vp]
     L.loam_sr_download.argtypes = [vp, ci, vp, ci, ctypes.POINTER(ci)]
     L.loam_sr_download_ints.argtypes = [vp, ci, vp, ci, ctypes.POINTER(ci)]
     L.loam_sr_download_floats.argtypes = [vp, ci, vp, ci, ctypes.POINTER(ci)]
@@ -185,6 +187,19 @@ def decode_packets(packets):
     out = np.empty((pk.shape[0] * 384, 3), np.float32)
     _check(lib().loam_debug_decode_packets(pk.ctypes.data, pk.shape[0], out.ctypes.data))
     return out
+
+
+def packet_front_end(params, packets, metadata=False):
+    """test hook: the device packet front end of the sensor `params` describes (VLP-16 or HDL-64E) -> xyz (n, 3)
+    and, with metadata=True, ring ids and relTime as loam_params.packet_metadata = 1 derives them"""
+    pk = _packets(packets)
+    n = pk.shape[0] * 384
+    xyz = np.empty((n, 3), np.float32)
+    ring = np.empty(n, np.int32) if metadata else None
+    rt = np.empty(n, np.float32) if metadata else None
+    _check(lib().loam_debug_packet_front_end(ctypes.byref(params), pk.ctypes.data, pk.shape[0], xyz.ctypes.data,
+                                             ring.ctypes.data if metadata else None, rt.ctypes.data if metadata else None))
+    return (xyz, ring, rt) if metadata else xyz
 
 
 class _Node:

@@ -94,7 +94,7 @@ struct LOHandle {
     A.corner_ind1 = d_c1.p; A.corner_ind2 = d_c2.p; A.surf_ind1 = d_s1.p; A.surf_ind2 = d_s2.p; A.surf_ind3 = d_s3.p;
     A.coeff = d_coeff.p; A.row_valid = d_row_valid.p; A.partials = d_partials.p; A.imu = imu;
     A.corner_roff = d_corner_roff.p; A.surf_roff = d_surf_roff.p; A.n_scans = P.n_scans;
-    A.fcap = fcap; A.max_iter = P.lo_max_iter; A.contiguous = (P.reserved[0] & 1) ? 0 : 1;   // dev flag bit 0: strided assignment (measured slower: neighbouring features share cells)
+    A.fcap = fcap; A.max_iter = P.lo_max_iter; A.contiguous = (P.dev_flags & 1) ? 0 : 1;   // dev flag bit 0: strided assignment (measured slower: neighbouring features share cells)
     frameCount++;  // :885
     const int do_full = frameCount >= skipFrameNum + 1 ? 1 : 0;
     A.less_sharp = sr.d_less_sharp.p; A.less_flat = sr.d_less_flat.p; A.full = sr.d_full.p;
@@ -104,7 +104,7 @@ struct LOHandle {
     // launch rate is the limit (coop_ctas > 0) -- or as separate small kernels that trickle into whatever the two
     // gang-scheduled persistent kernels leave free, which is +5 % throughput for ONE stream on a whole GPU
     // (measured: 4130-4190 vs 3930 sweeps/s, HDL-64).  Dev flags: bit 2 forces the separate kernels, bit 3 the epilogue.
-    A.epilogue = (P.reserved[0] & 4) ? 0 : ((P.reserved[0] & 8) ? 1 : (P.coop_ctas > 0 ? 1 : 0));
+    A.epilogue = (P.dev_flags & 4) ? 0 : ((P.dev_flags & 8) ? 1 : (P.coop_ctas > 0 ? 1 : 0));
     A.gb[0] = gp.g[0]; A.gb[1] = gp.g[1];
     A.ring_counts = sr.d_ring_counts.p; A.corner_roff_out = d_corner_roff.p; A.surf_roff_out = d_surf_roff.p;
     {

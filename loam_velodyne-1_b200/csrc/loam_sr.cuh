@@ -244,11 +244,21 @@ struct SRHandle {
     return rc;
   }
 
-  // raw-packet front end: `n_packets` VLP-16 data packets (1206 B each, HOST memory) holding one
-  // revolution.  The bytes go through the same staging ring / copy stream as an xyz sweep, are decoded
-  // by pk_decode_vlp16 on the node's stream, and the decoded points feed the unchanged node.
+  // raw-packet front end: `n_packets` Velodyne data packets (1206 B each, HOST memory) holding one revolution;
+  // VLP-16 format for a 16-ring handle, HDL-64E format for a 64-ring one.  The bytes go through the same
+  // staging ring / copy stream as an xyz sweep.  packet_metadata = 0: pk_decode writes the xyz cloud and the
+  // unchanged node follows; 1: pk_ring_meta also delivers ring ids and relTime from the packet fields, and
+  // sr_ring_ori (atan / atan2 per point, halfPassed) is not run at all.
+  bool packet_sensor(pk::SensorDesc* S) const {
+    S->n_scans = P.n_scans; S->lower_deg = P.ring_lower_deg; S->upper_deg = P.ring_upper_deg;
+    if (P.n_scans == 16 && P.ring_model == 0) { S->kind = pk::VLP16; return true; }
+    if (P.n_scans == 64 && P.ring_model == 1) { S->kind = pk::HDL64E; return true; }
+    return false;
+  }
   int process_packets(const unsigned char* packets, int n_packets, double stamp) {
     processed = false;
+    pk::SensorDesc S;
+    if (!packet_sensor(&S)) { set_error("no packet format for n_scans=%d ring_model=%d (VLP-16: 16 / 0, HDL-64E: 64 / 1)", P.n_scans, P.ring_model); return LOAM_ERR_ARG; }
     if (!systemInited) {  // :213-219
       systemInitCount++;
       if (systemInitCount >= P.system_delay) systemInited = true;
@@ -268,24 +278,41 @@ struct SRHandle {
     memcpy(st, packets, bytes);
     // first / last return of the revolution (scanRegistration.cpp:230-232 reads them on the host)
     int first = -1, lastf = -1;
-    float p0[3], pl[3];
-    for (int i = 0; i < n && first < 0; i++)
-      if (pk::decode_point(st + (size_t)(i / pk::POINTS_PER_PACKET) * pk::PACKET_BYTES, i % pk::POINTS_PER_PACKET, p0)) first = i;
-    for (int i = n - 1; i >= 0 && lastf < 0; i--)
-      if (pk::decode_point(st + (size_t)(i / pk::POINTS_PER_PACKET) * pk::PACKET_BYTES, i % pk::POINTS_PER_PACKET, pl)) lastf = i;
+    pk::Slot s0, sl;
+    for (int i = 0; i < n && first < 0; i++) {
+      s0 = pk::decode_slot(st + (size_t)(i / pk::POINTS_PER_PACKET) * pk::PACKET_BYTES, i % pk::POINTS_PER_PACKET, S);
+      if (s0.valid) first = i;
+    }
+    for (int i = n - 1; i >= 0 && lastf < 0; i--) {
+      sl = pk::decode_slot(st + (size_t)(i / pk::POINTS_PER_PACKET) * pk::PACKET_BYTES, i % pk::POINTS_PER_PACKET, S);
+      if (sl.valid) lastf = i;
+    }
     if (first < 0) return LOAM_NOT_READY;
     float startOri, endOri;
-    sweep_orientation(p0, pl, startOri, endOri);
+    sweep_orientation(s0.xyz, sl.xyz, startOri, endOri);
     unsigned char* d_pk = (unsigned char*)d_raw2[b].p;
     CUDA_OK(cudaStreamWaitEvent(copy_stream, ev_free[b], 0));
     CUDA_OK(cudaMemcpyAsync(d_pk, st, bytes, cudaMemcpyHostToDevice, copy_stream));
     CUDA_OK(cudaEventRecord(ev_copied[b], copy_stream));
     CUDA_OK(cudaStreamWaitEvent(stream, ev_copied[b], 0));
-    LAUNCH("pk_decode_vlp16", pk_decode_vlp16, n_packets < 1184 ? n_packets : 1184, 384, 0, stream, d_pk, n_packets, d_decoded.p);
-    CUDA_OK(cudaEventRecord(ev_free[b], stream));   // the packet bytes are consumed; d_decoded is ordered on `stream`
     d_raw_cur = d_decoded.p;
+    if (P.packet_metadata) {
+      pk::MetaSpan M;
+      M.first = first; M.last = lastf; M.az0 = s0.az; M.span = 0;
+      M.span = pk::meta_daz(lastf, sl.az, M);
+      meta_packets = d_pk; meta_n_packets = n_packets; meta_sensor = S; meta_span = M;
+      int rc = process_device(n, first, startOri, endOri, stamp, true);
+      CUDA_OK(cudaEventRecord(ev_free[b], stream));   // the packet bytes are consumed by pk_ring_meta
+      return rc;
+    }
+    LAUNCH("pk_decode", pk_decode, (n + 255) / 256 < 1184 ? (n + 255) / 256 : 1184, 256, 0, stream, d_pk, n_packets, S, d_decoded.p);
+    CUDA_OK(cudaEventRecord(ev_free[b], stream));   // the packet bytes are consumed; d_decoded is ordered on `stream`
     return process_device(n, first, startOri, endOri, stamp);
   }
+  const unsigned char* meta_packets = nullptr;
+  int meta_n_packets = 0;
+  pk::SensorDesc meta_sensor;
+  pk::MetaSpan meta_span;
 
   // :230-238
   static void sweep_orientation(const float* p0, const float* pl, float& startOri, float& endOri) {
@@ -316,7 +343,7 @@ struct SRHandle {
     return process_device(n, first, startOri, endOri, stamp);
   }
 
-  int process_device(int n, int first, float startOri, float endOri, double stamp) {
+  int process_device(int n, int first, float startOri, float endOri, double stamp, bool from_packet_metadata = false) {
     const int R = P.n_scans;
     const int nblk = (n + SR_BLK - 1) / SR_BLK;
     select_bank(cur_bank ^ 1);
@@ -327,11 +354,15 @@ struct SRHandle {
     init.h_min = INT_MAX;
     init.last_valid = -1;
     if (h_cnt_init.upload(d_cnt.p, init, stream) != LOAM_OK) { set_error("counter upload failed"); return LOAM_ERR_CUDA; }
-    LAUNCH("sr_ring_ori", sr_ring_ori, nblk, SR_BLK, 0, stream, d_raw_cur, n, 3, Pd, startOri, d_ring.p, d_ori.p, d_hist.p, nblk, d_cnt.p);
+    if (from_packet_metadata)
+      LAUNCH("pk_ring_meta", pk_ring_meta, nblk, SR_BLK, 0, stream, meta_packets, meta_n_packets, meta_sensor, meta_span, d_decoded.p, d_ring.p, d_ori.p,
+             d_hist.p, nblk, d_cnt.p);
+    else
+      LAUNCH("sr_ring_ori", sr_ring_ori, nblk, SR_BLK, 0, stream, d_raw_cur, n, 3, Pd, startOri, d_ring.p, d_ori.p, d_hist.p, nblk, d_cnt.p);
     LAUNCH("sr_ring_scan", sr_ring_scan, R, RSC_THREADS, 0, stream, d_hist.p, nblk, R, d_ring_start.p, d_scan_start.p, d_scan_end.p, d_cnt.p, cap,
            d_ring_tot.p, d_scan_ticket.p);
     LAUNCH("sr_scatter", sr_scatter, nblk, SR_BLK, 0, stream, d_raw_cur, n, 3, Pd, startOri, endOri, d_ring.p, d_ori.p, d_hist.p, d_ring_start.p, nblk,
-           d_cnt.p, d_full.p, d_pos.p, d_reltime.p);
+           d_cnt.p, d_full.p, d_pos.p, d_reltime.p, from_packet_metadata ? 1 : 0);
     if (has_imu && imu.pointer_last >= 0) {  // :286
       if (h_imu.upload(d_imu.p, imu, stream) != LOAM_OK) { set_error("imu upload failed"); return LOAM_ERR_CUDA; }
       ImuState* st_in = d_imu_state.p + imu_parity;

@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(SR_BLK) sr_scatter(const float* __restrict__ r
                                                      const short* __restrict__ ring, const float* __restrict__ ori_raw,
                                                      const int* __restrict__ base, const int* __restrict__ ring_start, int nblk,
                                                      const SRCounts* cnt, float4* __restrict__ full, int* __restrict__ pos_out,
-                                                     float* __restrict__ reltime_out) {
+                                                     float* __restrict__ reltime_out, int meta = 0) {
   __shared__ unsigned short wcount[SR_BLK / 32][SR_MAX_RINGS];
   for (int k = threadIdx.x; k < (SR_BLK / 32) * SR_MAX_RINGS; k += SR_BLK) (&wcount[0][0])[k] = 0;
   __syncthreads();
@@ -248,14 +248,19 @@ __global__ void __launch_bounds__(SR_BLK) sr_scatter(const float* __restrict__ r
     int pos = ring_start[rid] + base[rid * nblk + blockIdx.x] + off + rank_in_warp;
     const float* p = raw + (size_t)i * stride_floats;
     float px = p[1], py = p[2], pz = p[0];
-    float ori = ori_raw[i];
-    if (i <= cnt->h_min) {
-      bool latch;
-      ori = sr_ori_branch_a(ori, startOri, &latch);
+    float relTime;
+    if (meta) {   // packet metadata front end (pk_ring_meta): ori_raw already holds relTime
+      relTime = ori_raw[i];
     } else {
-      ori = sr_ori_branch_b(ori, endOri);
+      float ori = ori_raw[i];
+      if (i <= cnt->h_min) {
+        bool latch;
+        ori = sr_ori_branch_a(ori, startOri, &latch);
+      } else {
+        ori = sr_ori_branch_b(ori, endOri);
+      }
+      relTime = (ori - startOri) / (endOri - startOri);
     }
-    float relTime = (ori - startOri) / (endOri - startOri);
     const double scanPeriod = 0.1;  // :55
     float intensity = rid + scanPeriod * relTime;
     if (pos < P.max_points) full[pos] = make_float4(px, py, pz, intensity);

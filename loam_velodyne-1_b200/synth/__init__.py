@@ -41,6 +41,7 @@ def _load():
         L.synth_gt_pose.argtypes = [ctypes.c_void_p, ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p]
         L.synth_sweep.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
                                   ctypes.c_void_p, ctypes.c_int]
+        L.synth_sweep_grid.argtypes = L.synth_sweep.argtypes
         L.synth_imu.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         _lib = L
     return _lib
@@ -71,6 +72,13 @@ class Synth:
         stamp = ctypes.c_double()
         n = self.L.synth_sweep(self.h, k, self._buf.ctypes.data, self._buf.shape[0], ctypes.byref(stamp), self.threads)
         return self._buf[:n].copy(), stamp.value
+
+    def sweep_grid(self, k):
+        """the same sweep as the full firing grid: (azimuth steps, rings, 3) float32, NaN = no return"""
+        stamp = ctypes.c_double()
+        buf = np.empty((self.az, self.rings, 3), dtype=np.float32)
+        self.L.synth_sweep_grid(self.h, k, buf.ctypes.data, self.az * self.rings, ctypes.byref(stamp), self.threads)
+        return buf, stamp.value
 
     def imu(self, j):
         """IMU sample j at 200 Hz -> (t, quat xyzw float64[4], acc float32[3])"""
@@ -133,4 +141,46 @@ def vlp16_packets(xyz, stamp=0.0, drop=None):
         t = (t_us + int(p * 12 * 110.592)) & 0xFFFFFFFF
         pk[p, 1200:1204] = [t & 0xFF, (t >> 8) & 0xFF, (t >> 16) & 0xFF, (t >> 24) & 0xFF]
         pk[p, 1204], pk[p, 1205] = 0x37, 0x22                 # strongest return, VLP-16
+    return pk
+
+
+def hdl64_packets(grid, stamp=0.0):
+    """Encodes a preset-2 sweep given as the full firing grid (Synth.sweep_grid: (steps, 64, 3), ring r at
+    position r, NaN = no return) as HDL-64E data packets: (n_packets, 1206) uint8.  One azimuth step = one
+    firing of the 64 lasers = an upper block (flag 0xEEFF, lasers 32..63) followed by a lower block (0xDDFF,
+    lasers 0..31) with the same azimuth; 12 blocks = 6 firings per packet; the last packet is padded with
+    empty blocks that continue the azimuth ramp."""
+    g = np.asarray(grid, np.float64)
+    steps, R = g.shape[0], g.shape[1]
+    assert R == 64
+    d = np.sqrt((g ** 2).sum(axis=2))
+    valid = np.isfinite(d)
+    raw = np.where(valid, np.clip(np.rint(np.where(valid, d, 0.0) / 0.002), 1, 65535), 0).astype(np.uint16)
+    a = np.arange(steps)
+    phi = np.pi - np.pi / steps - 2.0 * np.pi * a / steps          # synth.cpp: clockwise spin, seam behind the sensor
+    az = np.rint((np.degrees(-phi) % 360.0) * 100.0).astype(np.int64) % 36000
+    nblk = 2 * steps
+    npk = (nblk + 11) // 12
+    step_az = int((az[1] - az[0]) % 36000) if steps > 1 else 18
+    pk = np.zeros((npk, VLP16_PACKET_BYTES), np.uint8)
+    for b in range(npk * 12):
+        p, k = divmod(b, 12)
+        o = 100 * k
+        st, upper = divmod(b, 2)
+        upper = upper == 0
+        pk[p, o], pk[p, o + 1] = 0xFF, (0xEE if upper else 0xDD)
+        aa = int(az[st]) if st < steps else int((az[-1] + step_az * (st - steps + 1)) % 36000)
+        pk[p, o + 2], pk[p, o + 3] = aa & 0xFF, aa >> 8
+        if st < steps:
+            rr = raw[st, 32:64] if upper else raw[st, 0:32]
+            body = np.zeros((32, 3), np.uint8)
+            body[:, 0] = rr & 0xFF
+            body[:, 1] = rr >> 8
+            body[:, 2] = (np.arange(32) * 5 + b) & 0xFF        # reflectivity: unused by LOAM
+            pk[p, o + 4:o + 100] = body.ravel()
+    t_us = int(stamp * 1e6)
+    for p in range(npk):
+        t = (t_us + int(p * 6 * 48.0)) & 0xFFFFFFFF
+        pk[p, 1200:1204] = [t & 0xFF, (t >> 8) & 0xFF, (t >> 16) & 0xFF, (t >> 24) & 0xFF]
+        pk[p, 1204], pk[p, 1205] = 0x37, 0x21                     # strongest return, HDL-64E
     return pk

@@ -291,7 +291,12 @@ int synth_has_imu(void* hv) { return ((Handle*)hv)->cfg.imu ? 1 : 0; }
 void synth_gt_pose(void* hv, double t, double* pos, double* rpy) { gt_pose(((Handle*)hv)->cfg.preset, t, pos, rpy); }
 
 // One sweep (index k, stamp = 0.1*k).  xyz: 3 floats per point.  Returns the number of points.
-int synth_sweep(void* hv, int k, float* xyz, int cap, double* stamp, int nthreads) {
+static int synth_sweep_impl(void* hv, int k, float* xyz, int cap, double* stamp, int nthreads, bool grid);
+int synth_sweep(void* hv, int k, float* xyz, int cap, double* stamp, int nthreads) { return synth_sweep_impl(hv, k, xyz, cap, stamp, nthreads, false); }
+// the same sweep as the full firing grid: azimuth-major, rings x azimuth steps slots, NaN where a ray gave no
+// return (what a packetiser needs: a data packet has a slot for every firing)
+int synth_sweep_grid(void* hv, int k, float* xyz, int cap, double* stamp, int nthreads) { return synth_sweep_impl(hv, k, xyz, cap, stamp, nthreads, true); }
+static int synth_sweep_impl(void* hv, int k, float* xyz, int cap, double* stamp, int nthreads, bool grid) {
   const Config& c = ((Handle*)hv)->cfg;
   const Sensor& s = c.sensor;
   const int R = s.rings, A = s.az;
@@ -337,6 +342,15 @@ int synth_sweep(void* hv, int k, float* xyz, int cap, double* stamp, int nthread
     for (auto& x : th) x.join();
   }
   int n = 0;
+  if (grid) {
+    const float nanv = __builtin_nanf("");
+    for (size_t i = 0; i < (size_t)R * A; i++) {
+      if ((int)i >= cap) break;
+      if (ok[i]) { xyz[3 * i] = tmp[3 * i]; xyz[3 * i + 1] = tmp[3 * i + 1]; xyz[3 * i + 2] = tmp[3 * i + 2]; }
+      else { xyz[3 * i] = nanv; xyz[3 * i + 1] = nanv; xyz[3 * i + 2] = nanv; }
+    }
+    return R * A;
+  }
   for (size_t i = 0; i < (size_t)R * A; i++) {
     if (!ok[i]) continue;
     if (n < cap) { xyz[3 * n] = tmp[3 * i]; xyz[3 * n + 1] = tmp[3 * i + 1]; xyz[3 * n + 2] = tmp[3 * i + 2]; }

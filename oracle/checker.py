@@ -18,7 +18,8 @@ class LoamParams(ctypes.Structure):
                 ("ring_lower_deg", ctypes.c_float), ("ring_upper_deg", ctypes.c_float),
                 ("max_points", ctypes.c_int), ("system_delay", ctypes.c_int),
                 ("lo_max_iter", ctypes.c_int), ("lm_max_iter", ctypes.c_int),
-                ("map_arena_points", ctypes.c_int), ("coop_ctas", ctypes.c_int), ("reserved", ctypes.c_int * 6)]
+                ("map_arena_points", ctypes.c_int), ("coop_ctas", ctypes.c_int),
+                ("dev_flags", ctypes.c_int), ("packet_metadata", ctypes.c_int), ("reserved", ctypes.c_int * 4)]
 
 
 class SweepResult(ctypes.Structure):
@@ -123,6 +124,8 @@ def _load(kind):
         L.chk_run_pipelined.restype = ctypes.c_double
         L.chk_run_pipelined.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
         L.chk_decode_packets.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+        L.chk_packet_front_end.argtypes = [ctypes.POINTER(LoamParams), ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        L.chk_push_packets.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.POINTER(SweepResult)]
         L.chk_solve_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     _libs[kind] = L
     return L
@@ -135,6 +138,21 @@ def decode_packets(packets, kind="port"):
     out = np.empty((pk.shape[0] * 384, 3), np.float32)
     _load(kind).chk_decode_packets(pk.ctypes.data, pk.shape[0], out.ctypes.data)
     return out
+
+
+def packet_front_end(params, packets, metadata=False, kind="port"):
+    """CPU restatement of the packet front end of the sensor `params` describes -> xyz (n, 3) and, with
+    metadata=True, the ring ids and relTime of the packet-metadata SR-1 (oracle/packet_port.hpp)"""
+    pk = np.ascontiguousarray(packets, dtype=np.uint8)
+    assert pk.ndim == 2 and pk.shape[1] == 1206
+    n = pk.shape[0] * 384
+    xyz = np.empty((n, 3), np.float32)
+    ring = np.empty(n, np.int32) if metadata else None
+    rt = np.empty(n, np.float32) if metadata else None
+    rc = _load(kind).chk_packet_front_end(ctypes.byref(params), pk.ctypes.data, pk.shape[0], xyz.ctypes.data,
+                                          ring.ctypes.data if metadata else None, rt.ctypes.data if metadata else None)
+    assert rc == 0
+    return (xyz, ring, rt) if metadata else xyz
 
 
 class Checker:
@@ -164,6 +182,13 @@ class Checker:
         xyz = np.ascontiguousarray(xyz, dtype=np.float32)
         res = SweepResult()
         self.L.chk_push_sweep(self.h, xyz.ctypes.data, xyz.shape[0], float(stamp), ctypes.byref(res))
+        return res
+
+    def push_packets(self, packets, stamp, metadata=False):
+        """one revolution of data packets (VLP-16 / HDL-64E by the handle's sensor); metadata = loam_params.packet_metadata"""
+        pk = np.ascontiguousarray(packets, dtype=np.uint8)
+        res = SweepResult()
+        self.L.chk_push_packets(self.h, pk.ctypes.data, pk.shape[0], 1 if metadata else 0, float(stamp), ctypes.byref(res))
         return res
 
     def cloud(self, which, cap=None):

@@ -35,6 +35,9 @@ void chk_solve_step(const float* AtA, const float* AtB, int batch, float thr, in
 /* port and reference: the three nodes on three threads with depth-2 queues, as the reference's processes run */
 double chk_run_pipelined(void* h, const float* xyz, const int* counts, const double* stamps, int n_sweeps, float* poses);
 void chk_decode_packets(const unsigned char* packets, int n_packets, float* xyz);
+/* port only: the packet front end (VLP-16 / HDL-64E by p->n_scans, ring_model) and a revolution of packets through the chain */
+int chk_packet_front_end(const loam_params* p, const unsigned char* packets, int n_packets, float* xyz, int* ring, float* reltime);
+int chk_push_packets(void* h, const unsigned char* packets, int n_packets, int packet_metadata, double stamp, loam_sweep_result* out);
 #ifdef __cplusplus
 }
 #endif

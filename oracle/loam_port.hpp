@@ -171,7 +171,11 @@ class ScanRegistration {
   }
 
   // laserCloudHandler :211-636.  xyz = /velodyne_points payload (3 floats per point).
-  bool process(const float* xyz, int n, int stride_floats, double stamp, SRFeatures& out) {
+  // meta_ring / meta_reltime (both or neither; indexed like xyz): SR-1's ring id and relTime supplied by the
+  // caller instead of being derived from the point with atan / atan2 / halfPassed (:248-284) -- the product's
+  // packet-metadata front end (packet_port.hpp sr1_meta_from_packets); everything else is the same handler
+  bool process(const float* xyz, int n, int stride_floats, double stamp, SRFeatures& out,
+               const int* meta_ring = nullptr, const float* meta_reltime = nullptr) {
     if (!systemInited) {  // :213-219
       systemInitCount++;
       if (systemInitCount >= P.system_delay) systemInited = true;
@@ -183,10 +187,12 @@ class ScanRegistration {
     double timeScanCur = stamp;
     pcl::PointCloud<pcl::PointXYZ> laserCloudIn;
     laserCloudIn.points.reserve(n);
+    std::vector<int> rawIndex;
     for (int i = 0; i < n; i++) {
       const float* p = xyz + (size_t)i * stride_floats;
       if (!std::isfinite(p[0]) || !std::isfinite(p[1]) || !std::isfinite(p[2])) continue;  // :228
       laserCloudIn.points.push_back(pcl::PointXYZ(p[0], p[1], p[2]));
+      if (meta_ring) rawIndex.push_back(i);
     }
     int cloudSize = (int)laserCloudIn.points.size();
     if (cloudSize == 0) return false;
@@ -205,9 +211,11 @@ class ScanRegistration {
       point.x = laserCloudIn.points[i].y;
       point.y = laserCloudIn.points[i].z;
       point.z = laserCloudIn.points[i].x;
-      float angle = atan(point.y / sqrt(point.x * point.x + point.z * point.z)) * 180 / M_PI;
+      float angle = meta_ring ? 0.f : atan(point.y / sqrt(point.x * point.x + point.z * point.z)) * 180 / M_PI;
       int scanID;
-      if (P.ring_model == 0) {  // :249-256
+      if (meta_ring) {
+        scanID = meta_ring[rawIndex[i]];
+      } else if (P.ring_model == 0) {  // :249-256
         int roundedAngle = int(angle + (angle < 0.0 ? -0.5 : +0.5));
         if (roundedAngle > 0) {
           scanID = roundedAngle;
@@ -226,8 +234,9 @@ class ScanRegistration {
         count--;
         continue;
       }
-      float ori = -atan2(point.x, point.z);  // :262-281
-      if (!halfPassed) {
+      float ori = meta_ring ? 0.f : -atan2(point.x, point.z);  // :262-281
+      if (meta_ring) {
+      } else if (!halfPassed) {
         if (ori < startOri - M_PI / 2) {
           ori += 2 * M_PI;
         } else if (ori > startOri + M_PI * 3 / 2) {
@@ -244,7 +253,7 @@ class ScanRegistration {
           ori -= 2 * M_PI;
         }
       }
-      float relTime = (ori - startOri) / (endOri - startOri);
+      float relTime = meta_ring ? meta_reltime[rawIndex[i]] : (ori - startOri) / (endOri - startOri);
       point.intensity = scanID + scanPeriod * relTime;  // :284
 
       if (imuPointerLast >= 0) {  // :286-349

@@ -435,6 +435,41 @@ double chk_run_pipelined(void* hv, const float* xyz, const int* counts, const do
   return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
+// the packet front end of the sensor p describes (VLP-16: 16 rings / ring_model 0, HDL-64E: 64 / 1): decoded xyz and,
+// when ring / reltime are given, the packet-metadata SR-1 quantities (packet_port.hpp)
+int chk_packet_front_end(const loam_params* p, const unsigned char* packets, int n_packets, float* xyz, int* ring, float* reltime) {
+  int kind;
+  if (p->n_scans == 16 && p->ring_model == 0) kind = 0;
+  else if (p->n_scans == 64 && p->ring_model == 1) kind = 1;
+  else return -1;
+  if (ring && reltime) {
+    sr1_meta_from_packets(packets, n_packets, kind, p->ring_lower_deg, p->ring_upper_deg, xyz, ring, reltime);
+  } else {
+    for (int q = 0; q < n_packets; q++) {
+      if (kind == 0) decode_vlp16_packet(packets + (size_t)1206 * q, xyz + (size_t)384 * 3 * q);
+      else decode_hdl64_packet(packets + (size_t)1206 * q, p->ring_lower_deg, p->ring_upper_deg, xyz + (size_t)384 * 3 * q);
+    }
+  }
+  return 0;
+}
+// one revolution of data packets through the whole chain; packet_metadata as loam_params.packet_metadata
+int chk_push_packets(void* hv, const unsigned char* packets, int n_packets, int packet_metadata, double stamp, loam_sweep_result* out) {
+  chk_handle* h = (chk_handle*)hv;
+  const int n = n_packets * 384;
+  std::vector<float> xyz((size_t)n * 3), rt;
+  std::vector<int> ring;
+  if (packet_metadata) { ring.resize(n); rt.resize(n); }
+  if (chk_packet_front_end(&h->P, packets, n_packets, xyz.data(), packet_metadata ? ring.data() : nullptr, packet_metadata ? rt.data() : nullptr) != 0) return -1;
+  loam_sweep_result& r = h->res;
+  r.sr_status = r.lo_status = r.lm_status = LOAM_NOT_READY;
+  double t0 = now_s();
+  bool ok = h->sr.process(xyz.data(), n, 3, stamp, h->feat, packet_metadata ? ring.data() : nullptr, packet_metadata ? rt.data() : nullptr);
+  double t1 = now_s();
+  h->busy[0] += t1 - t0;
+  if (ok) run_from_features(h, t1);
+  if (out) *out = r;
+  return r.sr_status;
+}
 // raw-packet front end: n_packets VLP-16 data packets -> n_packets * 384 points (NaN = no return)
 void chk_decode_packets(const unsigned char* packets, int n_packets, float* xyz) {
   for (int p = 0; p < n_packets; p++) decode_vlp16_packet(packets + (size_t)1206 * p, xyz + (size_t)384 * 3 * p);

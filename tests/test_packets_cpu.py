@@ -59,3 +59,61 @@ def test_packetizer_round_trip(checker, synth):
     dec2 = checker.decode_packets(synth.vlp16_packets(xyz, st, drop=drop))
     assert np.isnan(dec2[drop]).all() and np.array_equal(dec2[~drop], dec[~drop])
     assert int(cloud_checksum(pk)) == int(cloud_checksum(synth.vlp16_packets(xyz, st)))   # deterministic
+
+
+def test_hdl64_decoder_known_answers_and_round_trip(checker, synth):
+    """HDL-64E format: upper block (0xEEFF) = lasers 32..63, lower block (0xDDFF) = lasers 0..31, one azimuth per
+    block, laser k at -24.8 + 26.8 k / 63 deg; hand-computed points, then the synthetic packetiser round trip"""
+    P = checker.make_params(2)
+    pk = np.zeros((1, 1206), np.uint8)
+    for b in range(12):
+        o = 100 * b
+        pk[0, o], pk[0, o + 1] = 0xFF, (0xEE if b % 2 == 0 else 0xDD)
+        a = 27000 + 18 * (b // 2)
+        pk[0, o + 2], pk[0, o + 3] = a & 0xFF, a >> 8
+    pk[0, 4 + 3 * 31], pk[0, 5 + 3 * 31] = 5000 & 0xFF, 5000 >> 8          # block 0 (upper), k = 31 -> laser 63 (+2.0 deg), 10 m
+    pk[0, 104], pk[0, 105] = 10000 & 0xFF, 10000 >> 8                      # block 1 (lower), k = 0 -> laser 0 (-24.8 deg), 20 m
+    pts = checker.packet_front_end(P, pk)
+    assert pts.shape == (384, 3)
+    a, w = np.radians(270.0), np.radians(2.0)          # 270 deg clockwise from forward = pointing left
+    assert np.allclose(pts[31], [10 * np.cos(w) * np.cos(a), -10 * np.cos(w) * np.sin(a), 10 * np.sin(w)], atol=2e-5)
+    w = np.radians(-24.8)
+    assert np.allclose(pts[32], [20 * np.cos(w) * np.cos(a), -20 * np.cos(w) * np.sin(a), 20 * np.sin(w)], atol=4e-5)
+    assert np.isnan(pts[:31]).all() and np.isnan(pts[33:]).all()
+    S = synth.Synth(2)
+    grid, st = S.sweep_grid(2)
+    xyz, _ = S.sweep(2)
+    pk = synth.hdl64_packets(grid, st)
+    assert pk.shape == (334, 1206)
+    dec, ring, rt = checker.packet_front_end(P, pk, metadata=True)
+    fin = np.isfinite(dec[:, 0])
+    assert fin.sum() == xyz.shape[0]
+    # per firing the packet carries lasers 32..63 then 0..31: undo that to compare with the generator's order
+    d4 = dec[:grid.shape[0] * 64].reshape(-1, 2, 32, 3)
+    back = np.concatenate([d4[:, 1], d4[:, 0]], axis=1).reshape(-1, 3)
+    g = grid.reshape(-1, 3)
+    m = np.isfinite(g[:, 0])
+    assert np.array_equal(np.isfinite(back[:, 0]), m) and np.abs(back[m] - g[m]).max() < 0.0015   # 2 mm quantisation
+    # the metadata ring id is the ring scanRegistration.cpp:268-274 (bk variant) derives from the decoded point
+    px, py, pz = dec[fin, 1].astype(np.float64), dec[fin, 2].astype(np.float64), dec[fin, 0].astype(np.float64)
+    ang = np.degrees(np.arctan(py / np.sqrt(px * px + pz * pz)))
+    assert np.array_equal(((ang + 24.8) / (26.8 / 63) + 0.5).astype(int), ring[fin])
+    # and relTime follows the sweep phase the reference derives with atan2 (0.01 deg quantisation apart)
+    ori = -np.arctan2(px, pz)
+    ori = np.unwrap(ori[np.argsort(rt[fin], kind="stable")])
+    ref = (ori - ori[0]) / (ori[-1] - ori[0])
+    assert np.abs(np.sort(rt[fin]) - ref).max() < 1e-4 and rt[fin].min() == 0.0 and rt[fin].max() == 1.0
+
+
+def test_vlp16_metadata_front_end_matches_the_reference_quantities(checker, synth):
+    S = synth.Synth(1)
+    xyz, st = S.sweep(5)
+    pk = synth.vlp16_packets(xyz, st)
+    P = checker.make_params(1)
+    dec, ring, rt = checker.packet_front_end(P, pk, metadata=True)
+    assert np.array_equal(dec.view(np.uint32), checker.decode_packets(pk).view(np.uint32))
+    px, py, pz = dec[:, 1].astype(np.float64), dec[:, 2].astype(np.float64), dec[:, 0].astype(np.float64)
+    ang = np.degrees(np.arctan(py / np.sqrt(px * px + pz * pz)))
+    rounded = (ang + np.where(ang < 0, -0.5, 0.5)).astype(int)
+    assert np.array_equal(np.where(rounded > 0, rounded, rounded + 15), ring)
+    assert rt.min() == 0.0 and rt.max() == 1.0 and np.all(np.diff(rt.reshape(-1, 16)[:, 0]) >= 0)
