@@ -663,12 +663,81 @@ def run_seq64(args, rank, world, local_rank):
         host_wait[0] = (pkg.host_wait_ns() - w0) * 1e-9 / (n_threads * wall)
         return ev0.elapsed_time(ev1), wall, launches, results
 
-    sampler = ClockSampler(local_rank)
+    def run_arm_batch(resident):
+        """all sequences of this GPU in one loam_pipeline_batch: the scanRegistration chain is nine launches per
+        step for all of them; the library's own worker threads do the per-sequence odometry / mapping launches"""
+        Bt = pkg.PipelineBatch(P, len(mine), device=local_rank)
+        if resident:
+            bufs = {s: [torch.from_numpy(x).to(dev) for x, _ in data[s]] for s in mine}
+            aux = {s: [first_last(x) for x, _ in data[s]] for s in mine}
+        else:
+            bufs = {s: [torch.from_numpy(x).pin_memory() for x, _ in data[s]] for s in mine}
+            host = {s: [t.numpy() for t in bufs[s]] for s in mine}
+        results = {s: [] for s in mine}
+
+        def step(k):
+            st = [data[s][k][1] for s in mine]
+            if resident:
+                Bt.push_device([bufs[s][k].data_ptr() for s in mine], [data[s][k][0].shape[0] for s in mine],
+                               [aux[s][k][0] for s in mine], [aux[s][k][1] for s in mine], st)
+            else:
+                Bt.push_async([host[s][k] for s in mine], st)
+
+        def collect(keep):
+            for i, s in enumerate(mine):
+                r = Bt.pipes[i].collect()
+                if keep:
+                    results[s] += r
+
+        for k in range(W):
+            step(k)
+        collect(False)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        l0 = pkg.kernel_launch_count()
+        w0 = pkg.host_wait_ns()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        ev0.record()
+        for k in range(W, total):
+            step(k)
+            if (k - W) % 128 == 127:
+                collect(True)
+        collect(True)
+        torch.cuda.synchronize()
+        ev1.record()
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        launches = pkg.kernel_launch_count() - l0
+        host_wait[0] = (pkg.host_wait_ns() - w0) * 1e-9 / wall
+        prof = None
+        if resident and rank == 0 and not args.no_profile:
+            # per-kernel device time of the batched registration chain (serialising CUDA events, separate pass)
+            pkg.profile_enable(True)
+            for k in range(W, min(total, W + 12)):
+                step(k)
+            collect(False)
+            torch.cuda.synchronize()
+            prof = pkg.profile_report()
+            pkg.profile_enable(False)
+        del Bt
+        return ev0.elapsed_time(ev1), wall, launches, results, prof
+
+    batch = not args.no_batch
+    sampler = ClockSampler(local_rank, enabled=(rank == 0))
     sampler.start()
-    ms, wall, launches, res_r = run_arm(True)
-    wait_frac = host_wait[0]
-    clocks = sampler.stop()
-    ms_e, wall_e, _, res_e = run_arm(False)
+    prof = None
+    if batch:
+        ms, wall, launches, res_r, prof = run_arm_batch(True)
+        wait_frac = host_wait[0]
+        clocks = sampler.stop()
+        ms_e, wall_e, _, res_e, _ = run_arm_batch(False)
+    else:
+        ms, wall, launches, res_r = run_arm(True)
+        wait_frac = host_wait[0]
+        clocks = sampler.stop()
+        ms_e, wall_e, _, res_e = run_arm(False)
     same = all(len(res_r[s]) == len(res_e[s]) == K and all(bytes(a.transform_mapped) == bytes(b.transform_mapped) for a, b in zip(res_r[s], res_e[s])) for s in mine)
     t = torch.tensor([ms, wall_e * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
@@ -687,6 +756,47 @@ def run_seq64(args, rank, world, local_rank):
                 "e2e": {"value": n_seq * K / (e2e_ms * 1e-3), "unit": "sweeps/s", "h2d_bytes_per_step": n_seq * 28800 * 12, "d2h_bytes_per_step": n_seq * ctypes_sizeof_record(pkg),
                         "api": "loam_pipeline_push_async per sweep per sequence from pinned host memory + loam_pipeline_collect", "poses_identical_to_resident_arm": bool(same)},
                 "poses_gathered": [int(table.shape[0]), int(table.shape[1])], "roofline": None, "cpu_baseline": None}
+        if prof:
+            # batched scanRegistration kernels: ALGORITHMIC bytes per launch (SURVEY §8d per-point figures x the points of
+            # all sequences of this GPU in one launch) / live CUDA-event time, against the measured HBM peak
+            peak, peak_src = measured_peak()
+            Nb = float(np.mean([x.shape[0] for s_ in mine for x, _ in data[s_]])) * len(mine)
+            cnt = {k: float(np.mean([getattr(r, k) for s_ in mine for r in res_r[s_] if r.sr_status == 0])) * len(mine) for k in ("n_sharp", "n_less_sharp", "n_flat", "n_less_flat")}
+            per_pt = {"sr_ring_ori_b": 12 + 2 + 4, "sr_scatter_b": 12 + 2 + 4 + 16 + 4 + 4, "sr_curv_reject_b": 16 + 4 + 4 + 3, "sr_sort_sectors_b": 8 + 8,
+                      "sr_select_b": 4 + 4 + 2 + 2, "sr_lessflat_b": 16 + 1}
+            rows = []
+            tot_ms = sum(v[1] for v in prof.values())
+            for name, (calls, kms) in sorted(prof.items(), key=lambda kv: -kv[1][1]):
+                e = {"kernel": name, "calls": calls, "avg_launch_us": round(1e3 * kms / calls, 2), "share": round(kms / tot_ms, 4)}
+                ab = None
+                if name in per_pt:
+                    ab = per_pt[name] * Nb
+                    if name == "sr_lessflat_b":
+                        ab += 16 * cnt["n_less_flat"]
+                elif name == "sr_compact_b":
+                    ab = 32 * (cnt["n_sharp"] + cnt["n_less_sharp"] + cnt["n_flat"] + cnt["n_less_flat"])
+                if ab is not None:
+                    e["algorithmic_MB"] = round(ab / 1e6, 2)
+                    e["achieved"] = round(ab / (kms * 1e-3 / calls) / 1e9, 1)
+                    e["frac"] = round(e["achieved"] / peak, 4)
+                rows.append(e)
+            # sr_ring_ori_b evaluates an fp64 fdlibm atan and atan2 per point (bit-exact trig): it is bound by the FP64
+            # pipe, not by HBM; the sorts (sort_sectors, lessflat) and the greedy pick (select) by shared memory / latency
+            for r in rows:
+                if r["kernel"] == "sr_ring_ori_b":
+                    r["bound"] = "fp64 (2 fdlibm calls per point)"
+                elif r["kernel"] in ("sr_sort_sectors_b", "sr_lessflat_b", "sr_select_b"):
+                    r["bound"] = "smem / latency"
+                elif "frac" in r:
+                    r["bound"] = "hbm"
+            best = max((r for r in rows if r.get("bound") == "hbm"), key=lambda r: r["avg_launch_us"], default=None)
+            if best:
+                line["roofline"] = {"bound": "hbm", "kernel": best["kernel"], "achieved": best["achieved"], "peak": peak, "unit": "GB/s", "frac": best["frac"],
+                                    "traffic": None, "peak_source": peak_src, "avg_launch_us": best["avg_launch_us"],
+                                    "note": "dominant STREAMING kernel of the batched scanRegistration chain (%d sequences per launch); the per-sequence LM kernels are latency chains" % len(mine),
+                                    "kernels": [r for r in rows if "frac" in r]}
+            line["top_kernels"] = rows[:24]
+        line["config"]["batched_scan_registration"] = bool(batch)
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -703,6 +813,7 @@ def main():
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--workload", default="hdl64", choices=sorted(WORKLOADS))
     ap.add_argument("--host-threads", type=int, default=8, help="seq64: host threads feeding the pipelines of one GPU")
+    ap.add_argument("--no-batch", action="store_true", help="seq64: one pipeline per sequence fed by host threads (round-1 form) instead of loam_pipeline_batch_*")
     ap.add_argument("--dev-flags", type=int, default=0, help="development A/B switches passed through loam_params.dev_flags (0 = the shipped configuration)")
     ap.add_argument("--coop-ctas", type=int, default=None, help="CTAs of the cooperative LM kernels per pipeline (0 = one per SM; default 37 for seq64, else 0)")
     args = ap.parse_args()

@@ -243,6 +243,24 @@ loam_sr* loam_pipeline_sr(loam_pipeline* h);
 loam_lo* loam_pipeline_lo(loam_pipeline* h);
 loam_lm* loam_pipeline_lm(loam_pipeline* h);
 
+/* ---- many sequences on one GPU (BASELINE.json configs[4]) ----
+ * `count` independent pipelines whose scanRegistration passes are issued as ONE launch chain per step (a batched
+ * form of every kernel of scanRegistration.cpp:211-636, blockIdx.z = sequence); laserOdometry and laserMapping
+ * stay per sequence.  push_async takes one sweep per sequence (xyz[i]: n[i] points, HOST memory, stride_bytes
+ * apart) and only enqueues; results are collected per sequence with loam_pipeline_collect on
+ * loam_pipeline_batch_get(h, i) (do not destroy those handles: the batch owns them).  Sequences with IMU data
+ * are not supported here (use one loam_pipeline per sequence).  Not thread-safe. */
+typedef struct loam_pipeline_batch loam_pipeline_batch;
+int loam_pipeline_batch_create(const loam_params* p, int device, int count, loam_pipeline_batch** out);
+void loam_pipeline_batch_destroy(loam_pipeline_batch* h);
+int loam_pipeline_batch_size(loam_pipeline_batch* h);
+loam_pipeline* loam_pipeline_batch_get(loam_pipeline_batch* h, int i);
+int loam_pipeline_batch_push_async(loam_pipeline_batch* h, const float* const* xyz, const int* n, int stride_bytes,
+                                   const double* stamps);
+/* the same for sweeps that are already resident in device memory (the form of loam_pipeline_push_device) */
+int loam_pipeline_batch_push_device(loam_pipeline_batch* h, const float* const* d_xyz, const int* n,
+                                    const float* const* first_last_xyz, const int* first_index, const double* stamps);
+
 /* ---- allocation-free entry point ---- */
 /* allocation-free variant of the whole-cloud voxel filter.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code under CUDA graph

@@ -125,6 +125,12 @@ def lib():
     L.loam_pipeline_stream.restype = vp
     L.loam_pipeline_stream.argtypes = [vp]
     L.loam_pipeline_join.argtypes = [vp]
+    L.loam_pipeline_batch_create.argtypes = [ctypes.POINTER(LoamParams), ci, ci, ctypes.POINTER(vp)]
+    L.loam_pipeline_batch_destroy.argtypes = [vp]
+    L.loam_pipeline_batch_get.restype = vp
+    L.loam_pipeline_batch_get.argtypes = [vp, ci]
+    L.loam_pipeline_batch_push_async.argtypes = [vp, vp, vp, ci, vp]
+    L.loam_pipeline_batch_push_device.argtypes = [vp, vp, vp, vp, vp, vp]
     for f in ("sr", "lo", "lm"):
         fn = getattr(L, f"loam_pipeline_{f}")
         fn.restype = vp
@@ -454,3 +460,62 @@ def _borrow(cls, h, cap, L):
     obj.cap = cap
     obj.close = lambda: None
     return obj
+
+
+class PipelineBatch:
+    """`count` pipelines of one GPU whose scanRegistration passes go out as ONE launch chain per step
+    (loam_pipeline_batch_*, BASELINE.json configs[4]); self.pipes[i] is the i-th sequence's Pipeline view"""
+
+    def __init__(self, params, count, device=0):
+        self.L = lib()
+        self.h = ctypes.c_void_p()
+        _check(self.L.loam_pipeline_batch_create(ctypes.byref(params), device, count, ctypes.byref(self.h)))
+        self.count = count
+        self.pipes = []
+        for i in range(count):
+            p = Pipeline.__new__(Pipeline)
+            p.L = self.L
+            p.params = params
+            p.cap = params.max_points
+            p.h = ctypes.c_void_p(self.L.loam_pipeline_batch_get(self.h, i))
+            p.close = lambda: None
+            mk = lambda cls, h: _borrow(cls, h, params.max_points, self.L)
+            p.sr = mk(ScanRegistration, self.L.loam_pipeline_sr(p.h))
+            p.lo = mk(LaserOdometry, self.L.loam_pipeline_lo(p.h))
+            p.lm = mk(LaserMapping, self.L.loam_pipeline_lm(p.h))
+            self.pipes.append(p)
+        self._ptrs = (ctypes.c_void_p * count)()
+        self._n = (ctypes.c_int * count)()
+        self._st = (ctypes.c_double * count)()
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            self.L.loam_pipeline_batch_destroy(self.h)
+            self.h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def push_async(self, sweeps, stamps):
+        """sweeps: one (n_i, 3) float32 array per sequence (pageable or CUDA-pinned host memory)"""
+        keep = [np.ascontiguousarray(x, dtype=np.float32) for x in sweeps]
+        for i, x in enumerate(keep):
+            self._ptrs[i] = x.ctypes.data
+            self._n[i] = x.shape[0]
+            self._st[i] = float(stamps[i])
+        return _check(self.L.loam_pipeline_batch_push_async(self.h, self._ptrs, self._n, 12, self._st))
+
+    def push_device(self, d_ptrs, ns, first_last, first_index, stamps):
+        """sweeps resident in device memory: device pointers, point counts, per sequence the 6 floats (first xyz,
+        last xyz) and the index of the first finite point"""
+        fl = [np.ascontiguousarray(a, dtype=np.float32) for a in first_last]
+        flp = (ctypes.c_void_p * self.count)(*[a.ctypes.data for a in fl])
+        fi = (ctypes.c_int * self.count)(*[int(v) for v in first_index])
+        for i in range(self.count):
+            self._ptrs[i] = int(d_ptrs[i])
+            self._n[i] = int(ns[i])
+            self._st[i] = float(stamps[i])
+        return _check(self.L.loam_pipeline_batch_push_device(self.h, self._ptrs, self._n, flp, fi, self._st))

@@ -18,7 +18,8 @@ std::atomic<long long> g_host_node_ns[3];
 long long now_ns() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return (long long)ts.tv_sec * 1000000000ll + ts.tv_nsec; }
 int g_profile = 0;
 static thread_local char g_err[512] = "";
-static cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;
+static thread_local cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;   // per launching thread (the batch's workers launch too)
+static std::mutex g_prof_mu;
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -82,6 +83,7 @@ void prof_end(const char* name, cudaStream_t s) {
   cudaEventSynchronize(g_ev1);
   float ms = 0;
   cudaEventElapsedTime(&ms, g_ev0, g_ev1);
+  std::lock_guard<std::mutex> lk(g_prof_mu);
   ProfEntry& e = prof_table()[name];
   e.ms += ms;
   e.calls++;
@@ -137,6 +139,7 @@ struct loam_lo { LOHandle h; };
 struct loam_lm { LMHandle h; };
 struct loam_tm { TMHost h; };
 struct loam_pipeline { PipelineHandle h; };
+struct loam_pipeline_batch { PipelineBatch b; };
 
 extern "C" {
 

@@ -8,7 +8,11 @@
 // enqueues, a one-thread kernel snapshots the poses/counters of the sweep into a device ring, and
 // collect() reads the ring back (one small D2H) and runs transformMaintenance on the host.
 #pragma once
+#include <condition_variable>
 #include <deque>
+#include <functional>
+#include <mutex>
+#include <thread>
 #include "loam_lm.cuh"
 
 namespace loamgpu {
@@ -69,10 +73,14 @@ struct PipelineHandle {
   int next_slot = 0;
   loam_sweep_result res;
 
-  int init(const loam_params* p, int dev) {
+  bool sr_stream_shared = false;
+  // shared_sr_stream: the registration stream of a batch of pipelines (loam_pipeline_create_batch); the handle
+  // then does not own it
+  int init(const loam_params* p, int dev, cudaStream_t shared_sr_stream = nullptr) {
     CUDA_OK(cudaSetDevice(dev));
     CUDA_OK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-    CUDA_OK(cudaStreamCreateWithFlags(&sr_stream, cudaStreamNonBlocking));
+    if (shared_sr_stream) { sr_stream = shared_sr_stream; sr_stream_shared = true; }
+    else CUDA_OK(cudaStreamCreateWithFlags(&sr_stream, cudaStreamNonBlocking));
     int r = sr.init(p, dev, sr_stream);
     if (r != LOAM_OK) return r;
     r = lo.init(p, dev, stream);
@@ -92,7 +100,7 @@ struct PipelineHandle {
   }
   ~PipelineHandle() {
     if (sr.copy_stream) cudaStreamSynchronize(sr.copy_stream);
-    if (sr_stream) { cudaStreamSynchronize(sr_stream); cudaStreamDestroy(sr_stream); }
+    if (sr_stream) { cudaStreamSynchronize(sr_stream); if (!sr_stream_shared) cudaStreamDestroy(sr_stream); }
     if (lm.aux) cudaStreamSynchronize(lm.aux);
     if (lm.aux2) cudaStreamSynchronize(lm.aux2);
     if (lm_stream) { cudaStreamSynchronize(lm_stream); cudaStreamDestroy(lm_stream); }
@@ -234,6 +242,113 @@ struct PipelineHandle {
     if (c < 0) return c;
     if (out) *out = res;
     return res.sr_status;
+  }
+};
+
+// A batch of pipelines of one GPU whose scanRegistration passes are issued as ONE launch chain per step
+// (BASELINE.json configs[4]); laserOdometry / laserMapping stay per sequence on their own streams.  The
+// per-sequence host work (staging, the odometry / mapping launches) is spread over a few worker threads of
+// the library: the handles are independent, only the registration chain is common.
+struct BatchWorkers {
+  std::vector<std::thread> th;
+  std::mutex mu;
+  std::condition_variable cv, cv_done;
+  std::function<void(int)> job;
+  int gen = 0, pending = 0, T = 0, device = 0;
+  bool stop = false;
+  void start(int threads, int dev) {
+    T = threads; device = dev;
+    for (int t = 0; t < T; t++) th.emplace_back([this, t] { loop(t); });
+  }
+  void loop(int t) {
+    cudaSetDevice(device);
+    int seen = 0;
+    for (;;) {
+      std::function<void(int)> f;
+      {
+        std::unique_lock<std::mutex> l(mu);
+        cv.wait(l, [&] { return stop || gen != seen; });
+        if (stop) return;
+        seen = gen;
+        f = job;
+      }
+      f(t);
+      {
+        std::unique_lock<std::mutex> l(mu);
+        if (--pending == 0) cv_done.notify_all();
+      }
+    }
+  }
+  void run(const std::function<void(int)>& f) {
+    std::unique_lock<std::mutex> l(mu);
+    job = f; gen++; pending = T;
+    cv.notify_all();
+    cv_done.wait(l, [&] { return pending == 0; });
+  }
+  ~BatchWorkers() {
+    { std::unique_lock<std::mutex> l(mu); stop = true; }
+    cv.notify_all();
+    for (auto& t : th) t.join();
+  }
+};
+
+struct PipelineBatch {
+  std::vector<PipelineHandle*> pipes;
+  SRBatch srb;
+  BatchWorkers workers;
+  cudaStream_t sr_stream = nullptr;
+  int init(const loam_params* p, int dev, int count) {
+    CUDA_OK(cudaSetDevice(dev));
+    CUDA_OK(cudaStreamCreateWithFlags(&sr_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < count; i++) {
+      PipelineHandle* h = new PipelineHandle();
+      pipes.push_back(h);
+      int r = h->init(p, dev, sr_stream);
+      if (r != LOAM_OK) return r;
+    }
+    int r = srb.init(count);
+    if (r != LOAM_OK) return r;
+    workers.start(count < 8 ? count : 8, dev);
+    return SRBatch::set_attributes();
+  }
+  ~PipelineBatch() {
+    for (PipelineHandle* h : pipes) delete h;
+    if (sr_stream) { cudaStreamSynchronize(sr_stream); cudaStreamDestroy(sr_stream); }
+  }
+  // one sweep of every sequence; enqueue only
+  // first_last / first_index != nullptr: the sweeps are packed xyz in DEVICE memory (loam_pipeline_push_device's form)
+  int push_async(const float* const* xyz, const int* n, int stride_bytes, const double* stamps,
+                 const float* const* first_last = nullptr, const int* first_index = nullptr) {
+    const int B = (int)pipes.size(), T = workers.T;
+    std::vector<SRHandle*> hs(B);
+    std::vector<int> rcs(B, LOAM_NOT_READY), rcs2(B, LOAM_OK);
+    std::vector<std::string> errs(T);
+    for (int i = 0; i < B; i++) {
+      if ((int)pipes[i]->pending.size() >= PipelineHandle::RING) { set_error("result ring full: call collect"); return LOAM_ERR_CAPACITY; }
+      hs[i] = &pipes[i]->sr;
+    }
+    long long t0 = now_ns();
+    int r = srb.begin();
+    if (r < 0) return r;
+    workers.run([&](int t) {
+      for (int i = t; i < B; i += T) {
+        rcs[i] = first_last ? srb.prepare_device(hs[i], i, xyz[i], n[i], first_last[i], first_index[i], stamps[i])
+                            : srb.prepare(hs[i], i, xyz[i], n[i], stride_bytes, stamps[i]);
+        if (rcs[i] < 0) errs[t] = loam_last_error();
+      }
+    });
+    r = srb.launch(hs.data(), n, rcs.data());
+    g_host_node_ns[0] += now_ns() - t0;
+    if (r < 0) { for (auto& e : errs) if (!e.empty()) set_error("%s", e.c_str()); return r; }
+    workers.run([&](int t) {
+      for (int i = t; i < B; i += T) {
+        rcs2[i] = pipes[i]->after_registration(rcs[i], stamps[i]);
+        if (rcs2[i] < 0) errs[t] = loam_last_error();
+      }
+    });
+    for (int i = 0; i < B; i++)
+      if (rcs2[i] < 0) { for (auto& e : errs) if (!e.empty()) set_error("%s", e.c_str()); return rcs2[i]; }
+    return LOAM_OK;
   }
 };
 

@@ -3,7 +3,7 @@
 #pragma once
 #include <limits.h>
 #include <vector>
-#include "sr_kernels2.cuh"
+#include "sr_batch.cuh"
 #include "pose_math.cuh"
 #include "pk_decode.cuh"
 
@@ -189,7 +189,9 @@ struct SRHandle {
   }
 
   // laserCloudHandler :211-636.  Enqueues everything on `stream`; no host synchronisation.
-  int process(const float* xyz, int n, int stride_bytes, double stamp) {
+  // batch_item != nullptr: do everything up to (and excluding) the kernel launches and describe the pass in
+  // *batch_item; the caller launches the batched kernels for all sequences at once (SRBatch below)
+  int process(const float* xyz, int n, int stride_bytes, double stamp, SRDev* batch_item = nullptr) {
     processed = false;
     if (!systemInited) {  // :213-219
       systemInitCount++;
@@ -239,9 +241,31 @@ struct SRHandle {
     CUDA_OK(cudaMemcpyAsync(d_raw_cur, hr, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, copy_stream));
     CUDA_OK(cudaEventRecord(ev_copied[b], copy_stream));
     CUDA_OK(cudaStreamWaitEvent(stream, ev_copied[b], 0));
+    if (batch_item) {
+      if (has_imu && imu.pointer_last >= 0) { set_error("batched scanRegistration does not deskew with IMU data (use the per-sequence entry points)"); return LOAM_ERR_ARG; }
+      batch_ev_free = ev_free[b];
+      return prepare_batch_item(n, startOri, endOri, stamp, batch_item);
+    }
     int rc = process_device(n, first, startOri, endOri, stamp);
     CUDA_OK(cudaEventRecord(ev_free[b], stream));
     return rc;
+  }
+  cudaEvent_t batch_ev_free = nullptr;
+  int prepare_batch_item(int n, float startOri, float endOri, double stamp, SRDev* d) {
+    select_bank(cur_bank ^ 1);
+    CUDA_OK(cudaStreamWaitEvent(stream, bank[cur_bank].released, 0));   // consumers of the sweep before last
+    d->raw = d_raw_cur; d->n = n; d->nblk = (n + SR_BLK - 1) / SR_BLK; d->startOri = startOri; d->endOri = endOri; d->meta = 0;
+    d->ring = d_ring.p; d->ori = d_ori.p; d->hist = d_hist.p; d->ring_start = d_ring_start.p; d->scan_start = d_scan_start.p; d->scan_end = d_scan_end.p;
+    d->cnt = d_cnt.p; d->ring_tot = d_ring_tot.p; d->ticket = d_scan_ticket.p;
+    d->full = d_full.p; d->pos = d_pos.p; d->reltime = d_reltime.p; d->curv = d_curv.p; d->sort_ind = d_sort_ind.p;
+    d->picked = d_picked.p; d->label = d_label.p; d->gap = d_gap.p;
+    d->sharp_ring = d_sharp_ring.p; d->less_sharp_ring = d_less_sharp_ring.p; d->flat_ring = d_flat_ring.p; d->ring_counts = d_ring_counts.p;
+    d->lessflat_tmp = d_lessflat_tmp.p; d->sharp = d_sharp.p; d->less_sharp = d_less_sharp.p; d->flat = d_flat.p; d->less_flat = d_less_flat.p;
+    d->sharp_idx = d_sharp_idx.p; d->less_sharp_idx = d_less_sharp_idx.p; d->flat_idx = d_flat_idx.p;
+    last_n = n;
+    last_stamp = stamp;
+    processed = true;
+    return LOAM_OK;
   }
 
   // raw-packet front end: `n_packets` Velodyne data packets (1206 B each, HOST memory) holding one revolution;
@@ -327,7 +351,7 @@ struct SRHandle {
 
   // same, for a sweep that is already resident in device memory (packed xyz).  first_xyz/last_xyz:
   // host copies of the first / last finite point, first = index of the first finite point.
-  int process_resident(const float* d_xyz, int n, const float* first_xyz, const float* last_xyz, int first, double stamp) {
+  int process_resident(const float* d_xyz, int n, const float* first_xyz, const float* last_xyz, int first, double stamp, SRDev* batch_item = nullptr) {
     processed = false;
     if (!systemInited) {
       systemInitCount++;
@@ -340,6 +364,11 @@ struct SRHandle {
     float startOri, endOri;
     sweep_orientation(first_xyz, last_xyz, startOri, endOri);
     d_raw_cur = const_cast<float*>(d_xyz);
+    if (batch_item) {
+      if (has_imu && imu.pointer_last >= 0) { set_error("batched scanRegistration does not deskew with IMU data (use the per-sequence entry points)"); return LOAM_ERR_ARG; }
+      batch_ev_free = nullptr;
+      return prepare_batch_item(n, startOri, endOri, stamp, batch_item);
+    }
     return process_device(n, first, startOri, endOri, stamp);
   }
 
@@ -463,6 +492,90 @@ struct SRHandle {
     out[0] = s.rpy_start[1]; out[1] = s.rpy_start[2]; out[2] = s.rpy_start[0];
     out[3] = s.rpy_cur[1]; out[4] = s.rpy_cur[2]; out[5] = s.rpy_cur[0];
     for (int a = 0; a < 3; a++) { out[6 + a] = s.shift_from_start[a]; out[9 + a] = s.velo_from_start[a]; }
+  }
+};
+
+// One launch chain for the scanRegistration passes of many sequences (sr_batch.cuh).  The handles must have
+// been created on one device with the same parameters and a SHARED stream (loam_pipeline_create_batch).
+struct SRBatch {
+  static const int SLOTS = 4;
+  int B = 0;
+  DevBuf<SRDev> d_items;
+  SRDev* h_items[SLOTS] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev[SLOTS] = {nullptr, nullptr, nullptr, nullptr};
+  int next = 0;
+  int init(int count) {
+    B = count;
+    if (d_items.alloc((size_t)count) != LOAM_OK) return LOAM_ERR_CUDA;
+    for (int i = 0; i < SLOTS; i++) {
+      CUDA_OK(cudaMallocHost((void**)&h_items[i], sizeof(SRDev) * (size_t)count));
+      CUDA_OK(cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming));
+    }
+    return LOAM_OK;
+  }
+  ~SRBatch() {
+    for (int i = 0; i < SLOTS; i++) { if (h_items[i]) cudaFreeHost(h_items[i]); if (ev[i]) cudaEventDestroy(ev[i]); }
+  }
+  // rcs[i] = what the per-sequence call would have returned (LOAM_NOT_READY: swallowed by systemDelay / empty).
+  // begin() picks the staging slot, prepare(i) does sequence i's host side (any thread; one call per sequence),
+  // launch() issues the chain for the sequences that are ready.
+  SRDev* cur_items = nullptr;
+  int cur_slot = 0;
+  std::vector<SRDev> tmp_items;
+  int begin() {
+    cur_slot = next;
+    next = (next + 1) % SLOTS;
+    { HostWait hw; CUDA_OK(cudaEventSynchronize(ev[cur_slot])); }
+    cur_items = h_items[cur_slot];
+    tmp_items.resize(B);
+    return LOAM_OK;
+  }
+  int prepare(SRHandle* h, int i, const float* xyz, int n, int stride_bytes, double stamp) {
+    return h->process(xyz, n, stride_bytes, stamp, &tmp_items[i]);
+  }
+  int prepare_device(SRHandle* h, int i, const float* d_xyz, int n, const float* first_last_xyz, int first_index, double stamp) {
+    return h->process_resident(d_xyz, n, first_last_xyz, first_last_xyz + 3, first_index, stamp, &tmp_items[i]);
+  }
+  int launch(SRHandle* const* hs, const int* n, const int* rcs) {
+    SRDev* items = cur_items;
+    int m = 0, max_nblk = 1, max_cr = 1;
+    std::vector<int> who;
+    for (int i = 0; i < B; i++) {
+      if (rcs[i] < 0) return rcs[i];
+      if (rcs[i] == LOAM_OK) {
+        items[m] = tmp_items[i];
+        max_nblk = max_nblk > items[m].nblk ? max_nblk : items[m].nblk;
+        const int cr = (n[i] + CR_TILE - 1) / CR_TILE;
+        max_cr = max_cr > cr ? max_cr : cr;
+        who.push_back(i);
+        m++;
+      }
+    }
+    if (m == 0) return LOAM_OK;
+    SRHandle& h0 = *hs[who[0]];
+    cudaStream_t s = h0.stream;
+    const int R = h0.P.n_scans;
+    CUDA_OK(cudaMemcpyAsync(d_items.p, items, sizeof(SRDev) * (size_t)m, cudaMemcpyHostToDevice, s));
+    CUDA_OK(cudaEventRecord(ev[cur_slot], s));
+    if (g_profile == 3) prof_node("scanRegistration", s, true);
+    LAUNCH("sr_batch_init_b", sr_batch_init_b, m, 32, 0, s, d_items.p);
+    LAUNCH("sr_ring_ori_b", sr_ring_ori_b, dim3(max_nblk, 1, m), SR_BLK, 0, s, d_items.p, h0.Pd);
+    LAUNCH("sr_ring_scan_b", sr_ring_scan_b, dim3(R, 1, m), RSC_THREADS, 0, s, d_items.p, R, h0.cap);
+    LAUNCH("sr_scatter_b", sr_scatter_b, dim3(max_nblk, 1, m), SR_BLK, 0, s, d_items.p, h0.Pd);
+    LAUNCH("sr_curv_reject_b", sr_curv_reject_b, dim3(max_cr, 1, m), CR_TILE, 0, s, d_items.p);
+    LAUNCH("sr_sort_sectors_b", sr_sort_sectors_b, dim3(6, R, m), 512, 0, s, d_items.p);
+    LAUNCH("sr_select_b", sr_select_b, dim3(R, 1, m), SEL_THREADS, sizeof(SelShared), s, d_items.p);
+    LAUNCH("sr_lessflat_b", sr_lessflat_b, dim3(R, 1, m), 1024, sizeof(LessFlatSmem), s, d_items.p);
+    LAUNCH("sr_compact_b", sr_compact_b, dim3(R, 1, m), 128, 0, s, d_items.p, R, h0.cap);
+    CUDA_OK(cudaGetLastError());
+    for (int i : who)
+      if (hs[i]->batch_ev_free) CUDA_OK(cudaEventRecord(hs[i]->batch_ev_free, s));   // the raw staging buffers are consumed
+    return LOAM_OK;
+  }
+  static int set_attributes() {
+    CUDA_OK(cudaFuncSetAttribute(sr_select_b, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SelShared)));
+    CUDA_OK(cudaFuncSetAttribute(sr_lessflat_b, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LessFlatSmem)));
+    return LOAM_OK;
   }
 };
 

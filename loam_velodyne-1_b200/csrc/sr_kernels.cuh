@@ -101,7 +101,7 @@ __device__ __forceinline__ float sr_ori_branch_b(float ori, float endOri) {
 }
 
 // K-A: per raw point ring id + raw azimuth; per-block ring histogram; latch index by atomicMin
-__global__ void __launch_bounds__(SR_BLK) sr_ring_ori(const float* __restrict__ raw, int n, int stride_floats,
+__device__ __forceinline__ void sr_ring_ori_body(const float* __restrict__ raw, int n, int stride_floats,
                                                       SRParamsDev P, float startOri, short* __restrict__ ring,
                                                       float* __restrict__ ori_raw, int* __restrict__ hist, int nblk,
                                                       SRCounts* cnt) {
@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(SR_BLK) sr_ring_ori(const float* __restrict__ 
 // One CTA per ring scans that ring's row of block counts; the last CTA to finish (ticket counter)
 // turns the ring totals into ring_start / scanStartInd / scanEndInd.
 constexpr int RSC_THREADS = 256;
-__global__ void __launch_bounds__(RSC_THREADS) sr_ring_scan(int* __restrict__ hist, int nblk, int n_scans,
+__device__ __forceinline__ void sr_ring_scan_body(int* __restrict__ hist, int nblk, int n_scans,
                                                             int* __restrict__ ring_start, int* __restrict__ scan_start,
                                                             int* __restrict__ scan_end, SRCounts* cnt, int max_points,
                                                             int* ring_tot, unsigned int* ticket) {
@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(RSC_THREADS) sr_ring_scan(int* __restrict__ hi
 }
 
 // K-C: final azimuth -> relTime -> intensity (:262-284) and the stable ring-major scatter
-__global__ void __launch_bounds__(SR_BLK) sr_scatter(const float* __restrict__ raw, int n, int stride_floats,
+__device__ __forceinline__ void sr_scatter_body(const float* __restrict__ raw, int n, int stride_floats,
                                                      SRParamsDev P, float startOri, float endOri,
                                                      const short* __restrict__ ring, const float* __restrict__ ori_raw,
                                                      const int* __restrict__ base, const int* __restrict__ ring_start, int nblk,

@@ -15,7 +15,7 @@ constexpr int CR_HALO = 8;  // >= 6 (rejection reaches i+6), 5 for the stencil
 //   A(i): gap(i,i+1)>0.1, depth1>depth2, ratio test  -> marks i-5..i
 //   B(i): gap(i,i+1)>0.1, depth1<=depth2, ratio test -> marks i+1..i+6
 //   C(i): parallel-beam test                          -> marks i
-__global__ void __launch_bounds__(CR_TILE) sr_curv_reject(const float4* __restrict__ full, const SRCounts* __restrict__ cnt,
+__device__ __forceinline__ void sr_curv_reject_body(const float4* __restrict__ full, const SRCounts* __restrict__ cnt,
                                                           float* __restrict__ curvature, int* __restrict__ sort_ind,
                                                           unsigned char* __restrict__ picked, signed char* __restrict__ label,
                                                           unsigned char* __restrict__ gapflag) {
@@ -111,7 +111,7 @@ __device__ __forceinline__ void sector_bounds(const int* scan_start, const int* 
 
 // K-F: grid (6, R).  The reference's bubble sort (:466-474) swaps on strict '<' only, i.e. it is
 // a stable ascending sort by curvature == ascending sort of the key (curvature bits, index).
-__global__ void __launch_bounds__(512) sr_sort_sectors(const float* __restrict__ curvature, int* __restrict__ sort_ind,
+__device__ __forceinline__ void sr_sort_sectors_body(const float* __restrict__ curvature, int* __restrict__ sort_ind,
                                                        const int* __restrict__ scan_start, const int* __restrict__ scan_end,
                                                        SRCounts* cnt) {
   __shared__ unsigned long long keys[SR_SECTOR_CAP];
@@ -267,7 +267,7 @@ __device__ __forceinline__ void sel_sector(SelShared& S, int j, int sp, int ep, 
   __syncwarp();
 }
 
-__global__ void __launch_bounds__(SEL_THREADS) sr_select(const float* __restrict__ curvature, const int* __restrict__ sort_ind,
+__device__ __forceinline__ void sr_select_body(const float* __restrict__ curvature, const int* __restrict__ sort_ind,
                                                          const int* __restrict__ scan_start, const int* __restrict__ scan_end,
                                                          const int* __restrict__ ring_start, const unsigned char* __restrict__ gapflag,
                                                          unsigned char* __restrict__ picked, signed char* __restrict__ label,
@@ -437,7 +437,7 @@ struct LessFlatSmem {
   unsigned int k[2][SR_RING_CAP], v[2][SR_RING_CAP];
   CtaRadixSmem R;
 };
-__global__ void __launch_bounds__(1024, 2) sr_lessflat(const float4* __restrict__ full, const signed char* __restrict__ label,
+__device__ __forceinline__ void sr_lessflat_body(const float4* __restrict__ full, const signed char* __restrict__ label,
                                                     const int* __restrict__ scan_start, const int* __restrict__ scan_end,
                                                     float4* __restrict__ out_tmp, int* __restrict__ ring_counts,
                                                     SRCounts* cnt) {
@@ -573,7 +573,7 @@ __global__ void __launch_bounds__(1024, 2) sr_lessflat(const float4* __restrict_
 
 // K-I: one block per ring: offsets = exclusive scan over rings of the four per-ring counts, then
 // copy.  Emission order = ring -> sector -> pick order (:485-489,:531), less-flat ring -> voxel.
-__global__ void __launch_bounds__(128) sr_compact(const float4* __restrict__ full, const int* __restrict__ ring_counts,
+__device__ __forceinline__ void sr_compact_body(const float4* __restrict__ full, const int* __restrict__ ring_counts,
                                                   int n_scans, const int* __restrict__ sharp_idx,
                                                   const int* __restrict__ less_sharp_idx, const int* __restrict__ flat_idx,
                                                   const float4* __restrict__ lessflat_tmp, float4* __restrict__ sharp,

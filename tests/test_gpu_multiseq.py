@@ -114,3 +114,46 @@ def test_all_64_sequences_on_sub_grids_equal_the_oracle(pkg, checker, synth):
     assert not errs, errs
     for s in range(n_seq):
         assert len(got[s]) == nsw and got[s] == want[s], s
+
+
+@pytest.mark.parametrize("system_delay", [0, 2])
+def test_batched_scan_registration_equals_per_sequence_pipelines(pkg, synth, system_delay):
+    """loam_pipeline_batch_*: the scanRegistration passes of many sequences as one launch chain (blockIdx.z =
+    sequence).  Ragged point counts (dropped returns), a sequence with NaNs, systemDelay swallowing the first
+    sweeps: every pose, count and feature cloud of every sequence equals what its own pipeline produces"""
+    n_seq, nsw = 7, 18
+    P = pkg.make_params(1, system_delay=system_delay)
+    P.map_arena_points = 1 << 20
+    P.coop_ctas = 37
+    data = {}
+    rng = np.random.default_rng(3)
+    for s in range(n_seq):
+        S = synth.Synth(1, seed=2000 + s)
+        sw = []
+        for k in range(nsw):
+            x, st = S.sweep(k)
+            if s % 3 == 1:
+                x = x[: len(x) - 800 * (k % 4)]          # ragged: fewer points on some sweeps
+            if s == 2:
+                x = x.copy()
+                x[rng.choice(len(x), 200, replace=False), 0] = np.nan
+            sw.append((x, st))
+        data[s] = sw
+    ref = {}
+    clouds = {}
+    for s in range(n_seq):
+        G = pkg.Pipeline(P)
+        ref[s] = [_bits(G.push(x, st)) for x, st in data[s]]
+        clouds[s] = [G.sr.cloud(w).tobytes() for w in (0, 1, 2, 3, 4)]
+        del G
+    l0 = pkg.kernel_launch_count()
+    B = pkg.PipelineBatch(P, n_seq)
+    for k in range(nsw):
+        B.push_async([data[s][k][0] for s in range(n_seq)], [data[s][k][1] for s in range(n_seq)])
+    got = {s: [_bits(r) for r in B.pipes[s].collect()] for s in range(n_seq)}
+    launches = pkg.kernel_launch_count() - l0
+    for s in range(n_seq):
+        assert got[s] == ref[s], s
+        assert [B.pipes[s].sr.cloud(w).tobytes() for w in (0, 1, 2, 3, 4)] == clouds[s], s
+    # the registration chain is nine launches per step whatever the number of sequences
+    assert launches < nsw * (9 + n_seq * 24)
