@@ -8,6 +8,7 @@
 //   laserOdometry.cpp:436-437,905-906  kdtree*Last->setInputCloud      -> grid build, h ~ 1 m
 //   laserMapping.cpp:707-708           kdtree*FromMap->setInputCloud   -> grid build, h = 1.02 m
 #pragma once
+#include <cooperative_groups.h>
 #include "common.cuh"
 
 namespace loamgpu {
@@ -290,7 +291,53 @@ __device__ __forceinline__ void gridp_scatter(const GridBuf& g, const GridDesc& 
   }
 }
 
-inline int grid_build_pair(GridPair gp, int nblocks, cudaStream_t stream) {
+// The five phases as ONE kernel for clouds of up to a few hundred thousand points: a 16-CTA thread-block cluster
+// per index (blockIdx.y = which of the pair), phases separated by hardware cluster barriers instead of kernel
+// boundaries.  A cluster is not gang-scheduled over the whole GPU like a cooperative grid: it needs 16 CTA slots
+// of one GPC, so it runs beside the persistent LM kernels like any small kernel.
+constexpr int GC_CLUSTER = 16, GC_THREADS = 512;
+__global__ void __cluster_dims__(GC_CLUSTER, 1, 1) __launch_bounds__(GC_THREADS) grid_build_cluster(GridPair gp) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cl = cg::this_cluster();
+  const GridBuf g = gp.g[blockIdx.y];
+  if (!grid_enabled(g)) return;     // uniform over the cluster
+  __shared__ float s_mn[GC_THREADS / 32][3], s_mx[GC_THREADS / 32][3];
+  const int tid = blockIdx.x * GC_THREADS + threadIdx.x, nthr = GC_CLUSTER * GC_THREADS;
+  const int n = min(*g.n_ptr, g.cap);
+  {
+    float mn[3] = {3.0e38f, 3.0e38f, 3.0e38f}, mx[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+    for (int i = tid; i < n; i += nthr) {
+      const float4 p = g.pts[i];
+      mn[0] = fminf(mn[0], p.x); mx[0] = fmaxf(mx[0], p.x);
+      mn[1] = fminf(mn[1], p.y); mx[1] = fmaxf(mx[1], p.y);
+      mn[2] = fminf(mn[2], p.z); mx[2] = fmaxf(mx[2], p.z);
+    }
+    bbox_block_commit(g.bbox, mn, mx, s_mn, s_mx, GC_THREADS / 32);
+  }
+  __threadfence();
+  cl.sync();
+  const GridDesc d = gridp_setup(g, n, tid, nthr);
+  __threadfence();
+  cl.sync();
+  gridp_count(g, d, tid, nthr);
+  __threadfence();
+  cl.sync();
+  gridp_alloc(g, d, tid >> 5, nthr >> 5);
+  __threadfence();
+  cl.sync();
+  gridp_scatter(g, d, tid, nthr);
+}
+
+// small = both clouds are known (host side) to hold at most a few hundred thousand points: one cluster kernel;
+// otherwise the five grid-wide kernels, which scale to millions of points
+inline int grid_build_pair(GridPair gp, int nblocks, cudaStream_t stream, bool small = false) {
+  if (small) {
+    static bool attr = false;
+    if (!attr) { CUDA_OK(cudaFuncSetAttribute(grid_build_cluster, cudaFuncAttributeNonPortableClusterSizeAllowed, 1)); attr = true; }
+    LAUNCH("grid_build_cluster", grid_build_cluster, dim3(GC_CLUSTER, 2), GC_THREADS, 0, stream, gp);
+    CUDA_OK(cudaGetLastError());
+    return LOAM_OK;
+  }
   dim3 grid(nblocks, 2);
   LAUNCH("grid_bbox", grid_bbox, grid, 256, 0, stream, gp);
   LAUNCH("grid_setup", grid_setup, grid, 256, 0, stream, gp);

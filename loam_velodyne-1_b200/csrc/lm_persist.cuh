@@ -192,6 +192,8 @@ inline int lm_load_map(LMHandle& h, const char* path) {
   s.arenaCap = h.arena_cap;
   for (int T = 0; T < 2; T++) {
     s.bump[T] = (int)H.total[T];
+    if (T == 0) h.map_hint = 0;
+    h.map_hint += H.total[T];
     CUDA_OK(cudaMemcpy(h.d_cubes[T].p, cubes[T].data(), sizeof(CubeDesc) * CUBE_NUM, cudaMemcpyHostToDevice));
     if (H.total[T] > 0) CUDA_OK(cudaMemcpy(h.d_arena[T][0].p, pts[T].data(), sizeof(float4) * (size_t)H.total[T], cudaMemcpyHostToDevice));
     CUDA_OK(cudaMemset(h.d_touch[T].p, 0, sizeof(int) * CUBE_NUM));

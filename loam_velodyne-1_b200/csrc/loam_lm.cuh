@@ -49,6 +49,7 @@ struct LMHandle {
   LMImu imu;
   bool has_imu = false;
   LMState last_state;
+  long long map_hint = 0;   // points of a map loaded from a file (the host's only knowledge of the map size before the first sync)
   bool last_surround = false;
   int last_n_registered = 0;
   // What the node receives from laserOdometry (/laser_cloud_corner_last, _surf_last,
@@ -262,7 +263,10 @@ struct LMHandle {
     {
       GridPair gp;
       for (int T = 0; T < 2; T++) gp.g[T] = g_map[T].buf(d_E[T].p, &st->mapN[T], &st->optimize_enable, 1.02f);
-      int r = grid_build_pair(gp, 2 * nb, aux);
+      // the local map grows slowly: the size the host saw last (sync / collect) decides between the one-cluster
+      // build and the five grid-wide kernels (mapping-only stress: > 1 M points)
+      const bool small = (P.dev_flags & 16) == 0 && last_state.mapN[0] + last_state.mapN[1] < 400000 && map_hint < 400000;
+      int r = grid_build_pair(gp, 2 * nb, aux, small);
       if (r != LOAM_OK) return r;
       CUDA_OK(cudaEventRecord(ev_aux, aux));
       CUDA_OK(cudaStreamWaitEvent(stream, ev_aux, 0));

@@ -81,7 +81,7 @@ struct LOHandle {
     if (!systemInited) {  // :427-456
       LAUNCH("lo_adopt_first", lo_adopt_first, nb, 256, 0, stream, sr.d_cnt.p, sr.d_less_sharp.p, sr.d_less_flat.p, d_corner_last.p, d_surf_last.p);
       LAUNCH("lo_finish", lo_finish, 1, 32, 0, stream, d_state.p, sr.d_cnt.p, imu, 1, 0, sr.d_ring_counts.p, P.n_scans, d_corner_roff.p, d_surf_roff.p);
-      int r = grid_build_pair(gp, nb, stream);
+      int r = grid_build_pair(gp, nb, stream, (P.dev_flags & 16) == 0);
       if (r != LOAM_OK) return r;
       systemInited = true;
       last_published = false;
@@ -122,7 +122,7 @@ struct LOHandle {
       T.corner_last = d_corner_last.p; T.surf_last = d_surf_last.p; T.full_end = d_full_end.p; T.do_full = do_full;
       LAUNCH("lo_transform_to_end", lo_transform_to_end_kernel, 2 * nb, 256, 0, stream, T);
       LAUNCH("lo_finish", lo_finish, 1, 32, 0, stream, d_state.p, sr.d_cnt.p, imu, 0, do_full, sr.d_ring_counts.p, P.n_scans, d_corner_roff.p, d_surf_roff.p);
-      int r = grid_build_pair(gp, nb, stream);
+      int r = grid_build_pair(gp, nb, stream, (P.dev_flags & 16) == 0);   // the last clouds are feature clouds: always small
       if (r != LOAM_OK) return r;
     }
     if (do_full) { frameCount = 0; *published = true; }  // :910-911
