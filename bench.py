@@ -391,6 +391,7 @@ def run_mapstress(args, rank, world, local_rank, reference_only=False):
     W, K = max(args.warmup, 3), args.steps
     rec = record_lm_inputs_gpu(pkg, synth, preset, 260, seed=seed0 + rank)
     P = pkg.make_params(preset, system_delay=0)
+    P.dev_flags = args.dev_flags
     M = pkg.LaserMapping(P, device=local_rank)
     t_stamp = 0.0
     for dx in _lateral_offsets(8):

@@ -9,19 +9,19 @@
 #pragma once
 #include <cooperative_groups.h>
 #include "grid_index.cuh"
+#include "lm_cube_index.cuh"
 #include "linalg.cuh"
 #include "pose_math.cuh"
 #include "lo_kernels2.cuh"
 
 namespace loamgpu {
 
-constexpr int CUBE_W = 21, CUBE_H = 11, CUBE_D = 21;     // laserMapping.cpp:67-69
-constexpr int CUBE_NUM = CUBE_W * CUBE_H * CUBE_D;       // :70
 constexpr int PROC_MAX = 250;                            // cubes rewritten per mapped sweep
-constexpr int LM_THREADS = 256;   // half an SM: lo_optimize and the other streams run beside it
-constexpr int LM_WARPS = LM_THREADS / 32;
-
-struct CubeDesc { int off; int cnt; int dirty; int pad; };   // dirty: not known to be one point per voxel in voxel order (lm_refilter.cuh)
+#ifndef LOAM_LM_THREADS
+#define LOAM_LM_THREADS 256
+#endif
+constexpr int LM_THREADS = LOAM_LM_THREADS;   // 256 = half an SM: lo_optimize and the other streams run beside it
+constexpr int LM_THREADS_ALONE = 512;       // mapping on its own (synchronous pipeline, mapping-only node): twice the warps hide the 5-NN latency
 
 struct LMImu {   // host-maintained ring buffer, laserMapping.cpp:102-108,323-335
   double time[IMU_Q];
@@ -39,6 +39,8 @@ struct LMState {
   int validNum, surroundNum;            // :616-617
   int validInd[125], surroundInd[125];  // :72-73
   int gatherOff[2][126];                // start of each valid cube inside the local map
+  int gatherSrc[2][125];                // where each valid cube lay in the arena when the pass began (local-map download)
+  int verNext;                          // last cube version handed out (CubeDesc::ver, lm_cube_index.cuh)
   int mapN[2];                          // laserCloudCornerFromMapNum / SurfFromMapNum :680-681
   int stackN2[2];                       // laserCloudCornerStackNum2 / Surf :683,688
   int stackN[2];                        // laserCloudCornerStackNum / Surf after the filters :696,701
@@ -146,6 +148,7 @@ struct LMSetupArgs {
   const LOState* lo;        // transformSum of this sweep, cloud sizes
   CubeDesc* cubes[2];
   int phase;                // 1: pose prediction only (nothing of the cube map is touched); 2: the rest; 0: both
+  CIState* ci;              // per-cube index (lm_cube_index.cuh); nullptr = the index is rebuilt over the gathered local map
 };
 
 // K1: one block.  /laser_odom_to_init hand-off (:304-318), transformAssociateToMap (:422),
@@ -275,13 +278,14 @@ __global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
     s_ind[threadIdx.x] = in ? i + CUBE_W * j + CUBE_W * CUBE_H * k : -1;
   }
   __syncthreads();
-  __shared__ int s_vlist[125], s_nv;
+  __shared__ int s_vlist[125], s_nv, s_rankq[125];
   __shared__ int s_cnt[2][128];
   if (threadIdx.x == 0) {
     int nv = 0, ns = 0;
     for (int q = 0; q < 125; q++) {  // (i, j, k) loop order == q order
+      s_rankq[q] = -1;
       if (!s_in[q]) continue;
-      if (s_fov[q]) { s_vlist[nv] = s_ind[q]; st->validInd[nv++] = s_ind[q]; }
+      if (s_fov[q]) { s_rankq[q] = nv; s_vlist[nv] = s_ind[q]; st->validInd[nv++] = s_ind[q]; }
       st->surroundInd[ns++] = s_ind[q];
     }
     st->validNum = nv; st->surroundNum = ns;
@@ -294,7 +298,11 @@ __global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
   const int nv = s_nv;
   if (threadIdx.x < 250) {
     const int T = threadIdx.x / 125, v = threadIdx.x % 125;
-    s_cnt[T][v] = v < nv ? A.cubes[T][s_vlist[v]].cnt : 0;
+    CubeDesc d;
+    d.off = 0; d.cnt = 0;
+    if (v < nv) d = A.cubes[T][s_vlist[v]];
+    s_cnt[T][v] = d.cnt;
+    st->gatherSrc[T][v] = d.off;
   }
   __syncthreads();
   if (threadIdx.x < 64) {   // warp T scans its 125 counts
@@ -315,6 +323,84 @@ __global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
   }
   __syncthreads();
   if (threadIdx.x == 0) st->optimize_enable = (s_cnt[0][127] > 10 && s_cnt[1][127] > 100) ? 1 : 0;  // :706
+  if (A.ci == nullptr) return;
+  // ---- per-cube index (lm_cube_index.cuh): which slots the queries of this pass search, which of them are stale ----
+  CIState* ci = A.ci;
+  __shared__ int s_need[2], s_cur[2], s_reset[2], s_nb, s_npts, s_bcnt[256];
+  s_bcnt[threadIdx.x] = -1;
+  if (threadIdx.x < 2) { s_need[threadIdx.x] = 0; s_cur[threadIdx.x] = ci->cursor[threadIdx.x]; s_reset[threadIdx.x] = 0; }
+  if (threadIdx.x == 0) { s_nb = 0; s_npts = 0; }
+  __syncthreads();
+  const int T = threadIdx.x / 125, q = threadIdx.x % 125;
+  const bool mine = threadIdx.x < 250;
+  int slot = 0, wi = 0, wj = 0, wk = 0, cnt = 0, ver = 0, need = 0;
+  bool present = false, stale = false;
+  CISlot S;
+  if (mine) {
+    wi = s_center[0] - 2 + q / 25 - st->cenW; wj = s_center[1] - 2 + (q / 5) % 5 - st->cenH; wk = s_center[2] - 2 + q % 5 - st->cenD;
+    slot = ci_pmod5(wi) + 5 * ci_pmod5(wj) + 25 * ci_pmod5(wk);
+    S = ci->slot[T][slot];
+    if (s_rankq[q] >= 0) {
+      const CubeDesc d = A.cubes[T][s_ind[q]];
+      cnt = d.cnt; ver = d.ver;
+      present = cnt > 0;
+    }
+    if (present) {
+      stale = !(S.wi == wi && S.wj == wj && S.wk == wk && S.ver == ver && S.cnt == cnt && S.room >= cnt);
+      if (stale && S.room < cnt) { need = cnt + cnt / 8 + 256; atomicAdd(&s_need[T], need); }
+      if (cnt >= (1 << 24)) atomicOr(&st->error, 32);   // the position inside a cube is a 24-bit field of the candidate id
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < 2 && s_cur[threadIdx.x] + s_need[threadIdx.x] > ci->cap) { s_reset[threadIdx.x] = 1; s_cur[threadIdx.x] = 0; s_need[threadIdx.x] = 0; }
+  __syncthreads();
+  if (mine && s_reset[T]) {
+    // the index arena of this type is exhausted: every region is dropped and the local map is indexed from scratch
+    S.room = 0; S.ver = -1;
+    ci->slot[T][slot] = S;
+    need = 0;
+    if (present) { stale = true; need = cnt + cnt / 8 + 256; atomicAdd(&s_need[T], need); }
+  }
+  __syncthreads();
+  if (threadIdx.x < 2 && s_reset[threadIdx.x]) {
+    atomicAdd(&ci->stat[2], 1);
+    if (s_need[threadIdx.x] > ci->cap) { atomicOr(&st->error, 32); s_reset[threadIdx.x] = 2; }
+  }
+  __syncthreads();
+  if (mine) {
+    const bool fatal = s_reset[T] == 2;   // the local map does not fit the index arena: nothing is searched, the error flag is up
+    if (stale && !fatal) {
+      if (need) { S.base = atomicAdd(&s_cur[T], need); S.room = need; }
+      S.wi = wi; S.wj = wj; S.wk = wk; S.ver = ver; S.cnt = cnt; S.fill = 0;
+      ci->slot[T][slot] = S;
+      atomicAdd(&s_nb, 1);
+      atomicAdd(&s_npts, cnt);
+      s_bcnt[threadIdx.x] = cnt;
+    }
+    ci->win_slot[T][q] = (present && !fatal) ? slot : -1;
+    ci->win_cube[T][q] = s_ind[q];
+    if (T == 0) ci->win_rank[q] = s_rankq[q];
+  }
+  __syncthreads();
+  // build list, largest cube first: the clusters of ci_build walk it with a fixed stride, so the big cubes start at once
+  // and the small ones fill in behind them
+  if (mine && s_bcnt[threadIdx.x] >= 0) {
+    const int c = s_bcnt[threadIdx.x];
+    int rank = 0;
+    for (int j = 0; j < 250; j++) {
+      const int o = s_bcnt[j];
+      rank += (o > c || (o == c && j < (int)threadIdx.x)) ? 1 : 0;
+    }
+    ci->build[rank] = T * 125 + q;
+  }
+  if (threadIdx.x == 0) {
+    ci->nbuild = s_nb;
+    ci->cursor[0] = s_cur[0]; ci->cursor[1] = s_cur[1];
+    ci->org[0] = 50.0f * (float)(s_center[0] - 2 - st->cenW) - 25.0f;
+    ci->org[1] = 50.0f * (float)(s_center[1] - 2 - st->cenH) - 25.0f;
+    ci->org[2] = 50.0f * (float)(s_center[2] - 2 - st->cenD) - 25.0f;
+    ci->stat[0] += s_nb; ci->stat[1] += s_npts; ci->stat[3] = s_nb; ci->stat[4] = s_npts;
+  }
 }
 
 // K2: incoming clouds to the map with the predicted pose and back (:424-434, :683-691)
@@ -356,7 +442,7 @@ __global__ void __launch_bounds__(256) lm_gather_map(LMGatherArgs A) {
   const int nv = st->validNum;
   for (int v = threadIdx.x; v <= nv; v += 256) {
     s_off[v] = st->gatherOff[T][v];
-    s_src[v] = v < nv ? A.cubes[T][st->validInd[v]].off : 0;
+    s_src[v] = v < nv ? st->gatherSrc[T][v] : 0;
   }
   __syncthreads();
   const int total = s_off[nv];

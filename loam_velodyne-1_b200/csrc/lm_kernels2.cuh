@@ -12,6 +12,8 @@ struct LMOptArgs {
   const float4* stack[2];     // laserCloudCornerStack / SurfStack (sensor frame)
   const float4* map[2];       // laserCloudCornerFromMap / SurfFromMap
   GridView grid[2];
+  CIView ci[2];               // per-cube index (lm_optimize_ci)
+  const CIState* cis;
   double* partials;           // [2][gridDim][LO_NRED]
   int* nn_dbg[2];             // 5 neighbour indices per query of the last iteration (-1 if rejected)
   const LMImu* imu;
@@ -163,13 +165,20 @@ __device__ __forceinline__ void lm_transform_update(LMState* st, float* T, const
 // in flight instead of one on lane 0); (C) 28 threads sum the CTA's rows in query order in fp64;
 // then the per-CTA partials are exchanged through one grid barrier and every CTA redundantly
 // finishes the sum (ascending CTA order) and the 6x6 solve, so no broadcast is needed.
+// The block size is the launch's (LM_THREADS beside the other nodes' kernels, LM_THREADS_ALONE when the node has
+// the GPU to itself); nothing in the arithmetic depends on it.
 constexpr int LM_CH = 256;   // queries per CTA per pass
 constexpr int LM_KW = 16;    // lanes cooperating on one 5-NN query (8 was measured slower: 22.5 vs 20 us per iteration)
 #ifndef LOAM_LM_MAXREG
 #define LOAM_LM_MAXREG 128
 #endif
-__global__ void __maxnreg__(LOAM_LM_MAXREG) lm_optimize(LMOptArgs A) {
+// CI: neighbours come from the persistent per-cube indexes (lm_cube_index.cuh) instead of the index built over
+// the gathered local map; same candidates, same order, same ids after the conversion in the debug output
+template <bool CI>
+__device__ __forceinline__ void lm_optimize_body(const LMOptArgs& A) {
   cg::grid_group grid = cg::this_grid();
+  __shared__ int s_slot[CI ? 2 : 1][CI ? CI_WIN : 1], s_rank[CI ? CI_WIN : 1], s_goff[CI ? 2 : 1][CI ? 126 : 1];
+  __shared__ float s_org[3];
   __shared__ float s_T[6];
   __shared__ LMTrig s_trig;
   __shared__ float s_matP[36];
@@ -190,6 +199,12 @@ __global__ void __maxnreg__(LOAM_LM_MAXREG) lm_optimize(LMOptArgs A) {
     s_deg = st->isDegenerate;
     s_rows = 0;
   }
+  if (CI) {
+    for (int i = threadIdx.x; i < 2 * CI_WIN; i += blockDim.x) s_slot[i / CI_WIN][i % CI_WIN] = A.cis->win_slot[i / CI_WIN][i % CI_WIN];
+    for (int i = threadIdx.x; i < CI_WIN; i += blockDim.x) s_rank[i] = A.cis->win_rank[i];
+    for (int i = threadIdx.x; i < 2 * 126; i += blockDim.x) s_goff[i / 126][i % 126] = st->gatherOff[i / 126][i % 126];
+    if (threadIdx.x < 3) s_org[threadIdx.x] = A.cis->org[threadIdx.x];
+  }
   __syncthreads();
   const int Qc = st->stackN[0], Qs = st->stackN[1];
   const int Q = Qc + Qs;
@@ -200,7 +215,8 @@ __global__ void __maxnreg__(LOAM_LM_MAXREG) lm_optimize(LMOptArgs A) {
   int iters_done = 0;
   const bool enabled = st->optimize_enable != 0;
   if (enabled) {
-    const GridDesc gd0 = *A.grid[0].desc, gd1 = *A.grid[1].desc;
+    GridDesc gd0, gd1;
+    if (!CI) { gd0 = *A.grid[0].desc; gd1 = *A.grid[1].desc; }
     for (int iterCount = 0; iterCount < A.max_iter; iterCount++) {
       iters_done = iterCount + 1;
       if (threadIdx.x == 0) s_trig = lm_trig(s_T);
@@ -213,7 +229,7 @@ __global__ void __maxnreg__(LOAM_LM_MAXREG) lm_optimize(LMOptArgs A) {
         // ---- (A) 5-NN, LM_KW lanes per query (all groups of a warp run the same trip count) ----
         constexpr int GPW = 32 / LM_KW;   // groups per warp
         const int nq_pad = (nq + GPW - 1) / GPW * GPW;
-        for (int i = warp * GPW + (lane / LM_KW); i < nq_pad; i += LM_WARPS * GPW) {
+        for (int i = warp * GPW + (lane / LM_KW); i < nq_pad; i += (blockDim.x >> 5) * GPW) {
           const bool act = i < nq;
           const int q = (int)blockIdx.x + (c0 + (act ? i : 0)) * G;
           const int T = q < Qc ? 0 : 1;
@@ -222,13 +238,16 @@ __global__ void __maxnreg__(LOAM_LM_MAXREG) lm_optimize(LMOptArgs A) {
           // one chunk per CTA (always, at the configured sizes): s_nb[i] / s_found[i] still describe this
           // query's previous iteration, which bounds the new search
           const bool have_prev = act && iterCount > 0 && nmine <= LM_CH && s_found[i] != 0;
-          bool found = lm_knn5_group<LM_KW>(A.grid[T], T ? gd1 : gd0, pointSel.x, pointSel.y, pointSel.z, s_nb[act ? i : LM_CH + (lane / LM_KW)], have_prev);
+          float4* nb = s_nb[act ? i : LM_CH + (lane / LM_KW)];
+          bool found;
+          if (CI) found = ci_knn5_group<LM_KW>(A.ci[T], s_slot[T], s_org, pointSel.x, pointSel.y, pointSel.z, nb, have_prev);
+          else found = lm_knn5_group<LM_KW>(A.grid[T], T ? gd1 : gd0, pointSel.x, pointSel.y, pointSel.z, nb, have_prev);
           if (act && (lane & (LM_KW - 1)) == 0) s_found[i] = found ? 1 : 0;
         }
         __syncthreads();
         if (c0 == 0) PS();  // 1: kNN done
         // ---- (B) fit + Jacobian row, one thread per query ----
-        for (int i = threadIdx.x; i < nq; i += LM_THREADS) {
+        for (int i = threadIdx.x; i < nq; i += blockDim.x) {
           const int q = (int)blockIdx.x + (c0 + i) * G;
           const int T = q < Qc ? 0 : 1;
           const int k = T ? q - Qc : q;
@@ -251,7 +270,11 @@ __global__ void __maxnreg__(LOAM_LM_MAXREG) lm_optimize(LMOptArgs A) {
           s_row[i][7] = valid;
           int* dbg = A.nn_dbg[T] + (size_t)k * 5;
 #pragma unroll
-          for (int j = 0; j < 5; j++) dbg[j] = found ? __float_as_int(s_nb[i][j].w) : -1;
+          for (int j = 0; j < 5; j++) {
+            int id = found ? __float_as_int(s_nb[i][j].w) : -1;
+            if (CI && found) id = s_goff[T][s_rank[id >> 24]] + (id & 0x00ffffff);   // position in the gathered local map
+            dbg[j] = id;
+          }
         }
         __syncthreads();
         if (c0 == 0) PS();  // 2: fits done
@@ -280,7 +303,7 @@ __global__ void __maxnreg__(LOAM_LM_MAXREG) lm_optimize(LMOptArgs A) {
     }
   }
   if (!enabled) {  // no search happened: report "rejected" for every query
-    for (int q = blockIdx.x * LM_THREADS + threadIdx.x; q < (Qc + Qs) * 5; q += gridDim.x * LM_THREADS) {
+    for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < (Qc + Qs) * 5; q += gridDim.x * blockDim.x) {
       if (q < Qc * 5) A.nn_dbg[0][q] = -1; else A.nn_dbg[1][q - Qc * 5] = -1;
     }
   }
@@ -295,6 +318,8 @@ __global__ void __maxnreg__(LOAM_LM_MAXREG) lm_optimize(LMOptArgs A) {
   if (clk >= 0) g_phase_clk[1][0] = clk - 1;
 #undef PS
 }
+__global__ void __maxnreg__(LOAM_LM_MAXREG) lm_optimize(LMOptArgs A) { lm_optimize_body<false>(A); }
+__global__ void __maxnreg__(LOAM_LM_MAXREG) lm_optimize_ci(LMOptArgs A) { lm_optimize_body<true>(A); }
 
 // ---- map update: lm_refilter.cuh ----
 

@@ -165,7 +165,7 @@ inline int lm_load_map(LMHandle& h, const char* path) {
     for (int c = 0; c < CUBE_NUM && ok; c++) {
       if (cnt[c] < 0) { ok = false; break; }
       CubeDesc d;
-      d.off = (int)off; d.cnt = cnt[c]; d.dirty = cnt[c] > 0 && dirty[c] ? 1 : 0; d.pad = 0;
+      d.off = (int)off; d.cnt = cnt[c]; d.dirty = cnt[c] > 0 && dirty[c] ? 1 : 0; d.ver = 0;
       cubes[T][c] = d;
       off += cnt[c];
     }
@@ -205,7 +205,7 @@ inline int lm_load_map(LMHandle& h, const char* path) {
   h.mapFrameCount = H.mapFrameCount;
   h.imu = imu;
   h.has_imu = H.hasImu != 0;
-  return LOAM_OK;
+  return h.reset_index();
 }
 
 // binary PCD v0.7, FIELDS x y z intensity (what pcl::io::savePCDFileBinary writes for PointXYZI
@@ -221,6 +221,7 @@ inline int lm_export_pcd(LMHandle& h, int which, const char* path) {
   CUDA_OK(cudaStreamSynchronize(h.aux));
   CUDA_OK(cudaStreamSynchronize(h.aux2));
   const LMState& s = h.last_state;
+  if (which == LOAM_CLOUD_MAP_CORNER || which == LOAM_CLOUD_MAP_SURF) { int er = h.ensure_local_map(); if (er != LOAM_OK) return er; }
   std::vector<float4> pts;
   const float4* src = nullptr;
   int n = 0;

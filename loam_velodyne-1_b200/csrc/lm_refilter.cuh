@@ -378,7 +378,13 @@ __device__ __forceinline__ void rf_lower_bound_warp4(const unsigned int* a, int 
 // the output.  The work of a cube grows with the map (tens of thousands of old points in the
 // cubes around the sensor) and is bound by shared-memory probes and dependent L2 loads of ONE SM;
 // the cluster spreads it over eight.  Append-only cubes and the general path run on CTA 0 alone.
-constexpr int RF_SLICES = 8;
+#ifndef LOAM_RF_SLICES
+#define LOAM_RF_SLICES 8
+#endif
+#ifndef LOAM_RF_CLUSTERS
+#define LOAM_RF_CLUSTERS 8
+#endif
+constexpr int RF_SLICES = LOAM_RF_SLICES;
 __device__ __forceinline__ void rf_cube(const LMCubeArgs& A, const int T, const int r) {
   cg::cluster_group cluster = cg::this_cluster();
   const int srank = (int)cluster.block_rank();
@@ -583,7 +589,7 @@ __device__ __forceinline__ void rf_cube(const LMCubeArgs& A, const int T, const 
         int d_any = 0;
         for (int t = 0; t < RF_SLICES; t++) d_any |= cluster.map_shared_rank(s_x, t)[3];
         s_dirty = d_any;
-        if (base >= 0) { CubeDesc d; d.off = base; d.cnt = n_out; d.dirty = d_any; d.pad = 0; A.cubes[T][cube] = d; }
+        if (base >= 0) { CubeDesc d; d.off = base; d.cnt = n_out; d.dirty = d_any; d.ver = atomicAdd(&st->verNext, 1) + 1; A.cubes[T][cube] = d; }
       }
       cluster.sync();      // s_x stays valid until CTA 0 has read it
       if (srank != 0) return;
@@ -605,7 +611,7 @@ __device__ __forceinline__ void rf_cube(const LMCubeArgs& A, const int T, const 
     if (s_base < 0) goto done;
     for (int i = threadIdx.x; i < n_old; i += RF_THREADS) arena[s_base + i] = old[i];
     for (int j = threadIdx.x; j < n_new; j += RF_THREADS) arena[s_base + n_old + j] = ins_pts[nvals[j]];
-    if (threadIdx.x == 0) { CubeDesc d; d.off = s_base; d.cnt = n_out; d.dirty = 1; d.pad = 0; A.cubes[T][cube] = d; }
+    if (threadIdx.x == 0) { CubeDesc d; d.off = s_base; d.cnt = n_out; d.dirty = 1; d.ver = atomicAdd(&st->verNext, 1) + 1; A.cubes[T][cube] = d; }
     goto done;
   }
 
@@ -671,7 +677,7 @@ __device__ __forceinline__ void rf_cube(const LMCubeArgs& A, const int T, const 
     }
     if (dirty) s_dirty = 1;
     __syncthreads();
-    if (threadIdx.x == 0) { CubeDesc d; d.off = s_base; d.cnt = n_out; d.dirty = s_dirty; d.pad = 0; A.cubes[T][cube] = d; }
+    if (threadIdx.x == 0) { CubeDesc d; d.off = s_base; d.cnt = n_out; d.dirty = s_dirty; d.ver = atomicAdd(&st->verNext, 1) + 1; A.cubes[T][cube] = d; }
   }
 done:
   RS(4);
@@ -685,7 +691,7 @@ done:
   }
 }
 // one wave of clusters; a cluster walks the plan with stride (number of clusters)
-constexpr int RF_GRID = 8 * RF_SLICES;
+constexpr int RF_GRID = LOAM_RF_CLUSTERS * RF_SLICES;
 __global__ void __cluster_dims__(RF_SLICES, 1, 1) __launch_bounds__(RF_THREADS, 1) lm_refilter_cube(LMCubeArgs A) {
   const int T = blockIdx.y;
   const int np = A.st->nproc[T];

@@ -44,6 +44,17 @@ struct LMHandle {
   int vc_tile_cap = 0;
   DevBuf<double> d_partials;
   GridStorage g_map[2];
+  // per-cube persistent index (lm_cube_index.cuh); dev_flags bit 5 (32) selects the round-1 scheme
+  // instead: gather the local map and index all of it, every pass
+  bool use_ci = false;
+  int ci_cap = 0;
+  bool full_grid = true, concurrent_nodes = false;   // block size of the LM kernel: see lm_kernels2.cuh
+  DevBuf<CIState> d_ci;
+  DevBuf<int2> d_ci_cell[2];
+  DevBuf<float4> d_ci_pts[2];
+  // the gathered local map (laserCloudCornerFromMap / SurfFromMap) is only materialised when somebody asks for it
+  bool snap_pending = false;
+  int snap_arena = 0;
   PinnedBuf<LMState> h_state;
   PinnedRing<LMImu, 4> h_imu;
   LMImu imu;
@@ -91,10 +102,22 @@ struct LMHandle {
     if (ecap < 4 * cap) ecap = 4 * cap;
     coop_blocks = prop.multiProcessorCount;   // one CTA per SM unless the caller asks for a smaller grid
     if (P.coop_ctas > 0 && P.coop_ctas < coop_blocks) coop_blocks = P.coop_ctas;
+    {
+      long long want = 3LL * ecap + 65536;
+      if (P.dev_flags & 64) want = (long long)ecap + ecap / 8 + 256 * CI_WIN + 1024;   // test hook: the smallest legal arena (frequent resets)
+      if (want > (1LL << CI_ADDR_BITS)) want = 1LL << CI_ADDR_BITS;
+      ci_cap = (int)want;
+      // a local map of `ecap` points must fit the index arena with its head room, twice over
+      use_ci = (P.dev_flags & 32) == 0 && (long long)ecap + ecap / 8 + 256 * CI_WIN <= ci_cap;
+    }
     int per_sm = 0;
-    CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lm_optimize, LM_THREADS, 0));
+    if (use_ci) CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lm_optimize_ci, LM_THREADS_ALONE, 0));
+    else CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lm_optimize, LM_THREADS_ALONE, 0));
     if (per_sm < 1) { set_error("lm_optimize cannot be made resident"); return LOAM_ERR_CUDA; }
+    full_grid = coop_blocks == prop.multiProcessorCount;
+    if (use_ci) CUDA_OK(cudaFuncSetAttribute(ci_build, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     CUDA_OK(cudaFuncSetAttribute(lm_refilter_cube, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_SMEM));
+    if (RF_SLICES > 8) CUDA_OK(cudaFuncSetAttribute(lm_refilter_cube, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     CUDA_OK(cudaFuncSetAttribute(lm_bucket_new, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BN_SMEM));
     CUDA_OK(cudaFuncSetAttribute(vx_filter_coop, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     int r = LOAM_OK;
@@ -116,7 +139,8 @@ struct LMHandle {
       vc_tile_cap = (cap + VC_TILE - 1) / VC_TILE + 1;
       r |= d_shist[T].alloc((size_t)256 * vc_tile_cap); r |= d_ssorted[T].alloc(cap);
       r |= d_sdig[T].alloc(256); r |= d_sheads[T].alloc(svblk);
-      r |= g_map[T].alloc(ecap, 1 << 22, stream);
+      if (use_ci) { r |= d_ci_cell[T].alloc((size_t)CI_WIN * CI_TABLE); r |= d_ci_pts[T].alloc(ci_cap); }
+      else r |= g_map[T].alloc(ecap, 1 << 22, stream);
       if (r == LOAM_OK) {
         if (cudaMemsetAsync(d_rank[T].p, 0xff, sizeof(int) * CUBE_NUM, stream) != cudaSuccess) r = LOAM_ERR_CUDA;
         unsigned int init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
@@ -124,6 +148,7 @@ struct LMHandle {
         cudaStreamSynchronize(stream);
       }
     }
+    if (use_ci) r |= d_ci.alloc_zero(1, stream);
     r |= d_S.alloc(ecap); r |= d_surround.alloc(ecap); r |= d_ubbox.alloc(6);
     for (int k = 0; k < 2; k++) { r |= d_ukeys[k].alloc(ecap); r |= d_uvals[k].alloc(ecap); }
     r |= d_uhist.alloc((size_t)256 * enblk); r |= d_udig.alloc(256); r |= d_uheads.alloc(evblk);
@@ -150,6 +175,36 @@ struct LMHandle {
     imu.pointer_last = -1;
     last_state = init;
     CUDA_OK(cudaStreamSynchronize(stream));
+    return reset_index();
+  }
+  // every slot of the per-cube index forgets what it holds (start-up, map load)
+  int reset_index() {
+    snap_pending = false;
+    if (!use_ci) return LOAM_OK;
+    std::vector<CIState> h(1);
+    memset(h.data(), 0, sizeof(CIState));
+    for (int T = 0; T < 2; T++)
+      for (int s = 0; s < CI_WIN; s++) { h[0].slot[T][s].ver = -1; h[0].win_slot[T][s] = -1; }
+    h[0].cap = ci_cap;
+    CUDA_OK(cudaMemcpy(d_ci.p, h.data(), sizeof(CIState), cudaMemcpyHostToDevice));
+    return LOAM_OK;
+  }
+  // laserCloudCornerFromMap / SurfFromMap of the last pass, gathered when a download asks for them (the pass
+  // itself searches the per-cube indexes and never needs the concatenated cloud)
+  int materialize_local_map() {
+    if (!snap_pending) return LOAM_OK;
+    LMGatherArgs GA;
+    GA.st = d_state.p; GA.ecap = ecap;
+    for (int T = 0; T < 2; T++) { GA.cubes[T] = d_cubes[T].p; GA.arena[T] = d_arena[T][snap_arena].p; GA.E[T] = d_E[T].p; }
+    LAUNCH("lm_gather_map", lm_gather_map, dim3(4 * 148, 2), 256, 0, aux, GA);
+    CUDA_OK(cudaGetLastError());
+    snap_pending = false;
+    return LOAM_OK;
+  }
+  int ensure_local_map() {
+    int r = materialize_local_map();
+    if (r != LOAM_OK) return r;
+    CUDA_OK(cudaStreamSynchronize(aux));
     return LOAM_OK;
   }
   ~LMHandle() {
@@ -202,6 +257,7 @@ struct LMHandle {
     Input in;
     in.lo = lo.d_state.p; in.corner_last = lo.d_corner_last.p; in.surf_last = lo.d_surf_last.p; in.full_end = lo.d_full_end.p;
     int bank = -1;
+    concurrent_nodes = lo.stream != stream;
     if (lo.stream != stream) {
       bank = in_bank;
       in_bank ^= 1;
@@ -232,6 +288,7 @@ struct LMHandle {
     // K1a
     LMSetupArgs SA;
     SA.st = st; SA.lo = in.lo; SA.cubes[0] = d_cubes[0].p; SA.cubes[1] = d_cubes[1].p; SA.phase = 1;
+    SA.ci = use_ci ? d_ci.p : nullptr;
     LAUNCH("lm_setup", lm_setup, 1, 256, 0, stream, SA);
     CUDA_OK(cudaEventRecord(ev_fork, stream));
     CUDA_OK(cudaStreamWaitEvent(aux, ev_fork, 0));
@@ -254,6 +311,18 @@ struct LMHandle {
       }
       LAUNCH("vx_filter_coop", vx_filter_coop, dim3(VC_CLUSTER, 2), VC_THREADS, 0, stream, VA);
     }
+    if (use_ci) {
+      // K4 + K5: the slots K1b found stale (cubes the last sweep was inserted into, cubes that entered the window)
+      // are re-indexed; nothing is gathered
+      CIBuildArgs BA;
+      BA.ci = d_ci.p; BA.error = &st->error;
+      for (int T = 0; T < 2; T++) { BA.cubes[T] = d_cubes[T].p; BA.arena[T] = arena[T]; BA.cell[T] = d_ci_cell[T].p; BA.pts[T] = d_ci_pts[T].p; }
+      LAUNCH("ci_build", ci_build, dim3(CB_CLUSTER, CB_GRID_Y), CB_THREADS, 0, aux, BA);
+      CUDA_OK(cudaEventRecord(ev_aux, aux));
+      CUDA_OK(cudaStreamWaitEvent(stream, ev_aux, 0));
+      snap_pending = true;
+      snap_arena = cur_arena;
+    } else {
     // K4
     LMGatherArgs GA;
     GA.st = st; GA.ecap = ecap;
@@ -271,6 +340,7 @@ struct LMHandle {
       CUDA_OK(cudaEventRecord(ev_aux, aux));
       CUDA_OK(cudaStreamWaitEvent(stream, ev_aux, 0));
     }
+    }
     // K6
     if (has_imu) {
       if (h_imu.upload(d_imu.p, imu, stream) != LOAM_OK) { set_error("imu upload failed"); return LOAM_ERR_CUDA; }
@@ -278,11 +348,16 @@ struct LMHandle {
     {
       LMOptArgs OA;
       OA.st = st;
-      for (int T = 0; T < 2; T++) { OA.stack[T] = d_stack[T].p; OA.map[T] = d_E[T].p; OA.grid[T] = g_map[T].view(); OA.nn_dbg[T] = d_nn[T].p; }
+      for (int T = 0; T < 2; T++) {
+        OA.stack[T] = d_stack[T].p; OA.map[T] = d_E[T].p; OA.grid[T] = g_map[T].view(); OA.nn_dbg[T] = d_nn[T].p;
+        OA.ci[T].cell = d_ci_cell[T].p; OA.ci[T].pts = d_ci_pts[T].p;
+      }
+      OA.cis = d_ci.p;
       OA.partials = d_partials.p; OA.imu = d_imu.p; OA.has_imu = has_imu ? 1 : 0; OA.timeLaserOdometry = stamp; OA.max_iter = P.lm_max_iter;
       void* args[] = {&OA};
       if (g_profile) prof_begin(stream);
-      CUDA_OK(cudaLaunchCooperativeKernel((void*)lm_optimize, dim3(coop_blocks), dim3(LM_THREADS), args, 0, stream));
+      CUDA_OK(cudaLaunchCooperativeKernel(use_ci ? (void*)lm_optimize_ci : (void*)lm_optimize, dim3(coop_blocks),
+                                          dim3((full_grid && !concurrent_nodes && (P.dev_flags & 128) == 0) ? LM_THREADS_ALONE : LM_THREADS), args, 0, stream));
       g_launches++;
       if (g_profile) prof_end("lm_optimize", stream);
     }
@@ -401,6 +476,9 @@ struct LMHandle {
   }
 
   int compact() {
+    // the copy below overwrites the other arena: if the local-map snapshot of the last pass still points into it
+    // (two compactions since that pass), gather it first
+    if (snap_pending && snap_arena == (cur_arena ^ 1)) { int r = materialize_local_map(); if (r != LOAM_OK) return r; }
     LMCompactArgs CA;
     CA.st = d_state.p;
     for (int T = 0; T < 2; T++) {
