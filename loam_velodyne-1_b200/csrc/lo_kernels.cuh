@@ -32,6 +32,7 @@ struct LOState {
   int n_corner_last, n_surf_last, n_full_end;  // sizes of the device clouds
   int sum_decoded;         // laserMapping input only: transformSum was already decoded from the /laser_odom_to_init
                            // message by the caller (a ROS node's laserOdometryHandler, laserMapping.cpp:304-321)
+  int claim[8];            // lo_optimize: next unclaimed feature of the k-th correspondence search (zero between launches)
 };
 
 struct LOArgs {
@@ -54,6 +55,7 @@ struct LOArgs {
   int fcap;
   int max_iter;
   int contiguous;               // 1 = contiguous feature slices per CTA (the round-1 assignment), 0 = strided
+  int dynsearch;                // 1 = the correspondence searches (iterCount % 5 == 0) are claimed feature by feature
   // epilogue of the same kernel: TransformToEnd + swap (:875-899), bookkeeping (:901-903) and the rebuild of
   // the two indices (:905-906) -- the grid is resident anyway, so the node's tail costs four more grid
   // barriers instead of seven launches

@@ -226,8 +226,20 @@ __device__ __forceinline__ void red_finish(cg::grid_group& grid, double acc, dou
   if (clk >= 0) phase_stamp(which, clk);
   for (int u = t; u < LO_NRED * PS_GROUPS; u += blockDim.x) {
     const int e = u % LO_NRED, g = u / LO_NRED;
+    // same ascending sum as `for (b = g; b < gridDim.x; b += PS_GROUPS) v += part[b][e]`, ten loads in flight at a time
+    // (one dependent L2 round trip per partial was 5 us of every LM iteration)
     double v = 0.0;
-    for (int b = g; b < (int)gridDim.x; b += PS_GROUPS) v += __ldcg(&part[(size_t)b * LO_NRED + e]);
+    for (int b0 = g; b0 < (int)gridDim.x; b0 += 10 * PS_GROUPS) {
+      double x[10];
+#pragma unroll
+      for (int k = 0; k < 10; k++) {
+        const int b = b0 + k * PS_GROUPS;
+        x[k] = b < (int)gridDim.x ? __ldcg(&part[(size_t)b * LO_NRED + e]) : 0.0;
+      }
+#pragma unroll
+      for (int k = 0; k < 10; k++)
+        if (b0 + k * PS_GROUPS < (int)gridDim.x) v += x[k];
+    }
     s_g[g][e] = v;
   }
   __syncthreads();
@@ -292,11 +304,17 @@ __global__ void __maxnreg__(LOAM_LO_MAXREG) lo_optimize(LOArgs A) {
   // scans make them the expensive ones) are spread evenly over the CTAs instead of filling the first few,
   // which is what the slowest CTA at the iteration's grid barrier was waiting for.  A.contiguous = contiguous
   // slices.
+  // A.contiguous = 2: block-cyclic -- chunks of LO_WARPS consecutive features (one pass of the CTA), CTA b takes chunks
+  // b, b + G, ...: neighbouring features still share a pass (and their cells in L1/L2), while every CTA gets a piece of
+  // the cheap head of the list and a piece of the expensive tail.
   const int G = (int)gridDim.x;
   const int per = (F + G - 1) / G;
+  const bool cyclic = A.contiguous == 2;
+  const int nchunks = (F + LO_WARPS - 1) / LO_WARPS;
   const int f_lo = A.contiguous ? min((int)blockIdx.x * per, F) : (int)blockIdx.x;
   const int f_step = A.contiguous ? 1 : G;
-  const int nmine = A.contiguous ? min(f_lo + per, F) - f_lo : ((F > (int)blockIdx.x) ? (F - (int)blockIdx.x + G - 1) / G : 0);
+  const int nmine = cyclic ? ((nchunks > (int)blockIdx.x) ? (nchunks - (int)blockIdx.x + G - 1) / G : 0) * LO_WARPS
+                           : (A.contiguous ? min(f_lo + per, F) - f_lo : ((F > (int)blockIdx.x) ? (F - (int)blockIdx.x + G - 1) / G : 0));
   int iters_done = 0;
   const bool gate = st->cornerLastNum > 10 && st->surfLastNum > 100;  // :465
   if (gate) {
@@ -312,11 +330,55 @@ __global__ void __maxnreg__(LOAM_LO_MAXREG) lo_optimize(LOArgs A) {
       double acc = 0.0;
       long long dbg_t0 = 0;
       if (iterCount == 0 && PHASE_ON && threadIdx.x == 0) dbg_t0 = clock64();
+      // ---- correspondence search, balanced: a search costs 2 .. 10 us depending on where the feature lies, and with
+      // fixed slices the grid barrier of every fifth iteration waited 13 us for the slowest CTA.  Here the warps of
+      // the whole grid claim features one by one; the correspondences and this iteration's coefficients go to global
+      // memory (where they are kept anyway) and, behind one more grid barrier, the fixed slices below only rebuild
+      // the Jacobian rows -- so every sum is still taken over the same rows in the same order. ----
+      const bool searched = refresh && A.dynsearch != 0;
+      if (searched) {
+        int* ctr = &st->claim[iterCount / 5];
+        int nxt = 0;
+        if (lane == 0) nxt = atomicAdd(ctr, 1);
+        nxt = __shfl_sync(0xffffffffu, nxt, 0);
+        while (nxt < F) {
+          const int f = nxt;
+          if (lane == 0) nxt = atomicAdd(ctr, 1);   // the next claim travels while this feature is searched
+          const bool is_corner = f < n_sharp;
+          const float4 pt = is_corner ? A.sharp[f] : A.flat[f - n_sharp];
+          const float4 sel = lo_transform_to_start(pt, s_tr);
+          bool valid = false;
+          float4 coeff = make_float4(0, 0, 0, 0);
+          if (is_corner) {
+            int i1 = -1, i2 = -1;
+            lo_corner_search(A, s_roff[0], R, sel, n_sharp, n_corner_last, i1, i2);
+            if (lane == 0) {
+              A.corner_ind1[f] = i1; A.corner_ind2[f] = i2;
+              if (i2 >= 0) valid = lo_corner_residual(sel, A.corner_last[i1], A.corner_last[i2], iterCount, coeff);
+            }
+          } else {
+            const int g = f - n_sharp;
+            int i1 = -1, i2 = -1, i3 = -1;
+            lo_surf_search(A, s_roff[1], R, sel, n_flat, n_surf_last, i1, i2, i3);
+            if (lane == 0) {
+              A.surf_ind1[g] = i1; A.surf_ind2[g] = i2; A.surf_ind3[g] = i3;
+              if (i2 >= 0 && i3 >= 0) valid = lo_surf_residual(sel, A.surf_last[i1], A.surf_last[i2], A.surf_last[i3], iterCount, coeff);
+            }
+          }
+          if (lane == 0) {
+            A.coeff[(size_t)iterCount * A.fcap + f] = coeff;
+            A.row_valid[(size_t)iterCount * A.fcap + f] = valid ? 1 : 0;
+          }
+          nxt = __shfl_sync(0xffffffffu, nxt, 0);
+        }
+        __threadfence();
+        grid.sync();
+      }
       for (int j0 = 0; j0 < nmine; j0 += LO_WARPS) {
-        const int f = f_lo + (j0 + warp) * f_step;
+        const int f = cyclic ? ((j0 / LO_WARPS) * G + (int)blockIdx.x) * LO_WARPS + warp : f_lo + (j0 + warp) * f_step;
         const bool first_pass = (j0 == 0);
         s_row[warp * 32 + lane][7] = 0.f;
-        if (j0 + warp < nmine) {
+        if (cyclic ? f < F : j0 + warp < nmine) {
           // ---- transform, (search), residual -> row slab of this iteration ----
           const bool is_corner = f < n_sharp;
           const float4 pt = is_corner ? A.sharp[f] : A.flat[f - n_sharp];
@@ -329,7 +391,9 @@ __global__ void __maxnreg__(LOAM_LO_MAXREG) lo_optimize(LOArgs A) {
             int i1 = -1, i2 = -1;
             float4 t1, t2;
             bool have = false;
-            if (refresh) {
+            if (searched) {
+              if (first_pass) { i1 = __ldcg(&A.corner_ind1[f]); i2 = __ldcg(&A.corner_ind2[f]); }   // only to park the tripod in s_tri
+            } else if (refresh) {
               lo_corner_search(A, s_roff[0], R, sel, n_sharp, n_corner_last, i1, i2);
               if (lane == 0) { A.corner_ind1[f] = i1; A.corner_ind2[f] = i2; }
             } else if (first_pass) {
@@ -337,19 +401,21 @@ __global__ void __maxnreg__(LOAM_LO_MAXREG) lo_optimize(LOArgs A) {
               i2 = s_triok[warp] ? 0 : -1;
               t1 = s_tri[warp][0]; t2 = s_tri[warp][1];
             } else {
-              i1 = A.corner_ind1[f]; i2 = A.corner_ind2[f];
+              i1 = __ldcg(&A.corner_ind1[f]); i2 = __ldcg(&A.corner_ind2[f]);   // L2: another SM may have written them (dynamic search)
             }
             if (lane == 0) {
               if (!have && i2 >= 0) { t1 = A.corner_last[i1]; t2 = A.corner_last[i2]; }
               if (refresh && first_pass) { s_triok[warp] = i2 >= 0 ? 1 : 0; if (i2 >= 0) { s_tri[warp][0] = t1; s_tri[warp][1] = t2; } }
-              if (i2 >= 0) valid = lo_corner_residual(sel, t1, t2, iterCount, coeff);
+              if (i2 >= 0 && !searched) valid = lo_corner_residual(sel, t1, t2, iterCount, coeff);
             }
           } else {
             int g = f - n_sharp;
             int i1 = -1, i2 = -1, i3 = -1;
             float4 t1, t2, t3;
             bool have = false;
-            if (refresh) {
+            if (searched) {
+              if (first_pass) { i1 = __ldcg(&A.surf_ind1[g]); i2 = __ldcg(&A.surf_ind2[g]); i3 = __ldcg(&A.surf_ind3[g]); }
+            } else if (refresh) {
               lo_surf_search(A, s_roff[1], R, sel, n_flat, n_surf_last, i1, i2, i3);
               if (lane == 0) { A.surf_ind1[g] = i1; A.surf_ind2[g] = i2; A.surf_ind3[g] = i3; }
             } else if (first_pass) {
@@ -357,17 +423,17 @@ __global__ void __maxnreg__(LOAM_LO_MAXREG) lo_optimize(LOArgs A) {
               i2 = i3 = s_triok[warp] ? 0 : -1;
               t1 = s_tri[warp][0]; t2 = s_tri[warp][1]; t3 = s_tri[warp][2];
             } else {
-              i1 = A.surf_ind1[g]; i2 = A.surf_ind2[g]; i3 = A.surf_ind3[g];
+              i1 = __ldcg(&A.surf_ind1[g]); i2 = __ldcg(&A.surf_ind2[g]); i3 = __ldcg(&A.surf_ind3[g]);
             }
             if (lane == 0) {
               const bool ok = i2 >= 0 && i3 >= 0;
               if (!have && ok) { t1 = A.surf_last[i1]; t2 = A.surf_last[i2]; t3 = A.surf_last[i3]; }
               if (refresh && first_pass) { s_triok[warp] = ok ? 1 : 0; if (ok) { s_tri[warp][0] = t1; s_tri[warp][1] = t2; s_tri[warp][2] = t3; } }
-              if (ok) valid = lo_surf_residual(sel, t1, t2, t3, iterCount, coeff);
+              if (ok && !searched) valid = lo_surf_residual(sel, t1, t2, t3, iterCount, coeff);
             }
           }
           if (refresh && PHASE_ON && threadIdx.x == 0) g_dbg_clk[640 + blockIdx.x] = clock64();
-          if (lane == 0) {
+          if (lane == 0 && !searched) {
             A.coeff[(size_t)iterCount * A.fcap + f] = coeff;
             A.row_valid[(size_t)iterCount * A.fcap + f] = valid ? 1 : 0;
           }
@@ -376,9 +442,12 @@ __global__ void __maxnreg__(LOAM_LO_MAXREG) lo_optimize(LOArgs A) {
           // lane k re-evaluates the row this feature produced in iteration k ----
           if (lane <= iterCount) {
             size_t slot = (size_t)lane * A.fcap + f;
-            if (A.row_valid[slot]) {
+            // a slab is written once, in its own iteration, and fcap is a multiple of the L1 line: no SM can hold a
+            // stale sector of it (the newest slab may come from another SM: fetched from L2 to make that explicit)
+            const bool fresh = searched && lane == iterCount;
+            if (fresh ? __ldcg(&A.row_valid[slot]) : A.row_valid[slot]) {
               float a[6], b;
-              lo_row(pt, A.coeff[slot], s_trig, s_tr, a, b);
+              lo_row(pt, fresh ? __ldcg(&A.coeff[slot]) : A.coeff[slot], s_trig, s_tr, a, b);
               float* row = s_row[warp * 32 + lane];
 #pragma unroll
               for (int j = 0; j < 6; j++) row[j] = a[j];
@@ -415,6 +484,8 @@ __global__ void __maxnreg__(LOAM_LO_MAXREG) lo_optimize(LOArgs A) {
       if (s_stop) break;
     }
   }
+  // every CTA is behind the last iteration's grid barrier: nobody claims any more
+  if (gate && A.dynsearch && blockIdx.x == 0 && threadIdx.x < 8) st->claim[threadIdx.x] = 0;
   // without an iteration no grid barrier has been passed yet: the state written below (and by the epilogue)
   // is still being read by CTAs that are only now starting
   if (!gate) grid.sync();

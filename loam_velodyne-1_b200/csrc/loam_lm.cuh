@@ -77,6 +77,10 @@ struct LMHandle {
   int init(const loam_params* p, int dev, cudaStream_t s) {
     P = *p;
     device = dev;
+    if (P.lm_max_iter < 1 || P.lm_max_iter > 1000) { set_error("lm_max_iter = %d is outside 1 .. 1000 (the reference uses 10)", P.lm_max_iter); return LOAM_ERR_ARG; }
+    if (P.map_arena_points < 0 || (P.map_arena_points > 0 && P.map_arena_points < 4096)) {
+      set_error("map_arena_points = %d: 0 (default, 8 Mi points) or at least 4096", P.map_arena_points); return LOAM_ERR_ARG;
+    }
     CUDA_OK(cudaSetDevice(dev));
     cudaDeviceProp prop;
     CUDA_OK(cudaGetDeviceProperties(&prop, dev));
@@ -115,6 +119,10 @@ struct LMHandle {
     else CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lm_optimize, LM_THREADS_ALONE, 0));
     if (per_sm < 1) { set_error("lm_optimize cannot be made resident"); return LOAM_ERR_CUDA; }
     full_grid = coop_blocks == prop.multiProcessorCount;
+    if ((P.dev_flags & 512) == 0) {   // see loam_lo.cuh: the persistent kernel must not pin the SMs to a small shared-memory split
+      CUDA_OK(cudaFuncSetAttribute(lm_optimize, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+      CUDA_OK(cudaFuncSetAttribute(lm_optimize_ci, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+    }
     if (use_ci) CUDA_OK(cudaFuncSetAttribute(ci_build, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     CUDA_OK(cudaFuncSetAttribute(lm_refilter_cube, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_SMEM));
     if (RF_SLICES > 8) CUDA_OK(cudaFuncSetAttribute(lm_refilter_cube, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));

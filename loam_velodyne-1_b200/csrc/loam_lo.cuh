@@ -29,6 +29,9 @@ struct LOHandle {
   int init(const loam_params* p, int dev, cudaStream_t s) {
     P = *p;
     device = dev;
+    // one lane per accumulated row slab (lo_optimize), one claim counter per search: at most 32 iterations
+    if (P.lo_max_iter < 1 || P.lo_max_iter > 32) { set_error("lo_max_iter = %d is outside 1 .. 32 (the reference uses 25)", P.lo_max_iter); return LOAM_ERR_ARG; }
+    if (P.n_scans < 1 || P.n_scans > SR_MAX_RINGS || P.max_points < 64) { set_error("bad params"); return LOAM_ERR_ARG; }
     CUDA_OK(cudaSetDevice(dev));
     cudaDeviceProp prop;
     CUDA_OK(cudaGetDeviceProperties(&prop, dev));
@@ -36,10 +39,16 @@ struct LOHandle {
     if (s) stream = s; else { CUDA_OK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking)); own_stream = true; }
     CUDA_OK(cudaEventCreateWithFlags(&ev_dep, cudaEventDisableTiming));
     cap = P.max_points;
-    fcap = 36 * P.n_scans;
+    fcap = (36 * P.n_scans + 127) / 128 * 128;   // 2 + 4 features per sector and ring (scanRegistration.cpp:470-560), rounded to whole L1 lines
     int per_sm = 0;
     CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lo_optimize, LO_THREADS, 0));
     if (per_sm < 1) { set_error("lo_optimize cannot be made resident"); return LOAM_ERR_CUDA; }
+    // An SM cannot change its L1 / shared-memory split while a CTA is resident.  The persistent kernel itself needs
+    // 15 KB, but it sits on every SM for hundreds of microseconds: with the split sized for it alone, the other nodes'
+    // kernels that need 50 .. 200 KB (sr_select, sr_lessflat, lm_bucket_new, lm_refilter_cube) could not start
+    // anywhere until it had finished.  (dev_flags bit 9 keeps the driver's choice, for comparison.)
+    if ((P.dev_flags & 512) == 0)
+      CUDA_OK(cudaFuncSetAttribute(lo_optimize, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
     coop_blocks = prop.multiProcessorCount;   // one CTA per SM unless the caller asks for a smaller grid
     if (P.coop_ctas > 0 && P.coop_ctas < coop_blocks) coop_blocks = P.coop_ctas;
     int r = LOAM_OK;
@@ -94,7 +103,7 @@ struct LOHandle {
     A.corner_ind1 = d_c1.p; A.corner_ind2 = d_c2.p; A.surf_ind1 = d_s1.p; A.surf_ind2 = d_s2.p; A.surf_ind3 = d_s3.p;
     A.coeff = d_coeff.p; A.row_valid = d_row_valid.p; A.partials = d_partials.p; A.imu = imu;
     A.corner_roff = d_corner_roff.p; A.surf_roff = d_surf_roff.p; A.n_scans = P.n_scans;
-    A.fcap = fcap; A.max_iter = P.lo_max_iter; A.contiguous = (P.dev_flags & 1) ? 0 : 1;   // dev flag bit 0: strided assignment (measured slower: neighbouring features share cells)
+    A.fcap = fcap; A.max_iter = P.lo_max_iter; A.contiguous = (P.dev_flags & 1) ? 0 : ((P.dev_flags & 2) ? 2 : 1); A.dynsearch = (P.dev_flags & 256) ? 0 : 1;   // dev flag bit 0: strided assignment (measured slower: neighbouring features share cells)
     frameCount++;  // :885
     const int do_full = frameCount >= skipFrameNum + 1 ? 1 : 0;
     A.less_sharp = sr.d_less_sharp.p; A.less_flat = sr.d_less_flat.p; A.full = sr.d_full.p;

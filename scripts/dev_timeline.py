@@ -17,14 +17,15 @@ preset = int(sys.argv[1]) if len(sys.argv) > 1 else 2
 nsw = int(sys.argv[2]) if len(sys.argv) > 2 else 40
 out = sys.argv[3] if len(sys.argv) > 3 else os.path.join(ROOT, "gpurun_out", "timeline.csv")
 mode = int(sys.argv[4]) if len(sys.argv) > 4 else 2
+warm = int(sys.argv[5]) if len(sys.argv) > 5 else 20     # 5 = the sweeps the driver's --steps 20 --warmup 5 run times
 S = synth.Synth(preset)
-sweeps = [S.sweep(k) for k in range(nsw + 20)]
+sweeps = [S.sweep(k) for k in range(nsw + warm)]
 G = pkg.Pipeline(pkg.make_params(preset, system_delay=0), device=0)
-for k in range(20):
+for k in range(warm):
     G.push_async(*sweeps[k])
 G.collect()
 L.loam_debug_trace_enable(mode)
-for k in range(20, 20 + nsw):
+for k in range(warm, warm + nsw):
     G.push_async(*sweeps[k])
 G.collect()
 n = L.loam_debug_trace_dump(out.encode())
@@ -45,8 +46,8 @@ for s in streams:
     top = sorted(names.items(), key=lambda kv: -kv[1])[:8]
     print(f"stream {s}: busy {busy:.0f} us ({100 * busy / span:.0f}%)  " + "  ".join(f"{k}={v / nsw:.1f}" for k, v in top))
 # one steady-state period (two sweeps) as text: kernels in start order with stream tag
-mid = t0 + (t1 - t0) // 2
+mid = t0 + (t1 - t0) // 2 if warm >= 20 else t0
 tag = {s: "ABCDEFGH"[i] for i, s in enumerate(streams)}
-sel = sorted([e for e in ev if mid <= e[2] < mid + (3_000_000 if mode == 3 else 1_000_000) and e[3] - e[2] >= 4000], key=lambda e: e[2])
+sel = sorted([e for e in ev if mid <= e[2] < mid + (3_000_000 if mode == 3 else 1_000_000) * (1 if warm >= 20 else 4) and e[3] - e[2] >= 4000], key=lambda e: e[2])
 for e in sel:
     print(f"  {(e[2] - mid) / 1e3:8.1f} -> {(e[3] - mid) / 1e3:8.1f}  ({(e[3] - e[2]) / 1e3:6.1f} us)  " + "                    " * "ABCDEFGH".index(tag[e[1]]) + e[0])
