@@ -232,12 +232,16 @@ def algorithmic_bytes(kernel, s):
         return (N / 256.0) * 64 * 4.0 * 2
     if kernel in ("grid_count", "grid_scatter", "grid_bbox"):
         return (Nls + Nlf + M) / 2.0 * 24.0
+    if kernel == "grid_build_cluster":  # laserOdometry's two "last" clouds: point in (16), cell-ordered point + cell entry out (16 + 4)
+        return (Nls + Nlf) * 36.0
+    if kernel == "ci_build":            # with an incrementally maintained index only the inserted points count (16 r + 4 w)
+        return Q * 20.0
     return None
 
 
 def measured_traffic(kernel):
     """dram bytes per launch of `kernel` from the committed `ncu --set full` capture, if any"""
-    for name in ("r01_ncu_full_summary_s10.json", "r01_ncu_full_summary_s8.json", "r01_ncu_full_summary.json"):   # newest capture first
+    for name in ("r02_ncu_full_summary.json", "r01_ncu_full_summary_s10.json", "r01_ncu_full_summary_s8.json", "r01_ncu_full_summary.json"):   # newest capture first
         try:
             d = json.load(open(os.path.join(ROOT, "profiles", name)))
             return float(d[kernel]["dram_bytes_per_launch"])
@@ -457,6 +461,7 @@ def run_mapstress(args, rank, world, local_rank, reference_only=False):
         dist.barrier()
     sampler.mark()
     launches0 = pkg.kernel_launch_count()
+    ci0 = M1.ints(110)     # per-cube index counters (empty with --dev-flags 32: the index is rebuilt over the whole local map every pass)
     stream = torch.cuda.ExternalStream(M1.stream(), device=dev)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
@@ -473,6 +478,12 @@ def run_mapstress(args, rank, world, local_rank, reference_only=False):
         dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
     ms_max = float(ms_t[0].item())
     aft1, _, _, st1 = M1.state()
+    ci1 = M1.ints(110)
+    index_stats = None
+    if ci1.size == 8:
+        index_stats = {"kind": "per-cube, persistent (csrc/lm_cube_index.cuh)", "cube_slots_rebuilt_per_pass": float(ci1[0] - ci0[0]) / K,
+                       "points_reindexed_per_pass": float(ci1[1] - ci0[1]) / K, "arena_resets": int(ci1[2] - ci0[2]),
+                       "fraction_of_local_map_reindexed": float(ci1[1] - ci0[1]) / K / max(1.0, float(st1[3] + st1[4]))}
     stats = {"n_full": float(np.mean([r["full"].shape[0] for r in seq])), "n_sharp": 0.0, "n_flat": 0.0, "lo_iters": 0.0,
              "n_less_sharp": float(np.mean([r["corner"].shape[0] for r in seq])), "n_less_flat": float(np.mean([r["surf"].shape[0] for r in seq])),
              "lm_iters": float(st1[0]), "n_map_corner": float(st1[3]), "n_map_surf": float(st1[4]), "n_stack_corner": float(st1[5]), "n_stack_surf": float(st1[6])}
@@ -534,6 +545,7 @@ def run_mapstress(args, rank, world, local_rank, reference_only=False):
         line = {"metric": METRIC, "value": world * K / (ms_max * 1e-3), "unit": "sweeps/s", "n_gpus": world, "steps": K, "warmup": W,
                 "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": workload, "local_map_points": int(stats["n_map_corner"] + stats["n_map_surf"]), "replicas": 8, "street_spacing_m": 18.0,
+                           "spatial_index": index_stats or {"kind": "rebuilt over the whole gathered local map every pass (dev_flags bit 5)"},
                            "recorded_inputs": len(rec), "parallelism": f"seq{world}",
                            "l2": "inputs larger than L2: %d distinct input sets (%.0f MB) resident in HBM; the local map (~%.0f MB) is re-gathered from the cube arena every pass" % (span, sum(sum(t.numel() * 4 for t in x) for x in d_in) / 1e6, (stats["n_map_corner"] + stats["n_map_surf"]) * 16 / 1e6),
                            "timed_region": "K x LaserMapping::process (setup, stack transform, 0.2/0.4 m filters, local-map gather + grid index, LM loop, map insert + per-cube refilter, registered cloud, surround every 5th); CUDA events on the node's stream, no host sync inside"},

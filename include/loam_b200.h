@@ -50,6 +50,21 @@ typedef struct loam_params {
   int reserved[4];
 } loam_params;
 
+/* Hard limits of this build (compile-time constants of the kernels; the reference has none of them because it
+ * sizes std::vectors on the fly).  A sweep or a parameter block that exceeds one is refused with LOAM_ERR_ARG /
+ * LOAM_ERR_CAPACITY and a loam_last_error() text that names the limit; nothing is truncated silently.
+ *   LOAM_LIMIT_RINGS            n_scans                                   (SR_MAX_RINGS,  csrc/sr_kernels.cuh)
+ *   LOAM_LIMIT_RING_POINTS      less-flat candidates of one ring           (SR_RING_CAP:   shared-memory voxel filter)
+ *   LOAM_LIMIT_SECTOR_POINTS    points in one sixth of a ring              (SR_SECTOR_CAP: shared-memory sort)
+ *   LOAM_LIMIT_CUBES_PER_SWEEP  cubes one sweep inserts into, per type     (PROC_MAX,      csrc/lm_kernels.cuh)
+ *   LOAM_LIMIT_LO_ITERATIONS    lo_max_iter                                (one lane per accumulated row slab)
+ * BASELINE.json's largest sensor (128 rings x 2048 azimuths) uses half of the per-ring limits. */
+#define LOAM_LIMIT_RINGS 128
+#define LOAM_LIMIT_RING_POINTS 4096
+#define LOAM_LIMIT_SECTOR_POINTS 1024
+#define LOAM_LIMIT_CUBES_PER_SWEEP 250
+#define LOAM_LIMIT_LO_ITERATIONS 32
+
 /* preset: 1 = VLP-16 (reference defaults), 2 = HDL-64E, 4 = 128-ring (BASELINE.json configs) */
 int loam_params_preset(loam_params* p, int preset);
 

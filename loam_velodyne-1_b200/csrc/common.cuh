@@ -27,6 +27,23 @@ extern std::atomic<long long> g_host_wait_ns;   // host time spent blocked on ba
 long long now_ns();
 extern std::atomic<long long> g_host_node_ns[3];  // host time the pipeline spent enqueueing scanRegistration / laserOdometry / laserMapping
 struct HostNode { int i; long long t0; HostNode(int i_) : i(i_), t0(now_ns()) {} ~HostNode() { g_host_node_ns[i] += now_ns() - t0; } };
+// the capacity flags the kernels raise (SRCounts::error, LMState::error), spelled out for the caller
+inline void describe_sr_error(int flags) {
+  set_error("scanRegistration capacity exceeded:%s%s%s%s (flags %d; limits: include/loam_b200.h, \"Hard limits\")",
+            (flags & 1) ? " more than 1024 points in one sixth of a ring (LOAM_LIMIT_SECTOR_POINTS);" : "",
+            (flags & 2) ? " more than 4096 less-flat candidates on one ring (LOAM_LIMIT_RING_POINTS);" : "",
+            (flags & 4) ? " more points than loam_params.max_points;" : "",
+            (flags & ~7) ? " other;" : "", flags);
+}
+inline void describe_lm_error(int flags) {
+  set_error("laserMapping capacity exceeded:%s%s%s%s%s%s (flags %d; limits: include/loam_b200.h, \"Hard limits\")",
+            (flags & 1) ? " cube-map arena full (raise loam_params.map_arena_points);" : "",
+            (flags & 2) ? " more than 250 cubes rewritten by one sweep (LOAM_LIMIT_CUBES_PER_SWEEP);" : "",
+            (flags & 4) ? " a map point lies outside its cube's voxel range;" : "",
+            (flags & 8) ? " local map larger than map_arena_points / 4;" : "",
+            (flags & 16) ? " refilter scratch full (map_arena_points / 4);" : "",
+            (flags & 32) ? " per-cube index arena full or a cube above 16 Mi points;" : "", flags);
+}
 struct HostWait { long long t0; HostWait() : t0(now_ns()) {} ~HostWait() { g_host_wait_ns += now_ns() - t0; } };
 extern int g_profile;   // 0 off, 1 per-kernel CUDA events (serialising), 2 timeline stamps around every launch (non-serialising), 3 stamps at node boundaries only
 

@@ -126,6 +126,11 @@ __device__ __forceinline__ GridDesc grid_make_desc(const GridBuf& g, int n_given
   float mn[3], mx[3];
   for (int a = 0; a < 3; a++) { mn[a] = float_unflip(g.bbox[a]); mx[a] = float_unflip(g.bbox[3 + a]); }
   if (n <= 0) { mn[0] = mn[1] = mn[2] = 0.f; mx[0] = mx[1] = mx[2] = 0.f; }
+  // an infinite coordinate (NaN is ignored by fminf / fmaxf) must not turn the cell count into garbage or keep the
+  // loop below from ending: such a cloud gets one cell and no valid flag, every query then finds nothing
+  bool finite = true;
+  for (int a = 0; a < 3; a++) finite = finite && isfinite(mn[a]) && isfinite(mx[a]);
+  if (!finite) { mn[0] = mn[1] = mn[2] = 0.f; mx[0] = mx[1] = mx[2] = 0.f; d.valid = 0; }
   float h = g.h0;
   int nx, ny, nz;
   while (true) {

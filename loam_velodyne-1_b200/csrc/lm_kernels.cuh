@@ -6,6 +6,10 @@
 // per feature type.  Cubes are immutable segments; every mapped sweep appends one new block with
 // the refiltered contents of the touched cubes (part 2), so shifting the window (:454-614) moves
 // 8-byte descriptors instead of point clouds and the local map is one gather of <= 125 segments.
+// The scalar expressions restated in this file (cited below) come from loam_velodyne:
+//   Copyright 2013, Ji Zhang, Carnegie Mellon University
+//   Further contributions copyright (c) 2016, Southwest Research Institute.  All rights reserved.
+// BSD 3-clause; the full notice, conditions and disclaimer are retained in NOTICE.md at the repository root.
 #pragma once
 #include <cooperative_groups.h>
 #include "grid_index.cuh"

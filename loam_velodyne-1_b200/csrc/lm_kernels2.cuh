@@ -1,5 +1,9 @@
 // lm_kernels2.cuh -- laserMapping on sm_100a, part 2: the cooperative sweep-to-map LM kernel
 // (LM-8 .. LM-11) and the map update (LM-12 .. LM-14).
+// The scalar expressions restated in this file (cited below) come from loam_velodyne:
+//   Copyright 2013, Ji Zhang, Carnegie Mellon University
+//   Further contributions copyright (c) 2016, Southwest Research Institute.  All rights reserved.
+// BSD 3-clause; the full notice, conditions and disclaimer are retained in NOTICE.md at the repository root.
 #pragma once
 #include "lm_kernels.cuh"
 #include "sort_voxel.cuh"

@@ -144,6 +144,15 @@ inline int lm_load_map(LMHandle& h, const char* path) {
     set_error("%s is not a LOAMMAP1 file of a %dx%dx%d cube map", path, CUBE_W, CUBE_H, CUBE_D);
     return LOAM_ERR_ARG;
   }
+  // header fields that index arrays later on: refuse a file that would send them out of range
+  if (H.cen[0] < 0 || H.cen[0] >= CUBE_W || H.cen[1] < 0 || H.cen[1] >= CUBE_H || H.cen[2] < 0 || H.cen[2] >= CUBE_D ||
+      H.imuPointerLast < -1 || H.imuPointerLast >= IMU_Q || H.imuPointerFront < 0 || H.imuPointerFront >= IMU_Q ||
+      H.frameCount < 0 || H.mapFrameCount < 0) {
+    fclose(f);
+    set_error("%s: header fields out of range (window centre %d %d %d, imu pointers %d %d)", path, H.cen[0], H.cen[1], H.cen[2],
+              H.imuPointerLast, H.imuPointerFront);
+    return LOAM_ERR_ARG;
+  }
   ok = ok && fread(imu.time, sizeof(double), IMU_Q, f) == (size_t)IMU_Q;
   ok = ok && fread(imu.roll, sizeof(float), IMU_Q, f) == (size_t)IMU_Q;
   ok = ok && fread(imu.pitch, sizeof(float), IMU_Q, f) == (size_t)IMU_Q;

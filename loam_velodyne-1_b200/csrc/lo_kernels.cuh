@@ -6,6 +6,10 @@
 // so the whole loop is ONE cooperative kernel: one warp per feature, one grid-wide barrier per
 // iteration, and every block redundantly finishes the (deterministic) 27-term reduction and the
 // 6x6 solve so no second barrier or broadcast is needed.
+// The scalar expressions restated in this file (cited below) come from loam_velodyne:
+//   Copyright 2013, Ji Zhang, Carnegie Mellon University
+//   Further contributions copyright (c) 2016, Southwest Research Institute.  All rights reserved.
+// BSD 3-clause; the full notice, conditions and disclaimer are retained in NOTICE.md at the repository root.
 #pragma once
 #include <cooperative_groups.h>
 #include "grid_index.cuh"

@@ -105,6 +105,10 @@ static int download_array(const T* dev, int count, T* out, int cap, int* n, cuda
 using namespace loamgpu;
 
 // test hook: phase clocks of lo_optimize (which = 0) / lm_optimize (1); see common.cuh
+static_assert(loamgpu::SR_MAX_RINGS == LOAM_LIMIT_RINGS && loamgpu::SR_RING_CAP == LOAM_LIMIT_RING_POINTS &&
+              loamgpu::SR_SECTOR_CAP == LOAM_LIMIT_SECTOR_POINTS && loamgpu::PROC_MAX == LOAM_LIMIT_CUBES_PER_SWEEP,
+              "the limits documented in include/loam_b200.h are the kernels' constants");
+
 extern "C" int loam_debug_phase_enable(int on) {
 #ifdef LOAM_PHASE_CLOCKS
   CUDA_OK(cudaMemcpyToSymbol(g_phase_on, &on, sizeof(int)));

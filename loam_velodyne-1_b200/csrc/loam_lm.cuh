@@ -506,7 +506,7 @@ struct LMHandle {
     CUDA_OK(cudaMemcpyAsync(h_state.p, d_state.p, sizeof(LMState), cudaMemcpyDeviceToHost, stream));
     CUDA_OK(cudaStreamSynchronize(stream));
     last_state = *h_state.p;
-    if (last_state.error) { set_error("laserMapping capacity exceeded (flags %d)", last_state.error); return LOAM_ERR_CAPACITY; }
+    if (last_state.error) { describe_lm_error(last_state.error); return LOAM_ERR_CAPACITY; }
     if (last_state.bump[0] > arena_cap / 2 || last_state.bump[1] > arena_cap / 2) {
       int r = compact();
       if (r != LOAM_OK) return r;

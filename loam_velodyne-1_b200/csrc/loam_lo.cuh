@@ -31,7 +31,10 @@ struct LOHandle {
     device = dev;
     // one lane per accumulated row slab (lo_optimize), one claim counter per search: at most 32 iterations
     if (P.lo_max_iter < 1 || P.lo_max_iter > 32) { set_error("lo_max_iter = %d is outside 1 .. 32 (the reference uses 25)", P.lo_max_iter); return LOAM_ERR_ARG; }
-    if (P.n_scans < 1 || P.n_scans > SR_MAX_RINGS || P.max_points < 64) { set_error("bad params"); return LOAM_ERR_ARG; }
+    if (P.n_scans < 1 || P.n_scans > SR_MAX_RINGS || P.max_points < 64) {
+      set_error("n_scans = %d / max_points = %d: n_scans must be 1 .. %d (LOAM_LIMIT_RINGS), max_points at least 64", P.n_scans, P.max_points, SR_MAX_RINGS);
+      return LOAM_ERR_ARG;
+    }
     CUDA_OK(cudaSetDevice(dev));
     cudaDeviceProp prop;
     CUDA_OK(cudaGetDeviceProperties(&prop, dev));

@@ -185,7 +185,7 @@ struct PipelineHandle {
       r.sr_status = pd.sr_status; r.lo_status = pd.lo_status; r.lm_status = pd.lm_status;
       if (pd.sr_status == LOAM_OK) {
         const PipeRecord& q = h_ring.p[pd.slot];
-        if (q.cnt.error) { set_error("scanRegistration capacity exceeded (flags %d)", q.cnt.error); return LOAM_ERR_CAPACITY; }
+        if (q.cnt.error) { describe_sr_error(q.cnt.error); return LOAM_ERR_CAPACITY; }
         sr.last_counts = q.cnt;
         lo.last_n_sharp = q.cnt.n_sharp; lo.last_n_flat = q.cnt.n_flat;
         r.n_full = q.cnt.n_full; r.n_sharp = q.cnt.n_sharp; r.n_less_sharp = q.cnt.n_less_sharp;
@@ -202,7 +202,7 @@ struct PipelineHandle {
         if (pd.lo_status == LOAM_OK) {
           tm.on_odometry(q.transformSum, r.transform_mapped);
           if (pd.lm_status == LOAM_OK) {
-            if (q.lm_error) { set_error("laserMapping capacity exceeded (flags %d)", q.lm_error); return LOAM_ERR_CAPACITY; }
+            if (q.lm_error) { describe_lm_error(q.lm_error); return LOAM_ERR_CAPACITY; }
             r.lm_iters = q.lm_iters; r.lm_rows = q.lm_rows; r.lm_degenerate = q.lm_deg;
             r.n_map_corner = q.mapN[0]; r.n_map_surf = q.mapN[1]; r.n_stack_corner = q.stackN[0]; r.n_stack_surf = q.stackN[1];
             memcpy(r.transform_aft_mapped, q.aft, sizeof(float) * 6);

@@ -87,7 +87,10 @@ struct SRHandle {
   int init(const loam_params* p, int dev, cudaStream_t s) {
     P = *p;
     device = dev;
-    if (P.n_scans < 1 || P.n_scans > SR_MAX_RINGS || P.max_points < 64) { set_error("bad params"); return LOAM_ERR_ARG; }
+    if (P.n_scans < 1 || P.n_scans > SR_MAX_RINGS || P.max_points < 64) {
+      set_error("n_scans = %d / max_points = %d: n_scans must be 1 .. %d (LOAM_LIMIT_RINGS), max_points at least 64", P.n_scans, P.max_points, SR_MAX_RINGS);
+      return LOAM_ERR_ARG;
+    }
     CUDA_OK(cudaSetDevice(dev));
     cudaDeviceProp prop;
     CUDA_OK(cudaGetDeviceProperties(&prop, dev));
@@ -484,7 +487,7 @@ struct SRHandle {
     CUDA_OK(cudaMemcpyAsync(h_imu_state.p, imu_state_dev(), sizeof(ImuState), cudaMemcpyDeviceToHost, stream));
     CUDA_OK(cudaStreamSynchronize(stream));
     last_counts = *h_cnt.p;
-    if (last_counts.error) { set_error("scanRegistration capacity exceeded (flags %d)", last_counts.error); return LOAM_ERR_CAPACITY; }
+    if (last_counts.error) { describe_sr_error(last_counts.error); return LOAM_ERR_CAPACITY; }
     return LOAM_OK;
   }
   void imu_trans(float out[12]) const {  // :614-629

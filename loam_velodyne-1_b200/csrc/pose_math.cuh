@@ -7,6 +7,10 @@
 //     laserOdometry.cpp:858-864 -> laserMapping.cpp:304-318 / transformMaintenance.cpp:147-161
 //   tf::Quaternion::setRPY / tf::Matrix3x3::getRPY (tf is not vendored by the reference)
 // Trigonometry goes through loam/detmath.h so host and device agree bit for bit.
+// The scalar expressions restated in this file (cited below) come from loam_velodyne:
+//   Copyright 2013, Ji Zhang, Carnegie Mellon University
+//   Further contributions copyright (c) 2016, Southwest Research Institute.  All rights reserved.
+// BSD 3-clause; the full notice, conditions and disclaimer are retained in NOTICE.md at the repository root.
 #pragma once
 #include "loam/detmath.h"
 

@@ -8,6 +8,10 @@
 // `g++ -O2 -ffp-contract=off`, it produces the same bits as the reference compiled against the
 // same third-party definitions (oracle/defs/*.h); tests/test_oracle_vs_ref.py checks exactly that
 // against oracle/_ref (the reference's own .cpp files compiled from /root/reference).
+// The scalar expressions restated in this file (cited below) come from loam_velodyne:
+//   Copyright 2013, Ji Zhang, Carnegie Mellon University
+//   Further contributions copyright (c) 2016, Southwest Research Institute.  All rights reserved.
+// BSD 3-clause; the full notice, conditions and disclaimer are retained in NOTICE.md at the repository root.
 #pragma once
 #include <stdio.h>
 #include <string.h>
