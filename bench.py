@@ -244,9 +244,11 @@ def measured_traffic(kernel):
     for name in ("r02_ncu_full_summary.json", "r01_ncu_full_summary_s10.json", "r01_ncu_full_summary_s8.json", "r01_ncu_full_summary.json"):   # newest capture first
         try:
             d = json.load(open(os.path.join(ROOT, "profiles", name)))
-            return float(d[kernel]["dram_bytes_per_launch"])
         except Exception:
             continue
+        for k in (kernel, kernel + "_ci", kernel + "_kernel"):   # profile names vs function names (lm_optimize_ci, lo_transform_to_end_kernel)
+            if k in d and isinstance(d[k], dict) and "dram_bytes_per_launch" in d[k]:
+                return float(d[k]["dram_bytes_per_launch"])
     return None
 
 

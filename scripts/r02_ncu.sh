@@ -10,4 +10,6 @@ ncu --set full --clock-control none --import-source on --launch-skip 900 -c 48 -
 echo "full capture rc=$?"
 ncu -i gpurun_out/r02_ncu_full.ncu-rep --page raw --csv > gpurun_out/r02_ncu_full_raw.csv 2>/dev/null
 python scripts/dev_ncu_summary.py gpurun_out/r02_ncu_full_raw.csv gpurun_out/r02_ncu_full_summary.json > gpurun_out/r02_ncu_full_summary.txt 2>&1
-tail -30 gpurun_out/r02_ncu_full_summary.txt
+rm -f gpurun_out/r02_ncu_full.ncu-rep     # 100+ MB: only the exported pages travel back
+ls -la gpurun_out | head -30
+tail -40 gpurun_out/r02_ncu_full_summary.txt
