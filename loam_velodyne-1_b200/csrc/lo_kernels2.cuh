@@ -207,6 +207,25 @@ __device__ __forceinline__ void red_rows_warped(const float (*rows)[8], int nwar
       }
     }
 }
+// rows laid out [feature block][32 slabs], 2 * RED_GROUPS feature blocks per pass (two features per warp): group grp
+// sums block grp, then block RED_GROUPS + grp -- the order in which two successive one-feature-per-warp passes
+// (red_rows_warped twice) would have added them
+__device__ __forceinline__ void red_rows_paired(const float (*rows)[8], int used, double& acc) {
+  const int t = threadIdx.x;
+  if (t >= LO_NRED * RED_GROUPS) return;
+  const int e = t % LO_NRED, grp = t / LO_NRED;
+  int ri, rj;
+  red_entry(e, ri, rj);
+#pragma unroll
+  for (int p = 0; p < 2; p++)
+    for (int l = 0; l < used; l++) {
+      const float* row = rows[(p * RED_GROUPS + grp) * 32 + l];
+      if (row[7] != 0.f) {
+        if (e < 27) acc += (double)row[ri] * (double)row[rj];
+        else acc += 1.0;
+      }
+    }
+}
 // CTA total = groups in ascending order -> partials[blockIdx]; one grid barrier; every CTA then
 // sums all partials (16 interleaved lanes per entry, then ascending) into s_tot[28].
 constexpr int PS_GROUPS = 16;
@@ -268,9 +287,12 @@ __global__ void __maxnreg__(LOAM_LO_MAXREG) lo_optimize(LOArgs A) {
   __shared__ double s_tot[LO_NRED];
   __shared__ int s_rows;
   __shared__ int s_roff[2][SR_MAX_RINGS + 1];
-  __shared__ float s_row[LO_WARPS * 32][8];     // one row per (feature of this pass, iteration slab)
-  __shared__ float4 s_tri[LO_WARPS][3];         // tripod of the warp's first-pass feature
-  __shared__ int s_triok[LO_WARPS];
+  __shared__ float s_row[2 * LO_WARPS * 32][8]; // one row per (feature of this pass, iteration slab); the paired form holds two features per warp
+  __shared__ float4 s_tri[2 * LO_WARPS][3];     // tripod of the warp's first-pass feature(s)
+  __shared__ int s_triok[2 * LO_WARPS];
+  __shared__ float4 s_cur[2 * LO_WARPS];        // paired form: this iteration's coefficients, leader lane -> row lane
+  __shared__ int s_curok[2 * LO_WARPS];
+  static_assert(LO_WARPS == RED_GROUPS, "one reduction group per warp");
   const int lane = lane_id(), warp = threadIdx.x >> 5;
   LOState* st = A.st;
   int clk = (blockIdx.x == 0 && threadIdx.x == 0 && PHASE_ON) ? 1 : -1;
@@ -374,6 +396,86 @@ __global__ void __maxnreg__(LOAM_LO_MAXREG) lo_optimize(LOArgs A) {
         __threadfence();
         grid.sync();
       }
+      // ---- paired form (the shipped configuration: contiguous slices + claimed searches): TWO features per warp,
+      // lanes 0-15 / 16-31.  The serial part of an iteration -- the residual on one lane -- runs for both at once and a
+      // CTA's 16 features need one pass instead of two; the rows land in the same (feature, slab) slots and are added
+      // in the same order as by two one-feature passes. ----
+      const bool paired = A.dynsearch != 0 && A.contiguous == 1;
+      if (paired) {
+        const int half = lane >> 4, hl = lane & 15;
+        const int blk = half * LO_WARPS + warp;          // feature block inside the pass
+        for (int j0 = 0; j0 < nmine; j0 += 2 * LO_WARPS) {
+          const int fi = j0 + blk;
+          const bool act = fi < nmine;
+          const int f = f_lo + fi;
+          const bool first_pass = (j0 == 0);
+          s_row[blk * 32 + hl][7] = 0.f;
+          s_row[blk * 32 + 16 + hl][7] = 0.f;
+          const bool is_corner = f < n_sharp;
+          float4 pt = make_float4(0, 0, 0, 0);
+          if (act) pt = is_corner ? A.sharp[f] : A.flat[f - n_sharp];
+          if (act && hl == 0) {
+            const int g = f - n_sharp;
+            int i1 = -1, i2 = -1, i3 = -1;
+            float4 t1 = pt, t2 = pt, t3 = pt;
+            bool ok = false;
+            const bool cached = first_pass && !refresh;
+            if (cached) {
+              ok = s_triok[blk] != 0;
+              t1 = s_tri[blk][0]; t2 = s_tri[blk][1]; t3 = s_tri[blk][2];
+            } else if (!refresh || first_pass) {   // after a search only the first pass needs the tripod (to park it)
+              if (is_corner) { i1 = __ldcg(&A.corner_ind1[f]); i2 = __ldcg(&A.corner_ind2[f]); ok = i2 >= 0; }
+              else { i1 = __ldcg(&A.surf_ind1[g]); i2 = __ldcg(&A.surf_ind2[g]); i3 = __ldcg(&A.surf_ind3[g]); ok = i2 >= 0 && i3 >= 0; }
+              if (ok) {
+                if (is_corner) { t1 = A.corner_last[i1]; t2 = A.corner_last[i2]; }
+                else { t1 = A.surf_last[i1]; t2 = A.surf_last[i2]; t3 = A.surf_last[i3]; }
+              }
+              if (refresh) { s_triok[blk] = ok ? 1 : 0; if (ok) { s_tri[blk][0] = t1; s_tri[blk][1] = t2; s_tri[blk][2] = t3; } }
+            }
+            if (!refresh) {
+              bool valid = false;
+              float4 coeff = make_float4(0, 0, 0, 0);
+              if (ok) {
+                const float4 sel = lo_transform_to_start(pt, s_tr);
+                valid = is_corner ? lo_corner_residual(sel, t1, t2, iterCount, coeff) : lo_surf_residual(sel, t1, t2, t3, iterCount, coeff);
+              }
+              A.coeff[(size_t)iterCount * A.fcap + f] = coeff;
+              A.row_valid[(size_t)iterCount * A.fcap + f] = valid ? 1 : 0;
+              s_cur[blk] = coeff;
+              s_curok[blk] = valid ? 1 : 0;
+            }
+          }
+          __syncwarp();
+          // Jacobian of every row accumulated so far: lane hl takes the slabs hl and hl + 16 of its half's feature
+          if (act) {
+            for (int sl = hl; sl <= iterCount; sl += 16) {
+              const size_t slot = (size_t)sl * A.fcap + f;
+              bool v;
+              float4 cf;
+              if (sl == iterCount) {
+                if (refresh) { v = __ldcg(&A.row_valid[slot]) != 0; cf = __ldcg(&A.coeff[slot]); }   // written by the claiming warp, maybe on another SM
+                else { v = s_curok[blk] != 0; cf = s_cur[blk]; }
+              } else {
+                v = A.row_valid[slot] != 0; cf = A.coeff[slot];
+              }
+              if (v) {
+                float a[6], b;
+                lo_row(pt, cf, s_trig, s_tr, a, b);
+                float* row = s_row[blk * 32 + sl];
+#pragma unroll
+                for (int j = 0; j < 6; j++) row[j] = a[j];
+                row[6] = b;
+                row[7] = 1.f;
+              }
+            }
+          }
+          __syncthreads();
+          if (first_pass) PS();  // 0: features + rows of the first pass done
+          if (first_pass && iterCount == 0 && PHASE_ON && threadIdx.x == 0) g_dbg_clk[64 + blockIdx.x] = clock64() - dbg_t0;
+          red_rows_paired(s_row, iterCount + 1, acc);
+          __syncthreads();
+        }
+      } else
       for (int j0 = 0; j0 < nmine; j0 += LO_WARPS) {
         const int f = cyclic ? ((j0 / LO_WARPS) * G + (int)blockIdx.x) * LO_WARPS + warp : f_lo + (j0 + warp) * f_step;
         const bool first_pass = (j0 == 0);

@@ -21,12 +21,23 @@ warm = int(sys.argv[5]) if len(sys.argv) > 5 else 20     # 5 = the sweeps the dr
 S = synth.Synth(preset)
 sweeps = [S.sweep(k) for k in range(nsw + warm)]
 G = pkg.Pipeline(pkg.make_params(preset, system_delay=0), device=0)
+resident = len(sys.argv) > 6 and sys.argv[6] == "resident"    # sweeps already in HBM, as bench.py's `value` arm feeds them (no host staging copy)
+if resident:
+    import torch
+    dev_sweeps = [torch.from_numpy(x).cuda() for x, _ in sweeps]
+    def fl(x):
+        idx = np.nonzero(np.isfinite(x).all(axis=1))[0]
+        return np.concatenate([x[idx[0]], x[idx[-1]]]).astype(np.float32), int(idx[0])
+    aux = [fl(x) for x, _ in sweeps]
+    feed = lambda k: G.push_device(dev_sweeps[k].data_ptr(), sweeps[k][0].shape[0], aux[k][0], aux[k][1], sweeps[k][1])
+else:
+    feed = lambda k: G.push_async(*sweeps[k])
 for k in range(warm):
-    G.push_async(*sweeps[k])
+    feed(k)
 G.collect()
 L.loam_debug_trace_enable(mode)
 for k in range(warm, warm + nsw):
-    G.push_async(*sweeps[k])
+    feed(k)
 G.collect()
 n = L.loam_debug_trace_dump(out.encode())
 L.loam_debug_trace_enable(0)
