@@ -305,3 +305,33 @@ def test_solve_step_near_the_eigen_threshold(pkg, checker, thr):
     assert biteq(X0, Xo)
     m = dego == 1
     assert biteq(P0[m], Po[m])                                             # matP is only read while isDegenerate
+
+
+def test_documented_limits_are_refused_with_a_specific_message(pkg, synth):
+    """include/loam_b200.h "Hard limits": a parameter block or a sweep beyond a compile-time capacity of the kernels is
+    refused with an error text that names the limit -- never truncated silently, never a crash"""
+    P = pkg.make_params(1, system_delay=0)
+    P.lo_max_iter = 33
+    with pytest.raises(pkg.LoamError, match=r"lo_max_iter = 33 is outside 1 \.\. 32"):
+        pkg.Pipeline(P)
+    P = pkg.make_params(1, system_delay=0)
+    P.lm_max_iter = 0
+    with pytest.raises(pkg.LoamError, match="lm_max_iter"):
+        pkg.LaserMapping(P)
+    P = pkg.make_params(1, system_delay=0)
+    P.n_scans = 129
+    with pytest.raises(pkg.LoamError, match="LOAM_LIMIT_RINGS"):
+        pkg.ScanRegistration(P)
+    P = pkg.make_params(1, system_delay=0)
+    P.map_arena_points = 100
+    with pytest.raises(pkg.LoamError, match="map_arena_points"):
+        pkg.LaserMapping(P)
+    # one ring with far more points than its buffers hold: 9000 returns at -24 deg elevation (all on ring 2 of the HDL-64 model)
+    P = pkg.make_params(2, system_delay=0)
+    sr = pkg.ScanRegistration(P)
+    az = np.linspace(0.0, -2.0 * np.pi, 9000, endpoint=False)
+    rng = 10.0 + 0.5 * np.sin(7 * az)
+    xyz = np.stack([rng * np.cos(az), rng * np.sin(az), np.tan(np.radians(-24.0)) * rng], axis=1).astype(np.float32)
+    with pytest.raises(pkg.LoamError, match="LOAM_LIMIT_(SECTOR|RING)_POINTS"):
+        assert sr.process(xyz, 0.0) == 1     # the first sweep is swallowed (scanRegistration.cpp:213-219)
+        sr.process(xyz, 0.1)
