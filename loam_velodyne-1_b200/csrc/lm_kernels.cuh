@@ -76,6 +76,9 @@ struct LMState {
   // filters) already overwrites stackN / transformTobeMapped on the main stream
   int insN[2];
   float insT[6];
+  // the same snapshot, two deep, of what the pipeline's pose record of the pass reports: the record kernel runs on the
+  // second side stream, off the map-update chain, and may be late by a pass
+  struct Rec { float aft[6], bef[6]; int iters, rows, deg, mapN[2], stackN[2], pad; } rec[2];
 };
 
 struct LMTrig { float srx, crx, sry, cry, srz, crz; };

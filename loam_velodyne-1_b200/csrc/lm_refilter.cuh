@@ -51,6 +51,7 @@ struct LMInsertArgs {
   int* ins_cube[2];
   unsigned int* ins_key[2];
   int* touch_cnt[2];
+  int rec_slot;              // which LMState::rec the pass's record snapshot goes to
 };
 // K7a: stack points to the map with the refined pose, their cube and voxel (:980-1016)
 __global__ void __launch_bounds__(256) lm_insert_ids(LMInsertArgs A) {
@@ -67,6 +68,10 @@ __global__ void __launch_bounds__(256) lm_insert_ids(LMInsertArgs A) {
   if (blockIdx.x == 0 && threadIdx.x == 0) {   // what the side-stream kernels of this pass read (LMState::insN / insT)
     st->insN[0] = n0; st->insN[1] = n1;
     for (int i = 0; i < 6; i++) st->insT[i] = s_T[i];
+    LMState::Rec& R = st->rec[A.rec_slot & 1];
+    for (int i = 0; i < 6; i++) { R.aft[i] = st->transformAftMapped[i]; R.bef[i] = st->transformBefMapped[i]; }
+    R.iters = st->iters; R.rows = st->rows; R.deg = st->isDegenerate;
+    R.mapN[0] = st->mapN[0]; R.mapN[1] = st->mapN[1]; R.stackN[0] = n0; R.stackN[1] = n1;
   }
   const int cenW = st->cenW, cenH = st->cenH, cenD = st->cenD;
   for (int i = blockIdx.x * 256 + threadIdx.x; i < n0 + n1; i += gridDim.x * 256) {
@@ -198,6 +203,7 @@ __global__ void __launch_bounds__(1024, 1) lm_sort_new(LMSortNewArgs A) {
 // path sorts everything again, stably).
 constexpr int BN_THREADS = 512;
 constexpr int BN_GRID = 16;
+constexpr int BN_PER = 8, BN_TILE = BN_THREADS * BN_PER;
 constexpr size_t BN_SMEM = (size_t)RF_NEW_CAP * 16 + sizeof(CtaRadixSmem);
 __global__ void __launch_bounds__(BN_THREADS, 1) lm_bucket_new(LMSortNewArgs A) {
   extern __shared__ __align__(16) unsigned char bn_smem[];
@@ -207,40 +213,57 @@ __global__ void __launch_bounds__(BN_THREADS, 1) lm_bucket_new(LMSortNewArgs A) 
   unsigned int* v1 = k1 + RF_NEW_CAP;
   CtaRadixSmem& S = *(CtaRadixSmem*)(v1 + RF_NEW_CAP);
   __shared__ int s_ws[BN_THREADS / 32];
+  __shared__ int s_tile[BN_TILE];
   LMState* st = A.st;
   const int T = blockIdx.y;
   const int n = st->insN[T];
   const int np = st->nproc[T];
   if (blockIdx.x == 0 && threadIdx.x == 0) st->newSel[T] = 0;
-  const int per = (n + BN_THREADS - 1) / BN_THREADS;          // contiguous chunk per thread: stable
-  const int c0 = min(n, (int)threadIdx.x * per), c1 = min(n, c0 + per);
+  // The stack is walked in tiles of BN_TILE entries: a tile's cube ids are staged with coalesced loads, then every
+  // thread owns BN_PER consecutive entries of the tile (so the compaction is stable: stack order) -- one L2 round
+  // trip per tile instead of one per entry and thread.
   for (int r = blockIdx.x; r < np; r += gridDim.x) {
     const int cube = st->procCube[T][r];
     const int n_new = st->procNewCnt[T][r];
-    const bool sorted = st->procMode[T][r] != 0 && n_new <= RF_NEW_CAP;
+    const int mode = st->procMode[T][r];
+    const bool sorted = mode != 0 && n_new <= RF_NEW_CAP;
     unsigned int* gk = A.nk[T][0] + st->procNewOff[T][r];
     unsigned int* gv = A.nv[T][0] + st->procNewOff[T][r];
-    int cnt = 0;
-    for (int k = c0; k < c1; k++) cnt += (A.ins_cube[T][k] == cube) ? 1 : 0;
-    // exclusive prefix over the CTA
-    int x = cnt;
-    for (int o = 1; o < 32; o <<= 1) {
-      int y = __shfl_up_sync(0xffffffffu, x, o);
-      if (lane_id() >= o) x += y;
-    }
-    __syncthreads();
-    if (lane_id() == 31) s_ws[threadIdx.x >> 5] = x;
-    __syncthreads();
-    int pos = x - cnt;
-    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) pos += s_ws[w];
     unsigned int* dk = sorted ? k0 : gk;
     unsigned int* dv = sorted ? v0 : gv;
-    for (int k = c0; k < c1; k++) {
-      if (A.ins_cube[T][k] == cube) {
-        dk[pos] = ((unsigned int)r << 24) | (st->procMode[T][r] ? A.ins_key[T][k] : 0u);
-        dv[pos] = (unsigned int)k;
-        pos++;
+    int done = 0;
+    for (int t0 = 0; t0 < n; t0 += BN_TILE) {
+#pragma unroll
+      for (int u = 0; u < BN_PER; u++) {
+        const int idx = t0 + u * BN_THREADS + (int)threadIdx.x;
+        s_tile[u * BN_THREADS + threadIdx.x] = idx < n ? A.ins_cube[T][idx] : -1;
       }
+      __syncthreads();
+      unsigned int m = 0;
+#pragma unroll
+      for (int j = 0; j < BN_PER; j++) m |= (s_tile[threadIdx.x * BN_PER + j] == cube) ? (1u << j) : 0u;
+      const int cnt = __popc(m);
+      // exclusive prefix over the CTA
+      int x = cnt;
+      for (int o = 1; o < 32; o <<= 1) {
+        int y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane_id() >= o) x += y;
+      }
+      if (lane_id() == 31) s_ws[threadIdx.x >> 5] = x;
+      __syncthreads();
+      int pos = done + x - cnt, tot = 0;
+#pragma unroll
+      for (int w = 0; w < BN_THREADS / 32; w++) { const int c = s_ws[w]; if (w < (int)(threadIdx.x >> 5)) pos += c; tot += c; }
+      for (int j = 0; j < BN_PER; j++) {
+        if ((m >> j) & 1u) {
+          const int k = t0 + (int)threadIdx.x * BN_PER + j;
+          dk[pos] = ((unsigned int)r << 24) | (mode ? A.ins_key[T][k] : 0u);
+          dv[pos] = (unsigned int)k;
+          pos++;
+        }
+      }
+      done += tot;
+      __syncthreads();
     }
     __syncthreads();
     if (sorted) {

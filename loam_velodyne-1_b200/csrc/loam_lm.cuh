@@ -24,6 +24,9 @@ struct LMHandle {
   // LM loop -> map update -> window shift -> gather -> index -> LM loop that sets the mapping rate.
   cudaStream_t aux2 = nullptr;
   cudaEvent_t ev_reg = nullptr, ev_sur_in = nullptr, ev_sur_done = nullptr;
+  // pose record of a pass (loam_pipeline.cuh): snapshot slot of the pass, "map update enqueued" and "slot read" events
+  cudaEvent_t ev_upd = nullptr, ev_rec[2] = {nullptr, nullptr};
+  int rec_slot = 0, last_rec_slot = 0;
   int cap = 0, ecap = 0, arena_cap = 0, coop_blocks = 0;
   int cur_arena = 0;
   int sweeps_since_compact = 0;
@@ -99,6 +102,9 @@ struct LMHandle {
       CUDA_OK(cudaEventCreateWithFlags(&ev_reg, cudaEventDisableTiming));
       CUDA_OK(cudaEventCreateWithFlags(&ev_sur_in, cudaEventDisableTiming));
       CUDA_OK(cudaEventCreateWithFlags(&ev_sur_done, cudaEventDisableTiming));
+      CUDA_OK(cudaEventCreateWithFlags(&ev_upd, cudaEventDisableTiming));
+      CUDA_OK(cudaEventCreateWithFlags(&ev_rec[0], cudaEventDisableTiming));
+      CUDA_OK(cudaEventCreateWithFlags(&ev_rec[1], cudaEventDisableTiming));
     }
     cap = P.max_points;
     arena_cap = P.map_arena_points > 0 ? P.map_arena_points : (8 << 20);
@@ -224,6 +230,8 @@ struct LMHandle {
     if (ev_reg) cudaEventDestroy(ev_reg);
     if (ev_sur_in) cudaEventDestroy(ev_sur_in);
     if (ev_sur_done) cudaEventDestroy(ev_sur_done);
+    if (ev_upd) cudaEventDestroy(ev_upd);
+    for (int b = 0; b < 2; b++) if (ev_rec[b]) cudaEventDestroy(ev_rec[b]);
     for (int b = 0; b < 2; b++) {
       if (ev_in_ready[b]) cudaEventDestroy(ev_in_ready[b]);
       if (ev_in_done[b]) cudaEventDestroy(ev_in_done[b]);
@@ -374,6 +382,10 @@ struct LMHandle {
     {
       LMInsertArgs IA;
       IA.st = st;
+      last_rec_slot = rec_slot;
+      rec_slot ^= 1;
+      IA.rec_slot = last_rec_slot;
+      CUDA_OK(cudaStreamWaitEvent(stream, ev_rec[last_rec_slot], 0));   // the record of the pass before last has read this slot
       for (int T = 0; T < 2; T++) { IA.stack[T] = d_stack[T].p; IA.ins_pts[T] = d_ins_pts[T].p; IA.ins_cube[T] = d_ins_cube[T].p; IA.ins_key[T] = d_ins_key[T].p; IA.touch_cnt[T] = d_touch[T].p; }
       LAUNCH("lm_insert_ids", lm_insert_ids, nb, 256, 0, stream, IA);
       CUDA_OK(cudaEventRecord(ev_fork, stream));

@@ -43,11 +43,14 @@ __global__ void pipe_record(PipeRecord* out, const SRCounts* cnt, const ImuState
   *out = r;
 }
 // ... and its mapping part, appended on the mapping stream when the sweep was mapped
-__global__ void pipe_record_lm(PipeRecord* out, const LMState* lm) {
+// (second mapping side stream, behind the pass's map update: poses and counters come from the snapshot lm_insert_ids
+// took, because the next pass is already rewriting the live fields; error flags and arena pointers are read as they are)
+__global__ void pipe_record_lm(PipeRecord* out, const LMState* lm, int rec_slot) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  for (int i = 0; i < 6; i++) { out->aft[i] = lm->transformAftMapped[i]; out->bef[i] = lm->transformBefMapped[i]; }
-  out->lm_iters = lm->iters; out->lm_rows = lm->rows; out->lm_deg = lm->isDegenerate; out->lm_error = lm->error;
-  for (int T = 0; T < 2; T++) { out->mapN[T] = lm->mapN[T]; out->stackN[T] = lm->insN[T]; out->bump[T] = lm->bump[T]; }
+  const LMState::Rec& R = lm->rec[rec_slot & 1];
+  for (int i = 0; i < 6; i++) { out->aft[i] = R.aft[i]; out->bef[i] = R.bef[i]; }
+  out->lm_iters = R.iters; out->lm_rows = R.rows; out->lm_deg = R.deg; out->lm_error = lm->error;
+  for (int T = 0; T < 2; T++) { out->mapN[T] = R.mapN[T]; out->stackN[T] = R.stackN[T]; out->bump[T] = lm->bump[T]; }
 }
 // ... and the size of the surround map, on the stream that filters it
 __global__ void pipe_record_surround(PipeRecord* out, const LMState* lm) {
@@ -163,7 +166,12 @@ struct PipelineHandle {
         pd.lm_status = mrc;
       }
       if (pd.lm_status == LOAM_OK) {
-        LAUNCH("pipe_record_lm", pipe_record_lm, 1, 32, 0, lm.aux, h_ring.p + pd.slot, lm.d_state.p);   // behind the pass's map update
+        // behind the pass's map update, but on the second side stream: the next pass's window shift + index refresh (first
+        // side stream) do not queue behind a one-thread kernel
+        CUDA_OK(cudaEventRecord(lm.ev_upd, lm.aux));
+        CUDA_OK(cudaStreamWaitEvent(lm.aux2, lm.ev_upd, 0));
+        LAUNCH("pipe_record_lm", pipe_record_lm, 1, 32, 0, lm.aux2, h_ring.p + pd.slot, lm.d_state.p, lm.last_rec_slot);
+        CUDA_OK(cudaEventRecord(lm.ev_rec[lm.last_rec_slot], lm.aux2));
         if (lm.last_surround) LAUNCH("pipe_record_surround", pipe_record_surround, 1, 32, 0, lm.aux2, h_ring.p + pd.slot, lm.d_state.p);
       }
     }
