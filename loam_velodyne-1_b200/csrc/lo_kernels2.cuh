@@ -697,59 +697,55 @@ __global__ void __maxnreg__(LOAM_LO_MAXREG) lo_optimize(LOArgs A) {
 #undef PS
 }
 
-// TransformToEnd over less-sharp -> corner_last, less-flat -> surf_last, (optionally) full ->
-// full_end (:875-891); the buffer "swap" (:893-899) is the write into the *_last arrays.
-struct ToEndArgs {
-  LOState* st;
-  const SRCounts* cnt;
-  const ImuState* imu;
-  const float4* less_sharp; const float4* less_flat; const float4* full;
-  float4* corner_last; float4* surf_last; float4* full_end;
-  int do_full;
+// what the pipeline reports per sweep (loam_pipeline.cuh), written straight into the pinned host ring
+struct PipeRecord {
+  SRCounts cnt;
+  float imu_trans[12];
+  float transform[6], transformSum[6];
+  int lo_iters, lo_rows, lo_deg;
+  float aft[6], bef[6];
+  int lm_iters, lm_rows, lm_deg, lm_error;
+  int mapN[2], stackN[2], bump[2];
+  int surroundN, pad;
 };
-__global__ void __launch_bounds__(256) lo_transform_to_end_kernel(ToEndArgs A) {
-  __shared__ float s_tr[6];
-  __shared__ float s_imu[12];
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < 6; i++) s_tr[i] = A.st->transform[i];
-    lo_load_imu(A.imu, s_imu);
-  }
-  __syncthreads();
-  const int n0 = A.cnt->n_less_sharp, n1 = A.cnt->n_less_flat, n2 = A.do_full ? A.cnt->n_full : 0;
-  const int total = n0 + n1 + n2;
-  for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
-    if (i < n0) A.corner_last[i] = lo_transform_to_end(A.less_sharp[i], s_tr, s_imu);
-    else if (i < n0 + n1) A.surf_last[i - n0] = lo_transform_to_end(A.less_flat[i - n0], s_tr, s_imu);
-    else A.full_end[i - n0 - n1] = lo_transform_to_end(A.full[i - n0 - n1], s_tr, s_imu);
-  }
+// odometry part of a sweep's record (one thread)
+__device__ __forceinline__ void pipe_record_body(PipeRecord* out, const SRCounts* cnt, const ImuState* imu, const LOState* lo) {
+  PipeRecord r;
+  r.cnt = *cnt;
+  lo_load_imu(imu, r.imu_trans);
+  for (int i = 0; i < 6; i++) { r.transform[i] = lo->transform[i]; r.transformSum[i] = lo->transformSum[i]; }
+  r.lo_iters = lo->iters; r.lo_rows = lo->rows; r.lo_deg = lo->isDegenerate;
+  for (int i = 0; i < 6; i++) { r.aft[i] = 0.f; r.bef[i] = 0.f; }
+  r.lm_iters = 0; r.lm_rows = 0; r.lm_deg = 0; r.lm_error = 0;
+  for (int T = 0; T < 2; T++) { r.mapN[T] = 0; r.stackN[T] = 0; r.bump[T] = 0; }
+  r.surroundN = -1; r.pad = 0;   // -1: no surround map on this sweep (pipe_record_surround fills it in)
+  *out = r;
 }
 
-// bookkeeping after the swap (:901-903); mode 1 = first sweep (:427-456: plain adoption of the
+// bookkeeping after the swap (:901-903), one warp; mode 1 = first sweep (:427-456: plain adoption of the
 // clouds, transformSum seeded from the IMU, the *LastNum counters are NOT touched)
-__global__ void lo_finish(LOState* st, const SRCounts* cnt, const ImuState* imu, int first_sweep, int do_full,
-                          const int* ring_counts, int n_scans, int* corner_roff, int* surf_roff) {
+__device__ __forceinline__ void lo_finish_body(LOState* st, const SRCounts* cnt, const ImuState* imu, int first_sweep, int do_full,
+                                               const int* ring_counts, int n_scans, int* corner_roff, int* surf_roff) {
   // ring offset tables of the clouds that just became corner_last / surf_last (ring-major)
-  {
-    const int lane = threadIdx.x & 31;   // launched with one warp
-    for (int T = 0; T < 2; T++) {
-      int* roff = T ? surf_roff : corner_roff;
-      const int col = T ? 3 : 1;
-      int run = 0;
-      for (int r0 = 0; r0 < n_scans; r0 += 32) {
-        const int r = r0 + lane;
-        const int c = r < n_scans ? ring_counts[r * 4 + col] : 0;
-        int x = c;
-        for (int o = 1; o < 32; o <<= 1) {
-          int y = __shfl_up_sync(0xffffffffu, x, o);
-          if (lane >= o) x += y;
-        }
-        if (r < n_scans) roff[r] = run + x - c;
-        run += __shfl_sync(0xffffffffu, x, 31);
+  const int lane = threadIdx.x & 31;
+  for (int T = 0; T < 2; T++) {
+    int* roff = T ? surf_roff : corner_roff;
+    const int col = T ? 3 : 1;
+    int run = 0;
+    for (int r0 = 0; r0 < n_scans; r0 += 32) {
+      const int r = r0 + lane;
+      const int c = r < n_scans ? ring_counts[r * 4 + col] : 0;
+      int x = c;
+      for (int o = 1; o < 32; o <<= 1) {
+        int y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
       }
-      if (lane == 0) roff[n_scans] = run;
+      if (r < n_scans) roff[r] = run + x - c;
+      run += __shfl_sync(0xffffffffu, x, 31);
     }
+    if (lane == 0) roff[n_scans] = run;
   }
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  if (lane != 0) return;
   st->n_corner_last = cnt->n_less_sharp;
   st->n_surf_last = cnt->n_less_flat;
   if (first_sweep) {
@@ -765,6 +761,46 @@ __global__ void lo_finish(LOState* st, const SRCounts* cnt, const ImuState* imu,
     st->index_enable = (st->cornerLastNum > 10 && st->surfLastNum > 100) ? 1 : 0;
     if (do_full) st->n_full_end = cnt->n_full;
   }
+}
+__global__ void lo_finish(LOState* st, const SRCounts* cnt, const ImuState* imu, int first_sweep, int do_full,
+                          const int* ring_counts, int n_scans, int* corner_roff, int* surf_roff) {
+  if (blockIdx.x == 0 && threadIdx.x < 32) lo_finish_body(st, cnt, imu, first_sweep, do_full, ring_counts, n_scans, corner_roff, surf_roff);
+}
+
+// TransformToEnd over less-sharp -> corner_last, less-flat -> surf_last, (optionally) full ->
+// full_end (:875-891); the buffer "swap" (:893-899) is the write into the *_last arrays.  The same launch carries
+// the node's one-warp bookkeeping (CTA 0; nothing in this kernel reads what it writes) and, for a pipeline, the
+// sweep's pose record (last CTA, one thread; it reads what lo_optimize left, not what the bookkeeping writes):
+// two one-warp launches fewer on the odometry chain.
+struct ToEndArgs {
+  LOState* st;
+  const SRCounts* cnt;
+  const ImuState* imu;
+  const float4* less_sharp; const float4* less_flat; const float4* full;
+  float4* corner_last; float4* surf_last; float4* full_end;
+  int do_full;
+  const int* ring_counts; int n_scans; int* corner_roff; int* surf_roff;
+  PipeRecord* record;        // nullptr: no record (stand-alone node)
+};
+__global__ void __launch_bounds__(256) lo_transform_to_end_kernel(ToEndArgs A) {
+  __shared__ float s_tr[6];
+  __shared__ float s_imu[12];
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 6; i++) s_tr[i] = A.st->transform[i];
+    lo_load_imu(A.imu, s_imu);
+  }
+  __syncthreads();
+  const int n0 = A.cnt->n_less_sharp, n1 = A.cnt->n_less_flat, n2 = A.do_full ? A.cnt->n_full : 0;
+  const int total = n0 + n1 + n2;
+  if (A.record && blockIdx.x == gridDim.x - 1 && threadIdx.x == 255) pipe_record_body(A.record, A.cnt, A.imu, A.st);
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
+    if (i < n0) A.corner_last[i] = lo_transform_to_end(A.less_sharp[i], s_tr, s_imu);
+    else if (i < n0 + n1) A.surf_last[i - n0] = lo_transform_to_end(A.less_flat[i - n0], s_tr, s_imu);
+    else A.full_end[i - n0 - n1] = lo_transform_to_end(A.full[i - n0 - n1], s_tr, s_imu);
+  }
+  // the bookkeeping overwrites n_full_end / *_last counters that only LATER kernels read; st->transform, read above by
+  // every CTA, is not among the fields it writes
+  if (blockIdx.x == 0 && threadIdx.x < 32) lo_finish_body(A.st, A.cnt, A.imu, 0, A.do_full, A.ring_counts, A.n_scans, A.corner_roff, A.surf_roff);
 }
 
 __global__ void __launch_bounds__(256) lo_adopt_first(const SRCounts* cnt, const float4* less_sharp, const float4* less_flat,

@@ -132,8 +132,10 @@ struct LOHandle {
       T.st = d_state.p; T.cnt = sr.d_cnt.p; T.imu = imu;
       T.less_sharp = sr.d_less_sharp.p; T.less_flat = sr.d_less_flat.p; T.full = sr.d_full.p;
       T.corner_last = d_corner_last.p; T.surf_last = d_surf_last.p; T.full_end = d_full_end.p; T.do_full = do_full;
+      T.ring_counts = sr.d_ring_counts.p; T.n_scans = P.n_scans; T.corner_roff = d_corner_roff.p; T.surf_roff = d_surf_roff.p;
+      T.record = record_out;     // bookkeeping (lo_finish) and the pipeline's pose record ride on this launch
+      record_written = record_out != nullptr;
       LAUNCH("lo_transform_to_end", lo_transform_to_end_kernel, 2 * nb, 256, 0, stream, T);
-      LAUNCH("lo_finish", lo_finish, 1, 32, 0, stream, d_state.p, sr.d_cnt.p, imu, 0, do_full, sr.d_ring_counts.p, P.n_scans, d_corner_roff.p, d_surf_roff.p);
       int r = grid_build_pair(gp, nb, stream, (P.dev_flags & 16) == 0);   // the last clouds are feature clouds: always small
       if (r != LOAM_OK) return r;
     }
@@ -145,6 +147,10 @@ struct LOHandle {
   // the same pass fed from HOST copies of the six topics: a private scanRegistration handle on this
   // node's stream serves as the feature carrier (SRHandle::set_features)
   SRHandle* carrier = nullptr;
+  // set by a pipeline before process(): where the sweep's pose record goes; record_written tells it afterwards whether
+  // the pass wrote it (it does not on the first sweep and with the in-kernel tail)
+  PipeRecord* record_out = nullptr;
+  bool record_written = false;
   int process_host(const float* const clouds[5], const int counts[5], const float imu_trans[12], bool* published) {
     *published = false;
     if (!carrier) {

@@ -17,30 +17,11 @@
 
 namespace loamgpu {
 
-struct PipeRecord {
-  SRCounts cnt;
-  float imu_trans[12];
-  float transform[6], transformSum[6];
-  int lo_iters, lo_rows, lo_deg;
-  float aft[6], bef[6];
-  int lm_iters, lm_rows, lm_deg, lm_error;
-  int mapN[2], stackN[2], bump[2];
-  int surroundN, pad;
-};
-
-// odometry part of a sweep's record (pipeline stream) ...
+// odometry part of a sweep's record (PipeRecord, pipe_record_body: lo_kernels2.cuh) as a launch of its own -- only when
+// the odometry pass could not carry it (first sweep, in-kernel tail) ...
 __global__ void pipe_record(PipeRecord* out, const SRCounts* cnt, const ImuState* imu, const LOState* lo) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  PipeRecord r;
-  r.cnt = *cnt;
-  lo_load_imu(imu, r.imu_trans);
-  for (int i = 0; i < 6; i++) { r.transform[i] = lo->transform[i]; r.transformSum[i] = lo->transformSum[i]; }
-  r.lo_iters = lo->iters; r.lo_rows = lo->rows; r.lo_deg = lo->isDegenerate;
-  for (int i = 0; i < 6; i++) { r.aft[i] = 0.f; r.bef[i] = 0.f; }
-  r.lm_iters = 0; r.lm_rows = 0; r.lm_deg = 0; r.lm_error = 0;
-  for (int T = 0; T < 2; T++) { r.mapN[T] = 0; r.stackN[T] = 0; r.bump[T] = 0; }
-  r.surroundN = -1; r.pad = 0;   // -1: no surround map on this sweep (pipe_record_surround fills it in)
-  *out = r;
+  pipe_record_body(out, cnt, imu, lo);
 }
 // ... and its mapping part, appended on the mapping stream when the sweep was mapped
 // (second mapping side stream, behind the pass's map update: poses and counters come from the snapshot lm_insert_ids
@@ -148,13 +129,16 @@ struct PipelineHandle {
       pd.sr_status = LOAM_OK;
       bool pub = false;
       long long t_lo = now_ns();
+      lo.record_out = h_ring.p + pd.slot;
+      lo.record_written = false;
       int lrc = lo.process(sr, &pub);
+      lo.record_out = nullptr;
       if (lrc < 0) return lrc;
       if (g_profile == 3) prof_node("laserOdometry", stream, false);
       pd.lo_status = lrc;
       // record + release of the scanRegistration bank BEFORE the mapping is enqueued: the next
       // sweeps' registration / odometry do not wait for it
-      LAUNCH("pipe_record", pipe_record, 1, 32, 0, stream, h_ring.p + pd.slot, sr.d_cnt.p, sr.imu_state_dev(), lo.d_state.p);
+      if (!lo.record_written) LAUNCH("pipe_record", pipe_record, 1, 32, 0, stream, h_ring.p + pd.slot, sr.d_cnt.p, sr.imu_state_dev(), lo.d_state.p);
       int rr = sr.release_bank(stream);
       if (rr < 0) return rr;
       g_host_node_ns[1] += now_ns() - t_lo;
