@@ -143,7 +143,7 @@ struct PipelineHandle {
       if (rr < 0) return rr;
       g_host_node_ns[1] += now_ns() - t_lo;
       HostNode hn(2);
-      if (lrc == LOAM_OK && pub) {
+      if (lrc == LOAM_OK && pub && !(lo.P.dev_flags & 1024)) {
         int mrc = lm.process(lo, stamp);
         if (mrc < 0) return mrc;
         if (g_profile == 3) prof_node("laserMapping", lm_stream, false);
