@@ -209,51 +209,55 @@ __device__ __forceinline__ unsigned int ci_rows9_pos(const CIRows9& R, int t) {
 // The query's 3x3x3 block of lattice cells as 9 x-rows, the part of them inside cube column `di` (a row of
 // three cells crosses at most one cube boundary in x: the caller makes a second pass with di + 1 when it does).
 // bounded: only the cells a ball of squared radius r2 around the query reaches (grid_rows9_bounded).
+__device__ __forceinline__ void ci_row_range(const CIView& g, const int* s_slot, const float* s_org, int cx, int cy, int cz, int di,
+                                             bool bounded, float qx, float qy, float qz, float r2, int rowk, unsigned int& vb, unsigned int& ve) {
+  vb = 0; ve = 0;
+  const int oy = (rowk % 3) - 1, oz = (rowk / 3) - 1;
+  const int y = cy + oy, z = cz + oz;
+  if (y < 0 || y >= CI_SPAN || z < 0 || z >= CI_SPAN) return;
+  int x0 = cx - 1, x1 = cx + 1;
+  bool take = true;
+  if (bounded) {
+    const float margin = 4.0e-3f;
+    const float fx = qx - (s_org[0] + (float)cx * CI_H), fy = qy - (s_org[1] + (float)cy * CI_H), fz = qz - (s_org[2] + (float)cz * CI_H);
+    const float dyv = fmaxf((oy < 0 ? fy : (oy > 0 ? CI_H - fy : 0.f)) - margin, 0.f);
+    const float dzv = fmaxf((oz < 0 ? fz : (oz > 0 ? CI_H - fz : 0.f)) - margin, 0.f);
+    const float base = dyv * dyv + dzv * dzv;
+    take = base <= r2;
+    const float dxm = fmaxf(fx - margin, 0.f), dxp = fmaxf(CI_H - fx - margin, 0.f);
+    if (!(base + dxm * dxm <= r2)) x0 = cx;
+    if (!(base + dxp * dxp <= r2)) x1 = cx;
+  }
+  x0 = max(x0, di * CI_N);
+  x1 = min(x1, di * CI_N + CI_N - 1);
+  if (!take || x0 > x1) return;
+  const int dj = y / CI_N, dk = z / CI_N;
+  const int q = (di * 5 + dj) * 5 + dk;
+  const int slot = s_slot[q];
+  if (slot < 0) return;
+  const int2* row = g.cell + (size_t)slot * CI_TABLE + ((z - dk * CI_N) * CI_N + (y - dj * CI_N)) * CI_N - di * CI_N;
+  const int2 c0 = __ldg(&row[x0]);
+  const int2 c1 = __ldg(&row[x1]);
+  const unsigned int tag = (unsigned int)q << CI_ADDR_BITS;
+  vb = tag | (unsigned int)(c0.x - c0.y);
+  ve = tag | (unsigned int)c1.x;
+}
+// W = lanes cooperating on one query (32, 16 or 8): one lane per row; with W = 8 lane 0 also takes the ninth row
 template <int W>
 __device__ __forceinline__ void ci_rows9(const CIView& g, const int* s_slot, const float* s_org, int cx, int cy, int cz, int di,
                                          bool bounded, float qx, float qy, float qz, float r2, CIRows9& R) {
-  static_assert(W >= 16, "one lane per row");
+  static_assert(W == 8 || W == 16 || W == 32, "group size");
   const int gl = lane_id() & (W - 1);
   const unsigned int gmask = (W == 32) ? 0xffffffffu : (((1u << W) - 1u) << (lane_id() & ~(W - 1)));
-  unsigned int vb = 0, ve = 0;
-  if (gl < 9) {
-    const int oy = (gl % 3) - 1, oz = (gl / 3) - 1;
-    const int y = cy + oy, z = cz + oz;
-    if (y >= 0 && y < CI_SPAN && z >= 0 && z < CI_SPAN) {
-      int x0 = cx - 1, x1 = cx + 1;
-      bool take = true;
-      if (bounded) {
-        const float margin = 4.0e-3f;
-        const float fx = qx - (s_org[0] + (float)cx * CI_H), fy = qy - (s_org[1] + (float)cy * CI_H), fz = qz - (s_org[2] + (float)cz * CI_H);
-        const float dyv = fmaxf((oy < 0 ? fy : (oy > 0 ? CI_H - fy : 0.f)) - margin, 0.f);
-        const float dzv = fmaxf((oz < 0 ? fz : (oz > 0 ? CI_H - fz : 0.f)) - margin, 0.f);
-        const float base = dyv * dyv + dzv * dzv;
-        take = base <= r2;
-        const float dxm = fmaxf(fx - margin, 0.f), dxp = fmaxf(CI_H - fx - margin, 0.f);
-        if (!(base + dxm * dxm <= r2)) x0 = cx;
-        if (!(base + dxp * dxp <= r2)) x1 = cx;
-      }
-      x0 = max(x0, di * CI_N);
-      x1 = min(x1, di * CI_N + CI_N - 1);
-      if (take && x0 <= x1) {
-        const int dj = y / CI_N, dk = z / CI_N;
-        const int q = (di * 5 + dj) * 5 + dk;
-        const int slot = s_slot[q];
-        if (slot >= 0) {
-          const int2* row = g.cell + (size_t)slot * CI_TABLE + ((z - dk * CI_N) * CI_N + (y - dj * CI_N)) * CI_N - di * CI_N;
-          const int2 c0 = __ldg(&row[x0]);
-          const int2 c1 = __ldg(&row[x1]);
-          const unsigned int tag = (unsigned int)q << CI_ADDR_BITS;
-          vb = tag | (unsigned int)(c0.x - c0.y);
-          ve = tag | (unsigned int)c1.x;
-        }
-      }
-    }
-  }
+  unsigned int vb = 0, ve = 0, vb8 = 0, ve8 = 0;
+  if (gl < 9) ci_row_range(g, s_slot, s_org, cx, cy, cz, di, bounded, qx, qy, qz, r2, gl, vb, ve);
+  if (W == 8 && gl == 0) ci_row_range(g, s_slot, s_org, cx, cy, cz, di, bounded, qx, qy, qz, r2, 8, vb8, ve8);
   R.pre[0] = 0;
 #pragma unroll
   for (int k = 0; k < 9; k++) {
-    const unsigned int b = __shfl_sync(gmask, vb, k, W), en = __shfl_sync(gmask, ve, k, W);
+    unsigned int b, en;
+    if (W == 8 && k == 8) { b = __shfl_sync(gmask, vb8, 0, W); en = __shfl_sync(gmask, ve8, 0, W); }
+    else { b = __shfl_sync(gmask, vb, k, W); en = __shfl_sync(gmask, ve, k, W); }
     R.beg[k] = b;
     R.pre[k + 1] = R.pre[k] + (int)(en - b);
   }

@@ -511,7 +511,8 @@ __device__ __forceinline__ bool lm_knn5_group(const GridView& g, const GridDesc&
         r2 = fmaxf(r2, dd);
       }
       __syncwarp(gmask);   // every lane has read the old neighbours before any lane stores new ones
-      grid_rows9_bounded<W>(g, d, cx, cy, cz, qx, qy, qz, r2, R);
+      if constexpr (W >= 16) grid_rows9_bounded<W>(g, d, cx, cy, cz, qx, qy, qz, r2, R);
+      else grid_rows9<W>(g, d, cx, cy, cz, R);   // the bounded form needs a lane per row
     } else {
       grid_rows9<W>(g, d, cx, cy, cz, R);
     }

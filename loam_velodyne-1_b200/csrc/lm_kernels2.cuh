@@ -172,7 +172,10 @@ __device__ __forceinline__ void lm_transform_update(LMState* st, float* T, const
 // The block size is the launch's (LM_THREADS beside the other nodes' kernels, LM_THREADS_ALONE when the node has
 // the GPU to itself); nothing in the arithmetic depends on it.
 constexpr int LM_CH = 256;   // queries per CTA per pass
-constexpr int LM_KW = 16;    // lanes cooperating on one 5-NN query (8 was measured slower: 22.5 vs 20 us per iteration)
+#ifndef LOAM_LM_KW
+#define LOAM_LM_KW 16
+#endif
+constexpr int LM_KW = LOAM_LM_KW;    // lanes cooperating on one 5-NN query
 #ifndef LOAM_LM_MAXREG
 #define LOAM_LM_MAXREG 128
 #endif
