@@ -169,31 +169,6 @@ struct LMSortNewArgs {
   unsigned int* nk[2][2];   // ping-pong keys   (rank << 24 | voxel)
   unsigned int* nv[2][2];   // ping-pong values (stack index)
 };
-// K7c: one CTA per feature type.  The stack indices sorted by (destination cube rank, voxel,
-// stack order) for refiltered cubes and by (rank, stack order) for append-only cubes; points
-// outside the 21x11x21 window sort last and are dropped (:991-996).
-__global__ void __launch_bounds__(1024, 1) lm_sort_new(LMSortNewArgs A) {
-  __shared__ CtaRadixSmem S;
-  LMState* st = A.st;
-  const int T = blockIdx.x;
-  const int n = st->insN[T];
-  DBG_STAMP(0);
-  for (int k = threadIdx.x; k < n; k += blockDim.x) {
-    int cube = A.ins_cube[T][k];
-    int r = cube >= 0 ? A.cube_rank[T][cube] : -1;
-    unsigned int key = 0xffffffffu;
-    if (r >= 0) key = ((unsigned int)r << 24) | (st->procMode[T][r] ? A.ins_key[T][k] : 0u);
-    A.nk[T][0][k] = key;
-    A.nv[T][0][k] = (unsigned int)k;
-  }
-  __threadfence_block();
-  __syncthreads();
-  DBG_STAMP(1);
-  int sel = cta_radix_sort(A.nk[T][0], A.nv[T][0], A.nk[T][1], A.nv[T][1], n, 4, S);
-  DBG_STAMP(2);
-  if (threadIdx.x == 0) st->newSel[T] = sel;
-}
-
 // K7c': the same list built per cube instead of by one global sort.  CTA (r, T) pulls the points
 // of plan entry r out of the stack (stable compaction: stack order), sorts them by voxel in shared
 // memory when the cube is going to be merged (three 8-bit passes over a few thousand pairs) and

@@ -74,30 +74,6 @@ __device__ __forceinline__ bool lm_converged(const float* X, double thr) {
   return deltaR < thr && deltaT < thr;
 }
 
-// pose integration :830-856
-__device__ __forceinline__ void lo_integrate(LOState* st, const float* transform, const float* imu) {
-  float* transformSum = st->transformSum;
-  const float imuPitchStart = imu[0], imuYawStart = imu[1], imuRollStart = imu[2];
-  const float imuPitchLast = imu[3], imuYawLast = imu[4], imuRollLast = imu[5];
-  const float imuShiftFromStartX = imu[6], imuShiftFromStartY = imu[7], imuShiftFromStartZ = imu[8];
-  float rx, ry, rz, tx, ty, tz;
-  pm::AccumulateRotation(transformSum[0], transformSum[1], transformSum[2],
-                         -transform[0], -transform[1] * 1.05, -transform[2], rx, ry, rz);
-  float x1 = dm::cos(rz) * (transform[3] - imuShiftFromStartX) - dm::sin(rz) * (transform[4] - imuShiftFromStartY);
-  float y1 = dm::sin(rz) * (transform[3] - imuShiftFromStartX) + dm::cos(rz) * (transform[4] - imuShiftFromStartY);
-  float z1 = transform[5] * 1.05 - imuShiftFromStartZ;
-  float x2 = x1;
-  float y2 = dm::cos(rx) * y1 - dm::sin(rx) * z1;
-  float z2 = dm::sin(rx) * y1 + dm::cos(rx) * z1;
-  tx = transformSum[3] - (dm::cos(ry) * x2 + dm::sin(ry) * z2);
-  ty = transformSum[4] - y2;
-  tz = transformSum[5] - (-dm::sin(ry) * x2 + dm::cos(ry) * z2);
-  pm::PluginIMURotation(rx, ry, rz, imuPitchStart, imuYawStart, imuRollStart,
-                        imuPitchLast, imuYawLast, imuRollLast, rx, ry, rz);
-  transformSum[0] = rx; transformSum[1] = ry; transformSum[2] = rz;
-  transformSum[3] = tx; transformSum[4] = ty; transformSum[5] = tz;
-}
-
 // sines and cosines of up to 16 angles, one evaluation per lane: lane l < 16 writes sn[l] = sin(angles[l]),
 // lane 16 + l writes cs[l] = cos(angles[l])
 __device__ __forceinline__ void trig_table_warp(const float* angles, int count, float* sn, float* cs) {
