@@ -27,7 +27,7 @@ def build_cuda(force=False, verbose=False):
            "-Xcompiler", "-fPIC,-ffp-contract=off,-O2", "-shared",
            "-I", os.path.join(ROOT, "include"), "-I", csrc,
            os.path.join(csrc, "loam_b200.cu"), "-o", LIB, "-lcudart_static", "-lpthread", "-ldl", "-lrt"]
-    for var in ("LOAM_LO_MAXREG", "LOAM_LM_MAXREG", "LOAM_RF_SLICES", "LOAM_RF_CLUSTERS", "LOAM_LM_THREADS", "LOAM_LM_KW"):   # dev builds: register caps of the two persistent kernels
+    for var in ("LOAM_LO_MAXREG", "LOAM_LM_MAXREG", "LOAM_RF_SLICES", "LOAM_RF_CLUSTERS", "LOAM_LM_THREADS", "LOAM_LM_KW", "LOAM_LO_CELL_CORNER", "LOAM_LO_CELL_SURF"):   # dev builds: register caps of the two persistent kernels
         if os.environ.get(var):
             cmd.insert(1, "-D%s=%s" % (var, os.environ[var]))
     if os.environ.get("LOAM_LIB_OUT"):

@@ -5,6 +5,16 @@
 
 namespace loamgpu {
 
+// cell sizes of the two odometry indexes (any size gives the same exact 1-NN; it only trades candidates per cell
+// against how often a query has to walk further shells)
+#ifndef LOAM_LO_CELL_CORNER
+#define LOAM_LO_CELL_CORNER 1.0f
+#endif
+#ifndef LOAM_LO_CELL_SURF
+#define LOAM_LO_CELL_SURF 1.0f
+#endif
+constexpr float LO_CELL_CORNER = LOAM_LO_CELL_CORNER, LO_CELL_SURF = LOAM_LO_CELL_SURF;
+
 struct LOHandle {
   loam_params P;
   int device = 0;
@@ -87,8 +97,8 @@ struct LOHandle {
     if (g_profile == 3) prof_node("laserOdometry", stream, true);
     const ImuState* imu = sr.imu_state_dev();
     GridPair gp;
-    gp.g[0] = g_corner.buf(d_corner_last.p, &d_state.p->n_corner_last, &d_state.p->index_enable, 1.0f);
-    gp.g[1] = g_surf.buf(d_surf_last.p, &d_state.p->n_surf_last, &d_state.p->index_enable, 1.0f);
+    gp.g[0] = g_corner.buf(d_corner_last.p, &d_state.p->n_corner_last, &d_state.p->index_enable, LO_CELL_CORNER);
+    gp.g[1] = g_surf.buf(d_surf_last.p, &d_state.p->n_surf_last, &d_state.p->index_enable, LO_CELL_SURF);
     const int nb = 148;
     if (!systemInited) {  // :427-456
       LAUNCH("lo_adopt_first", lo_adopt_first, nb, 256, 0, stream, sr.d_cnt.p, sr.d_less_sharp.p, sr.d_less_flat.p, d_corner_last.p, d_surf_last.p);
