@@ -216,3 +216,57 @@ def test_map_window_shifts_keep_parity(pkg, checker, synth, tmp_path):
         for T in range(2):
             assert np.array_equal(fg["cnt"][T], fo["cnt"][T]) and np.array_equal(fg["pts"][T].view(np.uint32), fo["pts"][T].view(np.uint32)), (axis, off, T)
     assert len(cens) >= 5     # the window really moved
+
+
+def test_load_map_refuses_corrupt_and_foreign_files(pkg, checker, synth, tmp_path):
+    """a LOAMMAP1 file is input from outside: header fields that would index the cube array or the IMU ring out of
+    range, negative counts, truncation and a wrong magic are refused with an error -- and the node that refused a file
+    keeps working"""
+    rec = record_lm_inputs_oracle(checker, synth, 1, 14)
+    P = pkg.make_params(1, system_delay=0)
+    M = pkg.LaserMapping(P)
+    for r in rec[:4]:
+        _gpu_pass(M, r)
+    good = str(tmp_path / "good.loammap")
+    M.save_map(good)
+    raw = bytearray(open(good, "rb").read())
+    hdr = np.dtype([("magic", "S8"), ("version", "<i4"), ("dims", "<i4", 3), ("cen", "<i4", 3), ("frameCount", "<i4"),
+                    ("mapFrameCount", "<i4"), ("isDegenerate", "<i4"), ("tf", "<f4", (5, 6)), ("imuPointerFront", "<i4"),
+                    ("imuPointerLast", "<i4"), ("hasImu", "<i4"), ("imuQueLength", "<i4"), ("total", "<i8", 2)])
+
+    def variant(name, edit):
+        b = bytearray(raw)
+        H = np.frombuffer(b, hdr, 1)     # writable view of the header
+        edit(H[0], b)
+        p = str(tmp_path / (name + ".loammap"))
+        open(p, "wb").write(bytes(b))
+        return p
+
+    def set_field(field, value, idx=None):
+        def edit(H, b):
+            if idx is None:
+                H[field] = value
+            else:
+                H[field][idx] = value
+        return edit
+
+    bad = [variant("cen_hi", set_field("cen", 21, 0)), variant("cen_neg", set_field("cen", -1, 2)),
+           variant("imu_front", set_field("imuPointerFront", 100000)), variant("imu_last", set_field("imuPointerLast", -2)),
+           variant("frames", set_field("frameCount", -5)), variant("magic", set_field("magic", b"LOAMMAP2")),
+           variant("dims", set_field("dims", 22, 0)), variant("total", set_field("total", -1, 0))]
+    cnt_off = hdr.itemsize + 200 * 16      # IMU ring: 200 x (double + 2 floats)
+    assert int(np.frombuffer(raw, hdr, 1)[0]["imuQueLength"]) == 200
+    neg = bytearray(raw)
+    np.frombuffer(neg, "<i4", 1, cnt_off)[0] = -3
+    p = str(tmp_path / "neg_count.loammap"); open(p, "wb").write(bytes(neg)); bad.append(p)
+    p = str(tmp_path / "short.loammap"); open(p, "wb").write(bytes(raw[:len(raw) - 40])); bad.append(p)
+    for path in bad:
+        with pytest.raises(pkg.LoamError):
+            M.load_map(path)
+    # the node is still usable and still agrees with a node that never saw the bad files
+    N = pkg.LaserMapping(P)
+    N.load_map(good)
+    M.load_map(good)
+    for r in rec[4:8]:
+        a, b = _gpu_pass(M, r), _gpu_pass(N, r)
+        assert biteq(a[0], b[0]) and np.array_equal(a[3], b[3])
