@@ -165,7 +165,7 @@ struct LOHandle {
     *published = false;
     if (!carrier) {
       carrier = new SRHandle();
-      int r = carrier->init(&P, device, stream);
+      int r = carrier->init(&P, device, stream, true);
       if (r != LOAM_OK) { delete carrier; carrier = nullptr; return r; }
     }
     int r = carrier->set_features(clouds, counts, imu_trans);

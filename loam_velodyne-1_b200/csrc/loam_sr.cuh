@@ -84,9 +84,14 @@ struct SRHandle {
   SRCounts last_counts;
   bool processed = false;
 
-  int init(const loam_params* p, int dev, cudaStream_t s) {
+  // carrier_only: the handle will only ever hold features handed in from the host (set_features: laserOdometry fed from
+  // host copies of the six topics).  It then needs the two output banks, the counters and the IMU state -- not the raw
+  // staging ring (4 x 12 B x max_points pinned + device) nor the per-point scratch of the registration kernels.
+  bool carrier_only = false;
+  int init(const loam_params* p, int dev, cudaStream_t s, bool carrier = false) {
     P = *p;
     device = dev;
+    carrier_only = carrier;
     if (P.n_scans < 1 || P.n_scans > SR_MAX_RINGS || P.max_points < 64) {
       set_error("n_scans = %d / max_points = %d: n_scans must be 1 .. %d (LOAM_LIMIT_RINGS), max_points at least 64", P.n_scans, P.max_points, SR_MAX_RINGS);
       return LOAM_ERR_ARG;
@@ -102,15 +107,17 @@ struct SRHandle {
     nblk_cap = (cap + SR_BLK - 1) / SR_BLK;
     int R = P.n_scans;
     int r = LOAM_OK;
-    for (int b = 0; b < RAW_DEPTH; b++) { r |= d_raw2[b].alloc((size_t)cap * 3); r |= h_raw2[b].alloc((size_t)cap * 3); }
-    r |= d_ring.alloc(cap); r |= d_ori.alloc(cap); r |= d_reltime.alloc(cap);
-    r |= d_curv.alloc_zero(cap, stream); r |= d_hist.alloc((size_t)R * nblk_cap); r |= d_ring_start.alloc(R + 1);
-    r |= d_scan_start.alloc(R); r |= d_scan_end.alloc(R); r |= d_ring_tot.alloc_zero(SR_MAX_RINGS, stream); r |= d_scan_ticket.alloc_zero(1, stream); r |= d_pos.alloc(cap); r |= d_sort_ind.alloc_zero(cap, stream);
-    r |= d_picked.alloc_zero(cap + 16, stream); r |= d_gap.alloc_zero(cap + 16, stream); r |= d_steps.alloc(cap);
-    r |= d_label.alloc_zero(cap, stream);
+    const size_t pc = carrier ? 16 : (size_t)cap;          // per-point scratch of the registration kernels
+    const size_t pb = carrier ? 1 : (size_t)nblk_cap;
+    for (int b = 0; b < RAW_DEPTH; b++) { r |= d_raw2[b].alloc(pc * 3); r |= h_raw2[b].alloc(pc * 3); }
+    r |= d_ring.alloc(pc); r |= d_ori.alloc(pc); r |= d_reltime.alloc(pc);
+    r |= d_curv.alloc_zero(pc, stream); r |= d_hist.alloc((size_t)R * pb); r |= d_ring_start.alloc(R + 1);
+    r |= d_scan_start.alloc(R); r |= d_scan_end.alloc(R); r |= d_ring_tot.alloc_zero(SR_MAX_RINGS, stream); r |= d_scan_ticket.alloc_zero(1, stream); r |= d_pos.alloc(pc); r |= d_sort_ind.alloc_zero(pc, stream);
+    r |= d_picked.alloc_zero(pc + 16, stream); r |= d_gap.alloc_zero(pc + 16, stream); r |= d_steps.alloc(pc);
+    r |= d_label.alloc_zero(pc, stream);
     r |= d_sharp_ring.alloc((size_t)R * SR_SHARP_PER_RING); r |= d_less_sharp_ring.alloc((size_t)R * SR_LESS_SHARP_PER_RING);
     r |= d_flat_ring.alloc((size_t)R * SR_FLAT_PER_RING);
-    r |= d_blockmax.alloc(nblk_cap);
+    r |= d_blockmax.alloc(pb);
     r |= d_sharp_idx.alloc((size_t)R * SR_SHARP_PER_RING); r |= d_less_sharp_idx.alloc((size_t)R * SR_LESS_SHARP_PER_RING);
     r |= d_flat_idx.alloc((size_t)R * SR_FLAT_PER_RING);
     for (int b = 0; b < 2; b++) {
@@ -121,7 +128,7 @@ struct SRHandle {
       if (cudaEventCreateWithFlags(&k.released, cudaEventDisableTiming) != cudaSuccess) r = LOAM_ERR_CUDA;
     }
     select_bank(0);
-    r |= d_lessflat_tmp.alloc((size_t)R * SR_RING_CAP);
+    r |= d_lessflat_tmp.alloc(carrier ? 16 : (size_t)R * SR_RING_CAP);
     r |= d_imu.alloc(1); r |= d_imu_state.alloc_zero(2, stream);
     r |= h_cnt.alloc(1); r |= h_imu.alloc(); r |= h_cnt_init.alloc(); r |= h_imu_state.alloc(1);
     if (r != LOAM_OK) return LOAM_ERR_CUDA;
@@ -195,6 +202,7 @@ struct SRHandle {
   // batch_item != nullptr: do everything up to (and excluding) the kernel launches and describe the pass in
   // *batch_item; the caller launches the batched kernels for all sequences at once (SRBatch below)
   int process(const float* xyz, int n, int stride_bytes, double stamp, SRDev* batch_item = nullptr) {
+    if (carrier_only) { set_error("this handle only carries host-side features (no registration scratch)"); return LOAM_ERR_ARG; }
     processed = false;
     if (!systemInited) {  // :213-219
       systemInitCount++;
@@ -283,6 +291,7 @@ struct SRHandle {
     return false;
   }
   int process_packets(const unsigned char* packets, int n_packets, double stamp) {
+    if (carrier_only) { set_error("this handle only carries host-side features (no registration scratch)"); return LOAM_ERR_ARG; }
     processed = false;
     pk::SensorDesc S;
     if (!packet_sensor(&S)) { set_error("no packet format for n_scans=%d ring_model=%d (VLP-16: 16 / 0, HDL-64E: 64 / 1)", P.n_scans, P.ring_model); return LOAM_ERR_ARG; }
@@ -355,6 +364,7 @@ struct SRHandle {
   // same, for a sweep that is already resident in device memory (packed xyz).  first_xyz/last_xyz:
   // host copies of the first / last finite point, first = index of the first finite point.
   int process_resident(const float* d_xyz, int n, const float* first_xyz, const float* last_xyz, int first, double stamp, SRDev* batch_item = nullptr) {
+    if (carrier_only) { set_error("this handle only carries host-side features (no registration scratch)"); return LOAM_ERR_ARG; }
     processed = false;
     if (!systemInited) {
       systemInitCount++;
