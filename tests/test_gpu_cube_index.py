@@ -119,3 +119,100 @@ def test_per_cube_index_survives_window_shifts_and_map_reload(pkg, checker, synt
         _same_pass(A, B, i)
         i += 1
     assert built > 0 and int(A.ints(110)[0]) > 0
+
+
+def _cube_of(p, cen=(10, 5, 10)):
+    """laserMapping.cpp:983-989: cube indices of a map point (double arithmetic, truncation + fix-up for negatives)"""
+    out = []
+    for a in range(3):
+        v = float(p[a]) + 25.0
+        c = int(v / 50.0) + cen[a]
+        if v < 0:
+            c -= 1
+        out.append(c)
+    return out[0] + 21 * out[1] + 21 * 11 * out[2]
+
+
+def _write_map_file(path, clouds):
+    """a LOAMMAP1 file (csrc/lm_persist.cuh) holding the two given clouds, every cube flagged dirty (= "written by
+    someone else": the first refilter of a cube sorts it)"""
+    hdr = np.zeros(1, np.dtype([("magic", "S8"), ("version", "<i4"), ("dims", "<i4", 3), ("cen", "<i4", 3), ("frameCount", "<i4"),
+                                ("mapFrameCount", "<i4"), ("isDegenerate", "<i4"), ("tf", "<f4", (5, 6)), ("imuPointerFront", "<i4"),
+                                ("imuPointerLast", "<i4"), ("hasImu", "<i4"), ("imuQueLength", "<i4"), ("total", "<i8", 2)]))
+    hdr["magic"] = b"LOAMMAP1"; hdr["version"] = 1; hdr["dims"] = (21, 11, 21); hdr["cen"] = (10, 5, 10)
+    hdr["mapFrameCount"] = 4; hdr["imuPointerLast"] = -1; hdr["imuQueLength"] = 200
+    body = []
+    for T, pts in enumerate(clouds):
+        cube = np.array([_cube_of(p) for p in pts], np.int64)
+        order = np.argsort(cube, kind="stable")
+        cnt = np.bincount(cube, minlength=21 * 11 * 21).astype("<i4")
+        hdr["total"][0][T] = len(pts)
+        body += [cnt.tobytes(), (cnt > 0).astype(np.uint8).tobytes(), np.ascontiguousarray(pts[order], "<f4").tobytes()]
+    with open(path, "wb") as f:
+        f.write(hdr.tobytes())
+        f.write(np.zeros(200, "<f8").tobytes() + np.zeros(400, "<f4").tobytes())
+        for b in body:
+            f.write(b)
+
+
+def test_per_cube_index_at_cube_boundaries(pkg, checker, tmp_path):
+    """the one place where the per-cube index differs structurally from an index over the gathered map: neighbourhoods
+    that straddle cube faces, edges and corners (a row of three lattice cells split over two cubes, neighbours in up to
+    eight cubes, points stored a rounding error outside their cube), negative coordinates, cubes the FOV test leaves
+    out.  A hand-made map of line- and plane-shaped clusters centred ON the cube boundaries, queried by stack points
+    next to every cluster, over three passes between which the pose jumps by a cube: incremental node == per-pass-index
+    node == oracle in poses, counters and every 5-NN index list"""
+    rng = np.random.default_rng(77)
+    edges = np.array([-75.0, -25.0, 25.0, 75.0])
+
+    def centres(n):
+        c = np.stack([rng.uniform(-70, 70, n), rng.uniform(-28, 28, n), rng.uniform(-70, 70, n)], axis=1)
+        k = n // 6
+        c[:k, 0] = rng.choice(edges, k) + rng.uniform(-0.3, 0.3, k)                       # on a face
+        c[k:2 * k, 2] = rng.choice(edges, k) + rng.uniform(-0.3, 0.3, k)
+        c[2 * k:3 * k, 1] = rng.choice([-25.0, 25.0], k) + rng.uniform(-0.3, 0.3, k)
+        c[3 * k:4 * k, 0] = rng.choice(edges, k); c[3 * k:4 * k, 2] = rng.choice(edges, k)   # exactly on an edge
+        c[4 * k:5 * k, 0] = rng.choice(edges, k) + rng.uniform(-0.05, 0.05, k)              # around a corner
+        c[4 * k:5 * k, 1] = rng.choice([-25.0, 25.0], k) + rng.uniform(-0.05, 0.05, k)
+        c[4 * k:5 * k, 2] = rng.choice(edges, k) + rng.uniform(-0.05, 0.05, k)
+        return c
+
+    def corner_map(c):      # 30 points along a random line through every centre
+        d = rng.normal(size=(len(c), 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+        t = rng.uniform(-0.8, 0.8, (len(c), 30, 1))
+        return (c[:, None, :] + t * d[:, None, :] + rng.normal(0, 0.01, (len(c), 30, 3))).reshape(-1, 3)
+
+    def surf_map(c):        # 40 points on a random disc around every centre
+        n = rng.normal(size=(len(c), 3)); n /= np.linalg.norm(n, axis=1, keepdims=True)
+        u = np.cross(n, [0.3, 0.5, 0.8]); u /= np.linalg.norm(u, axis=1, keepdims=True)
+        v = np.cross(n, u)
+        a, b = rng.uniform(-0.8, 0.8, (2, len(c), 40, 1))
+        return (c[:, None, :] + a * u[:, None, :] + b * v[:, None, :] + rng.normal(0, 0.005, (len(c), 40, 3))).reshape(-1, 3)
+
+    cc, cs = centres(360), centres(360)
+    maps = [np.concatenate([m, np.zeros((len(m), 1))], axis=1).astype(np.float32) for m in (corner_map(cc), surf_map(cs))]
+    path = str(tmp_path / "boundaries.loammap")
+    _write_map_file(path, maps)
+    A, B = _node(pkg, 1), _node(pkg, 1, PER_PASS_INDEX)
+    C = checker.Checker(checker.make_params(1), "port")
+    A.load_map(path); B.load_map(path); C.lm_load_map(path)
+    found = 0
+    for i, jump in enumerate([(0.0, 0.0, 0.0), (52.0, 0.0, 0.0), (-49.5, 3.0, 51.0), (0.0, -2.0, -52.0)]):
+        tsum = np.zeros(6, np.float32); tsum[3:] = jump
+        def stack(c, k):
+            q = np.repeat(c, k, axis=0) + rng.uniform(-0.35, 0.35, (len(c) * k, 3)) - np.asarray(jump)
+            return np.concatenate([q, np.zeros((len(q), 1))], axis=1).astype(np.float32)
+        corner, surf = stack(cc, 2), stack(cs, 2)
+        full = surf[:64].copy()
+        o = C.lm_push(corner, surf, full, tsum, 10.0 + i)
+        assert A.process_host(corner, surf, full, tsum, 10.0 + i) == 0 and B.process_host(corner, surf, full, tsum, 10.0 + i) == 0
+        _same_pass(A, B, i)
+        aft, bef, tobe, st = A.state()
+        assert biteq(aft, o.transform_aft_mapped[:]) and (st[0], st[1], st[3], st[4]) == (o.lm_iters, o.lm_rows, o.n_map_corner, o.n_map_surf), i
+        nn_c, nn_s = A.ints(100), A.ints(101)
+        assert np.array_equal(nn_c, C.ints(100)) and np.array_equal(nn_s, C.ints(101)), i
+        found += int((nn_c.reshape(-1, 5)[:, 0] >= 0).sum() + (nn_s.reshape(-1, 5)[:, 0] >= 0).sum())
+        assert o.lm_iters >= 1
+    assert found > 1500, found         # the comparison is about real neighbour lists, not about "nothing found"
+    for w in (10, 11):
+        assert np.array_equal(A.cloud(w, cap=1 << 20).view(np.uint32), C.cloud(w).view(np.uint32)), w
