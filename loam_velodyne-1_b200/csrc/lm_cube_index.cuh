@@ -105,12 +105,16 @@ __global__ void __cluster_dims__(CB_CLUSTER, 1, 1) __launch_bounds__(CB_THREADS)
     float4* __restrict__ out = A.pts[T];
     const float ox = 50.0f * (float)S.wi - 25.0f, oy = 50.0f * (float)S.wj - 25.0f, oz = 50.0f * (float)S.wk - 25.0f;
     const int n = S.cnt;
+    // phase builds only: stamps of the cluster that builds the largest slot (first list entry), thread 0
+    const bool stamp = PHASE_ON && b == 0 && tid == 0;
+    if (stamp) { g_dbg_clk[960] = clock64(); g_dbg_clk[967] = n; g_dbg_clk[968] = nb; }
     {
       int4* c4 = (int4*)cell;
       for (int c = tid; c < CI_TABLE / 2; c += nthr) c4[c] = make_int4(0, 0, 0, 0);
     }
     __threadfence();
     cl.sync();
+    if (stamp) g_dbg_clk[961] = clock64();
     for (int i0 = tid; i0 < n; i0 += CB_ILP * nthr) {   // independent loads in flight per thread
       float4 p[CB_ILP];
 #pragma unroll
@@ -124,6 +128,7 @@ __global__ void __cluster_dims__(CB_CLUSTER, 1, 1) __launch_bounds__(CB_THREADS)
     }
     __threadfence();
     cl.sync();
+    if (stamp) g_dbg_clk[962] = clock64();
     {
       // one warp per x-row, CB_ROWS rows per warp: all counts are fetched first, the warp takes ONE range of the
       // slot's region for its rows (one atomic round trip instead of one per row)
@@ -167,6 +172,7 @@ __global__ void __cluster_dims__(CB_CLUSTER, 1, 1) __launch_bounds__(CB_THREADS)
     }
     __threadfence();
     cl.sync();
+    if (stamp) g_dbg_clk[963] = clock64();
     for (int i0 = tid; i0 < n; i0 += CB_ILP * nthr) {   // independent load -> atomic -> store chains per thread
       float4 p[CB_ILP];
       int dst[CB_ILP];
@@ -185,6 +191,7 @@ __global__ void __cluster_dims__(CB_CLUSTER, 1, 1) __launch_bounds__(CB_THREADS)
         if (dst[u] >= 0) { p[u].w = __int_as_float(i0 + u * nthr); out[dst[u]] = p[u]; }
       }
     }
+    if (stamp) g_dbg_clk[964] = clock64();
   }
 }
 
