@@ -161,12 +161,16 @@ struct LMSetupArgs {
 // K1: one block.  /laser_odom_to_init hand-off (:304-318), transformAssociateToMap (:422),
 // FOV probe point, centre cube + window shifts (:446-614), cube selection (:616-672) and the
 // offsets of the local-map gather (:674-681).
-__global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
+// Two kernels from one body: the pose prediction (phase 1, one warp, main stream) and the cube bookkeeping (phase 2,
+// side stream) are launched separately anyway, and a kernel that carries only its own phase's code misses the
+// instruction cache far less (both ran at 3 % issue utilisation, most stalls "no instruction").
+template <int PHASE>
+__device__ __forceinline__ void lm_setup_body(const LMSetupArgs& A) {
   LMState* st = A.st;
   __shared__ int s_shift[3], s_center[3];
   __shared__ unsigned char s_fov[125], s_in[125];
   __shared__ int s_ind[125];
-  if (threadIdx.x < 32 && A.phase != 2) {
+  if (PHASE != 2 && threadIdx.x < 32) {
     // pose prediction on one warp: the sines / cosines of the nine input angles of transformAssociateToMap are
     // evaluated by 18 lanes at once, lane 0 runs the closed forms against the table (pm::transformAssociateToMapV:
     // same expression trees, same bits)
@@ -199,7 +203,7 @@ __global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
       st->stackN2[0] = A.lo->n_corner_last; st->stackN2[1] = A.lo->n_surf_last;
     }
   }
-  if (A.phase == 1) return;
+  if (PHASE == 1) return;
   if (threadIdx.x == 0) {
     const float* T = st->transformTobeMapped;
     int cI = lm_cube_coord(T[3], st->cenW), cJ = lm_cube_coord(T[4], st->cenH), cK = lm_cube_coord(T[5], st->cenD);
@@ -409,6 +413,9 @@ __global__ void __launch_bounds__(256) lm_setup(LMSetupArgs A) {
     ci->stat[0] += s_nb; ci->stat[1] += s_npts; ci->stat[3] = s_nb; ci->stat[4] = s_npts;
   }
 }
+
+__global__ void __launch_bounds__(32) lm_setup(LMSetupArgs A) { lm_setup_body<1>(A); }
+__global__ void __launch_bounds__(256) lm_setup_cubes(LMSetupArgs A) { lm_setup_body<2>(A); }
 
 // K2: incoming clouds to the map with the predicted pose and back (:424-434, :683-691)
 struct LMStackArgs {

@@ -305,12 +305,12 @@ struct LMHandle {
     LMSetupArgs SA;
     SA.st = st; SA.lo = in.lo; SA.cubes[0] = d_cubes[0].p; SA.cubes[1] = d_cubes[1].p; SA.phase = 1;
     SA.ci = use_ci ? d_ci.p : nullptr;
-    LAUNCH("lm_setup", lm_setup, 1, 256, 0, stream, SA);
+    LAUNCH("lm_setup", lm_setup, 1, 32, 0, stream, SA);
     CUDA_OK(cudaEventRecord(ev_fork, stream));
     CUDA_OK(cudaStreamWaitEvent(aux, ev_fork, 0));
     // K1b on the side stream, behind the previous pass's map update (both work on the cube descriptors)
     SA.phase = 2;
-    LAUNCH("lm_setup_cubes", lm_setup, 1, 256, 0, aux, SA);
+    LAUNCH("lm_setup_cubes", lm_setup_cubes, 1, 256, 0, aux, SA);
     // K2
     LMStackArgs KA;
     KA.st = st; KA.in[0] = in.corner_last; KA.in[1] = in.surf_last; KA.out[0] = d_stack2[0].p; KA.out[1] = d_stack2[1].p;
